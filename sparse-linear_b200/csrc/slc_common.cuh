@@ -1,0 +1,266 @@
+// slc_common.cuh -- shared host/device plumbing of libsparselinear_b200.so
+// (handle layout, error reporting, stream-ordered buffers, element arithmetic).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <atomic>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "slc.h"
+
+namespace slc {
+
+// ---- per-thread state ---------------------------------------------------------------------
+
+struct ThreadState {
+  cudaStream_t stream = nullptr;
+  std::string last_error;
+};
+ThreadState &tls();
+inline cudaStream_t cur_stream() { return tls().stream; }
+
+int fail(int code, const char *fmt, ...);  // records the message, returns code
+extern std::atomic<int64_t> g_launches;
+
+#define SLC_CUDA(expr)                                                                       \
+  do {                                                                                       \
+    cudaError_t _e = (expr);                                                                 \
+    if (_e != cudaSuccess)                                                                   \
+      return ::slc::fail(_e == cudaErrorMemoryAllocation ? SLC_ERR_NOMEM : SLC_ERR_CUDA,     \
+                         "%s: CUDA error %s at %s:%d", __func__, cudaGetErrorString(_e),     \
+                         __FILE__, __LINE__);                                                \
+  } while (0)
+
+#define SLC_TRY(expr)                                                                        \
+  do {                                                                                       \
+    int _rc = (expr);                                                                        \
+    if (_rc != SLC_OK) return _rc;                                                           \
+  } while (0)
+
+// Count a kernel launch and surface launch-configuration errors immediately.
+#define SLC_LAUNCHED()                                                                       \
+  do {                                                                                       \
+    ::slc::g_launches.fetch_add(1, std::memory_order_relaxed);                               \
+    SLC_CUDA(cudaGetLastError());                                                            \
+  } while (0)
+
+// ---- stream-ordered device buffer ------------------------------------------------------------
+
+// Owns one cudaMallocAsync allocation.  Freed on the current stream, so a buffer may be
+// released right after the last kernel that reads it has been enqueued.
+template <class U>
+struct DevBuf {
+  U *p = nullptr;
+  size_t n = 0;
+  DevBuf() = default;
+  DevBuf(const DevBuf &) = delete;
+  DevBuf &operator=(const DevBuf &) = delete;
+  DevBuf(DevBuf &&o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+  DevBuf &operator=(DevBuf &&o) noexcept {
+    if (this != &o) { release(); p = o.p; n = o.n; o.p = nullptr; o.n = 0; }
+    return *this;
+  }
+  ~DevBuf() { release(); }
+  int alloc(size_t count) {
+    release();
+    n = count;
+    size_t bytes = (count ? count : 1) * sizeof(U);
+    cudaError_t e = cudaMallocAsync((void **)&p, bytes, cur_stream());
+    if (e != cudaSuccess) {
+      p = nullptr; n = 0;
+      (void)cudaGetLastError();
+      return fail(e == cudaErrorMemoryAllocation ? SLC_ERR_NOMEM : SLC_ERR_CUDA,
+                  "device allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+    }
+    return SLC_OK;
+  }
+  void release() {
+    if (p) { cudaFreeAsync(p, cur_stream()); p = nullptr; n = 0; }
+  }
+  U *take() { U *q = p; p = nullptr; n = 0; return q; }
+};
+
+inline void dev_free(void *p) {
+  if (p) cudaFreeAsync(p, cur_stream());
+}
+
+// ---- the handle ---------------------------------------------------------------------------------
+
+enum ElemType : int { ELEM_D = 'd', ELEM_Z = 'z' };
+enum SpmvKind : int { SPMV_AUTO = 0, SPMV_SELL = 1, SPMV_CSR_WARP = 2, SPMV_CSR_BALANCED = 3 };
+
+// Sliced-ELL plan (slices of 32 rows, column-major inside a slice, row per thread).
+struct SellPlan {
+  bool built = false;
+  int32_t nslices = 0;
+  int64_t padded = 0;        // stored elements including padding
+  int64_t *slice_ptr = nullptr;  // [nslices+1] element offsets
+  int32_t *rowlen = nullptr;     // [nrows]
+  int32_t *colidx = nullptr;     // [padded]
+  void *vals = nullptr;          // [padded]
+};
+
+// nnz-balanced CSR plan: fixed-size chunks of nonzeros, first row of each chunk.
+struct BalancedPlan {
+  bool built = false;
+  int32_t nchunks = 0;
+  int32_t *chunk_row = nullptr;  // [nchunks+1] first row touching each chunk
+};
+
+}  // namespace slc
+
+struct slc_matrix {
+  int elem = slc::ELEM_D;
+  int device = 0;
+  int32_t nrows = 0, ncols = 0;
+  int64_t nnz = 0;
+  // canonical CSC (what the reference's Matrix record holds)
+  int32_t *colptr = nullptr;
+  int32_t *rowidx = nullptr;
+  void *vals = nullptr;
+  // row-major mirror = CSC of the transpose, built on demand by the transpose kernels
+  bool has_csr = false;
+  int32_t *rowptr = nullptr;
+  int32_t *colidx = nullptr;
+  void *rvals = nullptr;
+  // row statistics (filled with the mirror)
+  int32_t max_rowlen = 0;
+  // product plans
+  int spmv_kind = slc::SPMV_AUTO;      // requested
+  int spmv_active = slc::SPMV_AUTO;    // chosen
+  slc::SellPlan sell;
+  slc::BalancedPlan bal;
+};
+
+namespace slc {
+
+inline size_t elem_size(int elem) { return elem == ELEM_Z ? 16 : 8; }
+
+int matrix_alloc(int elem, int32_t nrows, int32_t ncols, int64_t nnz, slc_matrix **out);
+void matrix_release(slc_matrix *m);
+
+// ---- element arithmetic -------------------------------------------------------------------------
+// The reference multiplies, rounds, adds, rounds (GHC with -msse2 only,
+// sparse-linear.cabal:33).  The __d*_rn intrinsics are never contracted into FMA, so a sum
+// taken in the reference's order is bit-identical to it.
+
+template <class T> struct Num;
+
+template <> struct Num<double> {
+  static constexpr int elem = ELEM_D;
+  static __host__ __device__ __forceinline__ double zero() { return 0.0; }
+  static __device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+  static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+  static __device__ __forceinline__ double conj(double a) { return a; }
+  static __device__ __forceinline__ bool eq(double a, double b) { return a == b; }
+};
+
+// Data.Complex: (x:+y)*(x':+y') = (x*x' - y*y') :+ (x*y' + y*x')
+template <> struct Num<double2> {
+  static constexpr int elem = ELEM_Z;
+  static __host__ __device__ __forceinline__ double2 zero() { return double2{0.0, 0.0}; }
+  static __device__ __forceinline__ double2 mul(double2 a, double2 b) {
+    return double2{__dsub_rn(__dmul_rn(a.x, b.x), __dmul_rn(a.y, b.y)),
+                   __dadd_rn(__dmul_rn(a.x, b.y), __dmul_rn(a.y, b.x))};
+  }
+  static __device__ __forceinline__ double2 add(double2 a, double2 b) {
+    return double2{__dadd_rn(a.x, b.x), __dadd_rn(a.y, b.y)};
+  }
+  static __device__ __forceinline__ double2 conj(double2 a) { return double2{a.x, -a.y}; }
+  static __device__ __forceinline__ bool eq(double2 a, double2 b) { return a.x == b.x && a.y == b.y; }
+};
+
+// ---- cache-hinted memory access -----------------------------------------------------------------
+// Matrix streams (indices, values) are read exactly once per product: keep them out of L1
+// and mark them first to go in L2, so the gathered vector stays resident in the 126 MB L2.
+
+__device__ __forceinline__ uint64_t policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ int32_t ld_stream(const int32_t *p, uint64_t pol) {
+  int32_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.s32 %0, [%1], %2;"
+               : "=r"(v) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ double ld_stream(const double *p, uint64_t pol) {
+  double v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f64 %0, [%1], %2;"
+               : "=d"(v) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ double2 ld_stream(const double2 *p, uint64_t pol) {
+  double2 v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;"
+               : "=d"(v.x), "=d"(v.y) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ int4 ld_stream(const int4 *p, uint64_t pol) {
+  int4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.s32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(pol));
+  return v;
+}
+// gathered operand: read-only path, allocate in L1, last to go in L2
+__device__ __forceinline__ double ld_gather(const double *p, uint64_t pol) {
+  double v;
+  asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ double2 ld_gather(const double2 *p, uint64_t pol) {
+  double2 v;
+  asm volatile("ld.global.nc.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;"
+               : "=d"(v.x), "=d"(v.y) : "l"(p), "l"(pol));
+  return v;
+}
+// streaming store of a result that is not read again by this kernel
+__device__ __forceinline__ void st_stream(double *p, double v) {
+  asm volatile("st.global.cs.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+__device__ __forceinline__ void st_stream(double2 *p, double2 v) {
+  asm volatile("st.global.cs.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(v.x), "d"(v.y) : "memory");
+}
+
+// ---- small helpers ------------------------------------------------------------------------------
+
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+int sm_count();
+
+// device primitives implemented in slc_prims.cu (radix sort, scans)
+int exclusive_scan_i32(const int32_t *in, int32_t *out, int64_t n);  // out may alias in
+int exclusive_scan_i64(const int64_t *in, int64_t *out, int64_t n);
+int inclusive_max_scan_i32(const int32_t *in, int32_t *out, int64_t n);
+// stable sort of (key, value) pairs on key bits [0, end_bit)
+int sort_pairs_u32(uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in, uint32_t *vals_out,
+                   int64_t n, int end_bit);
+int sort_pairs_u64(uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in, uint32_t *vals_out,
+                   int64_t n, int end_bit);
+
+// built in slc_transpose.cu
+template <class T>
+int transpose_csc(int32_t nrows, int32_t ncols, int64_t nnz, const int32_t *colptr,
+                  const int32_t *rowidx, const T *vals, bool conj, int32_t *out_ptr,
+                  int32_t *out_idx, T *out_vals);
+int ensure_csr(slc_matrix *m);
+
+inline int bits_for(uint32_t n) {  // bits needed to represent values in [0, n)
+  int b = 1;
+  while (b < 32 && (1ull << b) < (uint64_t)n) ++b;
+  return b;
+}
+
+}  // namespace slc

@@ -1,0 +1,290 @@
+// slc_core.cu -- library state, handles, upload/download.
+// Reference shapes: Matrix record Data/Matrix/Sparse.hs:67-76; withConstMatrix / fromForeign
+// Data/Matrix/Sparse/Foreign.hs:24-88 (paths relative to /root/reference/sparse-linear/src).
+#include "slc_common.cuh"
+
+namespace slc {
+
+std::atomic<int64_t> g_launches{0};
+
+ThreadState &tls() {
+  static thread_local ThreadState st;
+  return st;
+}
+
+int fail(int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  tls().last_error = buf;
+  return code;
+}
+
+int sm_count() {
+  static thread_local int cached_dev = -1, cached = 148;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev != cached_dev) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      cached = n;
+    cached_dev = dev;
+  }
+  return cached;
+}
+
+static int configure_pool_once() {
+  // Keep freed blocks in the stream-ordered pool: repeated products and SpGEMM calls reuse
+  // them instead of going back to the driver.
+  static thread_local int done_dev = -1;
+  int dev = 0;
+  SLC_CUDA(cudaGetDevice(&dev));
+  if (dev == done_dev) return SLC_OK;
+  cudaMemPool_t pool;
+  SLC_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+  uint64_t thr = UINT64_MAX;
+  SLC_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+  done_dev = dev;
+  return SLC_OK;
+}
+
+int matrix_alloc(int elem, int32_t nrows, int32_t ncols, int64_t nnz, slc_matrix **out) {
+  SLC_TRY(configure_pool_once());
+  slc_matrix *m = new (std::nothrow) slc_matrix();
+  if (!m) return fail(SLC_ERR_NOMEM, "out of host memory");
+  m->elem = elem;
+  m->nrows = nrows;
+  m->ncols = ncols;
+  m->nnz = nnz;
+  cudaGetDevice(&m->device);
+  DevBuf<int32_t> cp, ri;
+  DevBuf<char> v;
+  int rc = cp.alloc((size_t)ncols + 1);
+  if (rc == SLC_OK) rc = ri.alloc((size_t)nnz);
+  if (rc == SLC_OK) rc = v.alloc((size_t)nnz * elem_size(elem));
+  if (rc != SLC_OK) {
+    delete m;
+    return rc;
+  }
+  m->colptr = cp.take();
+  m->rowidx = ri.take();
+  m->vals = v.take();
+  *out = m;
+  return SLC_OK;
+}
+
+void matrix_release(slc_matrix *m) {
+  if (!m) return;
+  int prev = -1;
+  cudaGetDevice(&prev);
+  if (prev != m->device) cudaSetDevice(m->device);
+  dev_free(m->colptr);
+  dev_free(m->rowidx);
+  dev_free(m->vals);
+  dev_free(m->rowptr);
+  dev_free(m->colidx);
+  dev_free(m->rvals);
+  dev_free(m->sell.slice_ptr);
+  dev_free(m->sell.rowlen);
+  dev_free(m->sell.colidx);
+  dev_free(m->sell.vals);
+  dev_free(m->bal.chunk_row);
+  if (prev != m->device && prev >= 0) cudaSetDevice(prev);
+  delete m;
+}
+
+// One thread per stored entry: bounds, and strictly increasing rows inside a column.  A
+// descent is legal only at a column start, which a binary search over colptr confirms.
+__global__ void k_validate_entries(int32_t nrows, int32_t ncols, int64_t nnz,
+                                   const int32_t *__restrict__ colptr,
+                                   const int32_t *__restrict__ rowidx, int *__restrict__ flag) {
+  int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= nnz) return;
+  int32_t r = rowidx[p];
+  if (r < 0 || r >= nrows) {
+    atomicOr(flag, 1);
+    return;
+  }
+  if (p == 0) return;
+  if (rowidx[p - 1] >= r) {
+    int32_t lo = 0, hi = ncols;  // find some c with colptr[c] == p
+    while (lo < hi) {
+      int32_t mid = lo + ((hi - lo) >> 1);
+      if (colptr[mid] < (int32_t)p) lo = mid + 1;
+      else hi = mid;
+    }
+    if (lo > ncols || colptr[lo] != (int32_t)p) atomicOr(flag, 2);
+  }
+}
+
+template <class T>
+static int upload_impl(int32_t nrows, int32_t ncols, const int32_t *colptr, const int32_t *rowidx,
+                       const double *vals, slc_matrix **out) {
+  if (!out) return fail(SLC_ERR_INVALID, "upload: null output handle");
+  *out = nullptr;
+  if (nrows < 0 || ncols < 0) return fail(SLC_ERR_INVALID, "upload: negative dimension");
+  if (!colptr) return fail(SLC_ERR_INVALID, "upload: null column pointers");
+  if (colptr[0] != 0) return fail(SLC_ERR_FORMAT, "upload: pointers do not start at 0");
+  for (int32_t c = 0; c < ncols; ++c)
+    if (colptr[c] > colptr[c + 1])
+      return fail(SLC_ERR_FORMAT, "upload: pointers decrease at column %d", c);
+  const int64_t nnz = colptr[ncols];
+  if (nnz > 0 && (!rowidx || !vals)) return fail(SLC_ERR_INVALID, "upload: null index or value array");
+  slc_matrix *m = nullptr;
+  SLC_TRY(matrix_alloc(Num<T>::elem, nrows, ncols, nnz, &m));
+  cudaStream_t s = cur_stream();
+  cudaError_t e = cudaMemcpyAsync(m->colptr, colptr, ((size_t)ncols + 1) * sizeof(int32_t),
+                                  cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess && nnz)
+    e = cudaMemcpyAsync(m->rowidx, rowidx, (size_t)nnz * sizeof(int32_t), cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess && nnz)
+    e = cudaMemcpyAsync(m->vals, vals, (size_t)nnz * sizeof(T), cudaMemcpyHostToDevice, s);
+  DevBuf<int> flag;
+  int hflag = 0;
+  int rc = SLC_OK;
+  if (e == cudaSuccess) rc = flag.alloc(1);
+  if (e == cudaSuccess && rc == SLC_OK) e = cudaMemsetAsync(flag.p, 0, sizeof(int), s);
+  if (e == cudaSuccess && rc == SLC_OK && nnz) {
+    k_validate_entries<<<(unsigned)ceil_div(nnz, 256), 256, 0, s>>>(nrows, ncols, nnz, m->colptr,
+                                                                     m->rowidx, flag.p);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess && rc == SLC_OK)
+    e = cudaMemcpyAsync(&hflag, flag.p, sizeof(int), cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess && rc == SLC_OK) e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess || rc != SLC_OK) {
+    matrix_release(m);
+    if (rc != SLC_OK) return rc;
+    return fail(SLC_ERR_CUDA, "upload: CUDA error %s", cudaGetErrorString(e));
+  }
+  if (hflag) {
+    matrix_release(m);
+    return fail(SLC_ERR_FORMAT, (hflag & 1) ? "upload: row index out of bounds"
+                                            : "upload: row indices not increasing in a column");
+  }
+  *out = m;
+  return SLC_OK;
+}
+
+template <class T>
+static int download_impl(const slc_matrix *m, int32_t *colptr, int32_t *rowidx, double *vals) {
+  if (!m) return fail(SLC_ERR_INVALID, "download: null handle");
+  if (m->elem != Num<T>::elem) return fail(SLC_ERR_INVALID, "download: element type mismatch");
+  cudaStream_t s = cur_stream();
+  if (colptr)
+    SLC_CUDA(cudaMemcpyAsync(colptr, m->colptr, ((size_t)m->ncols + 1) * sizeof(int32_t),
+                             cudaMemcpyDeviceToHost, s));
+  if (rowidx && m->nnz)
+    SLC_CUDA(cudaMemcpyAsync(rowidx, m->rowidx, (size_t)m->nnz * sizeof(int32_t),
+                             cudaMemcpyDeviceToHost, s));
+  if (vals && m->nnz)
+    SLC_CUDA(cudaMemcpyAsync(vals, m->vals, (size_t)m->nnz * sizeof(T), cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  return SLC_OK;
+}
+
+}  // namespace slc
+
+using namespace slc;
+
+extern "C" {
+
+int slc_version(void) { return 100; }
+
+const char *slc_last_error(void) { return tls().last_error.c_str(); }
+
+int slc_device_count(int *count) {
+  if (!count) return fail(SLC_ERR_INVALID, "slc_device_count: null argument");
+  cudaError_t e = cudaGetDeviceCount(count);
+  if (e != cudaSuccess) {
+    *count = 0;
+    (void)cudaGetLastError();
+    return fail(SLC_ERR_CUDA, "slc_device_count: %s", cudaGetErrorString(e));
+  }
+  return SLC_OK;
+}
+
+int slc_set_device(int device) {
+  SLC_CUDA(cudaSetDevice(device));
+  return SLC_OK;
+}
+
+int slc_set_stream(void *cuda_stream) {
+  tls().stream = (cudaStream_t)cuda_stream;
+  return SLC_OK;
+}
+
+int slc_synchronize(void) {
+  SLC_CUDA(cudaStreamSynchronize(cur_stream()));
+  return SLC_OK;
+}
+
+int64_t slc_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int slc_host_alloc(void **ptr, int64_t bytes) {
+  if (!ptr || bytes < 0) return fail(SLC_ERR_INVALID, "slc_host_alloc: bad argument");
+  SLC_CUDA(cudaMallocHost(ptr, (size_t)(bytes ? bytes : 1)));
+  return SLC_OK;
+}
+int slc_host_free(void *ptr) {
+  if (ptr) SLC_CUDA(cudaFreeHost(ptr));
+  return SLC_OK;
+}
+int slc_dev_alloc(void **ptr, int64_t bytes) {
+  if (!ptr || bytes < 0) return fail(SLC_ERR_INVALID, "slc_dev_alloc: bad argument");
+  SLC_CUDA(cudaMalloc(ptr, (size_t)(bytes ? bytes : 1)));
+  return SLC_OK;
+}
+int slc_dev_free(void *ptr) {
+  if (ptr) SLC_CUDA(cudaFree(ptr));
+  return SLC_OK;
+}
+int slc_memcpy_h2d(void *dst_dev, const void *src_host, int64_t bytes) {
+  if (bytes < 0) return fail(SLC_ERR_INVALID, "slc_memcpy_h2d: negative size");
+  if (bytes) {
+    SLC_CUDA(cudaMemcpyAsync(dst_dev, src_host, (size_t)bytes, cudaMemcpyHostToDevice, cur_stream()));
+    SLC_CUDA(cudaStreamSynchronize(cur_stream()));
+  }
+  return SLC_OK;
+}
+int slc_memcpy_d2h(void *dst_host, const void *src_dev, int64_t bytes) {
+  if (bytes < 0) return fail(SLC_ERR_INVALID, "slc_memcpy_d2h: negative size");
+  if (bytes) {
+    SLC_CUDA(cudaMemcpyAsync(dst_host, src_dev, (size_t)bytes, cudaMemcpyDeviceToHost, cur_stream()));
+    SLC_CUDA(cudaStreamSynchronize(cur_stream()));
+  }
+  return SLC_OK;
+}
+
+int slc_d_upload(int32_t nrows, int32_t ncols, const int32_t *colptr, const int32_t *rowidx,
+                 const double *vals, slc_matrix **out) {
+  return upload_impl<double>(nrows, ncols, colptr, rowidx, vals, out);
+}
+int slc_z_upload(int32_t nrows, int32_t ncols, const int32_t *colptr, const int32_t *rowidx,
+                 const double *vals, slc_matrix **out) {
+  return upload_impl<double2>(nrows, ncols, colptr, rowidx, vals, out);
+}
+
+void slc_free(slc_matrix *m) { matrix_release(m); }
+
+int slc_dims(const slc_matrix *m, int32_t *nrows, int32_t *ncols, int64_t *nnz) {
+  if (!m) return fail(SLC_ERR_INVALID, "slc_dims: null handle");
+  if (nrows) *nrows = m->nrows;
+  if (ncols) *ncols = m->ncols;
+  if (nnz) *nnz = m->nnz;
+  return SLC_OK;
+}
+
+int slc_elem_type(const slc_matrix *m) { return m ? m->elem : 0; }
+
+int slc_d_download(const slc_matrix *m, int32_t *colptr, int32_t *rowidx, double *vals) {
+  return download_impl<double>(m, colptr, rowidx, vals);
+}
+int slc_z_download(const slc_matrix *m, int32_t *colptr, int32_t *rowidx, double *vals) {
+  return download_impl<double2>(m, colptr, rowidx, vals);
+}
+
+}  // extern "C"

@@ -1,0 +1,475 @@
+// slc_spgemm.cu -- SpGEMM, C = A B, both CSC.
+//
+// Reference: mm (Data/Matrix/Sparse.hs:691-702) over the scatter/gather accumulator
+// (Data/Vector/Sparse/ScatterGather.hs:37-147): for each column j of B, reset the workspace,
+// for (k, b) in B[:, j] in order scatter A[:, k] with c <- c + a*b, then gather in row order.
+// What the result must keep from that:
+//   * structural product: a row is present as soon as one term landed on it; zeros stay;
+//   * rows strictly increasing inside a column;
+//   * the terms of one entry are added in increasing k, starting from 0.
+//
+// Device formulation (CSC Gustavson, column j of C owned by one thread group):
+//   pass 0  products per column (upper bound on the column's length) -> size class
+//   pass 1  symbolic: rows hashed into a shared-memory table sized by the class -> exact counts
+//   scan    counts -> C.colptr
+//   pass 2  numeric: same table plus a value per slot.  The group walks B[:, j] sequentially and
+//           spreads A[:, k] over its lanes: rows inside one A column are distinct, so slots are
+//           touched by one lane per step and steps are separated by a group barrier -- every
+//           entry receives its terms in increasing k, exactly like the reference.  The occupied
+//           slots are then compacted, bitonic-sorted by row, and written out.
+//   Columns too long for shared memory use a per-block dense workspace in HBM (the reference's
+//   own accumulator, with a stamp instead of a full reset and a scan limited to [min,max] row).
+#include "slc_common.cuh"
+
+namespace slc {
+
+constexpr int NCLASS = 4;           // 0: <=64 products, 1: <=512, 2: <=2048, 3: dense fallback
+constexpr int CLASS_UB0 = 64, CLASS_UB1 = 512, CLASS_UB2 = 2048;  // table = 2 * bound
+
+// ---- pass 0: products per column, classification ------------------------------------------------
+
+__global__ void k_mm_upper(int32_t bc, const int32_t *__restrict__ bp, const int32_t *__restrict__ bi,
+                           const int32_t *__restrict__ ap, int32_t *__restrict__ ub,
+                           int32_t *__restrict__ klass, int32_t *__restrict__ class_count) {
+  const int32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  int cls = -1;
+  if (j < bc) {
+    int64_t total = 0;
+    for (int32_t q = bp[j]; q < bp[j + 1]; ++q) {
+      const int32_t k = bi[q];
+      total += ap[k + 1] - ap[k];
+    }
+    ub[j] = total > 0x7fffffffLL ? 0x7fffffff : (int32_t)total;
+    if (total == 0) cls = -1;
+    else if (total <= CLASS_UB0) cls = 0;
+    else if (total <= CLASS_UB1) cls = 1;
+    else if (total <= CLASS_UB2) cls = 2;
+    else cls = 3;
+    klass[j] = cls;
+  }
+  // warp-aggregated class histogram
+  for (int c = 0; c < NCLASS; ++c) {
+    const unsigned m = __ballot_sync(0xffffffffu, cls == c);
+    if (m && (threadIdx.x & 31) == (__ffs(m) - 1)) atomicAdd(class_count + c, __popc(m));
+  }
+}
+
+// Bucket the column ids by class.  Order inside a class follows block scheduling (roughly
+// ascending, which keeps neighbouring groups on neighbouring columns of A); results do not
+// depend on it because every column writes to its own range of C.
+__global__ void k_mm_bucket(int32_t bc, const int32_t *__restrict__ klass,
+                            const int32_t *__restrict__ class_base, int32_t *__restrict__ cursor,
+                            int32_t *__restrict__ cols) {
+  const int32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int cls = j < bc ? klass[j] : -1;
+  for (int c = 0; c < NCLASS; ++c) {
+    const unsigned m = __ballot_sync(0xffffffffu, cls == c);
+    if (!m) continue;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(m) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(cursor + c, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (cls == c) cols[class_base[c] + base + __popc(m & ((1u << lane) - 1))] = j;
+  }
+}
+
+// ---- group helpers ------------------------------------------------------------------------------
+
+template <int G>
+__device__ __forceinline__ void group_sync(unsigned mask) {
+  if (G <= 32) __syncwarp(mask);
+  else __syncthreads();
+}
+
+__device__ __forceinline__ uint32_t hash_row(int32_t i, int log2h) {
+  return ((uint32_t)i * 0x9E3779B1u) >> (32 - log2h);
+}
+
+// find or claim the slot of row i; returns the slot, *fresh = claimed now
+__device__ __forceinline__ int table_insert(int32_t *keys, int hmask, int log2h, int32_t i, bool *fresh) {
+  uint32_t h = hash_row(i, log2h);
+  for (;;) {
+    const int32_t old = atomicCAS(keys + h, -1, i);
+    if (old == -1) {
+      *fresh = true;
+      return (int)h;
+    }
+    if (old == i) {
+      *fresh = false;
+      return (int)h;
+    }
+    h = (h + 1) & hmask;
+  }
+}
+
+// ---- pass 1: symbolic ---------------------------------------------------------------------------
+// G lanes per column, table of H row slots per group in shared memory.
+template <int G, int H, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+k_mm_symbolic(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32_t *__restrict__ ap,
+              const int32_t *__restrict__ ai, const int32_t *__restrict__ bp,
+              const int32_t *__restrict__ bi, int32_t *__restrict__ cnt) {
+  constexpr int GROUPS = THREADS / G;
+  constexpr int LOG2H = (H == 128) ? 7 : (H == 1024) ? 10 : 12;
+  static_assert((1 << LOG2H) == H, "table size");
+  extern __shared__ int32_t smem_i32[];
+  const int g = threadIdx.x / G;
+  const int gl = threadIdx.x % G;
+  int32_t *keys = smem_i32 + (size_t)g * H;
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned mask = G >= 32 ? 0xffffffffu : (((1u << G) - 1u) << (lane / G * G));
+  const int32_t slot = blockIdx.x * GROUPS + g;
+  const bool active = slot < ncols_in_class;  // uniform per group
+  for (int s = gl; s < H; s += G) keys[s] = -1;
+  group_sync<G>(mask);
+  int32_t mine = 0;
+  int32_t j = 0;
+  if (active) {
+    j = cols[slot];
+    for (int32_t q = bp[j]; q < bp[j + 1]; ++q) {
+      const int32_t k = __ldg(bi + q);
+      const int32_t pe = __ldg(ap + k + 1);
+      for (int32_t p = __ldg(ap + k) + gl; p < pe; p += G) {
+        bool fresh;
+        table_insert(keys, H - 1, LOG2H, __ldg(ai + p), &fresh);
+        mine += fresh ? 1 : 0;
+      }
+    }
+  }
+  // group reduction of the per-lane claim counts
+  if (G <= 32) {
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) mine += __shfl_xor_sync(mask, mine, o, G <= 32 ? G : 32);
+    if (active && gl == 0) cnt[j] = mine;
+  } else {
+    __shared__ int32_t total;
+    if (threadIdx.x == 0) total = 0;
+    __syncthreads();
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+    if (lane == 0 && mine) atomicAdd(&total, mine);
+    __syncthreads();
+    if (active && threadIdx.x == 0) cnt[j] = total;
+  }
+}
+
+// ---- pass 2: numeric ----------------------------------------------------------------------------
+
+// in-place bitonic sort of n_pad (power of two) 64-bit items by a group of G lanes
+template <int G>
+__device__ __forceinline__ void group_bitonic(uint64_t *a, int n_pad, int gl, unsigned mask) {
+  for (int k = 2; k <= n_pad; k <<= 1) {
+    for (int jj = k >> 1; jj > 0; jj >>= 1) {
+      for (int t = gl; t < (n_pad >> 1); t += G) {
+        const int lo = ((t & ~(jj - 1)) << 1) | (t & (jj - 1));
+        const int hi = lo | jj;
+        const bool up = (lo & k) == 0;
+        const uint64_t x = a[lo], y = a[hi];
+        if ((x > y) == up) {
+          a[lo] = y;
+          a[hi] = x;
+        }
+      }
+      group_sync<G>(mask);
+    }
+  }
+}
+
+template <class T, int G, int H, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+k_mm_numeric(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32_t *__restrict__ ap,
+             const int32_t *__restrict__ ai, const T *__restrict__ av, const int32_t *__restrict__ bp,
+             const int32_t *__restrict__ bi, const T *__restrict__ bv, const int32_t *__restrict__ cp,
+             int32_t *__restrict__ ci, T *__restrict__ cv) {
+  constexpr int GROUPS = THREADS / G;
+  constexpr int LOG2H = (H == 128) ? 7 : (H == 1024) ? 10 : 12;
+  static_assert((1 << LOG2H) == H, "table size");
+  // layout per block: [GROUPS][H] values | [GROUPS][H/2] packed sort items | [GROUPS][H] keys |
+  // counters.  A column of this class has at most H/2 products, hence at most H/2 rows.
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T *vals_all = reinterpret_cast<T *>(smem_raw);
+  uint64_t *items_all = reinterpret_cast<uint64_t *>(vals_all + (size_t)GROUPS * H);
+  int32_t *keys_all = reinterpret_cast<int32_t *>(items_all + (size_t)GROUPS * (H / 2));
+  int32_t *counters = keys_all + (size_t)GROUPS * H;
+  const int g = threadIdx.x / G;
+  const int gl = threadIdx.x % G;
+  T *vals = vals_all + (size_t)g * H;
+  uint64_t *items = items_all + (size_t)g * (H / 2);
+  int32_t *keys = keys_all + (size_t)g * H;
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned mask = G >= 32 ? 0xffffffffu : (((1u << G) - 1u) << (lane / G * G));
+  const int32_t slot = blockIdx.x * GROUPS + g;
+  const bool active = slot < ncols_in_class;  // uniform per group
+  for (int s = gl; s < H; s += G) {
+    keys[s] = -1;
+    vals[s] = Num<T>::zero();
+  }
+  if (gl == 0) counters[g] = 0;
+  group_sync<G>(mask);
+  if (!active && G <= 32) return;  // whole sub-warp group leaves together
+  int32_t j = 0;
+  if (active) {
+    j = cols[slot];
+    const int32_t qe = bp[j + 1];
+    for (int32_t q = bp[j]; q < qe; ++q) {
+      const int32_t k = __ldg(bi + q);
+      const T b = bv[q];
+      const int32_t pe = __ldg(ap + k + 1);
+      for (int32_t p = __ldg(ap + k) + gl; p < pe; p += G) {
+        bool fresh;
+        const int s = table_insert(keys, H - 1, LOG2H, __ldg(ai + p), &fresh);
+        vals[s] = Num<T>::add(vals[s], Num<T>::mul(av[p], b));  // c + a*b, Sparse.hs:699
+      }
+      group_sync<G>(mask);  // all terms of inner index k land before any of k+1
+    }
+    // compact the occupied slots: item = row << 32 | slot
+    for (int s = gl; s < H; s += G) {
+      const int32_t key = keys[s];
+      if (key >= 0) {
+        const int at = atomicAdd(counters + g, 1);
+        items[at] = ((uint64_t)(uint32_t)key << 32) | (uint32_t)s;
+      }
+    }
+  }
+  group_sync<G>(mask);
+  const int n = counters[g];
+  int n_pad = 1;
+  while (n_pad < n) n_pad <<= 1;
+  for (int s = n + gl; s < n_pad; s += G) items[s] = ~0ull;
+  group_sync<G>(mask);
+  group_bitonic<G>(items, n_pad, gl, mask);
+  if (active) {
+    const int32_t base = cp[j];
+    for (int e = gl; e < n; e += G) {
+      const uint64_t it = items[e];
+      ci[base + e] = (int32_t)(it >> 32);
+      cv[base + e] = vals[(uint32_t)it];
+    }
+  }
+}
+
+// ---- dense fallback for very long columns -------------------------------------------------------
+// One block walks its share of the class-3 columns.  stamp[i] == j+1 marks row i as present in
+// the column being built, so no reset pass is needed between columns.
+template <class T, bool NUMERIC>
+__global__ void __launch_bounds__(256)
+k_mm_dense(int32_t ncols_in_class, const int32_t *__restrict__ cols, int32_t ar,
+           const int32_t *__restrict__ ap, const int32_t *__restrict__ ai, const T *__restrict__ av,
+           const int32_t *__restrict__ bp, const int32_t *__restrict__ bi, const T *__restrict__ bv,
+           int32_t *__restrict__ stamp_all, T *__restrict__ work_all, int32_t *__restrict__ cnt,
+           const int32_t *__restrict__ cp, int32_t *__restrict__ ci, T *__restrict__ cv) {
+  __shared__ int32_t s_min, s_max, s_count;
+  __shared__ int32_t s_warp[8];
+  int32_t *stamp = stamp_all + (size_t)blockIdx.x * ar;
+  T *work = NUMERIC ? work_all + (size_t)blockIdx.x * ar : nullptr;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int32_t slot = blockIdx.x; slot < ncols_in_class; slot += gridDim.x) {
+    const int32_t j = cols[slot];
+    const int32_t id = j + 1;
+    if (tid == 0) {
+      s_min = 0x7fffffff;
+      s_max = -1;
+      s_count = 0;
+    }
+    __syncthreads();
+    int32_t lmin = 0x7fffffff, lmax = -1;
+    for (int32_t q = bp[j]; q < bp[j + 1]; ++q) {
+      const int32_t k = bi[q];
+      const int32_t pe = ap[k + 1];
+      T b = Num<T>::zero();
+      if (NUMERIC) b = bv[q];
+      for (int32_t p = ap[k] + tid; p < pe; p += 256) {
+        const int32_t i = ai[p];
+        if (stamp[i] != id) {
+          stamp[i] = id;
+          if (NUMERIC) work[i] = Num<T>::zero();
+        }
+        if (NUMERIC) work[i] = Num<T>::add(work[i], Num<T>::mul(av[p], b));
+        lmin = min(lmin, i);
+        lmax = max(lmax, i);
+      }
+      __syncthreads();  // keep the terms of one entry in increasing inner index
+    }
+    atomicMin(&s_min, lmin);
+    atomicMax(&s_max, lmax);
+    __syncthreads();
+    const int32_t lo = s_min, hi = s_max;
+    // ordered compaction of the stamped rows in [lo, hi]
+    int32_t written = 0;
+    for (int32_t base_row = lo; base_row <= hi; base_row += 256) {
+      const int32_t i = base_row + tid;
+      const bool present = i <= hi && stamp[i] == id;
+      const unsigned bal = __ballot_sync(0xffffffffu, present);
+      if (lane == 0) s_warp[warp] = __popc(bal);
+      __syncthreads();
+      int32_t before = 0, total = 0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) {
+        const int32_t c = s_warp[w];
+        before += (w < warp) ? c : 0;
+        total += c;
+      }
+      if (NUMERIC && present) {
+        const int32_t at = cp[j] + written + before + __popc(bal & ((1u << lane) - 1));
+        ci[at] = i;
+        cv[at] = work[i];
+      }
+      written += total;
+      __syncthreads();
+    }
+    if (!NUMERIC && tid == 0) cnt[j] = written;
+    __syncthreads();
+  }
+}
+
+__global__ void k_widen(int64_t n, const int32_t *__restrict__ in, int64_t *__restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = in[i];
+}
+__global__ void k_narrow(int64_t n, const int64_t *__restrict__ in, int32_t *__restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (int32_t)in[i];
+}
+
+template <class T, int G, int H, int THREADS>
+static int run_symbolic(int32_t n, const int32_t *cols, const slc_matrix *a, const slc_matrix *b,
+                        int32_t *cnt) {
+  if (n == 0) return SLC_OK;
+  constexpr int GROUPS = THREADS / G;
+  const size_t smem = (size_t)GROUPS * H * sizeof(int32_t);
+  auto kern = k_mm_symbolic<G, H, THREADS>;
+  if (smem > 48 * 1024)
+    SLC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(unsigned)ceil_div(n, GROUPS), THREADS, smem, cur_stream()>>>(n, cols, a->colptr, a->rowidx,
+                                                                        b->colptr, b->rowidx, cnt);
+  SLC_LAUNCHED();
+  return SLC_OK;
+}
+
+template <class T, int G, int H, int THREADS>
+static int run_numeric(int32_t n, const int32_t *cols, const slc_matrix *a, const slc_matrix *b,
+                       slc_matrix *c) {
+  if (n == 0) return SLC_OK;
+  constexpr int GROUPS = THREADS / G;
+  const size_t smem = (size_t)GROUPS * H * (sizeof(T) + sizeof(int32_t)) +
+                      (size_t)GROUPS * (H / 2) * sizeof(uint64_t) + (size_t)GROUPS * sizeof(int32_t);
+  auto kern = k_mm_numeric<T, G, H, THREADS>;
+  if (smem > 48 * 1024)
+    SLC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(unsigned)ceil_div(n, GROUPS), THREADS, smem, cur_stream()>>>(
+      n, cols, a->colptr, a->rowidx, (const T *)a->vals, b->colptr, b->rowidx, (const T *)b->vals,
+      c->colptr, c->rowidx, (T *)c->vals);
+  SLC_LAUNCHED();
+  return SLC_OK;
+}
+
+template <class T>
+static int mm_entry(const slc_matrix *a, const slc_matrix *b, slc_matrix **out) {
+  if (!a || !b || !out) return fail(SLC_ERR_INVALID, "mm: null argument");
+  *out = nullptr;
+  if (a->elem != Num<T>::elem || b->elem != Num<T>::elem)
+    return fail(SLC_ERR_INVALID, "mm: element type mismatch");
+  if (a->ncols != b->nrows) return fail(SLC_ERR_DIM, "mm: inner dimension mismatch");
+  cudaStream_t s = cur_stream();
+  const int32_t ar = a->nrows, bc = b->ncols;
+
+  // pass 0
+  DevBuf<int32_t> ub, klass, ccount, cols, cnt, cursor, cbase;
+  SLC_TRY(ub.alloc((size_t)bc));
+  SLC_TRY(klass.alloc((size_t)bc));
+  SLC_TRY(ccount.alloc(NCLASS));
+  SLC_TRY(cursor.alloc(NCLASS));
+  SLC_TRY(cbase.alloc(NCLASS));
+  SLC_TRY(cols.alloc((size_t)bc));
+  SLC_TRY(cnt.alloc((size_t)bc + 1));
+  SLC_CUDA(cudaMemsetAsync(ccount.p, 0, NCLASS * sizeof(int32_t), s));
+  SLC_CUDA(cudaMemsetAsync(cursor.p, 0, NCLASS * sizeof(int32_t), s));
+  SLC_CUDA(cudaMemsetAsync(cnt.p, 0, ((size_t)bc + 1) * sizeof(int32_t), s));
+  int32_t hcount[NCLASS] = {0, 0, 0, 0}, hbase[NCLASS] = {0, 0, 0, 0};
+  if (bc > 0) {
+    const unsigned nb = (unsigned)ceil_div(bc, 256);
+    k_mm_upper<<<nb, 256, 0, s>>>(bc, b->colptr, b->rowidx, a->colptr, ub.p, klass.p, ccount.p);
+    SLC_LAUNCHED();
+    SLC_CUDA(cudaMemcpyAsync(hcount, ccount.p, sizeof hcount, cudaMemcpyDeviceToHost, s));
+    SLC_CUDA(cudaStreamSynchronize(s));
+    for (int c = 1; c < NCLASS; ++c) hbase[c] = hbase[c - 1] + hcount[c - 1];
+    SLC_CUDA(cudaMemcpyAsync(cbase.p, hbase, sizeof hbase, cudaMemcpyHostToDevice, s));
+    k_mm_bucket<<<nb, 256, 0, s>>>(bc, klass.p, cbase.p, cursor.p, cols.p);
+    SLC_LAUNCHED();
+  }
+
+  // dense-fallback workspace, bounded to ~4 GB
+  DevBuf<int32_t> stamp;
+  DevBuf<T> work;
+  int dense_blocks = 0;
+  if (hcount[3] > 0) {
+    const size_t per_block = (size_t)(ar > 0 ? ar : 1) * (sizeof(int32_t) + sizeof(T));
+    size_t fit = ((size_t)4 << 30) / per_block;
+    if (fit < 1) fit = 1;
+    dense_blocks = (int)(fit < (size_t)(2 * sm_count()) ? fit : (size_t)(2 * sm_count()));
+    if (dense_blocks > hcount[3]) dense_blocks = hcount[3];
+    SLC_TRY(stamp.alloc((size_t)dense_blocks * ar));
+    SLC_TRY(work.alloc((size_t)dense_blocks * ar));
+    SLC_CUDA(cudaMemsetAsync(stamp.p, 0, (size_t)dense_blocks * ar * sizeof(int32_t), s));
+  }
+
+  // pass 1: symbolic
+  SLC_TRY((run_symbolic<T, 8, 128, 128>(hcount[0], cols.p + hbase[0], a, b, cnt.p)));
+  SLC_TRY((run_symbolic<T, 32, 1024, 128>(hcount[1], cols.p + hbase[1], a, b, cnt.p)));
+  SLC_TRY((run_symbolic<T, 256, 4096, 256>(hcount[2], cols.p + hbase[2], a, b, cnt.p)));
+  if (hcount[3] > 0) {
+    k_mm_dense<T, false><<<dense_blocks, 256, 0, s>>>(hcount[3], cols.p + hbase[3], ar, a->colptr,
+                                                      a->rowidx, (const T *)a->vals, b->colptr, b->rowidx,
+                                                      (const T *)b->vals, stamp.p, work.p, cnt.p, nullptr,
+                                                      nullptr, nullptr);
+    SLC_LAUNCHED();
+    // the numeric pass reuses the stamps with the same ids: clear them
+    SLC_CUDA(cudaMemsetAsync(stamp.p, 0, (size_t)dense_blocks * ar * sizeof(int32_t), s));
+  }
+
+  // counts -> pointers (64-bit scan so an oversized product is reported, not wrapped)
+  DevBuf<int64_t> wide, ptr64;
+  SLC_TRY(wide.alloc((size_t)bc + 1));
+  SLC_TRY(ptr64.alloc((size_t)bc + 1));
+  k_widen<<<(unsigned)ceil_div((int64_t)bc + 1, 256), 256, 0, s>>>((int64_t)bc + 1, cnt.p, wide.p);
+  SLC_LAUNCHED();
+  SLC_TRY(exclusive_scan_i64(wide.p, ptr64.p, (int64_t)bc + 1));
+  int64_t nnzc = 0;
+  SLC_CUDA(cudaMemcpyAsync(&nnzc, ptr64.p + bc, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  if (nnzc > 0x7fffffffLL) return fail(SLC_ERR_RANGE, "mm: product has %lld entries, more than 32-bit pointers hold", (long long)nnzc);
+
+  slc_matrix *c = nullptr;
+  SLC_TRY(matrix_alloc(a->elem, ar, bc, nnzc, &c));
+  k_narrow<<<(unsigned)ceil_div((int64_t)bc + 1, 256), 256, 0, s>>>((int64_t)bc + 1, ptr64.p, c->colptr);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+
+  // pass 2: numeric
+  int rc = run_numeric<T, 8, 128, 128>(hcount[0], cols.p + hbase[0], a, b, c);
+  if (rc == SLC_OK) rc = run_numeric<T, 32, 1024, 128>(hcount[1], cols.p + hbase[1], a, b, c);
+  if (rc == SLC_OK) rc = run_numeric<T, 256, 4096, 256>(hcount[2], cols.p + hbase[2], a, b, c);
+  if (rc == SLC_OK && hcount[3] > 0) {
+    k_mm_dense<T, true><<<dense_blocks, 256, 0, s>>>(hcount[3], cols.p + hbase[3], ar, a->colptr, a->rowidx,
+                                                     (const T *)a->vals, b->colptr, b->rowidx,
+                                                     (const T *)b->vals, stamp.p, work.p, cnt.p, c->colptr,
+                                                     c->rowidx, (T *)c->vals);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (cudaGetLastError() != cudaSuccess) rc = fail(SLC_ERR_CUDA, "mm: dense pass launch failed");
+  }
+  if (rc != SLC_OK) {
+    matrix_release(c);
+    return rc;
+  }
+  *out = c;
+  return SLC_OK;
+}
+
+}  // namespace slc
+
+using namespace slc;
+
+extern "C" {
+int slc_d_mm(const slc_matrix *a, const slc_matrix *b, slc_matrix **c) { return mm_entry<double>(a, b, c); }
+int slc_z_mm(const slc_matrix *a, const slc_matrix *b, slc_matrix **c) { return mm_entry<double2>(a, b, c); }
+}

@@ -1,0 +1,669 @@
+// slc_spmv.cu -- SpMV (mulV / axpy / axpy_) and SpMM (FEAST multiplyWork / mulM).
+//
+// Reference semantics (Data/Matrix/Sparse.hs:433-471): walk the CSC columns in order and do
+// y[r] <- a*x[c] + y[r].  Seen from one output row that is: start from y0 (0 for mulV) and add
+// the row's terms in increasing column order, product rounded, then sum rounded.  The kernels
+// below gather along the row-major mirror instead of scattering along columns; wherever one
+// thread owns a whole row it adds the terms in exactly that order, so the result is bit-identical
+// to the reference; where a row is split across lanes the order is a fixed tree (deterministic,
+// within the 1e-12 tolerance).
+//
+// Kernel families, chosen per matrix from its row-length statistics (slc_set_spmv_kernel
+// overrides):
+//   SELL-32        rows grouped in slices of 32, stored column-major inside the slice, one thread
+//                  per row: index/value streams and the x gather are both lane-contiguous.  Used
+//                  when padding costs < 12.5 % (stencils).
+//   CSR balanced   fixed chunks of nonzeros per block, products staged in shared memory, rows
+//                  reduced from there; rows spanning chunks are stitched by a fix-up kernel.
+//                  Used for irregular (power-law) matrices.
+//   CSR warp/row   one warp per row with a shuffle tree; kept as a simple cross-check.
+#include <cstdlib>
+
+#include "slc_common.cuh"
+
+namespace slc {
+
+// =================================================================================================
+// plans
+// =================================================================================================
+
+constexpr int SELL_C = 32;
+constexpr int BAL_THREADS = 256;
+constexpr int BAL_ITEMS = 8;
+constexpr int BAL_CHUNK = BAL_THREADS * BAL_ITEMS;  // nonzeros per block
+
+// one warp per slice: row lengths and the slice width (elements = width * 32)
+__global__ void k_sell_widths(int32_t nrows, int32_t nslices, const int32_t *__restrict__ rowptr,
+                              int32_t *__restrict__ rowlen, int64_t *__restrict__ slice_elems,
+                              int32_t *__restrict__ max_len) {
+  const int32_t slice = (int32_t)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  const int lane = threadIdx.x & 31;
+  if (slice >= nslices) return;
+  const int32_t row = slice * SELL_C + lane;
+  int32_t len = 0;
+  if (row < nrows) {
+    len = rowptr[row + 1] - rowptr[row];
+    rowlen[row] = len;
+  }
+  int32_t w = len;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) w = max(w, __shfl_xor_sync(0xffffffffu, w, o));
+  if (lane == 0) {
+    slice_elems[slice] = (int64_t)w * SELL_C;
+    atomicMax(max_len, w);
+  }
+  if (slice == 0 && lane == 0) slice_elems[nslices] = 0;
+}
+
+template <class T>
+__global__ void k_sell_fill(int32_t nrows, int32_t nslices, const int32_t *__restrict__ rowptr,
+                            const int32_t *__restrict__ colidx, const T *__restrict__ vals,
+                            const int64_t *__restrict__ slice_ptr, int32_t *__restrict__ s_col,
+                            T *__restrict__ s_val) {
+  const int32_t slice = (int32_t)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  const int lane = threadIdx.x & 31;
+  if (slice >= nslices) return;
+  const int32_t row = slice * SELL_C + lane;
+  const int64_t base = slice_ptr[slice];
+  const int32_t width = (int32_t)((slice_ptr[slice + 1] - base) / SELL_C);
+  int32_t start = 0, len = 0;
+  if (row < nrows) {
+    start = rowptr[row];
+    len = rowptr[row + 1] - start;
+  }
+  for (int32_t k = 0; k < width; ++k) {
+    const int64_t at = base + (int64_t)k * SELL_C + lane;
+    if (k < len) {
+      s_col[at] = colidx[start + k];
+      s_val[at] = vals[start + k];
+    } else {  // padding is never read by the product kernels (they stop at rowlen)
+      s_col[at] = 0;
+      s_val[at] = Num<T>::zero();
+    }
+  }
+}
+
+// first row whose start is >= chunk start (rows that begin inside chunk b are owned by b)
+__global__ void k_bal_first_owned(int32_t nrows, int64_t nnz, int32_t nchunks,
+                                  const int32_t *__restrict__ rowptr, int32_t *__restrict__ first_owned) {
+  const int32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b > nchunks) return;
+  if (b == nchunks) {
+    first_owned[b] = nrows;
+    return;
+  }
+  const int64_t start = (int64_t)b * BAL_CHUNK;
+  int32_t lo = 0, hi = nrows;  // lower_bound over rowptr[0..nrows)
+  while (lo < hi) {
+    int32_t mid = lo + ((hi - lo) >> 1);
+    if ((int64_t)rowptr[mid] < start) lo = mid + 1;
+    else hi = mid;
+  }
+  first_owned[b] = lo;
+  (void)nnz;
+}
+
+template <class T>
+static int build_sell(slc_matrix *m) {
+  SellPlan &sp = m->sell;
+  if (sp.built) return SLC_OK;
+  cudaStream_t s = cur_stream();
+  const int32_t nslices = (int32_t)ceil_div(m->nrows, SELL_C);
+  DevBuf<int64_t> elems, sptr;
+  DevBuf<int32_t> rowlen, maxlen;
+  SLC_TRY(elems.alloc((size_t)nslices + 1));
+  SLC_TRY(sptr.alloc((size_t)nslices + 1));
+  SLC_TRY(rowlen.alloc((size_t)m->nrows));
+  SLC_TRY(maxlen.alloc(1));
+  SLC_CUDA(cudaMemsetAsync(maxlen.p, 0, sizeof(int32_t), s));
+  SLC_CUDA(cudaMemsetAsync(elems.p, 0, ((size_t)nslices + 1) * sizeof(int64_t), s));
+  if (nslices) {
+    k_sell_widths<<<(unsigned)ceil_div((int64_t)nslices * 32, 256), 256, 0, s>>>(
+        m->nrows, nslices, m->rowptr, rowlen.p, elems.p, maxlen.p);
+    SLC_LAUNCHED();
+  }
+  SLC_TRY(exclusive_scan_i64(elems.p, sptr.p, (int64_t)nslices + 1));
+  int64_t padded = 0;
+  int32_t hmax = 0;
+  SLC_CUDA(cudaMemcpyAsync(&padded, sptr.p + nslices, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaMemcpyAsync(&hmax, maxlen.p, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  m->max_rowlen = hmax;
+  sp.nslices = nslices;
+  sp.padded = padded;
+  sp.slice_ptr = sptr.take();
+  sp.rowlen = rowlen.take();
+  sp.built = true;  // widths known; arrays filled lazily by fill_sell
+  return SLC_OK;
+}
+
+template <class T>
+static int fill_sell(slc_matrix *m) {
+  SellPlan &sp = m->sell;
+  if (sp.colidx) return SLC_OK;
+  cudaStream_t s = cur_stream();
+  DevBuf<int32_t> sc;
+  DevBuf<T> sv;
+  SLC_TRY(sc.alloc((size_t)sp.padded));
+  SLC_TRY(sv.alloc((size_t)sp.padded));
+  if (sp.nslices) {
+    k_sell_fill<T><<<(unsigned)ceil_div((int64_t)sp.nslices * 32, 256), 256, 0, s>>>(
+        m->nrows, sp.nslices, m->rowptr, m->colidx, (const T *)m->rvals, sp.slice_ptr, sc.p, sv.p);
+    SLC_LAUNCHED();
+  }
+  sp.colidx = sc.take();
+  sp.vals = sv.take();
+  return SLC_OK;
+}
+
+static int build_balanced(slc_matrix *m) {
+  BalancedPlan &bp = m->bal;
+  if (bp.built) return SLC_OK;
+  const int32_t nchunks = (int32_t)ceil_div(m->nnz, BAL_CHUNK);
+  DevBuf<int32_t> fo;
+  SLC_TRY(fo.alloc((size_t)nchunks + 1));
+  k_bal_first_owned<<<(unsigned)ceil_div((int64_t)nchunks + 1, 256), 256, 0, cur_stream()>>>(
+      m->nrows, m->nnz, nchunks, m->rowptr, fo.p);
+  SLC_LAUNCHED();
+  bp.nchunks = nchunks;
+  bp.chunk_row = fo.take();
+  bp.built = true;
+  return SLC_OK;
+}
+
+// Build the mirror, measure the rows and settle on a kernel family.
+template <class T>
+static int ensure_plan(slc_matrix *m) {
+  SLC_TRY(ensure_csr(m));
+  SLC_TRY(build_sell<T>(m));  // cheap: gives padded size and max row length
+  int kind = m->spmv_kind;
+  if (kind == SPMV_AUTO) {
+    // Sliced ELL streams `padded` entries instead of nnz; accept up to 12.5 % extra traffic.
+    const bool regular = m->sell.padded <= m->nnz + m->nnz / 8 + 1024;
+    kind = regular ? SPMV_SELL : SPMV_CSR_BALANCED;
+  }
+  if (kind == SPMV_SELL) SLC_TRY(fill_sell<T>(m));
+  if (kind == SPMV_CSR_BALANCED) SLC_TRY(build_balanced(m));
+  m->spmv_active = kind;
+  return SLC_OK;
+}
+
+// =================================================================================================
+// SpMV kernels
+// =================================================================================================
+
+// ---- SELL-32, one thread per row ----------------------------------------------------------------
+// Per k the 32 lanes of a warp read 32 consecutive indices (128 B) and 32 consecutive values
+// (256/512 B); on a stencil the gathered x entries are consecutive too.  U entries are fetched
+// before any is used, so each thread keeps U index + U value loads in flight.
+template <class T, int U, bool ACC>
+__global__ void __launch_bounds__(256)
+k_spmv_sell(int32_t nrows, const int64_t *__restrict__ slice_ptr, const int32_t *__restrict__ rowlen,
+            const int32_t *__restrict__ colidx, const T *__restrict__ vals, const T *__restrict__ x,
+            T *__restrict__ y) {
+  const int32_t row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= nrows) return;
+  const uint64_t pol_s = policy_evict_first();
+  const uint64_t pol_x = policy_evict_last();
+  const int64_t base = __ldg(slice_ptr + (row >> 5)) + (threadIdx.x & 31);
+  const int32_t len = __ldg(rowlen + row);
+  const int32_t *ci = colidx + base;
+  const T *va = vals + base;
+  T acc = ACC ? y[row] : Num<T>::zero();
+  for (int32_t k = 0; k < len; k += U) {
+    int32_t c[U];
+    T a[U], xv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const bool ok = k + u < len;
+      c[u] = ok ? ld_stream(ci + (int64_t)(k + u) * SELL_C, pol_s) : 0;
+      a[u] = ok ? ld_stream(va + (int64_t)(k + u) * SELL_C, pol_s) : Num<T>::zero();
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) xv[u] = (k + u < len) ? ld_gather(x + c[u], pol_x) : Num<T>::zero();
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (k + u < len) acc = Num<T>::add(Num<T>::mul(a[u], xv[u]), acc);
+  }
+  st_stream(y + row, acc);
+}
+
+// ---- CSR, one warp per row ----------------------------------------------------------------------
+template <class T>
+__device__ __forceinline__ T warp_sum(T v);
+template <>
+__device__ __forceinline__ double warp_sum<double>(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = __dadd_rn(v, __shfl_down_sync(0xffffffffu, v, o));
+  return v;
+}
+template <>
+__device__ __forceinline__ double2 warp_sum<double2>(double2 v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    v.x = __dadd_rn(v.x, __shfl_down_sync(0xffffffffu, v.x, o));
+    v.y = __dadd_rn(v.y, __shfl_down_sync(0xffffffffu, v.y, o));
+  }
+  return v;
+}
+
+template <class T, bool ACC>
+__global__ void __launch_bounds__(256)
+k_spmv_csr_warp(int32_t nrows, const int32_t *__restrict__ rowptr, const int32_t *__restrict__ colidx,
+                const T *__restrict__ vals, const T *__restrict__ x, T *__restrict__ y) {
+  const int32_t row = (int32_t)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= nrows) return;
+  const uint64_t pol_s = policy_evict_first();
+  const uint64_t pol_x = policy_evict_last();
+  const int32_t beg = rowptr[row], end = rowptr[row + 1];
+  T acc = Num<T>::zero();
+  for (int32_t p = beg + lane; p < end; p += 32) {
+    const int32_t c = ld_stream(colidx + p, pol_s);
+    const T a = ld_stream(vals + p, pol_s);
+    acc = Num<T>::add(Num<T>::mul(a, ld_gather(x + c, pol_x)), acc);
+  }
+  acc = warp_sum<T>(acc);
+  if (lane == 0) y[row] = ACC ? Num<T>::add(acc, y[row]) : acc;
+}
+
+// ---- CSR, nnz-balanced --------------------------------------------------------------------------
+// Block b owns nonzeros [b*CHUNK, (b+1)*CHUNK).  Phase 1: coalesced loads, products into shared
+// memory.  Phase 2: the rows that START inside the chunk are reduced from shared memory (a thread
+// per row when the chunk holds many rows, a warp per row when it holds few); the piece of a row
+// that started in an earlier chunk goes to part_head[b], the piece of a row that runs past the
+// chunk goes to part_tail[b].  k_spmv_bal_fixup then adds the pieces of each spanning row in order.
+template <class T, bool ACC>
+__global__ void __launch_bounds__(BAL_THREADS)
+k_spmv_bal(int32_t nrows, int64_t nnz, const int32_t *__restrict__ rowptr,
+           const int32_t *__restrict__ colidx, const T *__restrict__ vals,
+           const int32_t *__restrict__ first_owned, const T *__restrict__ x, T *__restrict__ y,
+           T *__restrict__ part_head, T *__restrict__ part_tail) {
+  __shared__ T prod[BAL_CHUNK];
+  const int32_t b = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int64_t start = (int64_t)b * BAL_CHUNK;
+  const int64_t end = min(nnz, start + BAL_CHUNK);
+  const int32_t cnt = (int32_t)(end - start);
+  const uint64_t pol_s = policy_evict_first();
+  const uint64_t pol_x = policy_evict_last();
+
+  {
+    int32_t c[BAL_ITEMS];
+    T a[BAL_ITEMS];
+#pragma unroll
+    for (int i = 0; i < BAL_ITEMS; ++i) {
+      const int32_t e = i * BAL_THREADS + tid;
+      const bool ok = e < cnt;
+      c[i] = ok ? ld_stream(colidx + start + e, pol_s) : 0;
+      a[i] = ok ? ld_stream(vals + start + e, pol_s) : Num<T>::zero();
+    }
+#pragma unroll
+    for (int i = 0; i < BAL_ITEMS; ++i) {
+      const int32_t e = i * BAL_THREADS + tid;
+      if (e < cnt) prod[e] = Num<T>::mul(a[i], ld_gather(x + c[i], pol_x));
+    }
+  }
+  __syncthreads();
+
+  const int32_t fo = first_owned[b];
+  const int32_t fo_next = first_owned[b + 1];
+  // piece of the row that began before this chunk
+  const int64_t head_end = min((int64_t)rowptr[fo], end);  // rowptr[nrows] == nnz
+  const int32_t head_cnt = (int32_t)(head_end - start);   // may be 0
+  const int32_t nown = fo_next - fo;
+
+  if (nown >= 64) {  // many short rows: thread per row, terms added in column order
+    for (int32_t r = fo + tid; r < fo_next; r += BAL_THREADS) {
+      const int64_t rb = rowptr[r], re = rowptr[r + 1];
+      const int64_t se = min(re, end);
+      const bool complete = re <= end;
+      T acc = (ACC && complete) ? y[r] : Num<T>::zero();
+      for (int64_t p = rb; p < se; ++p) acc = Num<T>::add(prod[p - start], acc);
+      if (complete) y[r] = acc;
+      else part_tail[b] = acc;
+    }
+    if (tid == BAL_THREADS - 1) {  // head piece, sequential (short by construction here)
+      T acc = Num<T>::zero();
+      for (int32_t p = 0; p < head_cnt; ++p) acc = Num<T>::add(prod[p], acc);
+      part_head[b] = acc;
+    }
+  } else {  // few long rows: warp per segment, segment 0 is the head piece
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int32_t sgm = warp; sgm <= nown; sgm += BAL_THREADS / 32) {
+      int64_t sb, se;
+      bool complete = false;
+      int32_t r = -1;
+      if (sgm == 0) {
+        sb = start;
+        se = head_end;
+      } else {
+        r = fo + sgm - 1;
+        sb = rowptr[r];
+        const int64_t re = rowptr[r + 1];
+        se = min(re, end);
+        complete = re <= end;
+      }
+      T acc = Num<T>::zero();
+      for (int64_t p = sb + lane; p < se; p += 32) acc = Num<T>::add(prod[p - start], acc);
+      acc = warp_sum<T>(acc);
+      if (lane == 0) {
+        if (sgm == 0) part_head[b] = acc;
+        else if (complete) y[r] = ACC ? Num<T>::add(acc, y[r]) : acc;
+        else part_tail[b] = acc;
+      }
+    }
+  }
+}
+
+// One thread per chunk: if the last row owned by chunk b runs past the chunk, add its pieces.
+template <class T, bool ACC>
+__global__ void k_spmv_bal_fixup(int32_t nchunks, int64_t nnz, const int32_t *__restrict__ rowptr,
+                                 const int32_t *__restrict__ first_owned, const T *__restrict__ part_head,
+                                 const T *__restrict__ part_tail, T *__restrict__ y) {
+  const int32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nchunks) return;
+  const int32_t fo = first_owned[b], fo_next = first_owned[b + 1];
+  if (fo_next <= fo) return;
+  const int32_t r = fo_next - 1;
+  const int64_t re = rowptr[r + 1];
+  const int64_t end = min(nnz, (int64_t)(b + 1) * BAL_CHUNK);
+  if (re <= end) return;
+  T total = part_tail[b];
+  for (int32_t bb = b + 1; bb < nchunks; ++bb) {
+    total = Num<T>::add(total, part_head[bb]);
+    if (re <= min(nnz, (int64_t)(bb + 1) * BAL_CHUNK)) break;
+  }
+  y[r] = ACC ? Num<T>::add(total, y[r]) : total;
+}
+
+template <class T, bool ACC>
+__global__ void k_fill_zero_or_keep(int64_t n, T *__restrict__ y) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && !ACC) y[i] = Num<T>::zero();
+}
+
+// =================================================================================================
+// SpMM kernels:  Y[:, j] <- A X[:, j], column-major X and Y
+// =================================================================================================
+// One thread per row and JT columns per thread; the row's (index, value) pairs are read once per
+// column tile and reused for JT gathers.  Blocks are numbered tile-fastest, so the blocks that
+// share a row block (and its slice of A and window of X) run at the same time and meet in L2.
+template <class T, int JT, bool SELL>
+__global__ void __launch_bounds__(128)
+k_spmm_rows(int32_t nrows, int32_t ntiles, const int64_t *__restrict__ slice_ptr,
+            const int32_t *__restrict__ rowlen, const int32_t *__restrict__ rowptr,
+            const int32_t *__restrict__ colidx, const T *__restrict__ vals, const T *__restrict__ X,
+            int64_t ldx, T *__restrict__ Y, int64_t ldy, int32_t k) {
+  const int32_t rb = blockIdx.x / ntiles;
+  const int32_t tile = blockIdx.x - rb * ntiles;
+  const int32_t row = rb * blockDim.x + threadIdx.x;
+  if (row >= nrows) return;
+  const int32_t j0 = tile * JT;
+  const uint64_t pol_x = policy_evict_last();
+  int64_t base;
+  int32_t len;
+  int32_t stride;
+  if (SELL) {
+    base = __ldg(slice_ptr + (row >> 5)) + (threadIdx.x & 31);
+    len = __ldg(rowlen + row);
+    stride = SELL_C;
+  } else {
+    base = rowptr[row];
+    len = rowptr[row + 1] - (int32_t)base;
+    stride = 1;
+  }
+  T acc[JT];
+#pragma unroll
+  for (int j = 0; j < JT; ++j) acc[j] = Num<T>::zero();
+  const T *xb = X + (int64_t)j0 * ldx;
+  for (int32_t kk = 0; kk < len; ++kk) {
+    const int32_t c = __ldg(colidx + base + (int64_t)kk * stride);
+    const T a = __ldg(vals + base + (int64_t)kk * stride);
+    T xv[JT];
+#pragma unroll
+    for (int j = 0; j < JT; ++j)
+      xv[j] = (j0 + j < k) ? ld_gather(xb + (int64_t)j * ldx + c, pol_x) : Num<T>::zero();
+#pragma unroll
+    for (int j = 0; j < JT; ++j) acc[j] = Num<T>::add(Num<T>::mul(a, xv[j]), acc[j]);
+  }
+#pragma unroll
+  for (int j = 0; j < JT; ++j)
+    if (j0 + j < k) st_stream(Y + (int64_t)(j0 + j) * ldy + row, acc[j]);
+}
+
+// =================================================================================================
+// dispatch
+// =================================================================================================
+
+static int env_int(const char *name, int dflt) {
+  const char *v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
+
+template <class T, bool ACC>
+static int launch_sell(slc_matrix *m, const T *x, T *y) {
+  const SellPlan &sp = m->sell;
+  cudaStream_t s = cur_stream();
+  const unsigned nb = (unsigned)ceil_div(m->nrows, 256);
+  static const int u_env = env_int("SLC_SELL_U", 0);
+  int u = u_env;
+  if (u == 0) u = m->max_rowlen <= 4 ? 4 : (m->max_rowlen <= 12 ? 8 : 16);
+#define SLC_SELL_CASE(UU)                                                                          \
+  k_spmv_sell<T, UU, ACC><<<nb, 256, 0, s>>>(m->nrows, sp.slice_ptr, sp.rowlen, sp.colidx,         \
+                                             (const T *)sp.vals, x, y)
+  if (u <= 4) SLC_SELL_CASE(4);
+  else if (u <= 8) SLC_SELL_CASE(8);
+  else SLC_SELL_CASE(16);
+#undef SLC_SELL_CASE
+  SLC_LAUNCHED();
+  return SLC_OK;
+}
+
+template <class T, bool ACC>
+static int spmv_dev(slc_matrix *m, const T *x, T *y) {
+  if (m->nrows == 0) return SLC_OK;
+  cudaStream_t s = cur_stream();
+  if (m->nnz == 0) {
+    if (!ACC) SLC_CUDA(cudaMemsetAsync(y, 0, (size_t)m->nrows * sizeof(T), s));
+    return SLC_OK;
+  }
+  SLC_TRY(ensure_plan<T>(m));
+  switch (m->spmv_active) {
+    case SPMV_SELL:
+      return launch_sell<T, ACC>(m, x, y);
+    case SPMV_CSR_WARP: {
+      k_spmv_csr_warp<T, ACC><<<(unsigned)ceil_div((int64_t)m->nrows * 32, 256), 256, 0, s>>>(
+          m->nrows, m->rowptr, m->colidx, (const T *)m->rvals, x, y);
+      SLC_LAUNCHED();
+      return SLC_OK;
+    }
+    default: {
+      const BalancedPlan &bp = m->bal;
+      DevBuf<T> ph, pt;
+      SLC_TRY(ph.alloc((size_t)bp.nchunks));
+      SLC_TRY(pt.alloc((size_t)bp.nchunks));
+      k_spmv_bal<T, ACC><<<(unsigned)bp.nchunks, BAL_THREADS, 0, s>>>(
+          m->nrows, m->nnz, m->rowptr, m->colidx, (const T *)m->rvals, bp.chunk_row, x, y, ph.p, pt.p);
+      SLC_LAUNCHED();
+      k_spmv_bal_fixup<T, ACC><<<(unsigned)ceil_div(bp.nchunks, 256), 256, 0, s>>>(
+          bp.nchunks, m->nnz, m->rowptr, bp.chunk_row, ph.p, pt.p, y);
+      SLC_LAUNCHED();
+      return SLC_OK;
+    }
+  }
+}
+
+template <class T>
+static int check_handle(const slc_matrix *m, const char *fn) {
+  if (!m) return fail(SLC_ERR_INVALID, "%s: null handle", fn);
+  if (m->elem != Num<T>::elem) return fail(SLC_ERR_INVALID, "%s: element type mismatch", fn);
+  return SLC_OK;
+}
+
+template <class T, bool ACC>
+static int spmv_dev_entry(slc_matrix *m, const double *x, double *y, const char *fn) {
+  SLC_TRY(check_handle<T>(m, fn));
+  if ((m->ncols && !x) || (m->nrows && !y)) return fail(SLC_ERR_INVALID, "%s: null vector", fn);
+  return spmv_dev<T, ACC>(m, (const T *)x, (T *)y);
+}
+
+template <class T, bool ACC>
+static int spmv_host_entry(slc_matrix *m, const double *x, double *y, const char *fn) {
+  SLC_TRY(check_handle<T>(m, fn));
+  if ((m->ncols && !x) || (m->nrows && !y)) return fail(SLC_ERR_INVALID, "%s: null vector", fn);
+  cudaStream_t s = cur_stream();
+  DevBuf<T> dx, dy;
+  SLC_TRY(dx.alloc((size_t)m->ncols));
+  SLC_TRY(dy.alloc((size_t)m->nrows));
+  if (m->ncols)
+    SLC_CUDA(cudaMemcpyAsync(dx.p, x, (size_t)m->ncols * sizeof(T), cudaMemcpyHostToDevice, s));
+  if (ACC && m->nrows)
+    SLC_CUDA(cudaMemcpyAsync(dy.p, y, (size_t)m->nrows * sizeof(T), cudaMemcpyHostToDevice, s));
+  SLC_TRY((spmv_dev<T, ACC>(m, dx.p, dy.p)));
+  if (m->nrows)
+    SLC_CUDA(cudaMemcpyAsync(y, dy.p, (size_t)m->nrows * sizeof(T), cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  return SLC_OK;
+}
+
+template <class T>
+static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k) {
+  if (k == 0 || m->nrows == 0) return SLC_OK;
+  cudaStream_t s = cur_stream();
+  if (m->nnz == 0) {
+    SLC_CUDA(cudaMemset2DAsync(Y, (size_t)ldy * sizeof(T), 0, (size_t)m->nrows * sizeof(T), (size_t)k, s));
+    return SLC_OK;
+  }
+  SLC_TRY(ensure_plan<T>(m));
+  constexpr int JT = sizeof(T) == 16 ? 4 : 8;
+  const int32_t ntiles = (int32_t)ceil_div(k, JT);
+  const int64_t nblocks = ceil_div(m->nrows, 128) * ntiles;
+  if (nblocks > 0x7fffffffLL) return fail(SLC_ERR_RANGE, "mulM: grid too large");
+  if (m->spmv_active == SPMV_SELL) {
+    const SellPlan &sp = m->sell;
+    k_spmm_rows<T, JT, true><<<(unsigned)nblocks, 128, 0, s>>>(m->nrows, ntiles, sp.slice_ptr, sp.rowlen,
+                                                                nullptr, sp.colidx, (const T *)sp.vals, X,
+                                                                ldx, Y, ldy, k);
+  } else {
+    k_spmm_rows<T, JT, false><<<(unsigned)nblocks, 128, 0, s>>>(m->nrows, ntiles, nullptr, nullptr,
+                                                                 m->rowptr, m->colidx,
+                                                                 (const T *)m->rvals, X, ldx, Y, ldy, k);
+  }
+  SLC_LAUNCHED();
+  return SLC_OK;
+}
+
+template <class T>
+static int spmm_check(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
+                      const char *fn) {
+  SLC_TRY(check_handle<T>(m, fn));
+  if (k < 0) return fail(SLC_ERR_INVALID, "%s: negative column count", fn);
+  if (k > 0 && ((m->ncols && !X) || (m->nrows && !Y))) return fail(SLC_ERR_INVALID, "%s: null block", fn);
+  if (ldx < m->ncols)
+    return fail(SLC_ERR_DIM, "axpy_: column dimension %d does not match operand dimension %lld", m->ncols,
+                (long long)ldx);
+  if (ldy < m->nrows)
+    return fail(SLC_ERR_DIM, "axpy_: row dimension %d does not match result dimension %lld", m->nrows,
+                (long long)ldy);
+  return SLC_OK;
+}
+
+template <class T>
+static int spmm_dev_entry(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
+                          const char *fn) {
+  SLC_TRY(spmm_check<T>(m, X, ldx, Y, ldy, k, fn));
+  return spmm_dev<T>(m, (const T *)X, ldx, (T *)Y, ldy, k);
+}
+
+template <class T>
+static int spmm_host_entry(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
+                           const char *fn) {
+  SLC_TRY(spmm_check<T>(m, X, ldx, Y, ldy, k, fn));
+  if (k == 0) return SLC_OK;
+  cudaStream_t s = cur_stream();
+  // Device blocks are packed (leading dimension = ncols / nrows); the strided host blocks are
+  // moved with 2-D copies so only the active columns cross PCIe.
+  DevBuf<T> dX, dY;
+  SLC_TRY(dX.alloc((size_t)m->ncols * k));
+  SLC_TRY(dY.alloc((size_t)m->nrows * k));
+  if (m->ncols)
+    SLC_CUDA(cudaMemcpy2DAsync(dX.p, (size_t)m->ncols * sizeof(T), X, (size_t)ldx * sizeof(T),
+                               (size_t)m->ncols * sizeof(T), (size_t)k, cudaMemcpyHostToDevice, s));
+  SLC_TRY(spmm_dev<T>(m, dX.p, m->ncols, dY.p, m->nrows, k));
+  if (m->nrows)
+    SLC_CUDA(cudaMemcpy2DAsync(Y, (size_t)ldy * sizeof(T), dY.p, (size_t)m->nrows * sizeof(T),
+                               (size_t)m->nrows * sizeof(T), (size_t)k, cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  return SLC_OK;
+}
+
+}  // namespace slc
+
+using namespace slc;
+
+extern "C" {
+
+int slc_prepare(slc_matrix *m) {
+  if (!m) return fail(SLC_ERR_INVALID, "slc_prepare: null handle");
+  if (m->nnz == 0) return SLC_OK;
+  return m->elem == ELEM_D ? ensure_plan<double>(m) : ensure_plan<double2>(m);
+}
+
+int slc_set_spmv_kernel(slc_matrix *m, int kind) {
+  if (!m) return fail(SLC_ERR_INVALID, "slc_set_spmv_kernel: null handle");
+  if (kind < SPMV_AUTO || kind > SPMV_CSR_BALANCED)
+    return fail(SLC_ERR_INVALID, "slc_set_spmv_kernel: unknown kernel %d", kind);
+  m->spmv_kind = kind;
+  return SLC_OK;
+}
+
+int slc_plan_info(const slc_matrix *m, char *buf, int32_t buflen) {
+  if (!m || !buf || buflen <= 0) return fail(SLC_ERR_INVALID, "slc_plan_info: bad argument");
+  const char *names[] = {"unplanned", "sell32", "csr-warp", "csr-balanced"};
+  const double pad = m->nnz ? 100.0 * (double)(m->sell.padded - m->nnz) / (double)m->nnz : 0.0;
+  snprintf(buf, (size_t)buflen, "%s rows=%d cols=%d nnz=%lld max_rowlen=%d sell_padding=%.2f%% chunks=%d",
+           names[m->spmv_active], m->nrows, m->ncols, (long long)m->nnz, m->max_rowlen, pad,
+           m->bal.nchunks);
+  return SLC_OK;
+}
+
+int slc_d_mulv(slc_matrix *a, const double *x, double *y) {
+  return spmv_host_entry<double, false>(a, x, y, "mulV");
+}
+int slc_z_mulv(slc_matrix *a, const double *x, double *y) {
+  return spmv_host_entry<double2, false>(a, x, y, "mulV");
+}
+int slc_d_axpy(slc_matrix *a, const double *x, double *y) {
+  return spmv_host_entry<double, true>(a, x, y, "axpy_");
+}
+int slc_z_axpy(slc_matrix *a, const double *x, double *y) {
+  return spmv_host_entry<double2, true>(a, x, y, "axpy_");
+}
+int slc_d_mulv_dev(slc_matrix *a, const double *x, double *y) {
+  return spmv_dev_entry<double, false>(a, x, y, "mulV");
+}
+int slc_z_mulv_dev(slc_matrix *a, const double *x, double *y) {
+  return spmv_dev_entry<double2, false>(a, x, y, "mulV");
+}
+int slc_d_axpy_dev(slc_matrix *a, const double *x, double *y) {
+  return spmv_dev_entry<double, true>(a, x, y, "axpy_");
+}
+int slc_z_axpy_dev(slc_matrix *a, const double *x, double *y) {
+  return spmv_dev_entry<double2, true>(a, x, y, "axpy_");
+}
+
+int slc_d_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k) {
+  return spmm_host_entry<double>(a, X, ldx, Y, ldy, k, "mulM");
+}
+int slc_z_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k) {
+  return spmm_host_entry<double2>(a, X, ldx, Y, ldy, k, "mulM");
+}
+int slc_d_mulm_dev(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k) {
+  return spmm_dev_entry<double>(a, X, ldx, Y, ldy, k, "mulM");
+}
+int slc_z_mulm_dev(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k) {
+  return spmm_dev_entry<double2>(a, X, ldx, Y, ldy, k, "mulM");
+}
+
+}  // extern "C"

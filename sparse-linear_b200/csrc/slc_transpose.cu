@@ -1,0 +1,179 @@
+// slc_transpose.cu -- transpose / ctrans / hermitian and the row-major mirror.
+// Reference: transpose Data/Matrix/Sparse.hs:301-329 (counting sort over row indices, stable:
+// inside each output column the new indices appear in increasing original-column order,
+// values moved bit for bit), computePtrs :282-291, ctrans :371-375, hermitian :377-379.
+//
+// Device formulation: a stable LSD radix sort of (row index -> source position) over only the
+// bits a row index needs; the output pointers fall out of the sorted keys (first position of
+// each key) with no histogram or atomics; one gather kernel then moves column ids and values.
+#include "slc_common.cuh"
+
+namespace slc {
+
+__global__ void k_iota_keys(int64_t n, const int32_t *__restrict__ idx, uint32_t *__restrict__ keys,
+                            uint32_t *__restrict__ pos) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    keys[i] = (uint32_t)idx[i];
+    pos[i] = (uint32_t)i;
+  }
+}
+
+// ptr[r] = first sorted position whose key is >= r, for r in [0, nkeys]; each entry is written by
+// exactly one thread (the one sitting on the boundary that passes r).
+__global__ void k_ptrs_from_sorted(int64_t n, int32_t nkeys, const uint32_t *__restrict__ sorted,
+                                   int32_t *__restrict__ ptr) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > n) return;
+  int64_t prev = (i == 0) ? -1 : (int64_t)sorted[i - 1];
+  int64_t cur = (i == n) ? (int64_t)nkeys : (int64_t)sorted[i];
+  for (int64_t r = prev + 1; r <= cur; ++r) ptr[r] = (int32_t)i;
+}
+
+// column that owns stored position p: the c with colptr[c] <= p < colptr[c+1]
+__device__ __forceinline__ int32_t owner_of(const int32_t *__restrict__ ptr, int32_t n, int32_t p) {
+  int32_t lo = 0, hi = n;  // first index in [0, n] with ptr[idx] > p
+  while (lo < hi) {
+    int32_t mid = lo + ((hi - lo) >> 1);
+    if (__ldg(ptr + mid) <= p) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo - 1;
+}
+
+template <class T>
+__global__ void k_transpose_gather(int64_t nnz, int32_t ncols, const int32_t *__restrict__ colptr,
+                                   const T *__restrict__ vals, const uint32_t *__restrict__ perm,
+                                   bool conj, int32_t *__restrict__ out_idx, T *__restrict__ out_vals) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nnz) return;
+  const uint32_t p = perm[i];
+  out_idx[i] = owner_of(colptr, ncols, (int32_t)p);
+  T v = vals[p];
+  out_vals[i] = conj ? Num<T>::conj(v) : v;
+}
+
+template <class T>
+int transpose_csc(int32_t nrows, int32_t ncols, int64_t nnz, const int32_t *colptr,
+                  const int32_t *rowidx, const T *vals, bool conj, int32_t *out_ptr, int32_t *out_idx,
+                  T *out_vals) {
+  cudaStream_t s = cur_stream();
+  if (nnz == 0) {
+    SLC_CUDA(cudaMemsetAsync(out_ptr, 0, ((size_t)nrows + 1) * sizeof(int32_t), s));
+    return SLC_OK;
+  }
+  DevBuf<uint32_t> k0, k1, p0, p1;
+  SLC_TRY(k0.alloc(nnz));
+  SLC_TRY(k1.alloc(nnz));
+  SLC_TRY(p0.alloc(nnz));
+  SLC_TRY(p1.alloc(nnz));
+  const unsigned nb = (unsigned)ceil_div(nnz, 256);
+  k_iota_keys<<<nb, 256, 0, s>>>(nnz, rowidx, k0.p, p0.p);
+  SLC_LAUNCHED();
+  SLC_TRY(sort_pairs_u32(k0.p, k1.p, p0.p, p1.p, nnz, bits_for((uint32_t)nrows)));
+  k_ptrs_from_sorted<<<(unsigned)ceil_div(nnz + 1, 256), 256, 0, s>>>(nnz, nrows, k1.p, out_ptr);
+  SLC_LAUNCHED();
+  k_transpose_gather<T><<<nb, 256, 0, s>>>(nnz, ncols, colptr, vals, p1.p, conj, out_idx, out_vals);
+  SLC_LAUNCHED();
+  return SLC_OK;
+}
+
+template int transpose_csc<double>(int32_t, int32_t, int64_t, const int32_t *, const int32_t *,
+                                   const double *, bool, int32_t *, int32_t *, double *);
+template int transpose_csc<double2>(int32_t, int32_t, int64_t, const int32_t *, const int32_t *,
+                                    const double2 *, bool, int32_t *, int32_t *, double2 *);
+
+int ensure_csr(slc_matrix *m) {
+  if (m->has_csr) return SLC_OK;
+  DevBuf<int32_t> rp, ci;
+  DevBuf<char> rv;
+  SLC_TRY(rp.alloc((size_t)m->nrows + 1));
+  SLC_TRY(ci.alloc((size_t)m->nnz));
+  SLC_TRY(rv.alloc((size_t)m->nnz * elem_size(m->elem)));
+  if (m->elem == ELEM_D)
+    SLC_TRY(transpose_csc<double>(m->nrows, m->ncols, m->nnz, m->colptr, m->rowidx,
+                                  (const double *)m->vals, false, rp.p, ci.p, (double *)rv.p));
+  else
+    SLC_TRY(transpose_csc<double2>(m->nrows, m->ncols, m->nnz, m->colptr, m->rowidx,
+                                   (const double2 *)m->vals, false, rp.p, ci.p, (double2 *)rv.p));
+  m->rowptr = rp.take();
+  m->colidx = ci.take();
+  m->rvals = rv.take();
+  m->has_csr = true;
+  return SLC_OK;
+}
+
+// ---- hermitian: ctrans m == m on every field ----------------------------------------------------
+
+template <class T>
+__global__ void k_compare(int64_t nnz, int32_t nptr, const int32_t *__restrict__ pa,
+                          const int32_t *__restrict__ pb, const int32_t *__restrict__ ia,
+                          const int32_t *__restrict__ ib, const T *__restrict__ va,
+                          const T *__restrict__ vb, int *__restrict__ differ) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool bad = false;
+  if (i < nptr) bad |= pa[i] != pb[i];
+  if (i < nnz) bad |= (ia[i] != ib[i]) || !Num<T>::eq(va[i], vb[i]);
+  if (bad) atomicOr(differ, 1);
+}
+
+template <class T>
+static int transpose_entry(const slc_matrix *a, int conj, slc_matrix **at) {
+  if (!a || !at) return fail(SLC_ERR_INVALID, "transpose: null argument");
+  if (a->elem != Num<T>::elem) return fail(SLC_ERR_INVALID, "transpose: element type mismatch");
+  *at = nullptr;
+  slc_matrix *t = nullptr;
+  SLC_TRY(matrix_alloc(a->elem, a->ncols, a->nrows, a->nnz, &t));
+  int rc = transpose_csc<T>(a->nrows, a->ncols, a->nnz, a->colptr, a->rowidx, (const T *)a->vals,
+                            conj != 0, t->colptr, t->rowidx, (T *)t->vals);
+  if (rc != SLC_OK) {
+    matrix_release(t);
+    return rc;
+  }
+  *at = t;
+  return SLC_OK;
+}
+
+template <class T>
+static int hermitian_entry(const slc_matrix *a, int *result) {
+  if (!a || !result) return fail(SLC_ERR_INVALID, "hermitian: null argument");
+  if (a->elem != Num<T>::elem) return fail(SLC_ERR_INVALID, "hermitian: element type mismatch");
+  *result = 0;
+  if (a->nrows != a->ncols) return SLC_OK;  // dimensions are fields of the record too
+  slc_matrix *t = nullptr;
+  SLC_TRY(transpose_entry<T>(a, 1, &t));
+  DevBuf<int> differ;
+  int rc = differ.alloc(1);
+  int h = 1;
+  cudaStream_t s = cur_stream();
+  if (rc == SLC_OK) {
+    cudaMemsetAsync(differ.p, 0, sizeof(int), s);
+    int64_t n = a->nnz > (int64_t)a->ncols + 1 ? a->nnz : (int64_t)a->ncols + 1;
+    k_compare<T><<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(a->nnz, a->ncols + 1, a->colptr, t->colptr,
+                                                            a->rowidx, t->rowidx, (const T *)a->vals,
+                                                            (const T *)t->vals, differ.p);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&h, differ.p, sizeof(int), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) rc = fail(SLC_ERR_CUDA, "hermitian: CUDA error %s", cudaGetErrorString(e));
+  }
+  matrix_release(t);
+  if (rc == SLC_OK) *result = h ? 0 : 1;
+  return rc;
+}
+
+}  // namespace slc
+
+using namespace slc;
+
+extern "C" {
+int slc_d_transpose(const slc_matrix *a, int conj, slc_matrix **at) {
+  return transpose_entry<double>(a, conj, at);
+}
+int slc_z_transpose(const slc_matrix *a, int conj, slc_matrix **at) {
+  return transpose_entry<double2>(a, conj, at);
+}
+int slc_d_hermitian(const slc_matrix *a, int *result) { return hermitian_entry<double>(a, result); }
+int slc_z_hermitian(const slc_matrix *a, int *result) { return hermitian_entry<double2>(a, result); }
+}
