@@ -50,7 +50,7 @@ def _fn(p, name):
 
 
 def _ptr(a):
-    return C.c_void_p(a.ctypes.data) if a.size else C.c_void_p(a.ctypes.data or 0)
+    return C.c_void_p(a.ctypes.data)
 
 
 class DeviceMatrix:
@@ -110,6 +110,16 @@ class Matrix:
         self._dev = DeviceMatrix(handle)
         self.nrows, self.ncols, self._nnz = self._dev.dims()
         self._p = self._dev.elem()
+        self._pointers = self._indices = self._values = None
+        return self
+
+    @classmethod
+    def _from_devmatrix(cls, dm):
+        """A second view of an existing device matrix (shares the handle's owner)."""
+        self = cls.__new__(cls)
+        self._dev = dm
+        self.nrows, self.ncols, self._nnz = dm.dims()
+        self._p = dm.elem()
         self._pointers = self._indices = self._values = None
         return self
 

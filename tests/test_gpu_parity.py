@@ -1,0 +1,301 @@
+"""GPU parity: the CUDA path (through the C ABI) against the oracle on the same seeded inputs.
+
+Bar (BASELINE.json north_star): bit-exact sparsity structure for SpGEMM, transpose and assembly;
+values within 1e-12 relative norm-wise error; transpose values bit-identical.  Where the kernel
+keeps the reference's summation order (row per thread) the test also demands bit-identical values.
+"""
+import numpy as np
+import pytest
+
+import oracle
+from helpers import (TOL, arbitrary_matrix, arbitrary_triples, assert_same_structure, assert_values_close,
+                     random_csc, to_matrix)
+from sparse_linear_b200 import generators as g
+
+pytestmark = pytest.mark.gpu
+DTYPES = [np.float64, np.complex128]
+KINDS = {"auto": 0, "sell": 1, "csr-warp": 2, "csr-balanced": 3}
+
+
+def vec(rng, n, dtype):
+    v = rng.uniform(-1, 1, n)
+    if np.dtype(dtype).kind == "c":
+        v = v + 1j * rng.uniform(-1, 1, n)
+    return v.astype(dtype)
+
+
+def shapes():
+    return [(1, 1, 1.0), (5, 3, 0.5), (33, 65, 0.2), (257, 100, 0.05), (1000, 1000, 0.01), (64, 64, 0.0),
+            (300, 7, 0.9), (7, 3000, 0.3)]
+
+
+# ---- SpMV -----------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_mulv_and_axpy_match_oracle(sl, dtype, kind):
+    rng = np.random.default_rng(11)
+    for nr, nc, dens in shapes():
+        om = random_csc(rng, nr, nc, dens, dtype)
+        m = to_matrix(sl, om)
+        m.device().set_spmv_kernel(KINDS[kind])
+        x, y0 = vec(rng, nc, dtype), vec(rng, nr, dtype)
+        want = oracle.mulv(om, x)
+        got = sl.mulV(m, x)
+        assert_values_close(got, want)
+        if kind == "sell":   # a thread owns a row and adds in column order: bit-identical
+            np.testing.assert_array_equal(got, want)
+        want2 = oracle.axpy(om, x, y0)
+        got2 = sl.axpy(m, x, y0)
+        assert_values_close(got2, want2)
+        if kind == "sell":
+            np.testing.assert_array_equal(got2, want2)
+        y = y0.copy()
+        sl.axpy_(m, x, y)
+        np.testing.assert_array_equal(y, got2)
+
+
+@pytest.mark.parametrize("kind", ["csr-warp", "csr-balanced"])
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_mulv_irregular_rows(sl, dtype, kind):
+    """Power-law-like rows: empty rows, rows spanning several nnz chunks, a dense row."""
+    rng = np.random.default_rng(5)
+    nr, nc = 3000, 9000
+    lens = np.minimum((rng.pareto(1.2, nr) * 3).astype(np.int64), nc)
+    lens[7] = nc            # dense row: spans chunks
+    lens[8] = 0
+    lens[9] = 5000
+    lens[2990:] = 0         # trailing empty rows
+    rows = np.repeat(np.arange(nr), lens)
+    cols = np.concatenate([np.sort(rng.choice(nc, l, replace=False)) for l in lens]) if lens.sum() else []
+    vals = vec(rng, len(rows), dtype)
+    om = oracle.compress(nr, nc, rows, cols, vals)
+    m = to_matrix(sl, om)
+    m.device().set_spmv_kernel(KINDS[kind])
+    x, y0 = vec(rng, nc, dtype), vec(rng, nr, dtype)
+    assert_values_close(sl.mulV(m, x), oracle.mulv(om, x))
+    assert_values_close(sl.axpy(m, x, y0), oracle.axpy(om, x, y0))
+
+
+def test_mulv_summation_order_matches_reference(sl):
+    """Same witnesses as tests/test_oracle.py: column order, product and sum rounded separately."""
+    m = sl.fromTriples(1, 3, [(0, 0, 1e16), (0, 1, 1.0), (0, 2, -1e16)])
+    assert sl.mulV(m, np.ones(3)).tolist() == [0.0]
+    a = 1.0 + 2.0 ** -30
+    m2 = sl.fromTriples(1, 1, [(0, 0, a)])
+    assert sl.axpy(m2, np.array([a]), np.array([-(1.0 + 2.0 ** -29)])).tolist() == [0.0]
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_mulv_stencils_bit_exact(sl, dtype):
+    rng = np.random.default_rng(3)
+    for gm in (g.laplace2d_5pt(37, dtype), g.laplace3d_7pt(11, dtype), g.stencil3d_27pt((9, 10, 11), dtype)):
+        om = oracle.csc(*gm)
+        m = to_matrix(sl, gm)
+        x = vec(rng, gm.ncols, dtype)
+        got = sl.mulV(m, x)
+        assert "sell32" in m.device().plan_info()
+        np.testing.assert_array_equal(got, oracle.mulv(om, x))
+
+
+def test_mulv_identity_and_dimension_errors(sl):
+    v = np.arange(17, dtype=np.float64)
+    assert np.array_equal(sl.mulV(sl.ident(17), v), v)     # Sparse.hs:41-47
+    with pytest.raises(sl.SparseLinearError, match="axpy_: column dimension 17"):
+        sl.mulV(sl.ident(17), np.ones(3))
+    with pytest.raises(sl.SparseLinearError, match="axpy_: row dimension 17"):
+        sl.axpy(sl.ident(17), v, np.ones(3))
+
+
+# ---- SpMM -----------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("kind", ["auto", "csr-balanced"])
+def test_mulm_matches_oracle(sl, dtype, kind):
+    rng = np.random.default_rng(21)
+    for (nr, nc, dens), k in zip(shapes(), [1, 3, 4, 9, 64, 5, 8, 2]):
+        om = random_csc(rng, nr, nc, dens, dtype)
+        m = to_matrix(sl, om)
+        m.device().set_spmv_kernel(KINDS[kind])
+        X = np.asfortranarray(np.stack([vec(rng, nc, dtype) for _ in range(k)], axis=1))
+        want = oracle.mulm(om, X)
+        got = sl.mulM(m, X)
+        assert got.shape == (nr, k)
+        np.testing.assert_array_equal(got, want)     # a thread owns (row, column): reference order
+
+
+def test_mulm_stencil_block_and_column_range(sl):
+    """FEAST's multiplyWork: only an active column range is multiplied (Feast.hs:203-208)."""
+    rng = np.random.default_rng(2)
+    gm = g.laplace2d_5pt(20, np.complex128)
+    om, m = oracle.csc(*gm), to_matrix(sl, gm)
+    X = np.asfortranarray(rng.uniform(-1, 1, (400, 12)) + 1j * rng.uniform(-1, 1, (400, 12)))
+    full = sl.mulM(m, X)
+    np.testing.assert_array_equal(full, oracle.mulm(om, X))
+    part = sl.mulM(m, X[:, 3:8])
+    np.testing.assert_array_equal(part, full[:, 3:8])
+    with pytest.raises(sl.SparseLinearError, match="mulM: inner dimension mismatch"):
+        sl.mulM(m, X[:10])
+
+
+# ---- transpose ---------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_transpose_and_ctrans(sl, dtype):
+    rng = np.random.default_rng(31)
+    for nr, nc, dens in shapes():
+        om = random_csc(rng, nr, nc, dens, dtype)
+        m = to_matrix(sl, om)
+        for fn, ofn in ((sl.transpose, oracle.transpose), (sl.ctrans, oracle.ctrans)):
+            got, want = fn(m), ofn(om)
+            assert_same_structure(got, want)
+            np.testing.assert_array_equal(got.values, want.values)   # moved bit for bit
+        tt = sl.transpose(sl.transpose(m))
+        assert tt == m
+
+
+def test_ctrans_known_answers_and_hermitian(sl):
+    """sparse-linear/tests/Sparse.hs:61-73"""
+    import json, os
+    cases = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reference_known_answers.json")))
+    for c in cases["ctrans_fixed_points"]:
+        m = sl.fromTriples(c["nrows"], c["ncols"], [(r, col, complex(re, im)) for r, col, re, im in c["triples"]],
+                           dtype=np.complex128)
+        assert sl.ctrans(m) == m, c["name"]
+        assert sl.hermitian(m)
+    rng = np.random.default_rng(1)
+    a = to_matrix(sl, random_csc(rng, 40, 40, 0.2, np.complex128))
+    assert not sl.hermitian(a)
+    assert sl.hermitian(a + sl.ctrans(a))
+    assert not sl.hermitian(to_matrix(sl, random_csc(rng, 4, 5, 0.5, np.complex128)))
+    d = sl.diag(np.arange(9, dtype=np.float64))
+    assert sl.transpose(d) == d                                       # Sparse.hs:56-59
+
+
+# ---- triplet assembly ----------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_compress_matches_oracle(sl, dtype):
+    rng = np.random.default_rng(41)
+    for nr, nc in [(1, 1), (3, 5), (40, 40), (200, 10), (10, 2000), (513, 129)]:
+        for integer in (True, False):
+            r, c, v = arbitrary_triples(rng, nr, nc, dtype, integer)
+            want = oracle.compress(nr, nc, r, c, v)
+            got = sl.compress(nr, nc, r, c, v)
+            assert_same_structure(got, want)
+            np.testing.assert_array_equal(got.values, want.values)    # duplicates summed in input order
+            assert oracle.check_format(oracle.csc(got.nrows, got.ncols, got.pointers, got.indices, got.values)) == 0
+
+
+def test_compress_many_duplicates_zeros_and_empty(sl):
+    rng = np.random.default_rng(4)
+    r = rng.integers(0, 3, 5000)
+    c = rng.integers(0, 3, 5000)
+    v = rng.uniform(-1, 1, 5000)
+    v[::7] = 0.0
+    want, got = oracle.compress(3, 3, r, c, v), sl.compress(3, 3, r, c, v)
+    assert_same_structure(got, want)
+    np.testing.assert_array_equal(got.values, want.values)
+    e = sl.compress(4, 6, [], [], np.zeros(0))
+    assert e.pointers.tolist() == [0] * 7 and sl.nonZero(e) == 0
+    z = sl.fromTriples(2, 2, [(0, 0, 0.0), (1, 1, 1.0), (1, 1, -1.0)])
+    assert z.pointers.tolist() == [0, 1, 2] and z.values.tolist() == [0.0, 0.0]   # zeros are kept
+
+
+def test_compress_bounds_errors(sl):
+    """Sparse.hs:196-212: rows are checked before columns; the first offending position is reported."""
+    with pytest.raises(sl.SparseLinearError, match=r"compress: row index out of bounds \(0,3\) at 1") as e:
+        sl.compress(3, 3, [0, 3, 5], [0, 9, 0], [1.0, 1.0, 1.0])
+    assert e.value.pos == 1 and e.value.code == sl._capi.ERR_ROW_BOUNDS
+    with pytest.raises(sl.SparseLinearError, match=r"compress: column index out of bounds \(0,3\) at 1") as e:
+        sl.compress(3, 3, [0, 1, 2], [0, 9, -1], [1.0, 1.0, 1.0])
+    assert e.value.pos == 1 and e.value.code == sl._capi.ERR_COL_BOUNDS
+    n = 100000
+    r = np.zeros(n, dtype=np.int64)
+    r[[77777, 99999]] = -1
+    with pytest.raises(sl.SparseLinearError) as e:
+        sl.compress(5, 5, r, np.zeros(n, dtype=np.int64), np.ones(n))
+    assert e.value.pos == 77777
+
+
+# ---- SpGEMM ---------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_mm_matches_oracle(sl, dtype):
+    rng = np.random.default_rng(51)
+    cases = [(1, 1, 1, 1.0, 1.0), (6, 4, 5, 0.5, 0.5), (50, 60, 70, 0.1, 0.1), (300, 300, 300, 0.02, 0.02),
+             (40, 40, 40, 0.0, 0.3), (64, 512, 64, 0.5, 0.5),      # class 1/2 columns
+             (3000, 200, 50, 0.6, 0.9)]                            # > 2048 products: dense fallback
+    for nr, inner, nc, da, db in cases:
+        oa, ob = random_csc(rng, nr, inner, da, dtype), random_csc(rng, inner, nc, db, dtype)
+        want = oracle.mm(oa, ob)
+        got = sl.mm(to_matrix(sl, oa), to_matrix(sl, ob))
+        assert_same_structure(got, want)
+        np.testing.assert_array_equal(got.values, want.values)    # terms added in increasing inner index
+
+
+def test_mm_structural_zeros_and_errors(sl):
+    a = sl.fromTriples(1, 2, [(0, 0, 1.0), (0, 1, 1.0)])
+    b = sl.fromTriples(2, 1, [(0, 0, 1.0), (1, 0, -1.0)])
+    c = a * b
+    assert c.pointers.tolist() == [0, 1] and c.indices.tolist() == [0] and c.values.tolist() == [0.0]
+    z = sl.fromTriples(2, 2, [(0, 0, 0.0), (1, 1, 5.0)])
+    assert (z * z).pointers.tolist() == [0, 1, 2]
+    with pytest.raises(sl.SparseLinearError, match="mm: inner dimension mismatch"):
+        sl.mm(sl.ident(3), sl.ident(4))
+
+
+def test_mm_stencil_squared(sl):
+    gm = g.laplace3d_7pt(12)
+    om, m = oracle.csc(*gm), to_matrix(sl, gm)
+    want, got = oracle.mm(om, om), sl.mm(m, m)
+    assert_same_structure(got, want)
+    np.testing.assert_array_equal(got.values, want.values)
+    assert int(np.diff(got.pointers).max()) == 25
+
+
+# ---- lin / kronecker --------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_lin_and_kronecker_match_oracle(sl, dtype):
+    rng = np.random.default_rng(61)
+    for nr, nc in [(1, 1), (9, 4), (80, 90), (400, 3)]:
+        oa, ob = arbitrary_matrix(rng, nr, nc, dtype, False), arbitrary_matrix(rng, nr, nc, dtype, False)
+        al, be = (0.5 - 2j, 3.0 + 1j) if np.dtype(dtype).kind == "c" else (0.5, -3.0)
+        want = oracle.lin(al, oa, be, ob)
+        got = sl.lin(al, to_matrix(sl, oa), be, to_matrix(sl, ob))
+        assert_same_structure(got, want)
+        np.testing.assert_array_equal(got.values, want.values)
+    for (ar, ac), (br, bc) in [((1, 1), (1, 1)), ((3, 4), (5, 2)), ((12, 9), (7, 11))]:
+        oa, ob = arbitrary_matrix(rng, ar, ac, dtype, False), arbitrary_matrix(rng, br, bc, dtype, False)
+        want = oracle.kronecker(oa, ob)
+        got = sl.kronecker(to_matrix(sl, oa), to_matrix(sl, ob))
+        assert_same_structure(got, want)
+        np.testing.assert_array_equal(got.values, want.values)
+
+
+def test_configs_built_on_device_equal_generators(sl):
+    """cfg 1 and cfg 3 as the configs describe them: kronecker sums, built by the device kernels."""
+    n = 9
+    T, I = to_matrix(sl, g.tridiag(n)), sl.ident(n)
+    k = sl.kronecker
+    assert (k(I, T) + k(T, I)) == to_matrix(sl, g.laplace2d_5pt(n))
+    assert (k(k(I, I), T) + k(k(I, T), I) + k(k(T, I), I)) == to_matrix(sl, g.laplace3d_7pt(n))
+
+
+# ---- marshalling round trip -----------------------------------------------------------------------------------
+
+def test_upload_download_round_trip_and_validation(sl):
+    """fromForeign . withConstMatrix == id (Sparse.hs:138-145)"""
+    rng = np.random.default_rng(71)
+    for dtype in DTYPES:
+        om = random_csc(rng, 50, 60, 0.1, dtype)
+        m = to_matrix(sl, om)
+        back = sl.Matrix._from_devmatrix(m.device())    # downloads what was uploaded
+        assert back == m
+    bad = sl.Matrix(2, 3, [0, 2, 3], [2, 1, 0], np.ones(3))      # rows not increasing in column 0
+    with pytest.raises(sl.SparseLinearError, match="upload"):
+        bad.device()
+    bad2 = sl.Matrix(2, 3, [0, 1, 2], [0, 7], np.ones(2))        # row out of range
+    with pytest.raises(sl.SparseLinearError, match="upload"):
+        bad2.device()
