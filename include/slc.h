@@ -179,6 +179,26 @@ int slc_z_lin(const double *alpha, const slc_matrix *a, const double *beta, cons
 int slc_d_kronecker(const slc_matrix *a, const slc_matrix *b, slc_matrix **c);
 int slc_z_kronecker(const slc_matrix *a, const slc_matrix *b, slc_matrix **c);
 
+/* ---- one process per GPU: row-partitioned SpMV with the operand partitioned the same way -----
+   The reference has no distributed code; this is the multi-GPU form of mulV
+   (Data/Matrix/Sparse.hs:464-471) BASELINE.json's north_star asks for.  Rank `self` holds the row
+   block A[r0:r1, :] as an ordinary handle of shape (r1-r0) x ncols and the slice
+   x[splits[self]:splits[self+1]] in its own HBM; every rank maps the other ranks' slices with CUDA
+   IPC.  The product kernel gathers local columns from HBM and remote ("halo") columns straight from
+   the peer's memory over NVLink, so there is no separate exchange step.  The caller orders the
+   product after the peers have written their slices (one barrier per iteration). */
+
+/* 64-byte CUDA IPC handle of a device allocation made with slc_dev_alloc / cudaMalloc */
+int slc_ipc_export(const void *dev_ptr, void *handle64);
+int slc_ipc_import(const void *handle64, void **dev_ptr);
+int slc_ipc_close(void *dev_ptr);
+/* y_local <- A_local x.  splits[nparts+1] (host) are the column bounds of the slices, x_parts[nparts]
+   (host array) the device addresses of the slices as mapped in THIS process; 1 <= nparts <= 16. */
+int slc_d_mulv_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits,
+                        const double *const *x_parts, double *y_dev);
+int slc_z_mulv_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits,
+                        const double *const *x_parts, double *y_dev);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -39,6 +39,9 @@ SIGNATURES = {
     "slc_prepare": (C.c_int, [_hp]),
     "slc_set_spmv_kernel": (C.c_int, [_hp, C.c_int]),
     "slc_plan_info": (C.c_int, [_hp, C.c_char_p, C.c_int32]),
+    "slc_ipc_export": (C.c_int, [_vp, _vp]),
+    "slc_ipc_import": (C.c_int, [_vp, C.POINTER(_vp)]),
+    "slc_ipc_close": (C.c_int, [_vp]),
 }
 for _p in ("d", "z"):
     SIGNATURES.update({
@@ -48,6 +51,7 @@ for _p in ("d", "z"):
         "slc_%s_axpy" % _p: (C.c_int, [_hp, _vp, _vp]),
         "slc_%s_mulv_dev" % _p: (C.c_int, [_hp, _vp, _vp]),
         "slc_%s_axpy_dev" % _p: (C.c_int, [_hp, _vp, _vp]),
+        "slc_%s_mulv_dist_dev" % _p: (C.c_int, [_hp, C.c_int32, C.c_int32, _vp, _vp, _vp]),
         "slc_%s_mulm" % _p: (C.c_int, [_hp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32]),
         "slc_%s_mulm_dev" % _p: (C.c_int, [_hp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32]),
         "slc_%s_mm" % _p: (C.c_int, [_hp, _hp, C.POINTER(_hp)]),

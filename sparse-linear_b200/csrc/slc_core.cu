@@ -259,6 +259,27 @@ int slc_memcpy_d2h(void *dst_host, const void *src_dev, int64_t bytes) {
   return SLC_OK;
 }
 
+// ---- CUDA IPC: one process per GPU, peers map each other's x slices -------------------------------
+int slc_ipc_export(const void *dev_ptr, void *handle64) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  if (!dev_ptr || !handle64) return fail(SLC_ERR_INVALID, "slc_ipc_export: null argument");
+  cudaIpcMemHandle_t h;
+  SLC_CUDA(cudaIpcGetMemHandle(&h, const_cast<void *>(dev_ptr)));
+  memcpy(handle64, &h, sizeof h);
+  return SLC_OK;
+}
+int slc_ipc_import(const void *handle64, void **dev_ptr) {
+  if (!dev_ptr || !handle64) return fail(SLC_ERR_INVALID, "slc_ipc_import: null argument");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof h);
+  SLC_CUDA(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return SLC_OK;
+}
+int slc_ipc_close(void *dev_ptr) {
+  if (dev_ptr) SLC_CUDA(cudaIpcCloseMemHandle(dev_ptr));
+  return SLC_OK;
+}
+
 int slc_d_upload(int32_t nrows, int32_t ncols, const int32_t *colptr, const int32_t *rowidx,
                  const double *vals, slc_matrix **out) {
   return upload_impl<double>(nrows, ncols, colptr, rowidx, vals, out);

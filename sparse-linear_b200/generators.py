@@ -12,11 +12,14 @@ import numpy as np
 CSC = namedtuple("CSC", "nrows ncols colptr rowidx values")
 
 
-def _stencil(shape, offsets, weights, dtype):
-    """Structurally symmetric stencil on a row-major grid.  offsets: list of index tuples."""
+def _stencil(shape, offsets, weights, dtype, col_range=None):
+    """Structurally symmetric stencil on a row-major grid.  offsets: list of index tuples.
+    col_range=(c0, c1) builds only the column block A[:, c0:c1] (n rows, c1-c0 columns)."""
     shape = tuple(int(s) for s in shape)
     nd = len(shape)
-    n = int(np.prod(shape))
+    ntot = int(np.prod(shape))
+    c0, c1 = (0, ntot) if col_range is None else (int(col_range[0]), int(col_range[1]))
+    n = c1 - c0
     strides = [int(np.prod(shape[d + 1:])) for d in range(nd)]
     lin = [sum(o[d] * strides[d] for d in range(nd)) for o in offsets]
     order = np.argsort(lin, kind="stable")
@@ -25,7 +28,7 @@ def _stencil(shape, offsets, weights, dtype):
     lin = [lin[i] for i in order]
     if len(set(lin)) != len(lin):
         raise ValueError("grid too small for this stencil: offsets alias")
-    coords = np.unravel_index(np.arange(n, dtype=np.int64), shape)
+    coords = np.unravel_index(np.arange(c0, c1, dtype=np.int64), shape)
     k = len(offsets)
     valid = np.empty((n, k), dtype=bool)
     for j, o in enumerate(offsets):
@@ -40,9 +43,9 @@ def _stencil(shape, offsets, weights, dtype):
     colptr = np.zeros(n + 1, dtype=np.int64)
     np.cumsum(counts, out=colptr[1:])
     # entry (c, j): row = c + lin[j]   (column c; symmetric offset set => same as row view)
-    rows = (np.arange(n, dtype=np.int32)[:, None] + np.asarray(lin, dtype=np.int32)[None, :])[valid]
+    rows = (np.arange(c0, c1, dtype=np.int32)[:, None] + np.asarray(lin, dtype=np.int32)[None, :])[valid]
     vals = np.broadcast_to(np.asarray(weights, dtype=dtype)[None, :], (n, k))[valid]
-    return CSC(n, n, colptr.astype(np.int32), np.ascontiguousarray(rows, dtype=np.int32),
+    return CSC(ntot, n, colptr.astype(np.int32), np.ascontiguousarray(rows, dtype=np.int32),
                np.ascontiguousarray(vals, dtype=dtype))
 
 
@@ -60,7 +63,7 @@ def laplace3d_7pt(n, dtype=np.float64):
     return _stencil((n, n, n), offs, w, dtype)
 
 
-def stencil3d_27pt(shape, dtype=np.float64):
+def stencil3d_27pt(shape, dtype=np.float64, col_range=None):
     """cfg 5: 27-point stencil, centre 26, off-centre -1.  shape = n or (nz, ny, nx)."""
     if np.isscalar(shape):
         shape = (int(shape),) * 3
@@ -70,7 +73,7 @@ def stencil3d_27pt(shape, dtype=np.float64):
             for dx in (-1, 0, 1):
                 offs.append((dz, dy, dx))
                 w.append(26.0 if (dz, dy, dx) == (0, 0, 0) else -1.0)
-    return _stencil(shape, offs, w, dtype)
+    return _stencil(shape, offs, w, dtype, col_range)
 
 
 def tridiag(n, lo=-1.0, d=2.0, up=-1.0, dtype=np.float64):

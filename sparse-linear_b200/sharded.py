@@ -1,0 +1,266 @@
+"""Row-partitioned SpMV over the GPUs of one box: one process per GPU (torch.distributed for the
+plumbing), the operand x partitioned like the rows, remote ("halo") entries gathered by the product
+kernel itself from the peers' HBM over NVLink (CUDA-IPC mappings; see DistX in csrc/slc_spmv.cu).
+
+The reference has no distributed code; this is the multi-GPU form of mulV
+(Data/Matrix/Sparse.hs:464-471) that BASELINE.json's north_star asks for.
+
+Host-side pieces (partitioning, row blocks, handle exchange) are plain numpy / torch.distributed and
+are covered by world_size-2 gloo tests on the CPU (tests/test_sharded_gloo.py).
+"""
+import ctypes as C
+import json
+import os
+import time
+
+import numpy as np
+
+from . import _capi
+from .generators import CSC
+from .matrix import Matrix, SparseLinearError, _check
+
+
+# ---- partitioning (host) ---------------------------------------------------------------------------
+
+def uniform_splits(n, nparts, align=1):
+    """Contiguous blocks of (almost) equal size, boundaries on multiples of `align`."""
+    units = -(-n // align)
+    b = [min(n, align * ((units * p) // nparts)) for p in range(nparts)] + [n]
+    return np.asarray(b, dtype=np.int64)
+
+
+def balanced_splits(row_nnz, nparts):
+    """Contiguous row blocks with (almost) equal numbers of nonzeros (power-law matrices)."""
+    cum = np.concatenate([[0], np.cumsum(np.asarray(row_nnz, dtype=np.int64))])
+    total = cum[-1]
+    targets = (total * np.arange(1, nparts, dtype=np.int64)) // nparts
+    inner = np.searchsorted(cum, targets, side="left")
+    b = np.concatenate([[0], inner, [len(cum) - 1]]).astype(np.int64)
+    return np.maximum.accumulate(b)
+
+
+def row_block(m, r0, r1):
+    """A[r0:r1, :] of a CSC matrix, as a CSC of shape (r1-r0) x ncols with local row indices."""
+    keep = (m.rowidx >= r0) & (m.rowidx < r1)
+    cols = np.repeat(np.arange(m.ncols, dtype=np.int64), np.diff(m.colptr))
+    counts = np.bincount(cols[keep], minlength=m.ncols)
+    colptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+    return CSC(int(r1 - r0), m.ncols, colptr, (m.rowidx[keep] - r0).astype(np.int32),
+               np.ascontiguousarray(m.values[keep]))
+
+
+def exchange_objects(obj, dist, group=None):
+    """all_gather of one small picklable object per rank (IPC handles, sizes)."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return [obj]
+    out = [None] * dist.get_world_size(group)
+    dist.all_gather_object(out, obj, group=group)
+    return out
+
+
+# ---- device side --------------------------------------------------------------------------------------
+
+class ShardedSpMV:
+    """y_local = A[r0:r1, :] x with x sliced by `splits` over the ranks.
+
+    local: Matrix of shape (r1-r0) x ncols held by this rank.  Each rank owns x[splits[r]:splits[r+1]]
+    in a cudaMalloc'ed buffer that every other rank maps through CUDA IPC.
+    """
+
+    def __init__(self, local, splits, rank, world, dist=None, cpu_group=None):
+        self.local, self.rank, self.world, self.dist = local, rank, world, dist
+        self.splits = np.ascontiguousarray(splits, dtype=np.int32)
+        if len(self.splits) != world + 1 or self.splits[0] != 0 or self.splits[-1] != local.ncols:
+            raise SparseLinearError("axpy_: column dimension %d does not match operand dimension %d"
+                                    % (local.ncols, int(self.splits[-1])))
+        self.p = local._p
+        self.el = 16 if self.p == "z" else 8
+        lib = _capi.lib()
+        self.nloc_x = int(self.splits[rank + 1] - self.splits[rank])
+        self.x_ptr = C.c_void_p()
+        _check(lib.slc_dev_alloc(C.byref(self.x_ptr), max(self.nloc_x, 1) * self.el))
+        self.y_ptr = C.c_void_p()
+        _check(lib.slc_dev_alloc(C.byref(self.y_ptr), max(local.nrows, 1) * self.el))
+        handle = C.create_string_buffer(64)
+        _check(lib.slc_ipc_export(self.x_ptr, handle))
+        handles = exchange_objects(bytes(handle.raw), dist, cpu_group)
+        self.parts = (C.c_void_p * world)()
+        self._imported = []
+        for r in range(world):
+            if r == rank:
+                self.parts[r] = self.x_ptr.value
+            else:
+                ptr = C.c_void_p()
+                _check(lib.slc_ipc_import(C.create_string_buffer(handles[r], 64), C.byref(ptr)))
+                self.parts[r] = ptr.value
+                self._imported.append(ptr)
+        self.local.device().prepare()
+        self._fn = getattr(lib, "slc_%s_mulv_dist_dev" % self.p)
+        self._flag = None
+
+    def set_x(self, x_local):
+        x_local = np.ascontiguousarray(x_local, dtype=self.local.dtype)
+        assert len(x_local) == self.nloc_x
+        _check(_capi.lib().slc_memcpy_h2d(self.x_ptr, C.c_void_p(x_local.ctypes.data), x_local.nbytes))
+
+    def barrier(self):
+        """Order this rank's next product after every peer's writes to its x slice: a one-element
+        all-reduce enqueued on the current stream (no host synchronisation)."""
+        if self.world > 1:
+            import torch
+            if self._flag is None:
+                self._flag = torch.zeros(1, device="cuda")
+            self.dist.all_reduce(self._flag)
+
+    def product(self):
+        _check(self._fn(self.local.device().handle, self.world, self.rank,
+                        self.splits.ctypes.data_as(C.c_void_p), C.cast(self.parts, C.c_void_p), self.y_ptr))
+
+    def mulv(self):
+        self.barrier()
+        self.product()
+
+    def y(self):
+        out = np.empty(self.local.nrows, dtype=self.local.dtype)
+        _check(_capi.lib().slc_memcpy_d2h(C.c_void_p(out.ctypes.data), self.y_ptr, out.nbytes))
+        return out
+
+    def close(self):
+        lib = _capi.lib()
+        for p in self._imported:
+            lib.slc_ipc_close(p)
+        self._imported = []
+        if self.x_ptr:
+            lib.slc_dev_free(self.x_ptr)
+            self.x_ptr = None
+        if self.y_ptr:
+            lib.slc_dev_free(self.y_ptr)
+            self.y_ptr = None
+
+
+# ---- bench.py --gpus N ------------------------------------------------------------------------------------
+
+def bench_main(args, rank, world, local_rank, dist):
+    """cfg 5 row-partitioned over `world` GPUs.  strong: the 200^3 grid is cut into z-slabs;
+    weak: every rank holds its own 200-plane slab of a (200*world) x 200 x 200 grid."""
+    import torch
+    import sparse_linear_b200 as sl
+    from . import generators as g
+    import bench as B
+
+    n = args.grid or 200
+    if args.scaling == "weak":
+        shape = (n * world, n, n)
+    else:
+        shape = (n, n, n)
+    plane = shape[1] * shape[2]
+    ntot = shape[0] * plane
+    splits = uniform_splits(shape[0], world) * plane        # z-slabs
+    r0, r1 = int(splits[rank]), int(splits[rank + 1])
+    stream = torch.cuda.current_stream()
+    sl.set_stream(stream.cuda_stream)
+    cpu_group = dist.new_group(backend="gloo") if world > 1 else None
+
+    # A is symmetric, so the row block A[r0:r1, :] is the transpose of the column block A[:, r0:r1]
+    colblock = g.stencil3d_27pt(shape, col_range=(r0, r1))
+    cb = Matrix(colblock.ncols, colblock.nrows, colblock.colptr, colblock.rowidx, colblock.values)
+    local = sl.transpose(cb)                                 # (r1-r0) x ntot, on the device
+    del cb
+    sh = ShardedSpMV(local, splits, rank, world, dist, cpu_group)
+    xfull = g.uniform_vector(ntot, seed=0)
+    sh.set_x(xfull[r0:r1])
+    nnz_local = int(colblock.colptr[-1])
+    abytes_local = g.spmv_bytes(r1 - r0, r1 - r0, nnz_local)   # every x entry is read from HBM once, by its owner
+    tot = torch.tensor([float(abytes_local), float(nnz_local)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tot)
+    abytes, nnz = float(tot[0].item()), int(tot[1].item())
+
+    for _ in range(max(args.warmup, 3)):
+        sh.mulv()
+    torch.cuda.synchronize()
+    # parity on this rank's rows: y_local = (column block)^T x, summed on the host
+    want = np.add.reduceat(colblock.values * xfull[colblock.rowidx], colblock.colptr[:-1].astype(np.int64))
+    got = sh.y()
+    err = float(np.linalg.norm(got - want) / max(np.linalg.norm(want), 1e-300))
+
+    sampler = B.ClockSampler(local_rank)
+    l0 = sl.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler.start()
+    e0.record(stream)
+    for _ in range(args.steps):
+        sh.mulv()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop()
+    launches = sl.launch_count() - l0
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    errt = torch.tensor([err], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(errt, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / args.steps
+    value = abytes / (ms * 1e-3) / 1e9
+
+    # end to end: every step moves this rank's x slice from pinned host memory, multiplies, and
+    # brings its y slice back
+    e2e = None
+    if not args.no_e2e:
+        lib = _capi.lib()
+        xp = torch.from_numpy(np.ascontiguousarray(xfull[r0:r1])).pin_memory()
+        yp = torch.empty(r1 - r0, dtype=torch.float64).pin_memory()
+        steps_e2e = max(3, min(args.steps, 20))
+
+        def hstep():
+            _check(lib.slc_memcpy_h2d(sh.x_ptr, C.c_void_p(xp.data_ptr()), xp.numel() * 8))
+            sh.mulv()
+            _check(lib.slc_memcpy_d2h(C.c_void_p(yp.data_ptr()), sh.y_ptr, yp.numel() * 8))
+        for _ in range(2):
+            hstep()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(steps_e2e):
+            hstep()
+        torch.cuda.synchronize()
+        dt = torch.tensor([(time.perf_counter() - t0) / steps_e2e], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        dt = float(dt.item())
+        e2e = {"value": abytes / dt / 1e9, "unit": "GB/s", "ms_per_step": dt * 1e3, "steps": steps_e2e,
+               "h2d_bytes_per_step": int(ntot * 8), "d2h_bytes_per_step": int(ntot * 8),
+               "api": "ShardedSpMV (slc_memcpy_h2d + slc_d_mulv_dist_dev + slc_memcpy_d2h per rank)"}
+
+    if rank == 0:
+        peak, peak_src = B.peaks()
+        per_gpu = value / world
+        line = {
+            "metric": B.METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True,
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic (seeded numpy PCG64)",
+            "config": {"workload": "cfg5: 3D 27-point stencil %dx%dx%d, Double SpMV, row-partitioned in z-slabs over %d GPU(s); "
+                                   "halo entries gathered from peer HBM over NVLink inside the product kernel; "
+                                   "one 1-element NCCL all-reduce per step orders the ranks" % (shape + (world,)),
+                       "rows": ntot, "nnz": nnz, "algorithmic_bytes_per_step": abytes,
+                       "plan": local.device().plan_info(),
+                       "l2": "inputs larger than L2 (%.0f MB per GPU per step)" % (abytes / world / 1e6),
+                       "pct_of_nominal_8TBs_per_gpu": 100.0 * per_gpu / B.NOMINAL_HBM_GBS,
+                       "max_rel_err_vs_host_sum": float(errt.item())},
+            "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e,
+            "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
+                         "traffic": None, "peak_source": peak_src, "kernel": "k_spmv_sell<DistX>",
+                         "note": "per-GPU figure; step time includes the ordering all-reduce"},
+            "cpu_baseline": None,
+        }
+        print(json.dumps(line), flush=True)
+    sh.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
