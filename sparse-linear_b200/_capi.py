@@ -42,6 +42,11 @@ SIGNATURES = {
     "slc_ipc_export": (C.c_int, [_vp, _vp]),
     "slc_ipc_import": (C.c_int, [_vp, C.POINTER(_vp)]),
     "slc_ipc_close": (C.c_int, [_vp]),
+    "slc_peer_group_create": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(_vp), _vp]),
+    "slc_peer_group_connect": (C.c_int, [_vp, _vp]),
+    "slc_peer_barrier": (C.c_int, [_vp]),
+    "slc_peer_group_timed_out": (C.c_int, [_vp, C.POINTER(C.c_int)]),
+    "slc_peer_group_free": (None, [_vp]),
 }
 for _p in ("d", "z"):
     SIGNATURES.update({

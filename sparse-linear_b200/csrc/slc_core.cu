@@ -260,23 +260,55 @@ int slc_memcpy_d2h(void *dst_host, const void *src_dev, int64_t bytes) {
 }
 
 // ---- CUDA IPC: one process per GPU, peers map each other's x slices -------------------------------
-int slc_ipc_export(const void *dev_ptr, void *handle64) {
-  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
-  if (!dev_ptr || !handle64) return fail(SLC_ERR_INVALID, "slc_ipc_export: null argument");
-  cudaIpcMemHandle_t h;
-  SLC_CUDA(cudaIpcGetMemHandle(&h, const_cast<void *>(dev_ptr)));
-  memcpy(handle64, &h, sizeof h);
+// An IPC handle names a whole driver allocation, and small cudaMalloc requests are carved out of
+// larger ones, so the exported blob is the 64-byte handle of the containing allocation followed by
+// the 8-byte offset of the pointer inside it.
+static int containing_allocation(const void *p, void **base) {
+  typedef int (*range_fn)(unsigned long long *, size_t *, unsigned long long);
+  static range_fn fn = nullptr;
+  if (!fn) {
+    void *f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    SLC_CUDA(cudaGetDriverEntryPoint("cuMemGetAddressRange", &f, cudaEnableDefault, &q));
+    if (!f) return fail(SLC_ERR_CUDA, "cuMemGetAddressRange is not available");
+    fn = (range_fn)f;
+  }
+  unsigned long long b = 0;
+  size_t sz = 0;
+  if (fn(&b, &sz, (unsigned long long)(uintptr_t)p) != 0)
+    return fail(SLC_ERR_INVALID, "slc_ipc_export: not a device allocation");
+  *base = (void *)(uintptr_t)b;
   return SLC_OK;
 }
-int slc_ipc_import(const void *handle64, void **dev_ptr) {
-  if (!dev_ptr || !handle64) return fail(SLC_ERR_INVALID, "slc_ipc_import: null argument");
+
+int slc_ipc_export(const void *dev_ptr, void *handle72) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  if (!dev_ptr || !handle72) return fail(SLC_ERR_INVALID, "slc_ipc_export: null argument");
+  void *base = nullptr;
+  SLC_TRY(containing_allocation(dev_ptr, &base));
   cudaIpcMemHandle_t h;
-  memcpy(&h, handle64, sizeof h);
-  SLC_CUDA(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  SLC_CUDA(cudaIpcGetMemHandle(&h, base));
+  const int64_t off = (const char *)dev_ptr - (const char *)base;
+  memcpy(handle72, &h, sizeof h);
+  memcpy((char *)handle72 + sizeof h, &off, sizeof off);
+  return SLC_OK;
+}
+int slc_ipc_import(const void *handle72, void **dev_ptr) {
+  if (!dev_ptr || !handle72) return fail(SLC_ERR_INVALID, "slc_ipc_import: null argument");
+  cudaIpcMemHandle_t h;
+  int64_t off = 0;
+  memcpy(&h, handle72, sizeof h);
+  memcpy(&off, (const char *)handle72 + sizeof h, sizeof off);
+  void *base = nullptr;
+  SLC_CUDA(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+  *dev_ptr = (char *)base + off;
   return SLC_OK;
 }
 int slc_ipc_close(void *dev_ptr) {
-  if (dev_ptr) SLC_CUDA(cudaIpcCloseMemHandle(dev_ptr));
+  if (!dev_ptr) return SLC_OK;
+  void *base = nullptr;
+  SLC_TRY(containing_allocation(dev_ptr, &base));
+  SLC_CUDA(cudaIpcCloseMemHandle(base));
   return SLC_OK;
 }
 

@@ -20,6 +20,9 @@ from .generators import CSC
 from .matrix import Matrix, SparseLinearError, _check
 
 
+IPC_BYTES = 72   # SLC_IPC_HANDLE_BYTES
+
+
 # ---- partitioning (host) ---------------------------------------------------------------------------
 
 def uniform_splits(n, nparts, align=1):
@@ -81,9 +84,16 @@ class ShardedSpMV:
         _check(lib.slc_dev_alloc(C.byref(self.x_ptr), max(self.nloc_x, 1) * self.el))
         self.y_ptr = C.c_void_p()
         _check(lib.slc_dev_alloc(C.byref(self.y_ptr), max(local.nrows, 1) * self.el))
-        handle = C.create_string_buffer(64)
+        handle = C.create_string_buffer(IPC_BYTES)
         _check(lib.slc_ipc_export(self.x_ptr, handle))
-        handles = exchange_objects(bytes(handle.raw), dist, cpu_group)
+        self.group = C.c_void_p()
+        ghandle = C.create_string_buffer(IPC_BYTES)
+        _check(lib.slc_peer_group_create(world, rank, C.byref(self.group), ghandle))
+        both = exchange_objects((bytes(handle.raw), bytes(ghandle.raw)), dist, cpu_group)
+        handles = [b[0] for b in both]
+        _check(lib.slc_peer_group_connect(self.group, C.create_string_buffer(b"".join(b[1] for b in both),
+                                                                            IPC_BYTES * world)))
+        self.use_nccl_barrier = os.environ.get("SLC_BARRIER", "peer") == "nccl"
         self.parts = (C.c_void_p * world)()
         self._imported = []
         for r in range(world):
@@ -91,7 +101,7 @@ class ShardedSpMV:
                 self.parts[r] = self.x_ptr.value
             else:
                 ptr = C.c_void_p()
-                _check(lib.slc_ipc_import(C.create_string_buffer(handles[r], 64), C.byref(ptr)))
+                _check(lib.slc_ipc_import(C.create_string_buffer(handles[r], IPC_BYTES), C.byref(ptr)))
                 self.parts[r] = ptr.value
                 self._imported.append(ptr)
         self.local.device().prepare()
@@ -104,13 +114,23 @@ class ShardedSpMV:
         _check(_capi.lib().slc_memcpy_h2d(self.x_ptr, C.c_void_p(x_local.ctypes.data), x_local.nbytes))
 
     def barrier(self):
-        """Order this rank's next product after every peer's writes to its x slice: a one-element
-        all-reduce enqueued on the current stream (no host synchronisation)."""
-        if self.world > 1:
+        """Order this rank's next product after every peer's writes to its x slice.  Enqueued on the
+        current stream, no host synchronisation: the library's own peer-memory barrier kernel
+        (csrc/slc_peer.cu), or with SLC_BARRIER=nccl a one-element NCCL all-reduce."""
+        if self.world == 1:
+            return
+        if self.use_nccl_barrier:
             import torch
             if self._flag is None:
                 self._flag = torch.zeros(1, device="cuda")
             self.dist.all_reduce(self._flag)
+        else:
+            _check(_capi.lib().slc_peer_barrier(self.group))
+
+    def timed_out(self):
+        f = C.c_int(0)
+        _check(_capi.lib().slc_peer_group_timed_out(self.group, C.byref(f)))
+        return bool(f.value)
 
     def product(self):
         _check(self._fn(self.local.device().handle, self.world, self.rank,
@@ -130,6 +150,9 @@ class ShardedSpMV:
         for p in self._imported:
             lib.slc_ipc_close(p)
         self._imported = []
+        if self.group:
+            lib.slc_peer_group_free(self.group)
+            self.group = None
         if self.x_ptr:
             lib.slc_dev_free(self.x_ptr)
             self.x_ptr = None
@@ -247,7 +270,7 @@ def bench_main(args, rank, world, local_rank, dist):
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic (seeded numpy PCG64)",
             "config": {"workload": "cfg5: 3D 27-point stencil %dx%dx%d, Double SpMV, row-partitioned in z-slabs over %d GPU(s); "
                                    "halo entries gathered from peer HBM over NVLink inside the product kernel; "
-                                   "one 1-element NCCL all-reduce per step orders the ranks" % (shape + (world,)),
+                                   "one peer-memory barrier kernel per step orders the ranks" % (shape + (world,)),
                        "rows": ntot, "nnz": nnz, "algorithmic_bytes_per_step": abytes,
                        "plan": local.device().plan_info(),
                        "l2": "inputs larger than L2 (%.0f MB per GPU per step)" % (abytes / world / 1e6),
@@ -256,7 +279,9 @@ def bench_main(args, rank, world, local_rank, dist):
             "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e,
             "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
                          "traffic": None, "peak_source": peak_src, "kernel": "k_spmv_sell<DistX>",
-                         "note": "per-GPU figure; step time includes the ordering all-reduce"},
+                         "note": "per-GPU figure; step time includes the inter-GPU barrier",
+                         "barrier": "nccl all-reduce" if sh.use_nccl_barrier else "slc_peer_barrier",
+                         "barrier_timed_out": sh.timed_out()},
             "cpu_baseline": None,
         }
         print(json.dumps(line), flush=True)
