@@ -45,20 +45,32 @@ template <class T>
 struct LocalX {
   const T *x;
   __device__ __forceinline__ T operator()(int32_t c, uint64_t pol) const { return ld_gather(x + c, pol); }
+  __device__ __forceinline__ bool is_local(int32_t) const { return true; }
+  __device__ __forceinline__ T local(int32_t c, uint64_t pol) const { return ld_gather(x + c, pol); }
 };
 
 template <class T>
 struct DistX {
-  const T *parts[MAX_PARTS];
+  // this rank's own slice, resolved to scalars so the common (local) path indexes nothing
+  const T *self_x;
+  int32_t self_lo, self_hi;
+  int32_t nparts;
   int32_t splits[MAX_PARTS + 1];
-  int32_t nparts, self;
+  const T *parts[MAX_PARTS];
+  __device__ __forceinline__ bool is_local(int32_t c) const { return c >= self_lo && c < self_hi; }
+  __device__ __forceinline__ T local(int32_t c, uint64_t pol) const {
+    return ld_gather(self_x + (c - self_lo), pol);
+  }
+  // general form: the owner search only patches the pointer
   __device__ __forceinline__ T operator()(int32_t c, uint64_t pol) const {
-    const int32_t lo = splits[self];
-    if (c >= lo && c < splits[self + 1]) return ld_gather(parts[self] + (c - lo), pol);
-    int p = 0;
+    const T *p = self_x + (c - self_lo);
+    if (c < self_lo || c >= self_hi) {
+      int q = 0;
 #pragma unroll 1
-    while (p + 1 < nparts && c >= splits[p + 1]) ++p;
-    return __ldg(parts[p] + (c - splits[p]));
+      while (q + 1 < nparts && c >= splits[q + 1]) ++q;
+      p = parts[q] + (c - splits[q]);
+    }
+    return ld_gather(p, pol);
   }
 };
 
@@ -249,8 +261,18 @@ k_spmv_sell(int32_t nrows, const int64_t *__restrict__ slice_ptr, const int32_t 
       c[u] = ok ? ld_stream(ci + (int64_t)(k + u) * SELL_C, pol_s) : 0;
       a[u] = ok ? ld_stream(va + (int64_t)(k + u) * SELL_C, pol_s) : Num<T>::zero();
     }
+    // A batch whose columns are all in this GPU's slice (every batch, for an undistributed x)
+    // takes the straight-line path; only rows on a partition boundary pay for the owner search.
+    bool all_local = true;
 #pragma unroll
-    for (int u = 0; u < U; ++u) xv[u] = (k + u < len) ? xa(c[u], pol_x) : Num<T>::zero();
+    for (int u = 0; u < U; ++u) all_local &= (k + u >= len) || xa.is_local(c[u]);
+    if (all_local) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) xv[u] = (k + u < len) ? xa.local(c[u], pol_x) : Num<T>::zero();
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) xv[u] = (k + u < len) ? xa(c[u], pol_x) : Num<T>::zero();
+    }
 #pragma unroll
     for (int u = 0; u < U; ++u)
       if (k + u < len) acc = Num<T>::add(Num<T>::mul(a[u], xv[u]), acc);
@@ -462,6 +484,62 @@ k_spmm_rows(int32_t nrows, int32_t ntiles, const int64_t *__restrict__ slice_ptr
     if (j0 + j < k) st_stream(Y + (int64_t)(j0 + j) * ldy + row, acc[j]);
 }
 
+
+// Short rows (<= LMAX entries, e.g. 5- and 7-point stencils): the row's (index, value) pairs are
+// loaded once into registers and reused for a whole group of columns, so A is streamed once per
+// column group instead of once per column tile, and the LMAX*JT gathers of a tile are all in flight
+// before the first is used.
+template <class T, int JT, int LMAX, bool SELL>
+__global__ void __launch_bounds__(128)
+k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, const int64_t *__restrict__ slice_ptr,
+             const int32_t *__restrict__ rowlen, const int32_t *__restrict__ rowptr,
+             const int32_t *__restrict__ colidx, const T *__restrict__ vals, const T *__restrict__ X,
+             int64_t ldx, T *__restrict__ Y, int64_t ldy, int32_t k) {
+  const int32_t rb = blockIdx.x / ngroups;
+  const int32_t grp = blockIdx.x - rb * ngroups;
+  const int32_t row = rb * blockDim.x + threadIdx.x;
+  if (row >= nrows) return;
+  const uint64_t pol_s = policy_evict_first();
+  const uint64_t pol_x = policy_evict_last();
+  int64_t base;
+  int32_t len, stride;
+  if (SELL) {
+    base = __ldg(slice_ptr + (row >> 5)) + (threadIdx.x & 31);
+    len = __ldg(rowlen + row);
+    stride = SELL_C;
+  } else {
+    base = rowptr[row];
+    len = rowptr[row + 1] - (int32_t)base;
+    stride = 1;
+  }
+  int32_t c[LMAX];
+  T a[LMAX];
+#pragma unroll
+  for (int u = 0; u < LMAX; ++u) {
+    const bool ok = u < len;
+    c[u] = ok ? ld_stream(colidx + base + (int64_t)u * stride, pol_s) : 0;
+    a[u] = ok ? ld_stream(vals + base + (int64_t)u * stride, pol_s) : Num<T>::zero();
+  }
+  const int32_t jend = min(k, (grp + 1) * jgroup);
+  for (int32_t j0 = grp * jgroup; j0 < jend; j0 += JT) {
+    const T *xb = X + (int64_t)j0 * ldx;
+    T xv[LMAX][JT];
+#pragma unroll
+    for (int u = 0; u < LMAX; ++u)
+#pragma unroll
+      for (int j = 0; j < JT; ++j)
+        xv[u][j] = (u < len && j0 + j < jend) ? ld_gather(xb + (int64_t)j * ldx + c[u], pol_x) : Num<T>::zero();
+#pragma unroll
+    for (int j = 0; j < JT; ++j) {
+      T acc = Num<T>::zero();
+#pragma unroll
+      for (int u = 0; u < LMAX; ++u)
+        if (u < len) acc = Num<T>::add(Num<T>::mul(a[u], xv[u][j]), acc);
+      if (j0 + j < jend) st_stream(Y + (int64_t)(j0 + j) * ldy + row, acc);
+    }
+  }
+}
+
 // =================================================================================================
 // dispatch
 // =================================================================================================
@@ -585,7 +663,9 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   }
   xa.splits[nparts] = splits[nparts];
   xa.nparts = nparts;
-  xa.self = self;
+  xa.self_x = xa.parts[self];
+  xa.self_lo = splits[self];
+  xa.self_hi = splits[self + 1];
   return spmv_run<T, false, DistX<T>>(m, xa, (T *)y);
 }
 
@@ -598,6 +678,32 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
     return SLC_OK;
   }
   SLC_TRY(ensure_plan<T>(m));
+  if (m->max_rowlen <= 8) {  // short rows: registers hold the row, see k_spmm_short
+    static const int jg_env = env_int("SLC_SPMM_JG", 0), jt_env = env_int("SLC_SPMM_JT", 0);
+    const int32_t jgroup = jg_env > 0 ? jg_env : 16;
+    const int32_t ngroups = (int32_t)ceil_div(k, jgroup);
+    const int64_t nb = ceil_div(m->nrows, 128) * ngroups;
+    if (nb > 0x7fffffffLL) return fail(SLC_ERR_RANGE, "mulM: grid too large");
+    const bool sell = m->spmv_active == SPMV_SELL;
+    const SellPlan &sp = m->sell;
+    const int jt = jt_env > 0 ? jt_env : (sizeof(T) == 16 ? 2 : 4);
+#define SLC_SHORT(JT_, SELL_)                                                                        \
+  k_spmm_short<T, JT_, 8, SELL_><<<(unsigned)nb, 128, 0, s>>>(                                        \
+      m->nrows, ngroups, jgroup, sp.slice_ptr, sp.rowlen, m->rowptr, SELL_ ? sp.colidx : m->colidx,  \
+      SELL_ ? (const T *)sp.vals : (const T *)m->rvals, X, ldx, Y, ldy, k)
+    if (sell) {
+      if (jt <= 1) SLC_SHORT(1, true);
+      else if (jt == 2) SLC_SHORT(2, true);
+      else SLC_SHORT(4, true);
+    } else {
+      if (jt <= 1) SLC_SHORT(1, false);
+      else if (jt == 2) SLC_SHORT(2, false);
+      else SLC_SHORT(4, false);
+    }
+#undef SLC_SHORT
+    SLC_LAUNCHED();
+    return SLC_OK;
+  }
   constexpr int JT = sizeof(T) == 16 ? 4 : 8;
   const int32_t ntiles = (int32_t)ceil_div(k, JT);
   const int64_t nblocks = ceil_div(m->nrows, 128) * ntiles;

@@ -60,6 +60,7 @@ def test_partitioned_operand_matches_oracle(sl, dtype, kind):
 def test_sharded_wrapper_single_rank(sl):
     gm = g.stencil3d_27pt((10, 9, 8))
     m = to_matrix(sl, gm)
+    m.device().set_spmv_kernel(1)    # row per thread: bit-identical to the oracle
     sh = sharded.ShardedSpMV(m, np.array([0, gm.ncols]), 0, 1)
     x = g.uniform_vector(gm.ncols, seed=2)
     sh.set_x(x)
