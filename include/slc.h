@@ -188,6 +188,8 @@ int slc_z_kronecker(const slc_matrix *a, const slc_matrix *b, slc_matrix **c);
    the peer's memory over NVLink, so there is no separate exchange step.  The caller orders the
    product after the peers have written their slices (one barrier per iteration). */
 
+typedef struct slc_peer_group slc_peer_group;
+
 /* 72-byte export blob (CUDA IPC handle of the containing allocation + offset) of a pointer into
    a device allocation made with slc_dev_alloc / cudaMalloc */
 #define SLC_IPC_HANDLE_BYTES 72
@@ -199,19 +201,24 @@ int slc_ipc_close(void *dev_ptr);
    create: allocates this rank's flag array and exports it; connect: handles72 holds the nparts
    blobs in rank order (the caller gathers them, e.g. with torch.distributed); barrier: enqueued on
    the current stream, returns at once; every rank must call it the same number of times. */
-typedef struct slc_peer_group slc_peer_group;
 int slc_peer_group_create(int32_t nparts, int32_t self, slc_peer_group **out, void *handle72);
 int slc_peer_group_connect(slc_peer_group *g, const void *handles72);
 int slc_peer_barrier(slc_peer_group *g);
+/* The two halves of the barrier: signal = "my slice of x is written" (starts a new epoch),
+   wait = "every peer has signalled this epoch". */
+int slc_peer_signal(slc_peer_group *g);
+int slc_peer_wait(slc_peer_group *g);
 /* *flag <- 1 if a barrier gave up waiting for a peer (bounded spin), else 0 */
 int slc_peer_group_timed_out(slc_peer_group *g, int *flag);
 void slc_peer_group_free(slc_peer_group *g);
 /* y_local <- A_local x.  splits[nparts+1] (host) are the column bounds of the slices, x_parts[nparts]
-   (host array) the device addresses of the slices as mapped in THIS process; 1 <= nparts <= 16. */
+   (host array) the device addresses of the slices as mapped in THIS process; 1 <= nparts <= 16.
+   With sync != NULL the call orders itself against the peers: signal, the rows that need no peer,
+   wait, the boundary rows.  With sync == NULL the caller has already ordered the ranks. */
 int slc_d_mulv_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits,
-                        const double *const *x_parts, double *y_dev);
+                        const double *const *x_parts, double *y_dev, slc_peer_group *sync);
 int slc_z_mulv_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits,
-                        const double *const *x_parts, double *y_dev);
+                        const double *const *x_parts, double *y_dev, slc_peer_group *sync);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

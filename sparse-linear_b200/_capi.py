@@ -45,6 +45,8 @@ SIGNATURES = {
     "slc_peer_group_create": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(_vp), _vp]),
     "slc_peer_group_connect": (C.c_int, [_vp, _vp]),
     "slc_peer_barrier": (C.c_int, [_vp]),
+    "slc_peer_signal": (C.c_int, [_vp]),
+    "slc_peer_wait": (C.c_int, [_vp]),
     "slc_peer_group_timed_out": (C.c_int, [_vp, C.POINTER(C.c_int)]),
     "slc_peer_group_free": (None, [_vp]),
 }
@@ -56,7 +58,7 @@ for _p in ("d", "z"):
         "slc_%s_axpy" % _p: (C.c_int, [_hp, _vp, _vp]),
         "slc_%s_mulv_dev" % _p: (C.c_int, [_hp, _vp, _vp]),
         "slc_%s_axpy_dev" % _p: (C.c_int, [_hp, _vp, _vp]),
-        "slc_%s_mulv_dist_dev" % _p: (C.c_int, [_hp, C.c_int32, C.c_int32, _vp, _vp, _vp]),
+        "slc_%s_mulv_dist_dev" % _p: (C.c_int, [_hp, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp]),
         "slc_%s_mulm" % _p: (C.c_int, [_hp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32]),
         "slc_%s_mulm_dev" % _p: (C.c_int, [_hp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32]),
         "slc_%s_mm" % _p: (C.c_int, [_hp, _hp, C.POINTER(_hp)]),

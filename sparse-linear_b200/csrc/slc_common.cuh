@@ -105,6 +105,11 @@ struct SellPlan {
   int32_t *rowlen = nullptr;     // [nrows]
   int32_t *colidx = nullptr;     // [padded]
   void *vals = nullptr;          // [padded]
+  int32_t *slice_cmin = nullptr;  // [nslices] smallest / largest column of each slice
+  int32_t *slice_cmax = nullptr;
+  // distributed products: host copy of the slice ranges and the cached interior run
+  std::vector<int32_t> h_cmin, h_cmax;
+  int32_t interior_s0 = -1, interior_s1 = -1, interior_lo = 0, interior_hi = 0;
 };
 
 // nnz-balanced CSR plan: fixed-size chunks of nonzeros, first row of each chunk.
@@ -137,6 +142,10 @@ struct slc_matrix {
   int spmv_active = slc::SPMV_AUTO;    // chosen
   slc::SellPlan sell;
   slc::BalancedPlan bal;
+  // partition table of the last distributed product (device copy + host shadow)
+  void *dist_table = nullptr;
+  bool dist_table_valid = false;
+  alignas(8) unsigned char dist_table_host[256];
 };
 
 namespace slc {
@@ -243,8 +252,7 @@ int sm_count();
 // device primitives implemented in slc_prims.cu (radix sort, scans)
 int exclusive_scan_i32(const int32_t *in, int32_t *out, int64_t n);  // out may alias in
 int exclusive_scan_i64(const int64_t *in, int64_t *out, int64_t n);
-int inclusive_max_scan_i32(const int32_t *in, int32_t *out, int64_t n);
-// stable sort of (key, value) pairs on key bits [0, end_bit)
+// stable sort of (key, value) pairs on key bits [0, end_bit); the input buffers are scratch
 int sort_pairs_u32(uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in, uint32_t *vals_out,
                    int64_t n, int end_bit);
 int sort_pairs_u64(uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in, uint32_t *vals_out,

@@ -90,7 +90,10 @@ void matrix_release(slc_matrix *m) {
   dev_free(m->sell.rowlen);
   dev_free(m->sell.colidx);
   dev_free(m->sell.vals);
+  dev_free(m->sell.slice_cmin);
+  dev_free(m->sell.slice_cmax);
   dev_free(m->bal.chunk_row);
+  dev_free(m->dist_table);
   if (prev != m->device && prev >= 0) cudaSetDevice(prev);
   delete m;
 }

@@ -36,14 +36,20 @@ __device__ __forceinline__ unsigned long long global_ns() {
   return t;
 }
 
+// mode bit 0: signal (store my epoch into every peer's array); bit 1: wait (until every slot of my
+// own array reached the epoch).  Split in two, the signal goes out before the interior rows of a
+// product and the wait sits just before its boundary rows, so the peers' latency hides behind work.
 __global__ void k_peer_barrier(PeerTable peers, int32_t nparts, int32_t self, unsigned long long epoch,
-                               int *__restrict__ timeout_flag) {
+                               int mode, int *__restrict__ timeout_flag) {
   const int p = threadIdx.x;
   if (p >= nparts) return;
-  // everything this GPU wrote before the barrier (earlier in stream order) is visible to a peer
-  // that observes the epoch
-  __threadfence_system();
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peers.flags[p] + self), "l"(epoch) : "memory");
+  if (mode & 1) {
+    // everything this GPU wrote before the barrier (earlier in stream order) is visible to a peer
+    // that observes the epoch
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peers.flags[p] + self), "l"(epoch) : "memory");
+  }
+  if (!(mode & 2)) return;
   const unsigned long long *mine = peers.flags[self] + p;
   const unsigned long long t0 = global_ns();
   for (;;) {
@@ -110,17 +116,21 @@ int slc_peer_group_connect(slc_peer_group *g, const void *handles72) {
   return SLC_OK;
 }
 
-int slc_peer_barrier(slc_peer_group *g) {
-  if (!g) return fail(SLC_ERR_INVALID, "slc_peer_barrier: null group");
+static int peer_launch(slc_peer_group *g, int mode, const char *fn) {
+  if (!g) return fail(SLC_ERR_INVALID, "%s: null group", fn);
   if (g->nparts == 1) return SLC_OK;
-  if (!g->connected) return fail(SLC_ERR_INVALID, "slc_peer_barrier: group is not connected");
+  if (!g->connected) return fail(SLC_ERR_INVALID, "%s: group is not connected", fn);
   PeerTable t;
   for (int p = 0; p < MAX_PEERS; ++p) t.flags[p] = g->peer_flags[p];
-  g->epoch += 1;
-  k_peer_barrier<<<1, 32, 0, cur_stream()>>>(t, g->nparts, g->self, g->epoch, g->timeout_flag);
+  if (mode & 1) g->epoch += 1;
+  k_peer_barrier<<<1, 32, 0, cur_stream()>>>(t, g->nparts, g->self, g->epoch, mode, g->timeout_flag);
   SLC_LAUNCHED();
   return SLC_OK;
 }
+
+int slc_peer_barrier(slc_peer_group *g) { return peer_launch(g, 3, "slc_peer_barrier"); }
+int slc_peer_signal(slc_peer_group *g) { return peer_launch(g, 1, "slc_peer_signal"); }
+int slc_peer_wait(slc_peer_group *g) { return peer_launch(g, 2, "slc_peer_wait"); }
 
 int slc_peer_group_timed_out(slc_peer_group *g, int *flag) {
   if (!g || !flag) return fail(SLC_ERR_INVALID, "slc_peer_group_timed_out: null argument");

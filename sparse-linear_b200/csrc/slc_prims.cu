@@ -1,21 +1,108 @@
-// slc_prims.cu -- device-wide building blocks: prefix scans and the stable LSD radix sort
-// that transpose and triplet assembly are built on.
-#include <cub/device/device_radix_sort.cuh>
-#include <cub/device/device_scan.cuh>
-
+// slc_prims.cu -- device-wide building blocks, hand-written: exclusive prefix sums and the stable
+// LSD radix sort of (key, value) pairs that transpose and triplet assembly are built on.
+//
+// Radix sort, 8 bits per pass, three kernels per pass:
+//   k_radix_hist     per-tile digit histograms, stored digit-major  hist[digit][tile]
+//   exclusive scan   over that whole table: entry (d, t) becomes the first output position of the
+//                    keys of tile t with digit d (all smaller digits, then earlier tiles, come first)
+//   k_radix_scatter  re-reads the tile; a warp owns a contiguous run of keys and ranks them in index
+//                    order with __match_any_sync + per-warp digit counters in shared memory, so
+//                    equal digits keep their input order (stable); every key is then written to
+//                    base[d] + earlier-warps[d] + rank
+// Only the bits the caller says are significant are sorted (a row index of a 2M-row matrix needs
+// 21 bits = 3 passes, not 4).  All traffic is coalesced on the read side; on the write side a tile
+// of 4096 keys lands in 256 runs.
 #include "slc_common.cuh"
 
 namespace slc {
 
+// ---- exclusive scan --------------------------------------------------------------------------------
+
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 16;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+template <class U>
+__device__ __forceinline__ U block_sum(U v, U *warp_buf) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) warp_buf[warp] = v;
+  __syncthreads();
+  U total = 0;
+#pragma unroll
+  for (int w = 0; w < SCAN_THREADS / 32; ++w) total += warp_buf[w];
+  return total;
+}
+
+template <class U>
+__global__ void __launch_bounds__(SCAN_THREADS)
+k_scan_reduce(const U *__restrict__ in, U *__restrict__ tile_sums, int64_t n) {
+  __shared__ U warp_buf[SCAN_THREADS / 32];
+  const int64_t base = (int64_t)blockIdx.x * SCAN_TILE;
+  U s = 0;
+#pragma unroll
+  for (int it = 0; it < SCAN_ITEMS; ++it) {
+    const int64_t i = base + (int64_t)it * SCAN_THREADS + threadIdx.x;
+    if (i < n) s += in[i];
+  }
+  const U total = block_sum<U>(s, warp_buf);
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+// out[i] = tile_offset + sum of in[tile start .. i); each thread owns SCAN_ITEMS consecutive items
+// and reads all of them before writing, so out may alias in.
+template <class U>
+__global__ void __launch_bounds__(SCAN_THREADS)
+k_scan_apply(const U *in, U *out, const U *__restrict__ tile_offsets, int64_t n) {
+  __shared__ U warp_buf[SCAN_THREADS / 32];
+  const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+  U v[SCAN_ITEMS];
+  U s = 0;
+#pragma unroll
+  for (int it = 0; it < SCAN_ITEMS; ++it) {
+    v[it] = (base + it < n) ? in[base + it] : (U)0;
+    s += v[it];
+  }
+  // exclusive scan of the per-thread sums: inside the warp, then across warps
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  U incl = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const U t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) warp_buf[warp] = incl;
+  __syncthreads();
+  U before = tile_offsets ? tile_offsets[blockIdx.x] : (U)0;
+#pragma unroll
+  for (int w = 0; w < SCAN_THREADS / 32; ++w)
+    if (w < warp) before += warp_buf[w];
+  U run = before + (incl - s);
+#pragma unroll
+  for (int it = 0; it < SCAN_ITEMS; ++it) {
+    if (base + it < n) out[base + it] = run;
+    run += v[it];
+  }
+}
+
 template <class U>
 static int exclusive_scan_impl(const U *in, U *out, int64_t n) {
   if (n <= 0) return SLC_OK;
-  size_t tmp_bytes = 0;
-  SLC_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, in, out, n, cur_stream()));
-  DevBuf<char> tmp;
-  SLC_TRY(tmp.alloc(tmp_bytes));
-  SLC_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, in, out, n, cur_stream()));
-  g_launches.fetch_add(2, std::memory_order_relaxed);
+  cudaStream_t s = cur_stream();
+  const int64_t ntiles = ceil_div(n, SCAN_TILE);
+  if (ntiles == 1) {
+    k_scan_apply<U><<<1, SCAN_THREADS, 0, s>>>(in, out, nullptr, n);
+    SLC_LAUNCHED();
+    return SLC_OK;
+  }
+  DevBuf<U> sums;
+  SLC_TRY(sums.alloc((size_t)ntiles));
+  k_scan_reduce<U><<<(unsigned)ntiles, SCAN_THREADS, 0, s>>>(in, sums.p, n);
+  SLC_LAUNCHED();
+  SLC_TRY(exclusive_scan_impl<U>(sums.p, sums.p, ntiles));  // in place, one level up
+  k_scan_apply<U><<<(unsigned)ntiles, SCAN_THREADS, 0, s>>>(in, out, sums.p, n);
+  SLC_LAUNCHED();
   return SLC_OK;
 }
 
@@ -26,39 +113,124 @@ int exclusive_scan_i64(const int64_t *in, int64_t *out, int64_t n) {
   return exclusive_scan_impl<int64_t>(in, out, n);
 }
 
-struct MaxOp {
-  __host__ __device__ __forceinline__ int32_t operator()(int32_t a, int32_t b) const {
-    return a > b ? a : b;
-  }
-};
+// ---- radix sort -------------------------------------------------------------------------------------
 
-int inclusive_max_scan_i32(const int32_t *in, int32_t *out, int64_t n) {
-  if (n <= 0) return SLC_OK;
-  size_t tmp_bytes = 0;
-  SLC_CUDA(cub::DeviceScan::InclusiveScan(nullptr, tmp_bytes, in, out, MaxOp(), n, cur_stream()));
-  DevBuf<char> tmp;
-  SLC_TRY(tmp.alloc(tmp_bytes));
-  SLC_CUDA(cub::DeviceScan::InclusiveScan(tmp.p, tmp_bytes, in, out, MaxOp(), n, cur_stream()));
-  g_launches.fetch_add(2, std::memory_order_relaxed);
-  return SLC_OK;
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 keys per block
+constexpr int RS_BINS = 256;
+
+template <class K>
+__global__ void __launch_bounds__(RS_THREADS)
+k_radix_hist(const K *__restrict__ keys, int64_t n, int shift, int64_t ntiles, int32_t *__restrict__ hist) {
+  __shared__ int32_t cnt[RS_BINS];
+  cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const int64_t base = (int64_t)blockIdx.x * RS_TILE;
+#pragma unroll
+  for (int it = 0; it < RS_ITEMS; ++it) {
+    const int64_t i = base + (int64_t)it * RS_THREADS + threadIdx.x;
+    if (i < n) atomicAdd(&cnt[(int)((keys[i] >> shift) & (RS_BINS - 1))], 1);
+  }
+  __syncthreads();
+  hist[(int64_t)threadIdx.x * ntiles + blockIdx.x] = cnt[threadIdx.x];
+}
+
+template <class K>
+__global__ void __launch_bounds__(RS_THREADS)
+k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals_in, K *__restrict__ keys_out,
+                uint32_t *__restrict__ vals_out, int64_t n, int shift, int64_t ntiles,
+                const int32_t *__restrict__ hist_scanned) {
+  __shared__ int32_t wcnt[RS_WARPS][RS_BINS];
+  __shared__ int32_t tile_base[RS_BINS];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < RS_WARPS * RS_BINS; i += RS_THREADS) (&wcnt[0][0])[i] = 0;
+  tile_base[tid] = hist_scanned[(int64_t)tid * ntiles + blockIdx.x];
+  __syncthreads();
+
+  // warp `warp` owns keys [cb, cb + 32*RS_ITEMS), taken 32 at a time in index order
+  const int64_t cb = (int64_t)blockIdx.x * RS_TILE + (int64_t)warp * (32 * RS_ITEMS);
+  const unsigned lt = (1u << lane) - 1u;
+  K key[RS_ITEMS];
+  int32_t rank[RS_ITEMS];
+#pragma unroll
+  for (int it = 0; it < RS_ITEMS; ++it) {
+    const int64_t i = cb + it * 32 + lane;
+    const bool valid = i < n;
+    key[it] = valid ? keys_in[i] : (K)0;
+    const int d = (int)((key[it] >> shift) & (RS_BINS - 1));
+    const unsigned peers = __match_any_sync(0xffffffffu, valid ? d : RS_BINS);
+    rank[it] = 0;
+    if (valid) {
+      const int leader = __ffs(peers) - 1;
+      int32_t b = 0;
+      if (lane == leader) {
+        b = wcnt[warp][d];
+        wcnt[warp][d] = b + __popc(peers);
+      }
+      b = __shfl_sync(peers, b, leader);
+      rank[it] = b + __popc(peers & lt);
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  {  // counts per warp -> offsets of each warp inside the tile's run of digit `tid`
+    int32_t run = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w) {
+      const int32_t c = wcnt[w][tid];
+      wcnt[w][tid] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int it = 0; it < RS_ITEMS; ++it) {
+    const int64_t i = cb + it * 32 + lane;
+    if (i < n) {
+      const int d = (int)((key[it] >> shift) & (RS_BINS - 1));
+      const int64_t pos = (int64_t)tile_base[d] + wcnt[warp][d] + rank[it];
+      keys_out[pos] = key[it];
+      vals_out[pos] = vals_in[i];
+    }
+  }
 }
 
 template <class K>
 static int sort_pairs_impl(K *keys_in, K *keys_out, uint32_t *vals_in, uint32_t *vals_out, int64_t n,
                            int end_bit) {
   if (n <= 0) return SLC_OK;
+  if (n > 0x7fffffffLL) return fail(SLC_ERR_RANGE, "radix sort: more than 2^31-1 items");
+  cudaStream_t s = cur_stream();
+  const int max_bits = (int)sizeof(K) * 8;
   if (end_bit < 1) end_bit = 1;
-  size_t tmp_bytes = 0;
-  SLC_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, vals_in, vals_out, n,
-                                           0, end_bit, cur_stream()));
-  DevBuf<char> tmp;
-  SLC_TRY(tmp.alloc(tmp_bytes));
-  SLC_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0,
-                                           end_bit, cur_stream()));
-  g_launches.fetch_add(1 + (end_bit + 7) / 8, std::memory_order_relaxed);
+  if (end_bit > max_bits) end_bit = max_bits;
+  const int passes = (end_bit + 7) / 8;
+  const int64_t ntiles = ceil_div(n, RS_TILE);
+  DevBuf<int32_t> hist;
+  SLC_TRY(hist.alloc((size_t)ntiles * RS_BINS));
+  K *kin = keys_in, *kout = keys_out;
+  uint32_t *vin = vals_in, *vout = vals_out;
+  for (int p = 0; p < passes; ++p) {
+    const int shift = p * 8;
+    k_radix_hist<K><<<(unsigned)ntiles, RS_THREADS, 0, s>>>(kin, n, shift, ntiles, hist.p);
+    SLC_LAUNCHED();
+    SLC_TRY(exclusive_scan_i32(hist.p, hist.p, ntiles * RS_BINS));
+    k_radix_scatter<K><<<(unsigned)ntiles, RS_THREADS, 0, s>>>(kin, vin, kout, vout, n, shift, ntiles, hist.p);
+    SLC_LAUNCHED();
+    K *tk = kin; kin = kout; kout = tk;
+    uint32_t *tv = vin; vin = vout; vout = tv;
+  }
+  // after the swap the sorted data is in (kin, vin); the caller wants it in (keys_out, vals_out)
+  if (kin != keys_out) {
+    SLC_CUDA(cudaMemcpyAsync(keys_out, kin, (size_t)n * sizeof(K), cudaMemcpyDeviceToDevice, s));
+    SLC_CUDA(cudaMemcpyAsync(vals_out, vin, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+  }
   return SLC_OK;
 }
 
+// Both sorts overwrite their input buffers (they are the ping-pong scratch).
 int sort_pairs_u32(uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in, uint32_t *vals_out,
                    int64_t n, int end_bit) {
   return sort_pairs_impl<uint32_t>(keys_in, keys_out, vals_in, vals_out, n, end_bit);

@@ -45,30 +45,30 @@ template <class T>
 struct LocalX {
   const T *x;
   __device__ __forceinline__ T operator()(int32_t c, uint64_t pol) const { return ld_gather(x + c, pol); }
-  __device__ __forceinline__ bool is_local(int32_t) const { return true; }
-  __device__ __forceinline__ T local(int32_t c, uint64_t pol) const { return ld_gather(x + c, pol); }
+};
+
+// The partition table lives in device memory (slc_matrix::dist_table): the kernel parameter stays
+// three words, and the owner search -- taken only by rows on a partition boundary -- indexes
+// global memory instead of forcing the parameter block into local memory.
+struct DistTable {
+  int32_t nparts;
+  int32_t splits[MAX_PARTS + 1];
+  const void *parts[MAX_PARTS];
 };
 
 template <class T>
 struct DistX {
-  // this rank's own slice, resolved to scalars so the common (local) path indexes nothing
-  const T *self_x;
+  const T *self_x;  // this rank's own slice
   int32_t self_lo, self_hi;
-  int32_t nparts;
-  int32_t splits[MAX_PARTS + 1];
-  const T *parts[MAX_PARTS];
-  __device__ __forceinline__ bool is_local(int32_t c) const { return c >= self_lo && c < self_hi; }
-  __device__ __forceinline__ T local(int32_t c, uint64_t pol) const {
-    return ld_gather(self_x + (c - self_lo), pol);
-  }
-  // general form: the owner search only patches the pointer
+  const DistTable *tbl;
   __device__ __forceinline__ T operator()(int32_t c, uint64_t pol) const {
     const T *p = self_x + (c - self_lo);
     if (c < self_lo || c >= self_hi) {
       int q = 0;
+      const int np = tbl->nparts;
 #pragma unroll 1
-      while (q + 1 < nparts && c >= splits[q + 1]) ++q;
-      p = parts[q] + (c - splits[q]);
+      while (q + 1 < np && c >= tbl->splits[q + 1]) ++q;
+      p = static_cast<const T *>(tbl->parts[q]) + (c - tbl->splits[q]);
     }
     return ld_gather(p, pol);
   }
@@ -101,7 +101,8 @@ template <class T>
 __global__ void k_sell_fill(int32_t nrows, int32_t nslices, const int32_t *__restrict__ rowptr,
                             const int32_t *__restrict__ colidx, const T *__restrict__ vals,
                             const int64_t *__restrict__ slice_ptr, int32_t *__restrict__ s_col,
-                            T *__restrict__ s_val) {
+                            T *__restrict__ s_val, int32_t *__restrict__ slice_cmin,
+                            int32_t *__restrict__ slice_cmax) {
   const int32_t slice = (int32_t)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   const int lane = threadIdx.x & 31;
   if (slice >= nslices) return;
@@ -113,15 +114,29 @@ __global__ void k_sell_fill(int32_t nrows, int32_t nslices, const int32_t *__res
     start = rowptr[row];
     len = rowptr[row + 1] - start;
   }
+  int32_t cmin = 0x7fffffff, cmax = -1;
   for (int32_t k = 0; k < width; ++k) {
     const int64_t at = base + (int64_t)k * SELL_C + lane;
     if (k < len) {
-      s_col[at] = colidx[start + k];
+      const int32_t c = colidx[start + k];
+      s_col[at] = c;
       s_val[at] = vals[start + k];
+      cmin = min(cmin, c);
+      cmax = max(cmax, c);
     } else {  // padding is never read by the product kernels (they stop at rowlen)
       s_col[at] = 0;
       s_val[at] = Num<T>::zero();
     }
+  }
+  // column range of the slice: lets a distributed product find the rows that need no peer
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    cmin = min(cmin, __shfl_xor_sync(0xffffffffu, cmin, o));
+    cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, o));
+  }
+  if (lane == 0) {
+    slice_cmin[slice] = cmin;
+    slice_cmax[slice] = cmax;
   }
 }
 
@@ -184,17 +199,22 @@ static int fill_sell(slc_matrix *m) {
   SellPlan &sp = m->sell;
   if (sp.colidx) return SLC_OK;
   cudaStream_t s = cur_stream();
-  DevBuf<int32_t> sc;
+  DevBuf<int32_t> sc, cmin, cmax;
   DevBuf<T> sv;
   SLC_TRY(sc.alloc((size_t)sp.padded));
   SLC_TRY(sv.alloc((size_t)sp.padded));
+  SLC_TRY(cmin.alloc((size_t)sp.nslices));
+  SLC_TRY(cmax.alloc((size_t)sp.nslices));
   if (sp.nslices) {
     k_sell_fill<T><<<(unsigned)ceil_div((int64_t)sp.nslices * 32, 256), 256, 0, s>>>(
-        m->nrows, sp.nslices, m->rowptr, m->colidx, (const T *)m->rvals, sp.slice_ptr, sc.p, sv.p);
+        m->nrows, sp.nslices, m->rowptr, m->colidx, (const T *)m->rvals, sp.slice_ptr, sc.p, sv.p, cmin.p,
+        cmax.p);
     SLC_LAUNCHED();
   }
   sp.colidx = sc.take();
   sp.vals = sv.take();
+  sp.slice_cmin = cmin.take();
+  sp.slice_cmax = cmax.take();
   return SLC_OK;
 }
 
@@ -240,11 +260,11 @@ static int ensure_plan(slc_matrix *m) {
 // before any is used, so each thread keeps U index + U value loads in flight.
 template <class T, int U, bool ACC, class XA>
 __global__ void __launch_bounds__(256)
-k_spmv_sell(int32_t nrows, const int64_t *__restrict__ slice_ptr, const int32_t *__restrict__ rowlen,
-            const int32_t *__restrict__ colidx, const T *__restrict__ vals, const XA xa,
-            T *__restrict__ y) {
-  const int32_t row = blockIdx.x * blockDim.x + threadIdx.x;
-  if (row >= nrows) return;
+k_spmv_sell(int32_t row_begin, int32_t row_end, const int64_t *__restrict__ slice_ptr,
+            const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
+            const T *__restrict__ vals, const XA xa, T *__restrict__ y) {
+  const int32_t row = row_begin + blockIdx.x * blockDim.x + threadIdx.x;  // row_begin % 32 == 0
+  if (row >= row_end) return;
   const uint64_t pol_s = policy_evict_first();
   const uint64_t pol_x = policy_evict_last();
   const int64_t base = __ldg(slice_ptr + (row >> 5)) + (threadIdx.x & 31);
@@ -261,18 +281,8 @@ k_spmv_sell(int32_t nrows, const int64_t *__restrict__ slice_ptr, const int32_t 
       c[u] = ok ? ld_stream(ci + (int64_t)(k + u) * SELL_C, pol_s) : 0;
       a[u] = ok ? ld_stream(va + (int64_t)(k + u) * SELL_C, pol_s) : Num<T>::zero();
     }
-    // A batch whose columns are all in this GPU's slice (every batch, for an undistributed x)
-    // takes the straight-line path; only rows on a partition boundary pay for the owner search.
-    bool all_local = true;
 #pragma unroll
-    for (int u = 0; u < U; ++u) all_local &= (k + u >= len) || xa.is_local(c[u]);
-    if (all_local) {
-#pragma unroll
-      for (int u = 0; u < U; ++u) xv[u] = (k + u < len) ? xa.local(c[u], pol_x) : Num<T>::zero();
-    } else {
-#pragma unroll
-      for (int u = 0; u < U; ++u) xv[u] = (k + u < len) ? xa(c[u], pol_x) : Num<T>::zero();
-    }
+    for (int u = 0; u < U; ++u) xv[u] = (k + u < len) ? xa(c[u], pol_x) : Num<T>::zero();
 #pragma unroll
     for (int u = 0; u < U; ++u)
       if (k + u < len) acc = Num<T>::add(Num<T>::mul(a[u], xv[u]), acc);
@@ -550,17 +560,19 @@ static int env_int(const char *name, int dflt) {
 }
 
 template <class T, bool ACC, class XA>
-static int launch_sell(slc_matrix *m, const XA &xa, T *y) {
+static int launch_sell(slc_matrix *m, const XA &xa, T *y, int32_t row_begin = 0, int32_t row_end = -1) {
   const SellPlan &sp = m->sell;
   cudaStream_t s = cur_stream();
-  const unsigned nb = (unsigned)ceil_div(m->nrows, 256);
+  if (row_end < 0) row_end = m->nrows;
+  if (row_end <= row_begin) return SLC_OK;
+  const unsigned nb = (unsigned)ceil_div(row_end - row_begin, 256);
   static const int u_env = env_int("SLC_SELL_U", 0);
   int u = u_env;
   // measured on B200, 27-point stencil: U=8 6690 GB/s, U=4 6464, U=16 5425 (register pressure)
   if (u == 0) u = m->max_rowlen <= 4 ? 4 : 8;
 #define SLC_SELL_CASE(UU)                                                                          \
-  k_spmv_sell<T, UU, ACC, XA><<<nb, 256, 0, s>>>(m->nrows, sp.slice_ptr, sp.rowlen, sp.colidx,     \
-                                                 (const T *)sp.vals, xa, y)
+  k_spmv_sell<T, UU, ACC, XA><<<nb, 256, 0, s>>>(row_begin, row_end, sp.slice_ptr, sp.rowlen,      \
+                                                 sp.colidx, (const T *)sp.vals, xa, y)
   if (u <= 4) SLC_SELL_CASE(4);
   else if (u <= 8) SLC_SELL_CASE(8);
   else SLC_SELL_CASE(16);
@@ -644,7 +656,7 @@ static int spmv_host_entry(slc_matrix *m, const double *x, double *y, const char
 // y_local <- A_local x, x partitioned by column ranges over the GPUs of one box (see DistX)
 template <class T>
 static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits,
-                           const double *const *x_parts, double *y, const char *fn) {
+                           const double *const *x_parts, double *y, slc_peer_group *sync, const char *fn) {
   SLC_TRY(check_handle<T>(m, fn));
   if (nparts < 1 || nparts > MAX_PARTS) return fail(SLC_ERR_INVALID, "%s: 1..%d partitions supported", fn, MAX_PARTS);
   if (self < 0 || self >= nparts || !splits || !x_parts || (m->nrows && !y))
@@ -652,21 +664,78 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   if (splits[0] != 0 || splits[nparts] != m->ncols)
     return fail(SLC_ERR_DIM, "axpy_: column dimension %d does not match operand dimension %d", m->ncols,
                 splits[nparts]);
-  DistX<T> xa;
-  for (int p = 0; p < MAX_PARTS; ++p) xa.parts[p] = nullptr;
-  for (int p = 0; p <= MAX_PARTS; ++p) xa.splits[p] = m->ncols;
+  DistTable t;
+  memset(&t, 0, sizeof t);
+  for (int p = 0; p <= MAX_PARTS; ++p) t.splits[p] = m->ncols;
   for (int p = 0; p < nparts; ++p) {
     if (splits[p] > splits[p + 1]) return fail(SLC_ERR_INVALID, "%s: partition bounds decrease", fn);
     if (splits[p + 1] > splits[p] && !x_parts[p]) return fail(SLC_ERR_INVALID, "%s: null slice %d", fn, p);
-    xa.parts[p] = (const T *)x_parts[p];
-    xa.splits[p] = splits[p];
+    t.parts[p] = x_parts[p];
+    t.splits[p] = splits[p];
   }
-  xa.splits[nparts] = splits[nparts];
-  xa.nparts = nparts;
-  xa.self_x = xa.parts[self];
+  t.splits[nparts] = splits[nparts];
+  t.nparts = nparts;
+  // keep the table in HBM next to the matrix; refresh it only when the partition changes
+  static_assert(sizeof(DistTable) <= sizeof(m->dist_table_host), "dist table cache too small");
+  if (!m->dist_table) {
+    DevBuf<char> buf;
+    SLC_TRY(buf.alloc(sizeof(DistTable)));
+    m->dist_table = buf.take();
+    m->dist_table_valid = false;
+  }
+  if (!m->dist_table_valid || memcmp(m->dist_table_host, &t, sizeof t) != 0) {
+    memcpy(m->dist_table_host, &t, sizeof t);
+    SLC_CUDA(cudaMemcpyAsync(m->dist_table, m->dist_table_host, sizeof t, cudaMemcpyHostToDevice, cur_stream()));
+    m->dist_table_valid = true;
+  }
+  DistX<T> xa;
+  xa.self_x = (const T *)x_parts[self];
   xa.self_lo = splits[self];
   xa.self_hi = splits[self + 1];
-  return spmv_run<T, false, DistX<T>>(m, xa, (T *)y);
+  xa.tbl = (const DistTable *)m->dist_table;
+  if (m->nnz > 0) SLC_TRY(ensure_plan<T>(m));
+  if (sync) SLC_TRY(slc_peer_signal(sync));
+  if (m->nrows == 0 || m->nnz == 0 || m->spmv_active != SPMV_SELL) {
+    if (sync) SLC_TRY(slc_peer_wait(sync));
+    return spmv_run<T, false, DistX<T>>(m, xa, (T *)y);
+  }
+
+  // Sliced-ELL plan: the slices whose columns all fall inside this rank's own slice of x (for a
+  // z-slab stencil: everything but the first and last plane) run the undistributed kernel on a
+  // shifted base pointer, at full single-GPU speed; only the boundary slices take the peer path.
+  SellPlan &sp = m->sell;
+  if (sp.interior_lo != xa.self_lo || sp.interior_hi != xa.self_hi || sp.interior_s0 < 0) {
+    if (sp.h_cmin.empty() && sp.nslices) {
+      sp.h_cmin.resize(sp.nslices);
+      sp.h_cmax.resize(sp.nslices);
+      cudaStream_t s = cur_stream();
+      SLC_CUDA(cudaMemcpyAsync(sp.h_cmin.data(), sp.slice_cmin, (size_t)sp.nslices * 4, cudaMemcpyDeviceToHost, s));
+      SLC_CUDA(cudaMemcpyAsync(sp.h_cmax.data(), sp.slice_cmax, (size_t)sp.nslices * 4, cudaMemcpyDeviceToHost, s));
+      SLC_CUDA(cudaStreamSynchronize(s));
+    }
+    // longest run of consecutive all-local slices (empty slices count as local)
+    int32_t best0 = 0, best1 = 0, run0 = 0;
+    for (int32_t sl = 0; sl <= sp.nslices; ++sl) {
+      const bool local = sl < sp.nslices &&
+                         (sp.h_cmax[sl] < 0 || (sp.h_cmin[sl] >= xa.self_lo && sp.h_cmax[sl] < xa.self_hi));
+      if (!local) {
+        if (sl - run0 > best1 - best0) { best0 = run0; best1 = sl; }
+        run0 = sl + 1;
+      }
+    }
+    sp.interior_s0 = best0;
+    sp.interior_s1 = best1;
+    sp.interior_lo = xa.self_lo;
+    sp.interior_hi = xa.self_hi;
+  }
+  const int32_t r0 = sp.interior_s0 * SELL_C;
+  const int32_t r1 = min(m->nrows, sp.interior_s1 * SELL_C);
+  // interior first: it is the bulk of the work and needs nothing from the peers
+  SLC_TRY((launch_sell<T, false, LocalX<T>>(m, LocalX<T>{xa.self_x - xa.self_lo}, (T *)y, r0, r1)));
+  if (sync) SLC_TRY(slc_peer_wait(sync));
+  SLC_TRY((launch_sell<T, false, DistX<T>>(m, xa, (T *)y, 0, r0)));
+  SLC_TRY((launch_sell<T, false, DistX<T>>(m, xa, (T *)y, r1, m->nrows)));
+  return SLC_OK;
 }
 
 template <class T>
@@ -822,12 +891,12 @@ int slc_z_axpy_dev(slc_matrix *a, const double *x, double *y) {
 }
 
 int slc_d_mulv_dist_dev(slc_matrix *a, int32_t nparts, int32_t self, const int32_t *splits,
-                        const double *const *x_parts, double *y_dev) {
-  return spmv_dist_entry<double>(a, nparts, self, splits, x_parts, y_dev, "mulV");
+                        const double *const *x_parts, double *y_dev, slc_peer_group *sync) {
+  return spmv_dist_entry<double>(a, nparts, self, splits, x_parts, y_dev, sync, "mulV");
 }
 int slc_z_mulv_dist_dev(slc_matrix *a, int32_t nparts, int32_t self, const int32_t *splits,
-                        const double *const *x_parts, double *y_dev) {
-  return spmv_dist_entry<double2>(a, nparts, self, splits, x_parts, y_dev, "mulV");
+                        const double *const *x_parts, double *y_dev, slc_peer_group *sync) {
+  return spmv_dist_entry<double2>(a, nparts, self, splits, x_parts, y_dev, sync, "mulV");
 }
 
 int slc_d_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k) {

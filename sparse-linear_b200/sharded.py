@@ -132,13 +132,20 @@ class ShardedSpMV:
         _check(_capi.lib().slc_peer_group_timed_out(self.group, C.byref(f)))
         return bool(f.value)
 
-    def product(self):
+    def product(self, sync=None):
         _check(self._fn(self.local.device().handle, self.world, self.rank,
-                        self.splits.ctypes.data_as(C.c_void_p), C.cast(self.parts, C.c_void_p), self.y_ptr))
+                        self.splits.ctypes.data_as(C.c_void_p), C.cast(self.parts, C.c_void_p), self.y_ptr,
+                        sync))
 
     def mulv(self):
-        self.barrier()
-        self.product()
+        """One distributed product, ordered against the peers.  Default: the library signals, runs
+        the rows that need no peer, waits, then runs the boundary rows (the peers' latency hides
+        behind the interior).  SLC_BARRIER=nccl: a full NCCL barrier first, then the product."""
+        if self.world == 1 or self.use_nccl_barrier:
+            self.barrier()
+            self.product(None)
+        else:
+            self.product(self.group)
 
     def y(self):
         out = np.empty(self.local.nrows, dtype=self.local.dtype)

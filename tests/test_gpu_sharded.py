@@ -43,7 +43,7 @@ def test_partitioned_operand_matches_oracle(sl, dtype, kind):
             m.device().set_spmv_kernel(kind)
             y = np.zeros(blk.nrows, dtype=dtype)
             yd = _dev_array(sl, y)
-            rc = fn(m.device().handle, nparts, rank, xs.ctypes.data_as(C.c_void_p), C.cast(table, C.c_void_p), yd)
+            rc = fn(m.device().handle, nparts, rank, xs.ctypes.data_as(C.c_void_p), C.cast(table, C.c_void_p), yd, None)
             assert rc == 0, sl._capi.last_error()
             assert lib.slc_memcpy_d2h(C.c_void_p(y.ctypes.data), yd, y.nbytes) == 0
             lib.slc_dev_free(yd)
@@ -76,5 +76,5 @@ def test_bad_partition_is_rejected(sl):
     xs = np.array([0, 5, 15], dtype=np.int32)   # does not cover 16 columns
     table = (C.c_void_p * 2)(1, 1)
     rc = lib.slc_d_mulv_dist_dev(m.device().handle, 2, 0, xs.ctypes.data_as(C.c_void_p), C.cast(table, C.c_void_p),
-                                 C.c_void_p(1))
+                                 C.c_void_p(1), None)
     assert rc == sl._capi.ERR_DIM and "axpy_: column dimension 16" in sl._capi.last_error()
