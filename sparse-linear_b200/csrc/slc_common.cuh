@@ -142,6 +142,9 @@ struct slc_matrix {
   int spmv_active = slc::SPMV_AUTO;    // chosen
   slc::SellPlan sell;
   slc::BalancedPlan bal;
+  // side stream on which a distributed product runs its boundary rows
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   // partition table of the last distributed product (device copy + host shadow)
   void *dist_table = nullptr;
   bool dist_table_valid = false;

@@ -498,7 +498,42 @@ k_spmm_rows(int32_t nrows, int32_t ntiles, const int64_t *__restrict__ slice_ptr
 // Short rows (<= LMAX entries, e.g. 5- and 7-point stencils): the row's (index, value) pairs are
 // loaded once into registers and reused for a whole group of columns, so A is streamed once per
 // column group instead of once per column tile, and the LMAX*JT gathers of a tile are all in flight
-// before the first is used.
+// before the first is used.  The kernel is issue-bound, not bandwidth-bound (ncu, round 1: 235
+// instructions per (row, column) with LMAX = 8 on 5-entry rows), so LMAX is instantiated to the
+// matrix's exact longest row and a warp whose 32 rows are all full-length runs a branch-free,
+// predicate-free column loop; only boundary warps and the last partial column tile pay for predicates.
+template <class T, int JT, int LMAX, bool FULL>
+__device__ __forceinline__ void spmm_short_columns(const int32_t (&c)[LMAX], const T (&a)[LMAX], int32_t len,
+                                                   const T *__restrict__ X, int64_t ldx, T *__restrict__ Yrow,
+                                                   int64_t ldy, int32_t jbeg, int32_t jend, uint64_t pol_x) {
+  int32_t j0 = jbeg;
+  for (; j0 + JT <= jend; j0 += JT) {
+    const T *xb = X + (int64_t)j0 * ldx;
+    T xv[LMAX][JT];
+#pragma unroll
+    for (int u = 0; u < LMAX; ++u)
+#pragma unroll
+      for (int j = 0; j < JT; ++j)
+        xv[u][j] = (FULL || u < len) ? ld_gather(xb + (int64_t)j * ldx + c[u], pol_x) : Num<T>::zero();
+#pragma unroll
+    for (int j = 0; j < JT; ++j) {
+      T acc = Num<T>::zero();
+#pragma unroll
+      for (int u = 0; u < LMAX; ++u)
+        if (FULL || u < len) acc = Num<T>::add(Num<T>::mul(a[u], xv[u][j]), acc);
+      st_stream(Yrow + (int64_t)(j0 + j) * ldy, acc);
+    }
+  }
+  for (; j0 < jend; ++j0) {  // last partial tile, one column at a time
+    const T *xb = X + (int64_t)j0 * ldx;
+    T acc = Num<T>::zero();
+#pragma unroll
+    for (int u = 0; u < LMAX; ++u)
+      if (FULL || u < len) acc = Num<T>::add(Num<T>::mul(a[u], ld_gather(xb + c[u], pol_x)), acc);
+    st_stream(Yrow + (int64_t)j0 * ldy, acc);
+  }
+}
+
 template <class T, int JT, int LMAX, bool SELL>
 __global__ void __launch_bounds__(128)
 k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, const int64_t *__restrict__ slice_ptr,
@@ -508,20 +543,22 @@ k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, const int64_t *__re
   const int32_t rb = blockIdx.x / ngroups;
   const int32_t grp = blockIdx.x - rb * ngroups;
   const int32_t row = rb * blockDim.x + threadIdx.x;
-  if (row >= nrows) return;
+  const bool live = row < nrows;
   const uint64_t pol_s = policy_evict_first();
   const uint64_t pol_x = policy_evict_last();
-  int64_t base;
-  int32_t len, stride;
-  if (SELL) {
-    base = __ldg(slice_ptr + (row >> 5)) + (threadIdx.x & 31);
-    len = __ldg(rowlen + row);
-    stride = SELL_C;
-  } else {
-    base = rowptr[row];
-    len = rowptr[row + 1] - (int32_t)base;
-    stride = 1;
+  int64_t base = 0;
+  int32_t len = 0, stride = 1;
+  if (live) {
+    if (SELL) {
+      base = __ldg(slice_ptr + (row >> 5)) + (threadIdx.x & 31);
+      len = __ldg(rowlen + row);
+      stride = SELL_C;
+    } else {
+      base = rowptr[row];
+      len = rowptr[row + 1] - (int32_t)base;
+    }
   }
+  const bool full = __all_sync(0xffffffffu, live && len == LMAX);
   int32_t c[LMAX];
   T a[LMAX];
 #pragma unroll
@@ -530,24 +567,13 @@ k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, const int64_t *__re
     c[u] = ok ? ld_stream(colidx + base + (int64_t)u * stride, pol_s) : 0;
     a[u] = ok ? ld_stream(vals + base + (int64_t)u * stride, pol_s) : Num<T>::zero();
   }
-  const int32_t jend = min(k, (grp + 1) * jgroup);
-  for (int32_t j0 = grp * jgroup; j0 < jend; j0 += JT) {
-    const T *xb = X + (int64_t)j0 * ldx;
-    T xv[LMAX][JT];
-#pragma unroll
-    for (int u = 0; u < LMAX; ++u)
-#pragma unroll
-      for (int j = 0; j < JT; ++j)
-        xv[u][j] = (u < len && j0 + j < jend) ? ld_gather(xb + (int64_t)j * ldx + c[u], pol_x) : Num<T>::zero();
-#pragma unroll
-    for (int j = 0; j < JT; ++j) {
-      T acc = Num<T>::zero();
-#pragma unroll
-      for (int u = 0; u < LMAX; ++u)
-        if (u < len) acc = Num<T>::add(Num<T>::mul(a[u], xv[u][j]), acc);
-      if (j0 + j < jend) st_stream(Y + (int64_t)(j0 + j) * ldy + row, acc);
-    }
-  }
+  if (!live) return;
+  const int32_t jbeg = grp * jgroup;
+  const int32_t jend = min(k, jbeg + jgroup);
+  if (full)
+    spmm_short_columns<T, JT, LMAX, true>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x);
+  else
+    spmm_short_columns<T, JT, LMAX, false>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x);
 }
 
 // =================================================================================================
@@ -730,11 +756,37 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   }
   const int32_t r0 = sp.interior_s0 * SELL_C;
   const int32_t r1 = min(m->nrows, sp.interior_s1 * SELL_C);
-  // interior first: it is the bulk of the work and needs nothing from the peers
+  // The boundary slices (two planes of a z-slab) are a few blocks of latency-bound peer gathers:
+  // run them, behind the wait for the peers, on a side stream while the interior product -- the
+  // bulk of the work, which needs nothing from the peers -- fills the GPU on the caller's stream.
+  cudaStream_t main_s = cur_stream();
+  const bool has_boundary = r0 > 0 || r1 < m->nrows;
+  if (!has_boundary) {
+    SLC_TRY((launch_sell<T, false, LocalX<T>>(m, LocalX<T>{xa.self_x - xa.self_lo}, (T *)y, r0, r1)));
+    if (sync) SLC_TRY(slc_peer_wait(sync));
+    return SLC_OK;
+  }
+  if (!m->side_stream) {
+    // highest priority: the few boundary blocks take SM slots as soon as interior blocks retire,
+    // instead of queueing behind the ~30k blocks of the interior kernel
+    int prio_lo = 0, prio_hi = 0;
+    SLC_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    SLC_CUDA(cudaStreamCreateWithPriority(&m->side_stream, cudaStreamNonBlocking, prio_hi));
+    SLC_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming));
+    SLC_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));
+  }
+  SLC_CUDA(cudaEventRecord(m->ev_fork, main_s));  // after the signal, after everything that wrote x
+  SLC_CUDA(cudaStreamWaitEvent(m->side_stream, m->ev_fork, 0));
   SLC_TRY((launch_sell<T, false, LocalX<T>>(m, LocalX<T>{xa.self_x - xa.self_lo}, (T *)y, r0, r1)));
-  if (sync) SLC_TRY(slc_peer_wait(sync));
-  SLC_TRY((launch_sell<T, false, DistX<T>>(m, xa, (T *)y, 0, r0)));
-  SLC_TRY((launch_sell<T, false, DistX<T>>(m, xa, (T *)y, r1, m->nrows)));
+  tls().stream = m->side_stream;
+  int rc = SLC_OK;
+  if (sync) rc = slc_peer_wait(sync);
+  if (rc == SLC_OK) rc = launch_sell<T, false, DistX<T>>(m, xa, (T *)y, 0, r0);
+  if (rc == SLC_OK) rc = launch_sell<T, false, DistX<T>>(m, xa, (T *)y, r1, m->nrows);
+  tls().stream = main_s;
+  SLC_TRY(rc);
+  SLC_CUDA(cudaEventRecord(m->ev_join, m->side_stream));
+  SLC_CUDA(cudaStreamWaitEvent(main_s, m->ev_join, 0));
   return SLC_OK;
 }
 
@@ -747,28 +799,37 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
     return SLC_OK;
   }
   SLC_TRY(ensure_plan<T>(m));
-  if (m->max_rowlen <= 8) {  // short rows: registers hold the row, see k_spmm_short
-    static const int jg_env = env_int("SLC_SPMM_JG", 0), jt_env = env_int("SLC_SPMM_JT", 0);
-    const int32_t jgroup = jg_env > 0 ? jg_env : 16;
+  if (m->max_rowlen >= 1 && m->max_rowlen <= 8) {  // short rows: registers hold the row, see k_spmm_short
+    static const int jg_env = env_int("SLC_SPMM_JG", 0);
+    const int32_t jgroup = jg_env > 0 ? jg_env : 64;
     const int32_t ngroups = (int32_t)ceil_div(k, jgroup);
     const int64_t nb = ceil_div(m->nrows, 128) * ngroups;
     if (nb > 0x7fffffffLL) return fail(SLC_ERR_RANGE, "mulM: grid too large");
     const bool sell = m->spmv_active == SPMV_SELL;
     const SellPlan &sp = m->sell;
-    const int jt = jt_env > 0 ? jt_env : (sizeof(T) == 16 ? 2 : 4);
-#define SLC_SHORT(JT_, SELL_)                                                                        \
-  k_spmm_short<T, JT_, 8, SELL_><<<(unsigned)nb, 128, 0, s>>>(                                        \
+    constexpr int JTS = sizeof(T) == 16 ? 2 : 4;
+#define SLC_SHORT(L_, SELL_)                                                                         \
+  k_spmm_short<T, JTS, L_, SELL_><<<(unsigned)nb, 128, 0, s>>>(                                       \
       m->nrows, ngroups, jgroup, sp.slice_ptr, sp.rowlen, m->rowptr, SELL_ ? sp.colidx : m->colidx,  \
       SELL_ ? (const T *)sp.vals : (const T *)m->rvals, X, ldx, Y, ldy, k)
-    if (sell) {
-      if (jt <= 1) SLC_SHORT(1, true);
-      else if (jt == 2) SLC_SHORT(2, true);
-      else SLC_SHORT(4, true);
-    } else {
-      if (jt <= 1) SLC_SHORT(1, false);
-      else if (jt == 2) SLC_SHORT(2, false);
-      else SLC_SHORT(4, false);
+#define SLC_SHORT_L(L_)                                                                              \
+  case L_:                                                                                           \
+    if (sell) SLC_SHORT(L_, true);                                                                   \
+    else SLC_SHORT(L_, false);                                                                       \
+    break
+    switch (m->max_rowlen) {
+      SLC_SHORT_L(1);
+      SLC_SHORT_L(2);
+      SLC_SHORT_L(3);
+      SLC_SHORT_L(4);
+      SLC_SHORT_L(5);
+      SLC_SHORT_L(6);
+      SLC_SHORT_L(7);
+      default:
+        if (sell) SLC_SHORT(8, true);
+        else SLC_SHORT(8, false);
     }
+#undef SLC_SHORT_L
 #undef SLC_SHORT
     SLC_LAUNCHED();
     return SLC_OK;
