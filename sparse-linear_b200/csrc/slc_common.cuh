@@ -142,9 +142,9 @@ struct slc_matrix {
   int spmv_active = slc::SPMV_AUTO;    // chosen
   slc::SellPlan sell;
   slc::BalancedPlan bal;
-  // side stream on which a distributed product runs its boundary rows
-  cudaStream_t side_stream = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // streams and events of the pipelined host-operand product (upload / compute / download overlap)
+  cudaStream_t pipe_in = nullptr, pipe_out = nullptr;
+  std::vector<cudaEvent_t> pipe_events;
   // partition table of the last distributed product (device copy + host shadow)
   void *dist_table = nullptr;
   bool dist_table_valid = false;

@@ -94,11 +94,12 @@ void matrix_release(slc_matrix *m) {
   dev_free(m->sell.slice_cmax);
   dev_free(m->bal.chunk_row);
   dev_free(m->dist_table);
-  if (m->side_stream) {
-    cudaStreamSynchronize(m->side_stream);
-    cudaEventDestroy(m->ev_fork);
-    cudaEventDestroy(m->ev_join);
-    cudaStreamDestroy(m->side_stream);
+  if (m->pipe_in) {
+    cudaStreamSynchronize(m->pipe_in);
+    cudaStreamSynchronize(m->pipe_out);
+    for (auto e : m->pipe_events) cudaEventDestroy(e);
+    cudaStreamDestroy(m->pipe_in);
+    cudaStreamDestroy(m->pipe_out);
   }
   if (prev != m->device && prev >= 0) cudaSetDevice(prev);
   delete m;

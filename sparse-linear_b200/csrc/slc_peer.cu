@@ -21,6 +21,7 @@ struct slc_peer_group {
   unsigned long long *flags = nullptr;             // this rank's array: slot p is written by rank p
   unsigned long long *peer_flags[slc::MAX_PEERS];  // every rank's array as mapped here
   int *timeout_flag = nullptr;                     // device: set when a spin gave up
+  unsigned long long **table_dev = nullptr;        // device copy of peer_flags (for fused kernels)
   bool connected = false;
 };
 
@@ -112,6 +113,10 @@ int slc_peer_group_connect(slc_peer_group *g, const void *handles72) {
     SLC_TRY(slc_ipc_import((const char *)handles72 + (size_t)p * 72, &ptr));
     g->peer_flags[p] = (unsigned long long *)ptr;
   }
+  cudaError_t e = cudaMalloc((void **)&g->table_dev, MAX_PEERS * sizeof(unsigned long long *));
+  if (e == cudaSuccess)
+    e = cudaMemcpy(g->table_dev, g->peer_flags, MAX_PEERS * sizeof(unsigned long long *), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) return fail(SLC_ERR_CUDA, "slc_peer_group_connect: %s", cudaGetErrorString(e));
   g->connected = true;
   return SLC_OK;
 }
@@ -144,7 +149,26 @@ void slc_peer_group_free(slc_peer_group *g) {
     if (p != g->self && g->peer_flags[p]) slc_ipc_close(g->peer_flags[p]);
   cudaFree(g->flags);
   cudaFree(g->timeout_flag);
+  cudaFree(g->table_dev);
   delete g;
 }
 
 }  // extern "C"
+
+namespace slc {
+// For kernels that fuse the barrier (k_spmv_sell_dist): start a new epoch and expose the tables.
+int peer_sync_args(slc_peer_group *g, unsigned long long *const **flags, int **timeout_flag,
+                   unsigned long long *epoch, int32_t *nparts, int32_t *self) {
+  if (!g) return fail(SLC_ERR_INVALID, "peer sync: null group");
+  *flags = nullptr;
+  if (g->nparts == 1) return SLC_OK;
+  if (!g->connected) return fail(SLC_ERR_INVALID, "peer sync: group is not connected");
+  g->epoch += 1;
+  *flags = g->table_dev;
+  *timeout_flag = g->timeout_flag;
+  *epoch = g->epoch;
+  *nparts = g->nparts;
+  *self = g->self;
+  return SLC_OK;
+}
+}  // namespace slc

@@ -17,11 +17,16 @@
 //                  reduced from there; rows spanning chunks are stitched by a fix-up kernel.
 //                  Used for irregular (power-law) matrices.
 //   CSR warp/row   one warp per row with a shuffle tree; kept as a simple cross-check.
+#include <algorithm>
 #include <cstdlib>
 
 #include "slc_common.cuh"
 
 namespace slc {
+
+// implemented in slc_peer.cu: starts a new epoch and hands out what a fused kernel needs
+int peer_sync_args(slc_peer_group *g, unsigned long long *const **flags, int **timeout_flag,
+                   unsigned long long *epoch, int32_t *nparts, int32_t *self);
 
 // =================================================================================================
 // plans
@@ -259,12 +264,10 @@ static int ensure_plan(slc_matrix *m) {
 // (256/512 B); on a stencil the gathered x entries are consecutive too.  U entries are fetched
 // before any is used, so each thread keeps U index + U value loads in flight.
 template <class T, int U, bool ACC, class XA>
-__global__ void __launch_bounds__(256)
-k_spmv_sell(int32_t row_begin, int32_t row_end, const int64_t *__restrict__ slice_ptr,
-            const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
-            const T *__restrict__ vals, const XA xa, T *__restrict__ y) {
-  const int32_t row = row_begin + blockIdx.x * blockDim.x + threadIdx.x;  // row_begin % 32 == 0
-  if (row >= row_end) return;
+__device__ __forceinline__ void sell_row(int32_t row, const int64_t *__restrict__ slice_ptr,
+                                         const int32_t *__restrict__ rowlen,
+                                         const int32_t *__restrict__ colidx, const T *__restrict__ vals,
+                                         const XA &xa, T *__restrict__ y) {
   const uint64_t pol_s = policy_evict_first();
   const uint64_t pol_x = policy_evict_last();
   const int64_t base = __ldg(slice_ptr + (row >> 5)) + (threadIdx.x & 31);
@@ -288,6 +291,88 @@ k_spmv_sell(int32_t row_begin, int32_t row_end, const int64_t *__restrict__ slic
       if (k + u < len) acc = Num<T>::add(Num<T>::mul(a[u], xv[u]), acc);
   }
   st_stream(y + row, acc);
+}
+
+template <class T, int U, bool ACC, class XA>
+__global__ void __launch_bounds__(256)
+k_spmv_sell(int32_t row_begin, int32_t row_end, const int64_t *__restrict__ slice_ptr,
+            const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
+            const T *__restrict__ vals, const XA xa, T *__restrict__ y) {
+  const int32_t row = row_begin + blockIdx.x * blockDim.x + threadIdx.x;  // row_begin % 32 == 0
+  if (row >= row_end) return;
+  sell_row<T, U, ACC, XA>(row, slice_ptr, rowlen, colidx, vals, xa, y);
+}
+
+// ---- SELL-32, row-partitioned over the GPUs of one box: ONE launch per product ---------------------
+// The grid is  [boundary blocks | interior blocks].  Interior rows (all columns inside this rank's
+// slice of x) run the undistributed row body on a shifted base pointer.  Boundary rows gather some
+// columns from a peer's HBM over NVLink (DistX).  The ordering between ranks is fused in:
+//   * block 0 publishes this rank's epoch into every peer's flag array (release, system scope):
+//     "my slice of x is written" -- true when the kernel starts, by stream order;
+//   * every boundary block first waits (acquire, bounded spin) until all peers published the epoch.
+// Boundary blocks have the lowest block indices, so they are resident from the start: their wait
+// and their long-latency peer gathers overlap the interior blocks that fill the rest of the GPU.
+struct PeerSync {
+  unsigned long long *const *flags;  // device array [nparts]: every rank's flag array as mapped here
+  int *timeout_flag;
+  unsigned long long epoch;
+  int32_t nparts, self;
+};
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+template <class T, int U>
+__global__ void __launch_bounds__(256, sizeof(T) == 8 ? 6 : 4)
+k_spmv_sell_dist(int32_t nrows, int32_t r0, int32_t r1, const int64_t *__restrict__ slice_ptr,
+                 const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
+                 const T *__restrict__ vals, const DistX<T> xa, T *__restrict__ y, const PeerSync ps) {
+  const int32_t nbl = (r0 + 255) >> 8;            // boundary blocks below the interior
+  const int32_t nbh = (nrows - r1 + 255) >> 8;    // and above it
+  const int32_t b = blockIdx.x;
+  const bool boundary = b < nbl + nbh;
+  if (ps.flags != nullptr) {
+    if (b == 0 && (int)threadIdx.x < ps.nparts) {
+      __threadfence_system();
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(ps.flags[threadIdx.x] + ps.self), "l"(ps.epoch)
+                   : "memory");
+    }
+    if (boundary) {
+      if ((int)threadIdx.x < ps.nparts) {
+        const unsigned long long *mine = ps.flags[ps.self] + threadIdx.x;
+        const unsigned long long t0 = globaltimer_ns();
+        for (;;) {
+          unsigned long long v;
+          asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mine) : "memory");
+          if (v >= ps.epoch) break;
+          if (globaltimer_ns() - t0 > 5000000000ull) {
+            atomicExch(ps.timeout_flag, 1);
+            break;
+          }
+          __nanosleep(64);
+        }
+      }
+      __syncthreads();
+    }
+  }
+  if (boundary) {
+    int32_t row, limit;
+    if (b < nbl) {
+      row = b * 256 + threadIdx.x;
+      limit = r0;
+    } else {
+      row = r1 + (b - nbl) * 256 + threadIdx.x;
+      limit = nrows;
+    }
+    if (row < limit) sell_row<T, 4, false, DistX<T>>(row, slice_ptr, rowlen, colidx, vals, xa, y);
+  } else {
+    const int32_t row = r0 + (b - nbl - nbh) * 256 + threadIdx.x;
+    if (row < r1)
+      sell_row<T, U, false, LocalX<T>>(row, slice_ptr, rowlen, colidx, vals, LocalX<T>{xa.self_x - xa.self_lo}, y);
+  }
 }
 
 // ---- CSR, one warp per row ----------------------------------------------------------------------
@@ -641,6 +726,19 @@ static int spmv_run(slc_matrix *m, const XA &xa, T *y) {
   }
 }
 
+// host copy of the per-slice column ranges (used to split distributed and pipelined products)
+static int fetch_slice_ranges(slc_matrix *m) {
+  SellPlan &sp = m->sell;
+  if (!sp.h_cmin.empty() || sp.nslices == 0) return SLC_OK;
+  sp.h_cmin.resize(sp.nslices);
+  sp.h_cmax.resize(sp.nslices);
+  cudaStream_t s = cur_stream();
+  SLC_CUDA(cudaMemcpyAsync(sp.h_cmin.data(), sp.slice_cmin, (size_t)sp.nslices * 4, cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaMemcpyAsync(sp.h_cmax.data(), sp.slice_cmax, (size_t)sp.nslices * 4, cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  return SLC_OK;
+}
+
 template <class T, bool ACC>
 static int spmv_dev(slc_matrix *m, const T *x, T *y) {
   return spmv_run<T, ACC, LocalX<T>>(m, LocalX<T>{x}, y);
@@ -660,10 +758,72 @@ static int spmv_dev_entry(slc_matrix *m, const double *x, double *y, const char 
   return spmv_dev<T, ACC>(m, (const T *)x, (T *)y);
 }
 
+// Host operands, large banded matrix: the product is cut into row chunks.  Chunk i needs x only up
+// to the largest column its slices touch, so x is uploaded in pieces on one stream, chunk kernels
+// run on the caller's stream as their piece lands, and finished y chunks go back on a third
+// stream: H2D, compute and D2H overlap (PCIe is full duplex) instead of running back to back.
+constexpr int PIPE_MAX_CHUNKS = 32;
+
+template <class T, bool ACC>
+static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
+  *done = false;
+  static const int chunks_env = env_int("SLC_E2E_CHUNKS", 8);
+  const int want = chunks_env < 1 ? 1 : (chunks_env > PIPE_MAX_CHUNKS ? PIPE_MAX_CHUNKS : chunks_env);
+  if (want == 1 || m->nnz == 0 || m->nrows < (1 << 18)) return SLC_OK;
+  SLC_TRY(ensure_plan<T>(m));
+  if (m->spmv_active != SPMV_SELL) return SLC_OK;
+  SLC_TRY(fetch_slice_ranges(m));
+  SellPlan &sp = m->sell;
+  const int32_t rows_per = (int32_t)(ceil_div(ceil_div(m->nrows, want), 256) * 256);
+  const int nch = (int)ceil_div(m->nrows, rows_per);
+  if (!m->pipe_in) {
+    SLC_CUDA(cudaStreamCreateWithFlags(&m->pipe_in, cudaStreamNonBlocking));
+    SLC_CUDA(cudaStreamCreateWithFlags(&m->pipe_out, cudaStreamNonBlocking));
+    m->pipe_events.resize(2 * PIPE_MAX_CHUNKS + 1);
+    for (auto &e : m->pipe_events) SLC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  cudaStream_t main_s = cur_stream();
+  DevBuf<T> dx, dy;
+  SLC_TRY(dx.alloc((size_t)m->ncols));
+  SLC_TRY(dy.alloc((size_t)m->nrows));
+  cudaEvent_t ev_start = m->pipe_events[2 * PIPE_MAX_CHUNKS];
+  SLC_CUDA(cudaEventRecord(ev_start, main_s));
+  SLC_CUDA(cudaStreamWaitEvent(m->pipe_in, ev_start, 0));
+  SLC_CUDA(cudaStreamWaitEvent(m->pipe_out, ev_start, 0));
+  int32_t sent = 0;  // x[0, sent) is on its way
+  for (int i = 0; i < nch; ++i) {
+    const int32_t r0 = i * rows_per, r1 = (int32_t)std::min<int64_t>(m->nrows, (int64_t)(i + 1) * rows_per);
+    int32_t need = sent;
+    for (int32_t sl = r0 / SELL_C; sl < (int32_t)ceil_div(r1, SELL_C); ++sl) need = std::max(need, sp.h_cmax[sl] + 1);
+    if (need > sent) {
+      SLC_CUDA(cudaMemcpyAsync(dx.p + sent, x + sent, (size_t)(need - sent) * sizeof(T), cudaMemcpyHostToDevice,
+                               m->pipe_in));
+      sent = need;
+    }
+    if (ACC)
+      SLC_CUDA(cudaMemcpyAsync(dy.p + r0, y + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyHostToDevice, m->pipe_in));
+    cudaEvent_t ev_in = m->pipe_events[i], ev_k = m->pipe_events[PIPE_MAX_CHUNKS + i];
+    SLC_CUDA(cudaEventRecord(ev_in, m->pipe_in));
+    SLC_CUDA(cudaStreamWaitEvent(main_s, ev_in, 0));
+    SLC_TRY((launch_sell<T, ACC, LocalX<T>>(m, LocalX<T>{dx.p}, dy.p, r0, r1)));
+    SLC_CUDA(cudaEventRecord(ev_k, main_s));
+    SLC_CUDA(cudaStreamWaitEvent(m->pipe_out, ev_k, 0));
+    SLC_CUDA(cudaMemcpyAsync(y + r0, dy.p + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyDeviceToHost, m->pipe_out));
+  }
+  SLC_CUDA(cudaStreamSynchronize(m->pipe_out));
+  SLC_CUDA(cudaStreamSynchronize(m->pipe_in));
+  SLC_CUDA(cudaStreamSynchronize(main_s));
+  *done = true;
+  return SLC_OK;
+}
+
 template <class T, bool ACC>
 static int spmv_host_entry(slc_matrix *m, const double *x, double *y, const char *fn) {
   SLC_TRY(check_handle<T>(m, fn));
   if ((m->ncols && !x) || (m->nrows && !y)) return fail(SLC_ERR_INVALID, "%s: null vector", fn);
+  bool done = false;
+  SLC_TRY((spmv_host_pipelined<T, ACC>(m, (const T *)x, (T *)y, &done)));
+  if (done) return SLC_OK;
   cudaStream_t s = cur_stream();
   DevBuf<T> dx, dy;
   SLC_TRY(dx.alloc((size_t)m->ncols));
@@ -720,9 +880,8 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   xa.self_hi = splits[self + 1];
   xa.tbl = (const DistTable *)m->dist_table;
   if (m->nnz > 0) SLC_TRY(ensure_plan<T>(m));
-  if (sync) SLC_TRY(slc_peer_signal(sync));
   if (m->nrows == 0 || m->nnz == 0 || m->spmv_active != SPMV_SELL) {
-    if (sync) SLC_TRY(slc_peer_wait(sync));
+    if (sync) SLC_TRY(slc_peer_barrier(sync));  // separate barrier kernel, then the generic kernels
     return spmv_run<T, false, DistX<T>>(m, xa, (T *)y);
   }
 
@@ -731,14 +890,7 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   // shifted base pointer, at full single-GPU speed; only the boundary slices take the peer path.
   SellPlan &sp = m->sell;
   if (sp.interior_lo != xa.self_lo || sp.interior_hi != xa.self_hi || sp.interior_s0 < 0) {
-    if (sp.h_cmin.empty() && sp.nslices) {
-      sp.h_cmin.resize(sp.nslices);
-      sp.h_cmax.resize(sp.nslices);
-      cudaStream_t s = cur_stream();
-      SLC_CUDA(cudaMemcpyAsync(sp.h_cmin.data(), sp.slice_cmin, (size_t)sp.nslices * 4, cudaMemcpyDeviceToHost, s));
-      SLC_CUDA(cudaMemcpyAsync(sp.h_cmax.data(), sp.slice_cmax, (size_t)sp.nslices * 4, cudaMemcpyDeviceToHost, s));
-      SLC_CUDA(cudaStreamSynchronize(s));
-    }
+    SLC_TRY(fetch_slice_ranges(m));
     // longest run of consecutive all-local slices (empty slices count as local)
     int32_t best0 = 0, best1 = 0, run0 = 0;
     for (int32_t sl = 0; sl <= sp.nslices; ++sl) {
@@ -756,37 +908,21 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   }
   const int32_t r0 = sp.interior_s0 * SELL_C;
   const int32_t r1 = min(m->nrows, sp.interior_s1 * SELL_C);
-  // The boundary slices (two planes of a z-slab) are a few blocks of latency-bound peer gathers:
-  // run them, behind the wait for the peers, on a side stream while the interior product -- the
-  // bulk of the work, which needs nothing from the peers -- fills the GPU on the caller's stream.
-  cudaStream_t main_s = cur_stream();
-  const bool has_boundary = r0 > 0 || r1 < m->nrows;
-  if (!has_boundary) {
-    SLC_TRY((launch_sell<T, false, LocalX<T>>(m, LocalX<T>{xa.self_x - xa.self_lo}, (T *)y, r0, r1)));
-    if (sync) SLC_TRY(slc_peer_wait(sync));
-    return SLC_OK;
-  }
-  if (!m->side_stream) {
-    // highest priority: the few boundary blocks take SM slots as soon as interior blocks retire,
-    // instead of queueing behind the ~30k blocks of the interior kernel
-    int prio_lo = 0, prio_hi = 0;
-    SLC_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-    SLC_CUDA(cudaStreamCreateWithPriority(&m->side_stream, cudaStreamNonBlocking, prio_hi));
-    SLC_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming));
-    SLC_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));
-  }
-  SLC_CUDA(cudaEventRecord(m->ev_fork, main_s));  // after the signal, after everything that wrote x
-  SLC_CUDA(cudaStreamWaitEvent(m->side_stream, m->ev_fork, 0));
-  SLC_TRY((launch_sell<T, false, LocalX<T>>(m, LocalX<T>{xa.self_x - xa.self_lo}, (T *)y, r0, r1)));
-  tls().stream = m->side_stream;
-  int rc = SLC_OK;
-  if (sync) rc = slc_peer_wait(sync);
-  if (rc == SLC_OK) rc = launch_sell<T, false, DistX<T>>(m, xa, (T *)y, 0, r0);
-  if (rc == SLC_OK) rc = launch_sell<T, false, DistX<T>>(m, xa, (T *)y, r1, m->nrows);
-  tls().stream = main_s;
-  SLC_TRY(rc);
-  SLC_CUDA(cudaEventRecord(m->ev_join, m->side_stream));
-  SLC_CUDA(cudaStreamWaitEvent(main_s, m->ev_join, 0));
+  // one launch: [boundary blocks | interior blocks], barrier fused in (see k_spmv_sell_dist)
+  PeerSync ps;
+  memset(&ps, 0, sizeof ps);
+  if (sync) SLC_TRY(peer_sync_args(sync, &ps.flags, &ps.timeout_flag, &ps.epoch, &ps.nparts, &ps.self));
+  const int64_t nblocks = ceil_div(r0, 256) + ceil_div(m->nrows - r1, 256) + ceil_div(r1 - r0, 256);
+  cudaStream_t s = cur_stream();
+  static const int u_env = env_int("SLC_SELL_U", 0);
+  const int u = u_env ? u_env : (m->max_rowlen <= 4 ? 4 : 8);
+  if (u <= 4)
+    k_spmv_sell_dist<T, 4><<<(unsigned)nblocks, 256, 0, s>>>(m->nrows, r0, r1, sp.slice_ptr, sp.rowlen, sp.colidx,
+                                                             (const T *)sp.vals, xa, (T *)y, ps);
+  else
+    k_spmv_sell_dist<T, 8><<<(unsigned)nblocks, 256, 0, s>>>(m->nrows, r0, r1, sp.slice_ptr, sp.rowlen, sp.colidx,
+                                                             (const T *)sp.vals, xa, (T *)y, ps);
+  SLC_LAUNCHED();
   return SLC_OK;
 }
 
