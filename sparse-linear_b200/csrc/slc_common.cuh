@@ -137,6 +137,9 @@ struct slc_matrix {
   void *rvals = nullptr;
   // row statistics (filled with the mirror)
   int32_t max_rowlen = 0;
+  // banded matrices: the far off-diagonal distance (multiple of 32) that SpMM blocks interleave
+  // their warps by, 0 = none detected (see k_spmm_short)
+  int32_t band_stride = 0;
   // product plans
   int spmv_kind = slc::SPMV_AUTO;      // requested
   int spmv_active = slc::SPMV_AUTO;    // chosen

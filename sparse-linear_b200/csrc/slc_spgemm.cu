@@ -19,32 +19,46 @@
 //           slots are then compacted, bitonic-sorted by row, and written out.
 //   Columns too long for shared memory use a per-block dense workspace in HBM (the reference's
 //   own accumulator, with a stamp instead of a full reset and a scan limited to [min,max] row).
+//   Columns of B with few entries (<= 8: every stencil, most of a power-law matrix) skip the hash
+//   table altogether: ONE THREAD merges the <= 8 sorted columns of A that the column selects
+//   (k_mm_merge).  The merge emits rows in increasing order and adds the terms of a row in list
+//   order = increasing k, so structure and values are again the reference's, with no shared
+//   memory, no atomics and no sort.
+#include <cstdlib>
+
 #include "slc_common.cuh"
 
 namespace slc {
 
-constexpr int NCLASS = 4;           // 0: <=64 products, 1: <=512, 2: <=2048, 3: dense fallback
+// classes: 0/1 thread-per-column merge (<= 4 / <= 8 entries in B[:, j], <= MERGE_UB products);
+//          2: <= 64 products, 3: <= 512, 4: <= 2048 (hash tables of twice the bound); 5: dense fallback
+constexpr int NCLASS = 6;
+constexpr int CLS_MERGE4 = 0, CLS_MERGE8 = 1, CLS_HASH0 = 2, CLS_HASH1 = 3, CLS_HASH2 = 4, CLS_DENSE = 5;
 constexpr int CLASS_UB0 = 64, CLASS_UB1 = 512, CLASS_UB2 = 2048;  // table = 2 * bound
+constexpr int MERGE_UB = 256;
 
 // ---- pass 0: products per column, classification ------------------------------------------------
 
 __global__ void k_mm_upper(int32_t bc, const int32_t *__restrict__ bp, const int32_t *__restrict__ bi,
                            const int32_t *__restrict__ ap, int32_t *__restrict__ ub,
-                           int32_t *__restrict__ klass, int32_t *__restrict__ class_count) {
+                           int32_t *__restrict__ klass, int32_t *__restrict__ class_count, int merge_ok) {
   const int32_t j = blockIdx.x * blockDim.x + threadIdx.x;
   int cls = -1;
   if (j < bc) {
     int64_t total = 0;
-    for (int32_t q = bp[j]; q < bp[j + 1]; ++q) {
+    const int32_t q0 = bp[j], q1 = bp[j + 1];
+    for (int32_t q = q0; q < q1; ++q) {
       const int32_t k = bi[q];
       total += ap[k + 1] - ap[k];
     }
     ub[j] = total > 0x7fffffffLL ? 0x7fffffff : (int32_t)total;
     if (total == 0) cls = -1;
-    else if (total <= CLASS_UB0) cls = 0;
-    else if (total <= CLASS_UB1) cls = 1;
-    else if (total <= CLASS_UB2) cls = 2;
-    else cls = 3;
+    else if (merge_ok && q1 - q0 <= 4 && total <= MERGE_UB) cls = CLS_MERGE4;
+    else if (merge_ok && q1 - q0 <= 8 && total <= MERGE_UB) cls = CLS_MERGE8;
+    else if (total <= CLASS_UB0) cls = CLS_HASH0;
+    else if (total <= CLASS_UB1) cls = CLS_HASH1;
+    else if (total <= CLASS_UB2) cls = CLS_HASH2;
+    else cls = CLS_DENSE;
     klass[j] = cls;
   }
   // warp-aggregated class histogram
@@ -72,6 +86,83 @@ __global__ void k_mm_bucket(int32_t bc, const int32_t *__restrict__ klass,
     base = __shfl_sync(0xffffffffu, base, leader);
     if (cls == c) cols[class_base[c] + base + __popc(m & ((1u << lane) - 1))] = j;
   }
+}
+
+// ---- thread-per-column merge --------------------------------------------------------------------
+// Column j of C is the union of the columns A[:, k], k in B[:, j]: NB sorted lists.  The thread
+// keeps one cursor per list in registers (all loops are unrolled over NB), repeatedly takes the
+// smallest head row m, and adds a*b over the lists whose head is m in list order -- increasing k,
+// starting from 0, c + a*b (Sparse.hs:699) -- then advances those lists.  NUMERIC = false only
+// counts the distinct rows (symbolic pass).
+constexpr int32_t ROW_END = 0x7fffffff;  // past every valid row index
+
+template <class T, int NB, bool NUMERIC>
+__global__ void __launch_bounds__(128)
+k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32_t *__restrict__ ap,
+           const int32_t *__restrict__ ai, const T *__restrict__ av, const int32_t *__restrict__ bp,
+           const int32_t *__restrict__ bi, const T *__restrict__ bv, int32_t *__restrict__ cnt,
+           const int32_t *__restrict__ cp, int32_t *__restrict__ ci, T *__restrict__ cv) {
+  const int32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= ncols_in_class) return;
+  const int32_t j = cols[slot];
+  const int32_t q0 = bp[j];
+  const int32_t nb = bp[j + 1] - q0;
+  int32_t p[NB], pe[NB], head[NB];
+  T b[NB];
+#pragma unroll
+  for (int u = 0; u < NB; ++u) {
+    p[u] = 0;
+    pe[u] = 0;
+    head[u] = ROW_END;
+    b[u] = Num<T>::zero();
+    if (u < nb) {
+      const int32_t k = __ldg(bi + q0 + u);
+      p[u] = __ldg(ap + k);
+      pe[u] = __ldg(ap + k + 1);
+      if (NUMERIC) b[u] = __ldg(bv + q0 + u);
+      if (p[u] < pe[u]) head[u] = __ldg(ai + p[u]);
+    }
+  }
+  int32_t count = 0;
+  int32_t *co = nullptr;
+  T *vo = nullptr;
+  if (NUMERIC) {
+    const int32_t base = cp[j];
+    co = ci + base;
+    vo = cv + base;
+  }
+  for (;;) {
+    int32_t m = head[0];
+#pragma unroll
+    for (int u = 1; u < NB; ++u) m = min(m, head[u]);
+    if (m == ROW_END) break;
+    T acc = Num<T>::zero();
+#pragma unroll
+    for (int u = 0; u < NB; ++u) {
+      if (head[u] == m) {
+        if (NUMERIC) acc = Num<T>::add(acc, Num<T>::mul(__ldg(av + p[u]), b[u]));
+        ++p[u];
+        head[u] = p[u] < pe[u] ? __ldg(ai + p[u]) : ROW_END;
+      }
+    }
+    if (NUMERIC) {
+      co[count] = m;
+      vo[count] = acc;
+    }
+    ++count;
+  }
+  if (!NUMERIC) cnt[j] = count;
+}
+
+template <class T, int NB, bool NUMERIC>
+static int run_merge(int32_t n, const int32_t *cols, const slc_matrix *a, const slc_matrix *b, int32_t *cnt,
+                     slc_matrix *c) {
+  if (n == 0) return SLC_OK;
+  k_mm_merge<T, NB, NUMERIC><<<(unsigned)ceil_div(n, 128), 128, 0, cur_stream()>>>(
+      n, cols, a->colptr, a->rowidx, (const T *)a->vals, b->colptr, b->rowidx, (const T *)b->vals, cnt,
+      c ? c->colptr : nullptr, c ? c->rowidx : nullptr, c ? (T *)c->vals : nullptr);
+  SLC_LAUNCHED();
+  return SLC_OK;
 }
 
 // ---- group helpers ------------------------------------------------------------------------------
@@ -386,10 +477,12 @@ static int mm_entry(const slc_matrix *a, const slc_matrix *b, slc_matrix **out) 
   SLC_CUDA(cudaMemsetAsync(ccount.p, 0, NCLASS * sizeof(int32_t), s));
   SLC_CUDA(cudaMemsetAsync(cursor.p, 0, NCLASS * sizeof(int32_t), s));
   SLC_CUDA(cudaMemsetAsync(cnt.p, 0, ((size_t)bc + 1) * sizeof(int32_t), s));
-  int32_t hcount[NCLASS] = {0, 0, 0, 0}, hbase[NCLASS] = {0, 0, 0, 0};
+  int32_t hcount[NCLASS] = {}, hbase[NCLASS] = {};
+  const char *merge_env = getenv("SLC_MM_MERGE");  // SLC_MM_MERGE=0: hash tables for every column
+  const int merge_ok = !(merge_env && merge_env[0] == '0');
   if (bc > 0) {
     const unsigned nb = (unsigned)ceil_div(bc, 256);
-    k_mm_upper<<<nb, 256, 0, s>>>(bc, b->colptr, b->rowidx, a->colptr, ub.p, klass.p, ccount.p);
+    k_mm_upper<<<nb, 256, 0, s>>>(bc, b->colptr, b->rowidx, a->colptr, ub.p, klass.p, ccount.p, merge_ok);
     SLC_LAUNCHED();
     SLC_CUDA(cudaMemcpyAsync(hcount, ccount.p, sizeof hcount, cudaMemcpyDeviceToHost, s));
     SLC_CUDA(cudaStreamSynchronize(s));
@@ -403,23 +496,25 @@ static int mm_entry(const slc_matrix *a, const slc_matrix *b, slc_matrix **out) 
   DevBuf<int32_t> stamp;
   DevBuf<T> work;
   int dense_blocks = 0;
-  if (hcount[3] > 0) {
+  if (hcount[CLS_DENSE] > 0) {
     const size_t per_block = (size_t)(ar > 0 ? ar : 1) * (sizeof(int32_t) + sizeof(T));
     size_t fit = ((size_t)4 << 30) / per_block;
     if (fit < 1) fit = 1;
     dense_blocks = (int)(fit < (size_t)(2 * sm_count()) ? fit : (size_t)(2 * sm_count()));
-    if (dense_blocks > hcount[3]) dense_blocks = hcount[3];
+    if (dense_blocks > hcount[CLS_DENSE]) dense_blocks = hcount[CLS_DENSE];
     SLC_TRY(stamp.alloc((size_t)dense_blocks * ar));
     SLC_TRY(work.alloc((size_t)dense_blocks * ar));
     SLC_CUDA(cudaMemsetAsync(stamp.p, 0, (size_t)dense_blocks * ar * sizeof(int32_t), s));
   }
 
   // pass 1: symbolic
-  SLC_TRY((run_symbolic<T, 8, 128, 128>(hcount[0], cols.p + hbase[0], a, b, cnt.p)));
-  SLC_TRY((run_symbolic<T, 32, 1024, 128>(hcount[1], cols.p + hbase[1], a, b, cnt.p)));
-  SLC_TRY((run_symbolic<T, 256, 4096, 256>(hcount[2], cols.p + hbase[2], a, b, cnt.p)));
-  if (hcount[3] > 0) {
-    k_mm_dense<T, false><<<dense_blocks, 256, 0, s>>>(hcount[3], cols.p + hbase[3], ar, a->colptr,
+  SLC_TRY((run_merge<T, 4, false>(hcount[CLS_MERGE4], cols.p + hbase[CLS_MERGE4], a, b, cnt.p, nullptr)));
+  SLC_TRY((run_merge<T, 8, false>(hcount[CLS_MERGE8], cols.p + hbase[CLS_MERGE8], a, b, cnt.p, nullptr)));
+  SLC_TRY((run_symbolic<T, 8, 128, 128>(hcount[CLS_HASH0], cols.p + hbase[CLS_HASH0], a, b, cnt.p)));
+  SLC_TRY((run_symbolic<T, 32, 1024, 128>(hcount[CLS_HASH1], cols.p + hbase[CLS_HASH1], a, b, cnt.p)));
+  SLC_TRY((run_symbolic<T, 256, 4096, 256>(hcount[CLS_HASH2], cols.p + hbase[CLS_HASH2], a, b, cnt.p)));
+  if (hcount[CLS_DENSE] > 0) {
+    k_mm_dense<T, false><<<dense_blocks, 256, 0, s>>>(hcount[CLS_DENSE], cols.p + hbase[CLS_DENSE], ar, a->colptr,
                                                       a->rowidx, (const T *)a->vals, b->colptr, b->rowidx,
                                                       (const T *)b->vals, stamp.p, work.p, cnt.p, nullptr,
                                                       nullptr, nullptr);
@@ -446,11 +541,13 @@ static int mm_entry(const slc_matrix *a, const slc_matrix *b, slc_matrix **out) 
   g_launches.fetch_add(1, std::memory_order_relaxed);
 
   // pass 2: numeric
-  int rc = run_numeric<T, 8, 128, 128>(hcount[0], cols.p + hbase[0], a, b, c);
-  if (rc == SLC_OK) rc = run_numeric<T, 32, 1024, 128>(hcount[1], cols.p + hbase[1], a, b, c);
-  if (rc == SLC_OK) rc = run_numeric<T, 256, 4096, 256>(hcount[2], cols.p + hbase[2], a, b, c);
-  if (rc == SLC_OK && hcount[3] > 0) {
-    k_mm_dense<T, true><<<dense_blocks, 256, 0, s>>>(hcount[3], cols.p + hbase[3], ar, a->colptr, a->rowidx,
+  int rc = run_merge<T, 4, true>(hcount[CLS_MERGE4], cols.p + hbase[CLS_MERGE4], a, b, nullptr, c);
+  if (rc == SLC_OK) rc = run_merge<T, 8, true>(hcount[CLS_MERGE8], cols.p + hbase[CLS_MERGE8], a, b, nullptr, c);
+  if (rc == SLC_OK) rc = run_numeric<T, 8, 128, 128>(hcount[CLS_HASH0], cols.p + hbase[CLS_HASH0], a, b, c);
+  if (rc == SLC_OK) rc = run_numeric<T, 32, 1024, 128>(hcount[CLS_HASH1], cols.p + hbase[CLS_HASH1], a, b, c);
+  if (rc == SLC_OK) rc = run_numeric<T, 256, 4096, 256>(hcount[CLS_HASH2], cols.p + hbase[CLS_HASH2], a, b, c);
+  if (rc == SLC_OK && hcount[CLS_DENSE] > 0) {
+    k_mm_dense<T, true><<<dense_blocks, 256, 0, s>>>(hcount[CLS_DENSE], cols.p + hbase[CLS_DENSE], ar, a->colptr, a->rowidx,
                                                      (const T *)a->vals, b->colptr, b->rowidx,
                                                      (const T *)b->vals, stamp.p, work.p, cnt.p, c->colptr,
                                                      c->rowidx, (T *)c->vals);

@@ -619,15 +619,30 @@ __device__ __forceinline__ void spmm_short_columns(const int32_t (&c)[LMAX], con
   }
 }
 
+//
+// Row mapping.  stride32 == 0: a block owns blockDim.x consecutive rows.  stride32 == S/32 > 0 (banded
+// matrices whose rows reach S columns away, e.g. a 2-D grid of width S): the W warps of a block own
+// 32-row slices S rows apart, block b of a chunk of W*S rows taking slices {b + w*S/32}.  The window
+// of X that warp w gathers around column r+S is then the window warp w+1 gathers around its own
+// diagonal, so it is fetched from L2 once per block (L1 hit for the others) instead of once per warp.
 template <class T, int JT, int LMAX, bool SELL>
-__global__ void __launch_bounds__(128)
-k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, const int64_t *__restrict__ slice_ptr,
+__global__ void __launch_bounds__(256)
+k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, int32_t stride32,
+             const int64_t *__restrict__ slice_ptr,
              const int32_t *__restrict__ rowlen, const int32_t *__restrict__ rowptr,
              const int32_t *__restrict__ colidx, const T *__restrict__ vals, const T *__restrict__ X,
              int64_t ldx, T *__restrict__ Y, int64_t ldy, int32_t k) {
   const int32_t rb = blockIdx.x / ngroups;
   const int32_t grp = blockIdx.x - rb * ngroups;
-  const int32_t row = rb * blockDim.x + threadIdx.x;
+  int32_t row;
+  if (stride32 == 0) {
+    row = rb * blockDim.x + threadIdx.x;
+  } else {
+    const int32_t chunk = rb / stride32, b = rb - chunk * stride32;
+    const int64_t r64 = ((int64_t)chunk * (blockDim.x >> 5) * stride32 + (int64_t)(threadIdx.x >> 5) * stride32 + b) * 32 +
+                        (threadIdx.x & 31);
+    row = r64 < nrows ? (int32_t)r64 : nrows;
+  }
   const bool live = row < nrows;
   const uint64_t pol_s = policy_evict_first();
   const uint64_t pol_x = policy_evict_last();
@@ -937,17 +952,24 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
   SLC_TRY(ensure_plan<T>(m));
   if (m->max_rowlen >= 1 && m->max_rowlen <= 8) {  // short rows: registers hold the row, see k_spmm_short
     static const int jg_env = env_int("SLC_SPMM_JG", 0);
+    static const int stride_env = env_int("SLC_SPMM_STRIDE", -1);
+    static const int threads_env = env_int("SLC_SPMM_THREADS", 0);
     const int32_t jgroup = jg_env > 0 ? jg_env : 64;
     const int32_t ngroups = (int32_t)ceil_div(k, jgroup);
-    const int64_t nb = ceil_div(m->nrows, 128) * ngroups;
+    const int32_t stride = stride_env >= 0 ? stride_env : m->band_stride;
+    const int32_t stride32 = (stride >= 64 && stride % 32 == 0) ? stride / 32 : 0;
+    const int threads = threads_env ? threads_env : (stride32 ? 256 : 128);
+    const int64_t row_blocks = stride32 ? ceil_div(m->nrows, (int64_t)(threads / 32) * stride) * stride32
+                                        : ceil_div(m->nrows, threads);
+    const int64_t nb = row_blocks * ngroups;
     if (nb > 0x7fffffffLL) return fail(SLC_ERR_RANGE, "mulM: grid too large");
     const bool sell = m->spmv_active == SPMV_SELL;
     const SellPlan &sp = m->sell;
     constexpr int JTS = sizeof(T) == 16 ? 2 : 4;
 #define SLC_SHORT(L_, SELL_)                                                                         \
-  k_spmm_short<T, JTS, L_, SELL_><<<(unsigned)nb, 128, 0, s>>>(                                       \
-      m->nrows, ngroups, jgroup, sp.slice_ptr, sp.rowlen, m->rowptr, SELL_ ? sp.colidx : m->colidx,  \
-      SELL_ ? (const T *)sp.vals : (const T *)m->rvals, X, ldx, Y, ldy, k)
+  k_spmm_short<T, JTS, L_, SELL_><<<(unsigned)nb, threads, 0, s>>>(                                   \
+      m->nrows, ngroups, jgroup, stride32, sp.slice_ptr, sp.rowlen, m->rowptr,                        \
+      SELL_ ? sp.colidx : m->colidx, SELL_ ? (const T *)sp.vals : (const T *)m->rvals, X, ldx, Y, ldy, k)
 #define SLC_SHORT_L(L_)                                                                              \
   case L_:                                                                                           \
     if (sell) SLC_SHORT(L_, true);                                                                   \

@@ -277,7 +277,7 @@ def bench_main(args, rank, world, local_rank, dist):
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic (seeded numpy PCG64)",
             "config": {"workload": "cfg5: 3D 27-point stencil %dx%dx%d, Double SpMV, row-partitioned in z-slabs over %d GPU(s); "
                                    "halo entries gathered from peer HBM over NVLink inside the product kernel; "
-                                   "one peer-memory barrier kernel per step orders the ranks" % (shape + (world,)),
+                                   "the inter-GPU barrier (peer-memory flags) is fused into the same launch" % (shape + (world,)),
                        "rows": ntot, "nnz": nnz, "algorithmic_bytes_per_step": abytes,
                        "plan": local.device().plan_info(),
                        "l2": "inputs larger than L2 (%.0f MB per GPU per step)" % (abytes / world / 1e6),
@@ -285,9 +285,9 @@ def bench_main(args, rank, world, local_rank, dist):
                        "max_rel_err_vs_host_sum": float(errt.item())},
             "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e,
             "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": "k_spmv_sell<DistX>",
+                         "traffic": None, "peak_source": peak_src, "kernel": "k_spmv_sell_dist",
                          "note": "per-GPU figure; step time includes the inter-GPU barrier",
-                         "barrier": "nccl all-reduce" if sh.use_nccl_barrier else "slc_peer_barrier",
+                         "barrier": "nccl all-reduce" if sh.use_nccl_barrier else "peer-memory flags, fused in k_spmv_sell_dist",
                          "barrier_timed_out": sh.timed_out()},
             "cpu_baseline": None,
         }

@@ -220,10 +220,13 @@ def test_compress_bounds_errors(sl):
 
 # ---- SpGEMM ---------------------------------------------------------------------------------------------
 
+@pytest.mark.parametrize("merge", ["1", "0"])     # thread-per-column merge classes on / hash tables only
 @pytest.mark.parametrize("dtype", DTYPES)
-def test_mm_matches_oracle(sl, dtype):
+def test_mm_matches_oracle(sl, dtype, merge, monkeypatch):
+    monkeypatch.setenv("SLC_MM_MERGE", merge)
     rng = np.random.default_rng(51)
     cases = [(1, 1, 1, 1.0, 1.0), (6, 4, 5, 0.5, 0.5), (50, 60, 70, 0.1, 0.1), (300, 300, 300, 0.02, 0.02),
+             (500, 400, 300, 0.05, 0.005), (2000, 64, 900, 0.03, 0.08),   # <= 4 and <= 8 entries per column of B
              (40, 40, 40, 0.0, 0.3), (64, 512, 64, 0.5, 0.5),      # class 1/2 columns
              (3000, 200, 50, 0.6, 0.9)]                            # > 2048 products: dense fallback
     for nr, inner, nc, da, db in cases:
@@ -241,11 +244,16 @@ def test_mm_structural_zeros_and_errors(sl):
     assert c.pointers.tolist() == [0, 1] and c.indices.tolist() == [0] and c.values.tolist() == [0.0]
     z = sl.fromTriples(2, 2, [(0, 0, 0.0), (1, 1, 5.0)])
     assert (z * z).pointers.tolist() == [0, 1, 2]
+    # the accumulator starts from +0 (ScatterGather reset), so a lone -0 term comes out as +0
+    n = sl.fromTriples(1, 1, [(0, 0, -1.0)]) * sl.fromTriples(1, 1, [(0, 0, 0.0)])
+    assert n.values.tolist() == [0.0] and not np.signbit(n.values[0])
     with pytest.raises(sl.SparseLinearError, match="mm: inner dimension mismatch"):
         sl.mm(sl.ident(3), sl.ident(4))
 
 
-def test_mm_stencil_squared(sl):
+@pytest.mark.parametrize("merge", ["1", "0"])
+def test_mm_stencil_squared(sl, merge, monkeypatch):
+    monkeypatch.setenv("SLC_MM_MERGE", merge)
     gm = g.laplace3d_7pt(12)
     om, m = oracle.csc(*gm), to_matrix(sl, gm)
     want, got = oracle.mm(om, om), sl.mm(m, m)
