@@ -105,28 +105,38 @@ void matrix_release(slc_matrix *m) {
   delete m;
 }
 
-// One thread per stored entry: bounds, and strictly increasing rows inside a column.  A
-// descent is legal only at a column start, which a binary search over colptr confirms.
-__global__ void k_validate_entries(int32_t nrows, int32_t ncols, int64_t nnz,
-                                   const int32_t *__restrict__ colptr,
-                                   const int32_t *__restrict__ rowidx, int *__restrict__ flag) {
-  int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= nnz) return;
-  int32_t r = rowidx[p];
-  if (r < 0 || r >= nrows) {
-    atomicOr(flag, 1);
-    return;
+// Format check of an uploaded matrix (the reference's checkMatrix): row indices in bounds and strictly
+// increasing inside every column.  A descent rowidx[p-1] >= rowidx[p] is legal only where a column
+// starts at p, so: one thread per entry counts the descents, one thread per non-empty column counts
+// the descents that sit on its start, and the matrix is well formed iff the two counts agree.
+// acc[0] = out-of-bounds flag, acc[1] = descents, acc[2] = descents at column starts.
+__global__ void k_validate_entries(int32_t nrows, int64_t nnz, const int32_t *__restrict__ rowidx,
+                                   unsigned long long *__restrict__ acc) {
+  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool oob = false, descent = false;
+  if (p < nnz) {
+    const int32_t r = rowidx[p];
+    oob = r < 0 || r >= nrows;
+    descent = p > 0 && rowidx[p - 1] >= r;
   }
-  if (p == 0) return;
-  if (rowidx[p - 1] >= r) {
-    int32_t lo = 0, hi = ncols;  // find some c with colptr[c] == p
-    while (lo < hi) {
-      int32_t mid = lo + ((hi - lo) >> 1);
-      if (colptr[mid] < (int32_t)p) lo = mid + 1;
-      else hi = mid;
-    }
-    if (lo > ncols || colptr[lo] != (int32_t)p) atomicOr(flag, 2);
+  const unsigned d = __ballot_sync(0xffffffffu, descent);
+  const unsigned o = __ballot_sync(0xffffffffu, oob);
+  if ((threadIdx.x & 31) == 0) {
+    if (o) atomicOr(acc, 1ull);
+    if (d) atomicAdd(acc + 1, (unsigned long long)__popc(d));
   }
+}
+
+__global__ void k_validate_starts(int32_t ncols, const int32_t *__restrict__ colptr,
+                                  const int32_t *__restrict__ rowidx, unsigned long long *__restrict__ acc) {
+  const int32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+  bool descent = false;
+  if (c < ncols) {
+    const int32_t p = colptr[c];
+    descent = p > 0 && p < colptr[c + 1] && rowidx[p - 1] >= rowidx[p];
+  }
+  const unsigned d = __ballot_sync(0xffffffffu, descent);
+  if ((threadIdx.x & 31) == 0 && d) atomicAdd(acc + 2, (unsigned long long)__popc(d));
 }
 
 template <class T>
@@ -151,29 +161,29 @@ static int upload_impl(int32_t nrows, int32_t ncols, const int32_t *colptr, cons
     e = cudaMemcpyAsync(m->rowidx, rowidx, (size_t)nnz * sizeof(int32_t), cudaMemcpyHostToDevice, s);
   if (e == cudaSuccess && nnz)
     e = cudaMemcpyAsync(m->vals, vals, (size_t)nnz * sizeof(T), cudaMemcpyHostToDevice, s);
-  DevBuf<int> flag;
-  int hflag = 0;
+  DevBuf<unsigned long long> acc;
+  unsigned long long hacc[3] = {0, 0, 0};
   int rc = SLC_OK;
-  if (e == cudaSuccess) rc = flag.alloc(1);
-  if (e == cudaSuccess && rc == SLC_OK) e = cudaMemsetAsync(flag.p, 0, sizeof(int), s);
+  if (e == cudaSuccess) rc = acc.alloc(3);
+  if (e == cudaSuccess && rc == SLC_OK) e = cudaMemsetAsync(acc.p, 0, sizeof hacc, s);
   if (e == cudaSuccess && rc == SLC_OK && nnz) {
-    k_validate_entries<<<(unsigned)ceil_div(nnz, 256), 256, 0, s>>>(nrows, ncols, nnz, m->colptr,
-                                                                     m->rowidx, flag.p);
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+    k_validate_entries<<<(unsigned)ceil_div(nnz, 256), 256, 0, s>>>(nrows, nnz, m->rowidx, acc.p);
+    k_validate_starts<<<(unsigned)ceil_div(ncols, 256), 256, 0, s>>>(ncols, m->colptr, m->rowidx, acc.p);
+    g_launches.fetch_add(2, std::memory_order_relaxed);
     e = cudaGetLastError();
   }
   if (e == cudaSuccess && rc == SLC_OK)
-    e = cudaMemcpyAsync(&hflag, flag.p, sizeof(int), cudaMemcpyDeviceToHost, s);
+    e = cudaMemcpyAsync(hacc, acc.p, sizeof hacc, cudaMemcpyDeviceToHost, s);
   if (e == cudaSuccess && rc == SLC_OK) e = cudaStreamSynchronize(s);
   if (e != cudaSuccess || rc != SLC_OK) {
     matrix_release(m);
     if (rc != SLC_OK) return rc;
     return fail(SLC_ERR_CUDA, "upload: CUDA error %s", cudaGetErrorString(e));
   }
-  if (hflag) {
+  if (hacc[0] || hacc[1] != hacc[2]) {
     matrix_release(m);
-    return fail(SLC_ERR_FORMAT, (hflag & 1) ? "upload: row index out of bounds"
-                                            : "upload: row indices not increasing in a column");
+    return fail(SLC_ERR_FORMAT, hacc[0] ? "upload: row index out of bounds"
+                                        : "upload: row indices not increasing in a column");
   }
   *out = m;
   return SLC_OK;

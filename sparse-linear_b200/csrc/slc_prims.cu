@@ -7,11 +7,11 @@
 //                    keys of tile t with digit d (all smaller digits, then earlier tiles, come first)
 //   k_radix_scatter  re-reads the tile; a warp owns a contiguous run of keys and ranks them in index
 //                    order with __match_any_sync + per-warp digit counters in shared memory, so
-//                    equal digits keep their input order (stable); every key is then written to
-//                    base[d] + earlier-warps[d] + rank
+//                    equal digits keep their input order (stable); the tile is reordered by digit
+//                    in shared memory and then streamed to base[d] + position-in-run
 // Only the bits the caller says are significant are sorted (a row index of a 2M-row matrix needs
 // 21 bits = 3 passes, not 4).  All traffic is coalesced on the read side; on the write side a tile
-// of 4096 keys lands in 256 runs.
+// of 8192 keys lands in at most 256 contiguous runs.
 #include "slc_common.cuh"
 
 namespace slc {
@@ -115,17 +115,17 @@ int exclusive_scan_i64(const int64_t *in, int64_t *out, int64_t n) {
 
 // ---- radix sort -------------------------------------------------------------------------------------
 
-constexpr int RS_THREADS = 256;
+constexpr int RS_THREADS = 512;
 constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 keys per block
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 8192 keys per block
 constexpr int RS_BINS = 256;
 
 template <class K>
 __global__ void __launch_bounds__(RS_THREADS)
 k_radix_hist(const K *__restrict__ keys, int64_t n, int shift, int64_t ntiles, int32_t *__restrict__ hist) {
   __shared__ int32_t cnt[RS_BINS];
-  cnt[threadIdx.x] = 0;
+  if (threadIdx.x < RS_BINS) cnt[threadIdx.x] = 0;
   __syncthreads();
   const int64_t base = (int64_t)blockIdx.x * RS_TILE;
 #pragma unroll
@@ -134,31 +134,58 @@ k_radix_hist(const K *__restrict__ keys, int64_t n, int shift, int64_t ntiles, i
     if (i < n) atomicAdd(&cnt[(int)((keys[i] >> shift) & (RS_BINS - 1))], 1);
   }
   __syncthreads();
-  hist[(int64_t)threadIdx.x * ntiles + blockIdx.x] = cnt[threadIdx.x];
+  if (threadIdx.x < RS_BINS) hist[(int64_t)threadIdx.x * ntiles + blockIdx.x] = cnt[threadIdx.x];
 }
 
+// Shared memory of k_radix_scatter: the tile's keys and values in digit order, the per-warp digit
+// counters, and two tables of 256.
+template <class K>
+constexpr size_t radix_scatter_smem() {
+  return (size_t)RS_TILE * (sizeof(K) + sizeof(uint32_t)) + (size_t)(RS_WARPS + 2) * RS_BINS * sizeof(int32_t) +
+         8 * sizeof(int32_t);
+}
+
+// Pass 1 of 2 inside the tile: every key gets its position in the tile's digit order -- keys of a
+// smaller digit first, then earlier warps, then index order inside the warp (__match_any_sync rank),
+// which keeps the sort stable -- and is parked there in shared memory.  Pass 2 streams the parked
+// tile out: neighbouring threads hold neighbouring keys of the same digit, whose global positions
+// are consecutive, so the writes are coalesced runs instead of one sector per key.
 template <class K>
 __global__ void __launch_bounds__(RS_THREADS)
 k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals_in, K *__restrict__ keys_out,
                 uint32_t *__restrict__ vals_out, int64_t n, int shift, int64_t ntiles,
                 const int32_t *__restrict__ hist_scanned) {
-  __shared__ int32_t wcnt[RS_WARPS][RS_BINS];
-  __shared__ int32_t tile_base[RS_BINS];
+  extern __shared__ __align__(16) unsigned char rs_smem[];
+  K *skeys = reinterpret_cast<K *>(rs_smem);                         // [RS_TILE]
+  uint32_t *svals = reinterpret_cast<uint32_t *>(skeys + RS_TILE);   // [RS_TILE]
+  int32_t *wcnt = reinterpret_cast<int32_t *>(svals + RS_TILE);      // [RS_WARPS][RS_BINS]
+  int32_t *local_base = wcnt + RS_WARPS * RS_BINS;                   // [RS_BINS] start of digit d in the tile
+  int32_t *gshift = local_base + RS_BINS;                            // [RS_BINS] global start - local start
+  int32_t *wsum = gshift + RS_BINS;                                  // [8]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  for (int i = tid; i < RS_WARPS * RS_BINS; i += RS_THREADS) (&wcnt[0][0])[i] = 0;
-  tile_base[tid] = hist_scanned[(int64_t)tid * ntiles + blockIdx.x];
+  for (int i = tid; i < RS_WARPS * RS_BINS; i += RS_THREADS) wcnt[i] = 0;
+  int32_t tile_base = 0;
+  if (tid < RS_BINS) tile_base = hist_scanned[(int64_t)tid * ntiles + blockIdx.x];
   __syncthreads();
 
   // warp `warp` owns keys [cb, cb + 32*RS_ITEMS), taken 32 at a time in index order
-  const int64_t cb = (int64_t)blockIdx.x * RS_TILE + (int64_t)warp * (32 * RS_ITEMS);
+  const int64_t tb = (int64_t)blockIdx.x * RS_TILE;
+  const int64_t cb = tb + (int64_t)warp * (32 * RS_ITEMS);
   const unsigned lt = (1u << lane) - 1u;
   K key[RS_ITEMS];
+  uint32_t val[RS_ITEMS];
   int32_t rank[RS_ITEMS];
 #pragma unroll
   for (int it = 0; it < RS_ITEMS; ++it) {
     const int64_t i = cb + it * 32 + lane;
     const bool valid = i < n;
     key[it] = valid ? keys_in[i] : (K)0;
+    val[it] = valid ? vals_in[i] : 0u;
+  }
+  int32_t *mycnt = wcnt + warp * RS_BINS;
+#pragma unroll
+  for (int it = 0; it < RS_ITEMS; ++it) {
+    const bool valid = cb + it * 32 + lane < n;
     const int d = (int)((key[it] >> shift) & (RS_BINS - 1));
     const unsigned peers = __match_any_sync(0xffffffffu, valid ? d : RS_BINS);
     rank[it] = 0;
@@ -166,8 +193,8 @@ k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals
       const int leader = __ffs(peers) - 1;
       int32_t b = 0;
       if (lane == leader) {
-        b = wcnt[warp][d];
-        wcnt[warp][d] = b + __popc(peers);
+        b = mycnt[d];
+        mycnt[d] = b + __popc(peers);
       }
       b = __shfl_sync(peers, b, leader);
       rank[it] = b + __popc(peers & lt);
@@ -175,25 +202,50 @@ k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals
     __syncwarp();
   }
   __syncthreads();
-  {  // counts per warp -> offsets of each warp inside the tile's run of digit `tid`
-    int32_t run = 0;
+  int32_t total = 0, incl = 0;
+  if (tid < RS_BINS) {  // counts per warp -> offset of each warp inside the tile's run of digit `tid`
 #pragma unroll
     for (int w = 0; w < RS_WARPS; ++w) {
-      const int32_t c = wcnt[w][tid];
-      wcnt[w][tid] = run;
-      run += c;
+      const int32_t c = wcnt[w * RS_BINS + tid];
+      wcnt[w * RS_BINS + tid] = total;
+      total += c;
     }
+    incl = total;  // exclusive scan of the digit totals over the 256 threads
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) wsum[warp] = incl;
+  }
+  __syncthreads();
+  if (tid < RS_BINS) {
+    int32_t before = 0;
+#pragma unroll
+    for (int w = 0; w < RS_BINS / 32; ++w)
+      if (w < warp) before += wsum[w];
+    const int32_t lb = before + incl - total;
+    local_base[tid] = lb;
+    gshift[tid] = tile_base - lb;
   }
   __syncthreads();
 #pragma unroll
   for (int it = 0; it < RS_ITEMS; ++it) {
-    const int64_t i = cb + it * 32 + lane;
-    if (i < n) {
+    if (cb + it * 32 + lane < n) {
       const int d = (int)((key[it] >> shift) & (RS_BINS - 1));
-      const int64_t pos = (int64_t)tile_base[d] + wcnt[warp][d] + rank[it];
-      keys_out[pos] = key[it];
-      vals_out[pos] = vals_in[i];
+      const int32_t lp = local_base[d] + mycnt[d] + rank[it];
+      skeys[lp] = key[it];
+      svals[lp] = val[it];
     }
+  }
+  __syncthreads();
+  const int32_t count = (int32_t)min((int64_t)RS_TILE, n - tb);
+  for (int32_t i = tid; i < count; i += RS_THREADS) {
+    const K kk = skeys[i];
+    const int d = (int)((kk >> shift) & (RS_BINS - 1));
+    const int64_t pos = (int64_t)gshift[d] + i;
+    keys_out[pos] = kk;
+    vals_out[pos] = svals[i];
   }
 }
 
@@ -210,6 +262,8 @@ static int sort_pairs_impl(K *keys_in, K *keys_out, uint32_t *vals_in, uint32_t 
   const int64_t ntiles = ceil_div(n, RS_TILE);
   DevBuf<int32_t> hist;
   SLC_TRY(hist.alloc((size_t)ntiles * RS_BINS));
+  SLC_CUDA(cudaFuncSetAttribute(k_radix_scatter<K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)radix_scatter_smem<K>()));
   K *kin = keys_in, *kout = keys_out;
   uint32_t *vin = vals_in, *vout = vals_out;
   for (int p = 0; p < passes; ++p) {
@@ -217,7 +271,8 @@ static int sort_pairs_impl(K *keys_in, K *keys_out, uint32_t *vals_in, uint32_t 
     k_radix_hist<K><<<(unsigned)ntiles, RS_THREADS, 0, s>>>(kin, n, shift, ntiles, hist.p);
     SLC_LAUNCHED();
     SLC_TRY(exclusive_scan_i32(hist.p, hist.p, ntiles * RS_BINS));
-    k_radix_scatter<K><<<(unsigned)ntiles, RS_THREADS, 0, s>>>(kin, vin, kout, vout, n, shift, ntiles, hist.p);
+    k_radix_scatter<K><<<(unsigned)ntiles, RS_THREADS, radix_scatter_smem<K>(), s>>>(kin, vin, kout, vout, n, shift,
+                                                                                    ntiles, hist.p);
     SLC_LAUNCHED();
     K *tk = kin; kin = kout; kout = tk;
     uint32_t *tv = vin; vin = vout; vout = tv;
