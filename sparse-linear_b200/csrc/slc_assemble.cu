@@ -17,8 +17,7 @@ namespace slc {
 
 __global__ void k_coo_check_pack(int64_t n, int32_t nrows, int32_t ncols, int rowbits,
                                  const int32_t *__restrict__ rows, const int32_t *__restrict__ cols,
-                                 uint64_t *__restrict__ keys, uint32_t *__restrict__ pos,
-                                 unsigned long long *__restrict__ first_bad) {
+                                 uint64_t *__restrict__ keys, unsigned long long *__restrict__ first_bad) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int32_t r = rows[i], c = cols[i];
@@ -27,7 +26,6 @@ __global__ void k_coo_check_pack(int64_t n, int32_t nrows, int32_t ncols, int ro
   if (bad_r) atomicMin(first_bad + 0, (unsigned long long)i);
   if (bad_c) atomicMin(first_bad + 1, (unsigned long long)i);
   keys[i] = (bad_r || bad_c) ? 0ull : (((uint64_t)(uint32_t)c << rowbits) | (uint32_t)r);
-  pos[i] = (uint32_t)i;
 }
 
 __global__ void k_head_flags(int64_t n, const uint64_t *__restrict__ keys, int32_t *__restrict__ head) {
@@ -103,7 +101,7 @@ static int compress_entry(int32_t nrows, int32_t ncols, int64_t n, const int32_t
   SLC_CUDA(cudaMemcpyAsync(dvals.p, vals, (size_t)n * sizeof(T), cudaMemcpyHostToDevice, s));
   SLC_CUDA(cudaMemsetAsync(bad.p, 0xff, 2 * sizeof(unsigned long long), s));
   const unsigned nb = (unsigned)ceil_div(n, 256);
-  k_coo_check_pack<<<nb, 256, 0, s>>>(n, nrows, ncols, rowbits, drows.p, dcols.p, k0.p, p0.p, bad.p);
+  k_coo_check_pack<<<nb, 256, 0, s>>>(n, nrows, ncols, rowbits, drows.p, dcols.p, k0.p, bad.p);
   SLC_LAUNCHED();
   unsigned long long hbad[2];
   SLC_CUDA(cudaMemcpyAsync(hbad, bad.p, sizeof hbad, cudaMemcpyDeviceToHost, s));
@@ -121,14 +119,15 @@ static int compress_entry(int32_t nrows, int32_t ncols, int64_t n, const int32_t
   drows.release();
   dcols.release();
 
-  SLC_TRY(sort_pairs_u64(k0.p, k1.p, p0.p, p1.p, n, rowbits + colbits));
-  k0.release();
-  p0.release();
+  // the values carried by the sort are the input positions (generated by its first pass)
+  uint64_t *skey = nullptr;
+  uint32_t *sperm = nullptr;
+  SLC_TRY(sort_pairs_u64(nullptr, k0.p, k1.p, p0.p, p1.p, n, rowbits + colbits, true, &skey, &sperm));
 
   SLC_TRY(head.alloc(n + 1));
   SLC_TRY(seg.alloc(n + 1));
   SLC_CUDA(cudaMemsetAsync(head.p + n, 0, sizeof(int32_t), s));
-  k_head_flags<<<nb, 256, 0, s>>>(n, k1.p, head.p);
+  k_head_flags<<<nb, 256, 0, s>>>(n, skey, head.p);
   SLC_LAUNCHED();
   SLC_TRY(exclusive_scan_i32(head.p, seg.p, n + 1));
   int32_t nnz_out = 0;
@@ -139,7 +138,7 @@ static int compress_entry(int32_t nrows, int32_t ncols, int64_t n, const int32_t
   DevBuf<uint32_t> ocol;
   int rc = ocol.alloc((size_t)nnz_out);
   if (rc == SLC_OK) {
-    k_reduce_runs<T><<<nb, 256, 0, s>>>(n, rowbits, k1.p, p1.p, head.p, seg.p, dvals.p, m->rowidx, ocol.p,
+    k_reduce_runs<T><<<nb, 256, 0, s>>>(n, rowbits, skey, sperm, head.p, seg.p, dvals.p, m->rowidx, ocol.p,
                                         (T *)m->vals);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     k_ptrs_from_sorted_u32<<<(unsigned)ceil_div((int64_t)nnz_out + 1, 256), 256, 0, s>>>(nnz_out, ncols,

@@ -94,7 +94,13 @@ inline void dev_free(void *p) {
 // ---- the handle ---------------------------------------------------------------------------------
 
 enum ElemType : int { ELEM_D = 'd', ELEM_Z = 'z' };
-enum SpmvKind : int { SPMV_AUTO = 0, SPMV_SELL = 1, SPMV_CSR_WARP = 2, SPMV_CSR_BALANCED = 3 };
+enum SpmvKind : int {
+  SPMV_AUTO = 0,
+  SPMV_SELL = 1,
+  SPMV_CSR_WARP = 2,
+  SPMV_CSR_BALANCED = 3,       // nnz chunks, merge-style kernel (k_spmv_merge)
+  SPMV_CSR_BALANCED_SMEM = 4,  // nnz chunks, products staged in shared memory (k_spmv_bal)
+};
 
 // Sliced-ELL plan (slices of 32 rows, column-major inside a slice, row per thread).
 struct SellPlan {
@@ -250,6 +256,21 @@ __device__ __forceinline__ void st_stream(double2 *p, double2 v) {
   asm volatile("st.global.cs.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(v.x), "d"(v.y) : "memory");
 }
 
+// ---- keeping a batch of gathers in flight -------------------------------------------------------
+// ptxas sinks independent loads below the arithmetic on earlier ones to reuse their registers, which
+// turns a batch of N gathers into several exposed memory latencies (ncu, round 1: k_spmm_short
+// stalled at 6 points per column tile, 3 loads in flight instead of 10).  Neither barriers nor
+// volatile asm stop it: .nc loads move across both.  A true data dependence does: OR one word of
+// every value of the batch (`probe`), mask it with a kernel argument that is always 0 (`zmask`, opaque
+// to the compiler) and XOR the result into the first operand of every chain (`tie`).  Values are
+// unchanged, and no product can issue before every load of the batch has been issued.
+__device__ __forceinline__ uint32_t probe(double v) { return (uint32_t)__double2hiint(v); }
+__device__ __forceinline__ uint32_t probe(double2 v) { return (uint32_t)__double2hiint(v.x); }
+__device__ __forceinline__ void tie(double &v, uint32_t r) {
+  v = __hiloint2double(__double2hiint(v) ^ (int)r, __double2loint(v));
+}
+__device__ __forceinline__ void tie(double2 &v, uint32_t r) { tie(v.x, r); }
+
 // ---- small helpers ------------------------------------------------------------------------------
 
 inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
@@ -258,11 +279,13 @@ int sm_count();
 // device primitives implemented in slc_prims.cu (radix sort, scans)
 int exclusive_scan_i32(const int32_t *in, int32_t *out, int64_t n);  // out may alias in
 int exclusive_scan_i64(const int64_t *in, int64_t *out, int64_t n);
-// stable sort of (key, value) pairs on key bits [0, end_bit); the input buffers are scratch
-int sort_pairs_u32(uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in, uint32_t *vals_out,
-                   int64_t n, int end_bit);
-int sort_pairs_u64(uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in, uint32_t *vals_out,
-                   int64_t n, int end_bit);
+// stable sort of (key, value) pairs on key bits [0, end_bit).  (ka, va) / (kb, vb) are ping-pong
+// scratch; the first pass reads keys from `src` if given (left intact; needs iota_vals) else from ka,
+// and takes values from va, or 0..n-1 when iota_vals.  *res_k / *res_v: the buffers holding the result.
+int sort_pairs_u32(const uint32_t *src, uint32_t *ka, uint32_t *kb, uint32_t *va, uint32_t *vb, int64_t n,
+                   int end_bit, bool iota_vals, uint32_t **res_k, uint32_t **res_v);
+int sort_pairs_u64(const uint64_t *src, uint64_t *ka, uint64_t *kb, uint32_t *va, uint32_t *vb, int64_t n,
+                   int end_bit, bool iota_vals, uint64_t **res_k, uint32_t **res_v);
 
 // built in slc_transpose.cu
 template <class T>

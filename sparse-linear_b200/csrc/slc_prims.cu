@@ -6,12 +6,15 @@
 //   exclusive scan   over that whole table: entry (d, t) becomes the first output position of the
 //                    keys of tile t with digit d (all smaller digits, then earlier tiles, come first)
 //   k_radix_scatter  re-reads the tile; a warp owns a contiguous run of keys and ranks them in index
-//                    order with __match_any_sync + per-warp digit counters in shared memory, so
-//                    equal digits keep their input order (stable); the tile is reordered by digit
-//                    in shared memory and then streamed to base[d] + position-in-run
+//                    order (eight ballots find the lanes with the same digit) against per-warp digit
+//                    counters in shared memory, so equal digits keep their input order (stable); the
+//                    tile is reordered by digit in shared memory and then streamed to
+//                    base[d] + position-in-run
 // Only the bits the caller says are significant are sorted (a row index of a 2M-row matrix needs
 // 21 bits = 3 passes, not 4).  All traffic is coalesced on the read side; on the write side a tile
-// of 8192 keys lands in at most 256 contiguous runs.
+// of 4096 keys lands in at most 256 contiguous runs.  The first pass can read its keys from a
+// caller's array that must stay intact (a matrix's row indices) and take the positions 0..n-1 as
+// values without reading them; the result is handed back by pointer, never copied.
 #include "slc_common.cuh"
 
 namespace slc {
@@ -115,26 +118,47 @@ int exclusive_scan_i64(const int64_t *in, int64_t *out, int64_t n) {
 
 // ---- radix sort -------------------------------------------------------------------------------------
 
-constexpr int RS_THREADS = 512;
+constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 8192 keys per block
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 keys per block
 constexpr int RS_BINS = 256;
 
+__device__ __forceinline__ uint32_t ld_once(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint64_t ld_once(const uint64_t *p) {
+  uint64_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(v) : "l"(p));
+  return v;
+}
+
+// All RS_ITEMS keys of a thread are loaded before the first shared-memory atomic (ncu, round 1: with
+// the load inside the loop every atomic waited for its own load, 16 exposed latencies per thread).
 template <class K>
 __global__ void __launch_bounds__(RS_THREADS)
 k_radix_hist(const K *__restrict__ keys, int64_t n, int shift, int64_t ntiles, int32_t *__restrict__ hist) {
   __shared__ int32_t cnt[RS_BINS];
-  if (threadIdx.x < RS_BINS) cnt[threadIdx.x] = 0;
-  __syncthreads();
+  cnt[threadIdx.x] = 0;  // RS_THREADS == RS_BINS
   const int64_t base = (int64_t)blockIdx.x * RS_TILE;
+  K key[RS_ITEMS];
+  if (base + RS_TILE <= n) {
 #pragma unroll
-  for (int it = 0; it < RS_ITEMS; ++it) {
-    const int64_t i = base + (int64_t)it * RS_THREADS + threadIdx.x;
-    if (i < n) atomicAdd(&cnt[(int)((keys[i] >> shift) & (RS_BINS - 1))], 1);
+    for (int it = 0; it < RS_ITEMS; ++it) key[it] = ld_once(keys + base + it * RS_THREADS + threadIdx.x);
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < RS_ITEMS; ++it) atomicAdd(&cnt[(int)((key[it] >> shift) & (RS_BINS - 1))], 1);
+  } else {
+    __syncthreads();
+    for (int it = 0; it < RS_ITEMS; ++it) {
+      const int64_t i = base + (int64_t)it * RS_THREADS + threadIdx.x;
+      if (i < n) atomicAdd(&cnt[(int)((keys[i] >> shift) & (RS_BINS - 1))], 1);
+    }
   }
   __syncthreads();
-  if (threadIdx.x < RS_BINS) hist[(int64_t)threadIdx.x * ntiles + blockIdx.x] = cnt[threadIdx.x];
+  hist[(int64_t)threadIdx.x * ntiles + blockIdx.x] = cnt[threadIdx.x];
 }
 
 // Shared memory of k_radix_scatter: the tile's keys and values in digit order, the per-warp digit
@@ -142,104 +166,144 @@ k_radix_hist(const K *__restrict__ keys, int64_t n, int shift, int64_t ntiles, i
 template <class K>
 constexpr size_t radix_scatter_smem() {
   return (size_t)RS_TILE * (sizeof(K) + sizeof(uint32_t)) + (size_t)(RS_WARPS + 2) * RS_BINS * sizeof(int32_t) +
-         8 * sizeof(int32_t);
+         RS_WARPS * sizeof(int32_t);
+}
+
+// lanes of the warp whose digit equals this lane's.  __match_any_sync does this in one instruction,
+// but its cost grows with the number of distinct values in the warp (ncu, round 1: 64 % of the
+// scatter kernel's stall samples sat behind MATCH with ~30 distinct digits per warp); eight ballots
+// cost the same whatever the data.
+__device__ __forceinline__ unsigned digit_peers(int d) {
+  unsigned peers = 0xffffffffu;
+#pragma unroll
+  for (int b = 0; b < 8; ++b) {
+    const bool bit = (d >> b) & 1;
+    const unsigned m = __ballot_sync(0xffffffffu, bit);
+    peers &= bit ? m : ~m;
+  }
+  return peers;
 }
 
 // Pass 1 of 2 inside the tile: every key gets its position in the tile's digit order -- keys of a
-// smaller digit first, then earlier warps, then index order inside the warp (__match_any_sync rank),
-// which keeps the sort stable -- and is parked there in shared memory.  Pass 2 streams the parked
-// tile out: neighbouring threads hold neighbouring keys of the same digit, whose global positions
-// are consecutive, so the writes are coalesced runs instead of one sector per key.
-template <class K>
-__global__ void __launch_bounds__(RS_THREADS)
+// smaller digit first, then earlier warps, then index order inside the warp, which keeps the sort
+// stable -- and is parked there in shared memory.  Pass 2 streams the parked tile out: neighbouring
+// threads hold neighbouring keys of the same digit, whose global positions are consecutive, so the
+// writes are coalesced runs instead of one sector per key.  IOTA: the values are the input positions
+// themselves (first pass of a sort that carries positions) and are not read.
+template <class K, bool IOTA>
+__global__ void __launch_bounds__(RS_THREADS, 3)
 k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals_in, K *__restrict__ keys_out,
                 uint32_t *__restrict__ vals_out, int64_t n, int shift, int64_t ntiles,
-                const int32_t *__restrict__ hist_scanned) {
+                const int32_t *__restrict__ hist_scanned, uint32_t zmask) {
   extern __shared__ __align__(16) unsigned char rs_smem[];
   K *skeys = reinterpret_cast<K *>(rs_smem);                         // [RS_TILE]
   uint32_t *svals = reinterpret_cast<uint32_t *>(skeys + RS_TILE);   // [RS_TILE]
   int32_t *wcnt = reinterpret_cast<int32_t *>(svals + RS_TILE);      // [RS_WARPS][RS_BINS]
   int32_t *local_base = wcnt + RS_WARPS * RS_BINS;                   // [RS_BINS] start of digit d in the tile
   int32_t *gshift = local_base + RS_BINS;                            // [RS_BINS] global start - local start
-  int32_t *wsum = gshift + RS_BINS;                                  // [8]
+  int32_t *wsum = gshift + RS_BINS;                                  // [RS_WARPS]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  for (int i = tid; i < RS_WARPS * RS_BINS; i += RS_THREADS) wcnt[i] = 0;
-  int32_t tile_base = 0;
-  if (tid < RS_BINS) tile_base = hist_scanned[(int64_t)tid * ntiles + blockIdx.x];
-  __syncthreads();
+#pragma unroll
+  for (int w = 0; w < RS_WARPS; ++w) wcnt[w * RS_BINS + tid] = 0;
+  const int32_t tile_base = hist_scanned[(int64_t)tid * ntiles + blockIdx.x];  // digit `tid`
 
   // warp `warp` owns keys [cb, cb + 32*RS_ITEMS), taken 32 at a time in index order
   const int64_t tb = (int64_t)blockIdx.x * RS_TILE;
   const int64_t cb = tb + (int64_t)warp * (32 * RS_ITEMS);
+  const bool full_tile = tb + RS_TILE <= n;
   const unsigned lt = (1u << lane) - 1u;
   K key[RS_ITEMS];
-  uint32_t val[RS_ITEMS];
   int32_t rank[RS_ITEMS];
+  if (full_tile) {
 #pragma unroll
-  for (int it = 0; it < RS_ITEMS; ++it) {
-    const int64_t i = cb + it * 32 + lane;
-    const bool valid = i < n;
-    key[it] = valid ? keys_in[i] : (K)0;
-    val[it] = valid ? vals_in[i] : 0u;
+    for (int it = 0; it < RS_ITEMS; ++it) key[it] = ld_once(keys_in + cb + it * 32 + lane);
+    // the values are only needed after the ranking: start them towards L2 now (one line per lane)
+    if (!IOTA && lane < RS_ITEMS) asm volatile("prefetch.global.L2 [%0];" ::"l"(vals_in + cb + lane * 32));
+  } else {
+#pragma unroll
+    for (int it = 0; it < RS_ITEMS; ++it) {
+      const int64_t i = cb + it * 32 + lane;
+      key[it] = i < n ? keys_in[i] : (K)0;
+    }
   }
+  __syncthreads();
   int32_t *mycnt = wcnt + warp * RS_BINS;
 #pragma unroll
   for (int it = 0; it < RS_ITEMS; ++it) {
-    const bool valid = cb + it * 32 + lane < n;
+    const bool valid = full_tile || cb + it * 32 + lane < n;
     const int d = (int)((key[it] >> shift) & (RS_BINS - 1));
-    const unsigned peers = __match_any_sync(0xffffffffu, valid ? d : RS_BINS);
+    unsigned peers = digit_peers(d);
+    if (!full_tile) peers &= __ballot_sync(0xffffffffu, valid);
     rank[it] = 0;
-    if (valid) {
-      const int leader = __ffs(peers) - 1;
-      int32_t b = 0;
-      if (lane == leader) {
-        b = mycnt[d];
-        mycnt[d] = b + __popc(peers);
-      }
-      b = __shfl_sync(peers, b, leader);
-      rank[it] = b + __popc(peers & lt);
+    int32_t b = 0;
+    const int leader = __ffs(peers) - 1;
+    if (valid && lane == leader) {
+      b = mycnt[d];
+      mycnt[d] = b + __popc(peers);
     }
+    b = __shfl_sync(0xffffffffu, b, leader & 31);
+    rank[it] = b + __popc(peers & lt);
     __syncwarp();
   }
   __syncthreads();
-  int32_t total = 0, incl = 0;
-  if (tid < RS_BINS) {  // counts per warp -> offset of each warp inside the tile's run of digit `tid`
+  // counts per warp -> offset of each warp inside the tile's run of digit `tid`
+  int32_t total = 0;
 #pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w) {
-      const int32_t c = wcnt[w * RS_BINS + tid];
-      wcnt[w * RS_BINS + tid] = total;
-      total += c;
-    }
-    incl = total;  // exclusive scan of the digit totals over the 256 threads
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += t;
-    }
-    if (lane == 31) wsum[warp] = incl;
+  for (int w = 0; w < RS_WARPS; ++w) {
+    const int32_t c = wcnt[w * RS_BINS + tid];
+    wcnt[w * RS_BINS + tid] = total;
+    total += c;
   }
+  int32_t incl = total;  // exclusive scan of the digit totals over the 256 threads
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) wsum[warp] = incl;
   __syncthreads();
-  if (tid < RS_BINS) {
+  {
     int32_t before = 0;
 #pragma unroll
-    for (int w = 0; w < RS_BINS / 32; ++w)
+    for (int w = 0; w < RS_WARPS; ++w)
       if (w < warp) before += wsum[w];
     const int32_t lb = before + incl - total;
     local_base[tid] = lb;
     gshift[tid] = tile_base - lb;
   }
   __syncthreads();
+  if (full_tile) {
+    uint32_t val[RS_ITEMS];
+    if (!IOTA) {
 #pragma unroll
-  for (int it = 0; it < RS_ITEMS; ++it) {
-    if (cb + it * 32 + lane < n) {
+      for (int it = 0; it < RS_ITEMS; ++it) val[it] = ld_once(vals_in + cb + it * 32 + lane);
+      uint32_t r = 0;  // every load is issued before the first value is parked (see probe/tie)
+#pragma unroll
+      for (int it = 0; it < RS_ITEMS; ++it) r |= val[it];
+      val[0] ^= r & zmask;
+    }
+#pragma unroll
+    for (int it = 0; it < RS_ITEMS; ++it) {
       const int d = (int)((key[it] >> shift) & (RS_BINS - 1));
       const int32_t lp = local_base[d] + mycnt[d] + rank[it];
       skeys[lp] = key[it];
-      svals[lp] = val[it];
+      svals[lp] = IOTA ? (uint32_t)(cb + it * 32 + lane) : val[it];
+    }
+  } else {
+#pragma unroll
+    for (int it = 0; it < RS_ITEMS; ++it) {
+      const int64_t i = cb + it * 32 + lane;
+      if (i < n) {
+        const int d = (int)((key[it] >> shift) & (RS_BINS - 1));
+        const int32_t lp = local_base[d] + mycnt[d] + rank[it];
+        skeys[lp] = key[it];
+        svals[lp] = IOTA ? (uint32_t)i : vals_in[i];
+      }
     }
   }
   __syncthreads();
   const int32_t count = (int32_t)min((int64_t)RS_TILE, n - tb);
+#pragma unroll 4
   for (int32_t i = tid; i < count; i += RS_THREADS) {
     const K kk = skeys[i];
     const int d = (int)((kk >> shift) & (RS_BINS - 1));
@@ -249,9 +313,15 @@ k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals
   }
 }
 
+// Stable sort of (key, value) pairs on key bits [0, end_bit).  (ka, va) and (kb, vb) are ping-pong
+// scratch.  The first pass reads its keys from `src` when given (which is left untouched) and from ka
+// otherwise; its values are va, or the positions 0..n-1 when iota_vals.  *res_k / *res_v say which
+// scratch buffers hold the sorted pairs.
 template <class K>
-static int sort_pairs_impl(K *keys_in, K *keys_out, uint32_t *vals_in, uint32_t *vals_out, int64_t n,
-                           int end_bit) {
+static int sort_pairs_impl(const K *src, K *ka, K *kb, uint32_t *va, uint32_t *vb, int64_t n, int end_bit,
+                           bool iota_vals, K **res_k, uint32_t **res_v) {
+  *res_k = ka;
+  *res_v = va;
   if (n <= 0) return SLC_OK;
   if (n > 0x7fffffffLL) return fail(SLC_ERR_RANGE, "radix sort: more than 2^31-1 items");
   cudaStream_t s = cur_stream();
@@ -262,37 +332,48 @@ static int sort_pairs_impl(K *keys_in, K *keys_out, uint32_t *vals_in, uint32_t 
   const int64_t ntiles = ceil_div(n, RS_TILE);
   DevBuf<int32_t> hist;
   SLC_TRY(hist.alloc((size_t)ntiles * RS_BINS));
-  SLC_CUDA(cudaFuncSetAttribute(k_radix_scatter<K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)radix_scatter_smem<K>()));
-  K *kin = keys_in, *kout = keys_out;
-  uint32_t *vin = vals_in, *vout = vals_out;
+  static bool attr_set = false;  // per instantiation (K)
+  if (!attr_set) {
+    SLC_CUDA(cudaFuncSetAttribute(k_radix_scatter<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)radix_scatter_smem<K>()));
+    SLC_CUDA(cudaFuncSetAttribute(k_radix_scatter<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)radix_scatter_smem<K>()));
+    attr_set = true;
+  }
+  const K *kin = src ? src : ka;
+  const uint32_t *vin = va;
+  K *kout = src ? ka : kb;
+  uint32_t *vout = src ? va : vb;
+  if (src && !iota_vals) return fail(SLC_ERR_INVALID, "radix sort: a separate key source needs positional values");
   for (int p = 0; p < passes; ++p) {
     const int shift = p * 8;
     k_radix_hist<K><<<(unsigned)ntiles, RS_THREADS, 0, s>>>(kin, n, shift, ntiles, hist.p);
     SLC_LAUNCHED();
     SLC_TRY(exclusive_scan_i32(hist.p, hist.p, ntiles * RS_BINS));
-    k_radix_scatter<K><<<(unsigned)ntiles, RS_THREADS, radix_scatter_smem<K>(), s>>>(kin, vin, kout, vout, n, shift,
-                                                                                    ntiles, hist.p);
+    if (p == 0 && iota_vals)
+      k_radix_scatter<K, true><<<(unsigned)ntiles, RS_THREADS, radix_scatter_smem<K>(), s>>>(kin, nullptr, kout, vout, n,
+                                                                                           shift, ntiles, hist.p, 0u);
+    else
+      k_radix_scatter<K, false><<<(unsigned)ntiles, RS_THREADS, radix_scatter_smem<K>(), s>>>(kin, vin, kout, vout, n,
+                                                                                            shift, ntiles, hist.p, 0u);
     SLC_LAUNCHED();
-    K *tk = kin; kin = kout; kout = tk;
-    uint32_t *tv = vin; vin = vout; vout = tv;
-  }
-  // after the swap the sorted data is in (kin, vin); the caller wants it in (keys_out, vals_out)
-  if (kin != keys_out) {
-    SLC_CUDA(cudaMemcpyAsync(keys_out, kin, (size_t)n * sizeof(K), cudaMemcpyDeviceToDevice, s));
-    SLC_CUDA(cudaMemcpyAsync(vals_out, vin, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+    *res_k = kout;
+    *res_v = vout;
+    kin = kout;
+    vin = vout;
+    kout = (kout == ka) ? kb : ka;
+    vout = (vout == va) ? vb : va;
   }
   return SLC_OK;
 }
 
-// Both sorts overwrite their input buffers (they are the ping-pong scratch).
-int sort_pairs_u32(uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in, uint32_t *vals_out,
-                   int64_t n, int end_bit) {
-  return sort_pairs_impl<uint32_t>(keys_in, keys_out, vals_in, vals_out, n, end_bit);
+int sort_pairs_u32(const uint32_t *src, uint32_t *ka, uint32_t *kb, uint32_t *va, uint32_t *vb, int64_t n,
+                   int end_bit, bool iota_vals, uint32_t **res_k, uint32_t **res_v) {
+  return sort_pairs_impl<uint32_t>(src, ka, kb, va, vb, n, end_bit, iota_vals, res_k, res_v);
 }
-int sort_pairs_u64(uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in, uint32_t *vals_out,
-                   int64_t n, int end_bit) {
-  return sort_pairs_impl<uint64_t>(keys_in, keys_out, vals_in, vals_out, n, end_bit);
+int sort_pairs_u64(const uint64_t *src, uint64_t *ka, uint64_t *kb, uint32_t *va, uint32_t *vb, int64_t n,
+                   int end_bit, bool iota_vals, uint64_t **res_k, uint32_t **res_v) {
+  return sort_pairs_impl<uint64_t>(src, ka, kb, va, vb, n, end_bit, iota_vals, res_k, res_v);
 }
 
 }  // namespace slc

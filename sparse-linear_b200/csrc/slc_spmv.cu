@@ -250,7 +250,7 @@ static int ensure_plan(slc_matrix *m) {
     kind = regular ? SPMV_SELL : SPMV_CSR_BALANCED;
   }
   if (kind == SPMV_SELL) SLC_TRY(fill_sell<T>(m));
-  if (kind == SPMV_CSR_BALANCED) SLC_TRY(build_balanced(m));
+  if (kind == SPMV_CSR_BALANCED || kind == SPMV_CSR_BALANCED_SMEM) SLC_TRY(build_balanced(m));
   m->spmv_active = kind;
   return SLC_OK;
 }
@@ -524,6 +524,192 @@ __global__ void k_spmv_bal_fixup(int32_t nchunks, int64_t nnz, const int32_t *__
   y[r] = ACC ? Num<T>::add(total, y[r]) : total;
 }
 
+// ---- CSR, nnz-balanced, merge-style: registers and shuffles instead of a shared-memory round trip ----
+// Same chunks, same part_head / part_tail / fix-up contract as k_spmv_bal.  Thread t of a block owns
+// the 8 CONSECUTIVE nonzeros [8t, 8t+8) of the chunk: two 128-bit index loads and four (eight for
+// Complex) 128-bit value loads, all issued together with the 8 gathers of x.  It finds the row of
+// its first nonzero with one binary search over the chunk's own slice of rowptr, then walks: rows
+// that begin and end inside its 8 nonzeros are written straight to y; the sum up to its first row
+// end (`head`) and the sum after its last one (`tail`) are stitched to the neighbouring threads with
+// a segmented scan over the block (shuffles inside a warp, 8 partials across warps).  ncu, round 1,
+// on k_spmv_bal: the thread-per-row reduction read the staged products with ~16-way bank conflicts
+// (row starts 16 doubles apart on average) and cost as many cycles per chunk as the chunk's whole
+// HBM budget, and the gathers were issued two at a time.
+// Order of additions inside a row: left to right inside a thread, scan tree across threads
+// (deterministic; within the 1e-12 tolerance, like k_spmv_bal).
+constexpr int MG_ITEMS = BAL_ITEMS;  // 8 nonzeros per thread, BAL_THREADS threads: the same BAL_CHUNK
+
+template <class T>
+struct Carry {
+  T v;
+  int f;  // 1: a row ended inside, v is what follows the last row end; 0: v is the whole range
+};
+template <class T>
+__device__ __forceinline__ Carry<T> carry_join(const Carry<T> &a, const Carry<T> &b) {  // a, then b
+  Carry<T> r;
+  r.f = a.f | b.f;
+  r.v = b.f ? b.v : Num<T>::add(a.v, b.v);
+  return r;
+}
+__device__ __forceinline__ double shfl_up_t(double v, int o) { return __shfl_up_sync(0xffffffffu, v, o); }
+__device__ __forceinline__ double2 shfl_up_t(double2 v, int o) {
+  return double2{__shfl_up_sync(0xffffffffu, v.x, o), __shfl_up_sync(0xffffffffu, v.y, o)};
+}
+__device__ __forceinline__ void ld_stream8(const int32_t *p, int32_t (&c)[8], uint64_t pol) {
+  const int4 a = ld_stream(reinterpret_cast<const int4 *>(p), pol);
+  const int4 b = ld_stream(reinterpret_cast<const int4 *>(p) + 1, pol);
+  c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w;
+  c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
+}
+__device__ __forceinline__ void ld_stream8(const double *p, double (&a)[8], uint64_t pol) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const double2 v = ld_stream(reinterpret_cast<const double2 *>(p) + i, pol);
+    a[2 * i] = v.x;
+    a[2 * i + 1] = v.y;
+  }
+}
+__device__ __forceinline__ void ld_stream8(const double2 *p, double2 (&a)[8], uint64_t pol) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) a[i] = ld_stream(p + i, pol);
+}
+
+template <class T, bool ACC, class XA>
+__global__ void __launch_bounds__(BAL_THREADS)
+k_spmv_merge(int32_t nrows, int64_t nnz, uint32_t zmask, const int32_t *__restrict__ rowptr,
+             const int32_t *__restrict__ colidx, const T *__restrict__ vals,
+             const int32_t *__restrict__ first_owned, const XA xa, T *__restrict__ y,
+             T *__restrict__ part_head, T *__restrict__ part_tail) {
+  __shared__ Carry<T> warp_carry[BAL_THREADS / 32];
+  const int32_t b = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t start = (int64_t)b * BAL_CHUNK;
+  const int64_t end = min(nnz, start + BAL_CHUNK);
+  const uint64_t pol_s = policy_evict_first();
+  const uint64_t pol_x = policy_evict_last();
+  const int32_t fo = first_owned[b], fo_next = first_owned[b + 1];
+
+  const int64_t p0 = start + (int64_t)tid * MG_ITEMS;
+  const int32_t cnt = (int32_t)max((int64_t)0, min((int64_t)MG_ITEMS, end - p0));
+  int32_t c[MG_ITEMS];
+  T a[MG_ITEMS], xv[MG_ITEMS];
+  if (cnt == MG_ITEMS) {
+    ld_stream8(colidx + p0, c, pol_s);
+    ld_stream8(vals + p0, a, pol_s);
+#pragma unroll
+    for (int i = 0; i < MG_ITEMS; ++i) xv[i] = xa(c[i], pol_x);
+    uint32_t r = 0;  // the 8 gathers are issued together (see probe/tie)
+#pragma unroll
+    for (int i = 0; i < MG_ITEMS; ++i) r |= probe(xv[i]);
+    tie(xv[0], r & zmask);
+  } else {
+#pragma unroll
+    for (int i = 0; i < MG_ITEMS; ++i) {
+      const bool ok = i < cnt;
+      c[i] = ok ? colidx[p0 + i] : 0;
+      a[i] = ok ? vals[p0 + i] : Num<T>::zero();
+      xv[i] = ok ? xa(c[i], pol_x) : Num<T>::zero();
+    }
+  }
+
+  // rows of this chunk that hold no entry at all: the product is 0 (mulV) / leaves y alone (axpy)
+  if (!ACC)
+    for (int32_t r = fo + tid; r < fo_next; r += BAL_THREADS)
+      if (rowptr[r + 1] == rowptr[r]) y[r] = Num<T>::zero();
+
+  Carry<T> mine;
+  mine.v = Num<T>::zero();
+  mine.f = 0;
+  T head = Num<T>::zero();
+  int32_t head_row = -1;
+  if (cnt > 0) {
+    // row of p0: the last row that starts at or before p0 (it is not empty, it contains p0); it is
+    // fo - 1 when no row of this chunk starts that early
+    int32_t lo = fo, hi = fo_next;  // first q in [fo, fo_next] with rowptr[q] > p0
+    while (lo < hi) {
+      const int32_t mid = lo + ((hi - lo) >> 1);
+      if ((int64_t)__ldg(rowptr + mid) <= p0) lo = mid + 1;
+      else hi = mid;
+    }
+    int32_t r = lo - 1;
+    int64_t row_end = __ldg(rowptr + r + 1);
+    T sum = Num<T>::zero();
+#pragma unroll
+    for (int i = 0; i < MG_ITEMS; ++i) {
+      if (i < cnt) {
+        const int64_t p = p0 + i;
+        if (p >= row_end) {  // row r ended at p: hand its sum over, move to the row that holds p
+          if (!mine.f) {
+            head = sum;
+            head_row = r;
+            mine.f = 1;
+          } else {
+            y[r] = ACC ? Num<T>::add(sum, y[r]) : sum;
+          }
+          sum = Num<T>::zero();
+          do {
+            ++r;
+            row_end = __ldg(rowptr + r + 1);
+          } while (row_end <= p);
+        }
+        sum = Num<T>::add(sum, Num<T>::mul(a[i], xv[i]));
+      }
+    }
+    if (row_end == p0 + cnt) {  // the open row ends exactly where this thread's range does
+      if (!mine.f) {
+        head = sum;
+        head_row = r;
+        mine.f = 1;
+      } else {
+        y[r] = ACC ? Num<T>::add(sum, y[r]) : sum;
+      }
+      sum = Num<T>::zero();
+    }
+    mine.v = sum;
+  }
+
+  // inclusive segmented scan of the carries over the block
+  Carry<T> inc = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    Carry<T> up;
+    up.v = shfl_up_t(inc.v, o);
+    up.f = __shfl_up_sync(0xffffffffu, inc.f, o);
+    if (lane >= o) inc = carry_join(up, inc);
+  }
+  if (lane == 31) warp_carry[warp] = inc;
+  Carry<T> prev;  // exclusive inside the warp
+  prev.v = shfl_up_t(inc.v, 1);
+  prev.f = __shfl_up_sync(0xffffffffu, inc.f, 1);
+  if (lane == 0) {
+    prev.v = Num<T>::zero();
+    prev.f = 0;
+  }
+  __syncthreads();
+  Carry<T> before;  // everything in the warps below this one
+  before.v = Num<T>::zero();
+  before.f = 0;
+#pragma unroll
+  for (int w = 0; w < BAL_THREADS / 32; ++w)
+    if (w < warp) before = carry_join(before, warp_carry[w]);
+  const Carry<T> in = carry_join(before, prev);  // what flows into this thread
+
+  if (mine.f) {  // the row that ends first in this thread: earlier threads' share + head
+    const T total = Num<T>::add(in.v, head);
+    if (head_row < fo) part_head[b] = total;  // it began in an earlier chunk: the fix-up kernel adds it
+    else y[head_row] = ACC ? Num<T>::add(total, y[head_row]) : total;
+  }
+  if (tid == BAL_THREADS - 1) {
+    const Carry<T> all = carry_join(in, mine);
+    // all.f: the row still open at the end of the chunk began in it.  Otherwise no row ends in this
+    // chunk and all of it is one piece of a long row -- its first piece if that row starts exactly at
+    // the chunk start (then the chunk owns it and the fix-up kernel looks for it in part_tail).
+    const bool owns_open_row = all.f || (fo < fo_next && (int64_t)rowptr[fo] == start);
+    if (owns_open_row) part_tail[b] = all.v;
+    else part_head[b] = all.v;
+  }
+}
+
 template <class T, bool ACC>
 __global__ void k_fill_zero_or_keep(int64_t n, T *__restrict__ y) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -590,7 +776,8 @@ k_spmm_rows(int32_t nrows, int32_t ntiles, const int64_t *__restrict__ slice_ptr
 template <class T, int JT, int LMAX, bool FULL>
 __device__ __forceinline__ void spmm_short_columns(const int32_t (&c)[LMAX], const T (&a)[LMAX], int32_t len,
                                                    const T *__restrict__ X, int64_t ldx, T *__restrict__ Yrow,
-                                                   int64_t ldy, int32_t jbeg, int32_t jend, uint64_t pol_x) {
+                                                   int64_t ldy, int32_t jbeg, int32_t jend, uint64_t pol_x,
+                                                   uint32_t zmask) {
   int32_t j0 = jbeg;
   for (; j0 + JT <= jend; j0 += JT) {
     const T *xb = X + (int64_t)j0 * ldx;
@@ -600,6 +787,16 @@ __device__ __forceinline__ void spmm_short_columns(const int32_t (&c)[LMAX], con
 #pragma unroll
       for (int j = 0; j < JT; ++j)
         xv[u][j] = (FULL || u < len) ? ld_gather(xb + (int64_t)j * ldx + c[u], pol_x) : Num<T>::zero();
+    {  // all LMAX*JT gathers are issued before the first product (see probe/tie)
+      uint32_t r = 0;
+#pragma unroll
+      for (int u = 0; u < LMAX; ++u)
+#pragma unroll
+        for (int j = 0; j < JT; ++j) r |= probe(xv[u][j]);
+      r &= zmask;
+#pragma unroll
+      for (int j = 0; j < JT; ++j) tie(xv[0][j], r);
+    }
 #pragma unroll
     for (int j = 0; j < JT; ++j) {
       T acc = Num<T>::zero();
@@ -627,7 +824,7 @@ __device__ __forceinline__ void spmm_short_columns(const int32_t (&c)[LMAX], con
 // diagonal, so it is fetched from L2 once per block (L1 hit for the others) instead of once per warp.
 template <class T, int JT, int LMAX, bool SELL>
 __global__ void __launch_bounds__(256)
-k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, int32_t stride32,
+k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, int32_t stride32, uint32_t zmask,
              const int64_t *__restrict__ slice_ptr,
              const int32_t *__restrict__ rowlen, const int32_t *__restrict__ rowptr,
              const int32_t *__restrict__ colidx, const T *__restrict__ vals, const T *__restrict__ X,
@@ -671,9 +868,98 @@ k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, int32_t stride32,
   const int32_t jbeg = grp * jgroup;
   const int32_t jend = min(k, jbeg + jgroup);
   if (full)
-    spmm_short_columns<T, JT, LMAX, true>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x);
+    spmm_short_columns<T, JT, LMAX, true>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x, zmask);
   else
-    spmm_short_columns<T, JT, LMAX, false>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x);
+    spmm_short_columns<T, JT, LMAX, false>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x, zmask);
+}
+
+// Longer rows (SELL plan, e.g. the 27-point stencil): a block owns blockDim.x consecutive rows and ALL
+// k columns.  Each thread first copies its own row's (index, value) pairs from the SELL stream into
+// shared memory (laid out [entry][thread]: conflict-free, thread-private, so no barrier), which makes
+// this the only pass over A in HBM; entries past `kcap` (what fits in the block's shared memory) are
+// re-read through L1 for every column tile.  The block then walks the columns JT at a time; inside
+// a tile KU entries x JT columns = KU*JT gathers are issued together (probe/tie) and added in the
+// reference's order, entry after entry, for every column.  ncu, round 1, on the per-tile-grid kernel
+// this replaces (k_spmm_rows): A was streamed 16 times (11.4 GB DRAM reads for 6.7 GB compulsory)
+// and half of the stall samples sat between an index load and the gather that needs it.
+template <class T, int JT, int KU>
+__global__ void __launch_bounds__(256)
+k_spmm_panel(int32_t nrows, int32_t kcap, uint32_t zmask, const int64_t *__restrict__ slice_ptr,
+             const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
+             const T *__restrict__ vals, const T *__restrict__ X, int64_t ldx, T *__restrict__ Y,
+             int64_t ldy, int32_t k) {
+  extern __shared__ __align__(16) unsigned char panel_smem[];
+  const int32_t nt = blockDim.x, tid = threadIdx.x;
+  T *s_a = reinterpret_cast<T *>(panel_smem) + tid;                                       // [kcap][nt]
+  int32_t *s_c = reinterpret_cast<int32_t *>(panel_smem + (size_t)kcap * nt * sizeof(T)) + tid;  // [kcap][nt]
+  const int32_t row = blockIdx.x * nt + tid;
+  if (row >= nrows) return;
+  const uint64_t pol_s = policy_evict_first();
+  const uint64_t pol_x = policy_evict_last();
+  const int64_t base = __ldg(slice_ptr + (row >> 5)) + (tid & 31);
+  const int32_t len = __ldg(rowlen + row);
+  const int32_t nst = min(len, kcap);
+  const int32_t *ci = colidx + base;
+  const T *va = vals + base;
+  for (int32_t e = 0; e < nst; ++e) {
+    s_c[e * nt] = ld_stream(ci + (int64_t)e * SELL_C, pol_s);
+    s_a[e * nt] = ld_stream(va + (int64_t)e * SELL_C, pol_s);
+  }
+  T *Yrow = Y + row;
+  for (int32_t j0 = 0; j0 < k; j0 += JT) {
+    const T *xb = X + (int64_t)j0 * ldx;
+    T acc[JT];
+#pragma unroll
+    for (int j = 0; j < JT; ++j) acc[j] = Num<T>::zero();
+    int32_t e = 0;
+    if (j0 + JT <= k) {  // full column tile: batches of KU staged entries, no predicates
+      for (; e + KU <= nst; e += KU) {
+        int32_t c[KU];
+        T a[KU], xv[KU][JT];
+#pragma unroll
+        for (int u = 0; u < KU; ++u) {
+          c[u] = s_c[(e + u) * nt];
+          a[u] = s_a[(e + u) * nt];
+        }
+#pragma unroll
+        for (int u = 0; u < KU; ++u)
+#pragma unroll
+          for (int j = 0; j < JT; ++j) xv[u][j] = ld_gather(xb + (int64_t)j * ldx + c[u], pol_x);
+        uint32_t r = 0;
+#pragma unroll
+        for (int u = 0; u < KU; ++u)
+#pragma unroll
+          for (int j = 0; j < JT; ++j) r |= probe(xv[u][j]);
+        r &= zmask;
+#pragma unroll
+        for (int j = 0; j < JT; ++j) tie(xv[0][j], r);
+#pragma unroll
+        for (int u = 0; u < KU; ++u)
+#pragma unroll
+          for (int j = 0; j < JT; ++j) acc[j] = Num<T>::add(Num<T>::mul(a[u], xv[u][j]), acc[j]);
+      }
+    }
+    for (; e < len; ++e) {  // leftovers: one entry at a time, any tile width
+      int32_t c;
+      T a;
+      if (e < nst) {
+        c = s_c[e * nt];
+        a = s_a[e * nt];
+      } else {
+        c = __ldg(ci + (int64_t)e * SELL_C);
+        a = __ldg(va + (int64_t)e * SELL_C);
+      }
+      T xv[JT];
+#pragma unroll
+      for (int j = 0; j < JT; ++j)
+        xv[j] = (j0 + j < k) ? ld_gather(xb + (int64_t)j * ldx + c, pol_x) : Num<T>::zero();
+#pragma unroll
+      for (int j = 0; j < JT; ++j) acc[j] = Num<T>::add(Num<T>::mul(a, xv[j]), acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < JT; ++j)
+      if (j0 + j < k) st_stream(Yrow + (int64_t)(j0 + j) * ldy, acc[j]);
+  }
 }
 
 // =================================================================================================
@@ -730,8 +1016,13 @@ static int spmv_run(slc_matrix *m, const XA &xa, T *y) {
       DevBuf<T> ph, pt;
       SLC_TRY(ph.alloc((size_t)bp.nchunks));
       SLC_TRY(pt.alloc((size_t)bp.nchunks));
-      k_spmv_bal<T, ACC, XA><<<(unsigned)bp.nchunks, BAL_THREADS, 0, s>>>(
-          m->nrows, m->nnz, m->rowptr, m->colidx, (const T *)m->rvals, bp.chunk_row, xa, y, ph.p, pt.p);
+      static const int smem_env = env_int("SLC_BAL_SMEM", 0);  // 1: the shared-memory kernel for kind 3 too
+      if (m->spmv_active == SPMV_CSR_BALANCED_SMEM || smem_env)
+        k_spmv_bal<T, ACC, XA><<<(unsigned)bp.nchunks, BAL_THREADS, 0, s>>>(
+            m->nrows, m->nnz, m->rowptr, m->colidx, (const T *)m->rvals, bp.chunk_row, xa, y, ph.p, pt.p);
+      else
+        k_spmv_merge<T, ACC, XA><<<(unsigned)bp.nchunks, BAL_THREADS, 0, s>>>(
+            m->nrows, m->nnz, 0u, m->rowptr, m->colidx, (const T *)m->rvals, bp.chunk_row, xa, y, ph.p, pt.p);
       SLC_LAUNCHED();
       k_spmv_bal_fixup<T, ACC><<<(unsigned)ceil_div(bp.nchunks, 256), 256, 0, s>>>(
           bp.nchunks, m->nnz, m->rowptr, bp.chunk_row, ph.p, pt.p, y);
@@ -941,6 +1232,53 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   return SLC_OK;
 }
 
+// k_spmm_panel: block size, shared-memory budget and batch shape.  Defaults from the round-1 sweep on
+// the 27-point stencil; the environment variables exist for that sweep.
+template <class T, int JT, int KU>
+static int launch_panel_inst(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, int threads,
+                             int32_t kcap) {
+  const SellPlan &sp = m->sell;
+  const size_t smem = (size_t)kcap * threads * (sizeof(T) + sizeof(int32_t));
+  static size_t smem_set = 0;  // per instantiation
+  if (smem > smem_set) {
+    SLC_CUDA(cudaFuncSetAttribute(k_spmm_panel<T, JT, KU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set = smem;
+  }
+  const int64_t nb = ceil_div(m->nrows, threads);
+  k_spmm_panel<T, JT, KU><<<(unsigned)nb, threads, smem, cur_stream()>>>(
+      m->nrows, kcap, 0u, sp.slice_ptr, sp.rowlen, sp.colidx, (const T *)sp.vals, X, ldx, Y, ldy, k);
+  SLC_LAUNCHED();
+  return SLC_OK;
+}
+
+template <class T>
+static int launch_panel(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k) {
+  static const int threads_env = env_int("SLC_PANEL_THREADS", 0);
+  static const int smem_env = env_int("SLC_PANEL_SMEM_KB", 0);
+  static const int jt_env = env_int("SLC_PANEL_JT", 0);
+  static const int ku_env = env_int("SLC_PANEL_KU", 0);
+  int threads = threads_env ? threads_env : 128;
+  threads = std::max(32, std::min(256, threads / 32 * 32));
+  const int budget_kb = smem_env ? std::min(smem_env, 200) : (threads <= 128 ? 48 : 96);
+  const int32_t kcap =
+      std::max(1, std::min<int32_t>(m->max_rowlen, (int32_t)((size_t)budget_kb * 1024 / ((size_t)threads * (sizeof(T) + 4)))));
+  // batch depth: the one that leaves fewer single-entry leftovers on the longest row
+  int ku = ku_env ? ku_env : ((m->max_rowlen % 3) < (m->max_rowlen % 4) ? 3 : 4);
+  if (m->max_rowlen < 3) ku = 2;
+  const bool wide = jt_env ? jt_env >= 8 : sizeof(T) == 8;  // 8 columns per tile for Double, 4 for Complex
+#define SLC_PANEL(JT_, KU_) return launch_panel_inst<T, JT_, KU_>(m, X, ldx, Y, ldy, k, threads, kcap)
+  if (wide) {
+    if (ku <= 2) SLC_PANEL(8, 2);
+    if (ku == 3) SLC_PANEL(8, 3);
+    SLC_PANEL(8, 4);
+  } else {
+    if (ku <= 2) SLC_PANEL(4, 2);
+    if (ku == 3) SLC_PANEL(4, 3);
+    SLC_PANEL(4, 4);
+  }
+#undef SLC_PANEL
+}
+
 template <class T>
 static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k) {
   if (k == 0 || m->nrows == 0) return SLC_OK;
@@ -968,7 +1306,7 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
     constexpr int JTS = sizeof(T) == 16 ? 2 : 4;
 #define SLC_SHORT(L_, SELL_)                                                                         \
   k_spmm_short<T, JTS, L_, SELL_><<<(unsigned)nb, threads, 0, s>>>(                                   \
-      m->nrows, ngroups, jgroup, stride32, sp.slice_ptr, sp.rowlen, m->rowptr,                        \
+      m->nrows, ngroups, jgroup, stride32, 0u, sp.slice_ptr, sp.rowlen, m->rowptr,                     \
       SELL_ ? sp.colidx : m->colidx, SELL_ ? (const T *)sp.vals : (const T *)m->rvals, X, ldx, Y, ldy, k)
 #define SLC_SHORT_L(L_)                                                                              \
   case L_:                                                                                           \
@@ -992,6 +1330,8 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
     SLC_LAUNCHED();
     return SLC_OK;
   }
+  static const int panel_env = env_int("SLC_SPMM_PANEL", 1);
+  if (m->spmv_active == SPMV_SELL && panel_env) return launch_panel<T>(m, X, ldx, Y, ldy, k);
   constexpr int JT = sizeof(T) == 16 ? 4 : 8;
   const int32_t ntiles = (int32_t)ceil_div(k, JT);
   const int64_t nblocks = ceil_div(m->nrows, 128) * ntiles;
@@ -1068,7 +1408,7 @@ int slc_prepare(slc_matrix *m) {
 
 int slc_set_spmv_kernel(slc_matrix *m, int kind) {
   if (!m) return fail(SLC_ERR_INVALID, "slc_set_spmv_kernel: null handle");
-  if (kind < SPMV_AUTO || kind > SPMV_CSR_BALANCED)
+  if (kind < SPMV_AUTO || kind > SPMV_CSR_BALANCED_SMEM)
     return fail(SLC_ERR_INVALID, "slc_set_spmv_kernel: unknown kernel %d", kind);
   m->spmv_kind = kind;
   return SLC_OK;
@@ -1076,7 +1416,7 @@ int slc_set_spmv_kernel(slc_matrix *m, int kind) {
 
 int slc_plan_info(const slc_matrix *m, char *buf, int32_t buflen) {
   if (!m || !buf || buflen <= 0) return fail(SLC_ERR_INVALID, "slc_plan_info: bad argument");
-  const char *names[] = {"unplanned", "sell32", "csr-warp", "csr-balanced"};
+  const char *names[] = {"unplanned", "sell32", "csr-warp", "csr-balanced", "csr-balanced-smem"};
   const double pad = m->nnz ? 100.0 * (double)(m->sell.padded - m->nnz) / (double)m->nnz : 0.0;
   snprintf(buf, (size_t)buflen, "%s rows=%d cols=%d nnz=%lld max_rowlen=%d sell_padding=%.2f%% chunks=%d",
            names[m->spmv_active], m->nrows, m->ncols, (long long)m->nnz, m->max_rowlen, pad,

@@ -4,20 +4,13 @@
 // values moved bit for bit), computePtrs :282-291, ctrans :371-375, hermitian :377-379.
 //
 // Device formulation: a stable LSD radix sort of (row index -> source position) over only the
-// bits a row index needs; the output pointers fall out of the sorted keys (first position of
-// each key) with no histogram or atomics; one gather kernel then moves column ids and values.
+// bits a row index needs, reading the row indices in place; the output pointers fall out of the
+// sorted keys (first position of each key) with no histogram or atomics; the column of every
+// stored position is expanded once (k_expand_cols) and one gather kernel then moves column ids
+// and values.  (Round 1 searched colptr per entry inside the gather: 23 dependent loads each.)
 #include "slc_common.cuh"
 
 namespace slc {
-
-__global__ void k_iota_keys(int64_t n, const int32_t *__restrict__ idx, uint32_t *__restrict__ keys,
-                            uint32_t *__restrict__ pos) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) {
-    keys[i] = (uint32_t)idx[i];
-    pos[i] = (uint32_t)i;
-  }
-}
 
 // ptr[r] = first sorted position whose key is >= r, for r in [0, nkeys]; each entry is written by
 // exactly one thread (the one sitting on the boundary that passes r).
@@ -41,16 +34,64 @@ __device__ __forceinline__ int32_t owner_of(const int32_t *__restrict__ ptr, int
   return lo - 1;
 }
 
+// colid[p] = the column that owns stored position p.  A thread takes 8 consecutive positions: one
+// binary search for the first, then a walk along colptr (empty columns are stepped over).
+constexpr int EXPAND_ITEMS = 8;
+__global__ void k_expand_cols(int64_t nnz, int32_t ncols, const int32_t *__restrict__ colptr,
+                              uint32_t *__restrict__ colid) {
+  const int64_t p0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * EXPAND_ITEMS;
+  if (p0 >= nnz) return;
+  int32_t c = owner_of(colptr, ncols, (int32_t)p0);
+  int32_t next = __ldg(colptr + c + 1);
+  uint32_t out[EXPAND_ITEMS];
+#pragma unroll
+  for (int e = 0; e < EXPAND_ITEMS; ++e) {
+    const int64_t p = p0 + e;
+    while (p < nnz && next <= p) {  // p < nnz: some column owns p, so c + 1 stays below ncols
+      ++c;
+      next = __ldg(colptr + c + 1);
+    }
+    out[e] = (uint32_t)c;
+  }
+  if (p0 + EXPAND_ITEMS <= nnz) {
+    uint4 *dst = reinterpret_cast<uint4 *>(colid + p0);  // p0 is a multiple of 8: 32-byte aligned
+    dst[0] = make_uint4(out[0], out[1], out[2], out[3]);
+    dst[1] = make_uint4(out[4], out[5], out[6], out[7]);
+  } else {
+    for (int e = 0; p0 + e < nnz; ++e) colid[p0 + e] = out[e];
+  }
+}
+
+// out[i] = (column, value) of source position perm[i]; 4 entries per thread, all loads of one level
+// issued before the next level.
+constexpr int GATHER_ITEMS = 4;
 template <class T>
-__global__ void k_transpose_gather(int64_t nnz, int32_t ncols, const int32_t *__restrict__ colptr,
-                                   const T *__restrict__ vals, const uint32_t *__restrict__ perm,
-                                   bool conj, int32_t *__restrict__ out_idx, T *__restrict__ out_vals) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nnz) return;
-  const uint32_t p = perm[i];
-  out_idx[i] = owner_of(colptr, ncols, (int32_t)p);
-  T v = vals[p];
-  out_vals[i] = conj ? Num<T>::conj(v) : v;
+__global__ void __launch_bounds__(256)
+k_transpose_gather(int64_t nnz, const uint32_t *__restrict__ colid, const T *__restrict__ vals,
+                   const uint32_t *__restrict__ perm, bool conj, int32_t *__restrict__ out_idx,
+                   T *__restrict__ out_vals) {
+  const int64_t base = (int64_t)blockIdx.x * (256 * GATHER_ITEMS) + threadIdx.x;
+  uint32_t p[GATHER_ITEMS];
+#pragma unroll
+  for (int u = 0; u < GATHER_ITEMS; ++u) {
+    const int64_t i = base + u * 256;
+    p[u] = i < nnz ? perm[i] : 0u;
+  }
+  uint32_t c[GATHER_ITEMS];
+  T v[GATHER_ITEMS];
+#pragma unroll
+  for (int u = 0; u < GATHER_ITEMS; ++u) {
+    c[u] = __ldg(colid + p[u]);
+    v[u] = __ldg(vals + p[u]);
+  }
+#pragma unroll
+  for (int u = 0; u < GATHER_ITEMS; ++u) {
+    const int64_t i = base + u * 256;
+    if (i < nnz) {
+      out_idx[i] = (int32_t)c[u];
+      out_vals[i] = conj ? Num<T>::conj(v[u]) : v[u];
+    }
+  }
 }
 
 template <class T>
@@ -67,13 +108,17 @@ int transpose_csc(int32_t nrows, int32_t ncols, int64_t nnz, const int32_t *colp
   SLC_TRY(k1.alloc(nnz));
   SLC_TRY(p0.alloc(nnz));
   SLC_TRY(p1.alloc(nnz));
-  const unsigned nb = (unsigned)ceil_div(nnz, 256);
-  k_iota_keys<<<nb, 256, 0, s>>>(nnz, rowidx, k0.p, p0.p);
+  // keys = the row indices, read in place by the first pass; values = source positions
+  uint32_t *skey = nullptr, *sperm = nullptr;
+  SLC_TRY(sort_pairs_u32(reinterpret_cast<const uint32_t *>(rowidx), k0.p, k1.p, p0.p, p1.p, nnz,
+                         bits_for((uint32_t)nrows), true, &skey, &sperm));
+  k_ptrs_from_sorted<<<(unsigned)ceil_div(nnz + 1, 256), 256, 0, s>>>(nnz, nrows, skey, out_ptr);
   SLC_LAUNCHED();
-  SLC_TRY(sort_pairs_u32(k0.p, k1.p, p0.p, p1.p, nnz, bits_for((uint32_t)nrows)));
-  k_ptrs_from_sorted<<<(unsigned)ceil_div(nnz + 1, 256), 256, 0, s>>>(nnz, nrows, k1.p, out_ptr);
+  uint32_t *colid = (skey == k0.p) ? k1.p : k0.p;  // the key buffer the sort left free
+  k_expand_cols<<<(unsigned)ceil_div(ceil_div(nnz, EXPAND_ITEMS), 256), 256, 0, s>>>(nnz, ncols, colptr, colid);
   SLC_LAUNCHED();
-  k_transpose_gather<T><<<nb, 256, 0, s>>>(nnz, ncols, colptr, vals, p1.p, conj, out_idx, out_vals);
+  k_transpose_gather<T><<<(unsigned)ceil_div(nnz, 256 * GATHER_ITEMS), 256, 0, s>>>(nnz, colid, vals, sperm, conj,
+                                                                                  out_idx, out_vals);
   SLC_LAUNCHED();
   return SLC_OK;
 }

@@ -14,7 +14,7 @@ from sparse_linear_b200 import generators as g
 
 pytestmark = pytest.mark.gpu
 DTYPES = [np.float64, np.complex128]
-KINDS = {"auto": 0, "sell": 1, "csr-warp": 2, "csr-balanced": 3}
+KINDS = {"auto": 0, "sell": 1, "csr-warp": 2, "csr-balanced": 3, "csr-balanced-smem": 4}
 
 
 def vec(rng, n, dtype):
@@ -55,7 +55,7 @@ def test_mulv_and_axpy_match_oracle(sl, dtype, kind):
         np.testing.assert_array_equal(y, got2)
 
 
-@pytest.mark.parametrize("kind", ["csr-warp", "csr-balanced"])
+@pytest.mark.parametrize("kind", ["csr-warp", "csr-balanced", "csr-balanced-smem"])
 @pytest.mark.parametrize("dtype", DTYPES)
 def test_mulv_irregular_rows(sl, dtype, kind):
     """Power-law-like rows: empty rows, rows spanning several nnz chunks, a dense row."""
@@ -75,6 +75,32 @@ def test_mulv_irregular_rows(sl, dtype, kind):
     x, y0 = vec(rng, nc, dtype), vec(rng, nr, dtype)
     assert_values_close(sl.mulV(m, x), oracle.mulv(om, x))
     assert_values_close(sl.axpy(m, x, y0), oracle.axpy(om, x, y0))
+
+
+@pytest.mark.parametrize("kind", ["csr-balanced", "csr-balanced-smem"])
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_mulv_balanced_chunk_edges(sl, dtype, kind):
+    """Rows placed against the 2048-nonzero chunk grid of the balanced kernels: a row that is exactly
+    one chunk, one that starts on a chunk start and covers three, rows ending exactly on a chunk end
+    or on a thread's 8-nonzero range, empty rows on either side of a boundary, a ragged tail."""
+    rng = np.random.default_rng(9)
+    lens = np.array([2048, 0, 6144, 0, 0, 5, 2043, 8, 8, 16, 1, 7, 0, 2008, 3000, 1096, 0, 4096 + 2048 - 7, 7,
+                     1, 1, 1, 0, 13, 4099, 0, 0, 3], dtype=np.int64)
+    nr, nc = len(lens) + 2, 7000          # two trailing empty rows
+    lens = np.concatenate([lens, [0, 0]])
+    rows = np.repeat(np.arange(nr), lens)
+    cols = np.concatenate([np.sort(rng.choice(nc, l, replace=False)) for l in lens])
+    om = oracle.compress(nr, nc, rows, cols, vec(rng, len(rows), dtype))
+    m = to_matrix(sl, om)
+    m.device().set_spmv_kernel(KINDS[kind])
+    x, y0 = vec(rng, nc, dtype), vec(rng, nr, dtype)
+    got = sl.mulV(m, x)
+    assert kind in m.device().plan_info()
+    assert_values_close(got, oracle.mulv(om, x))
+    assert np.all(got[lens == 0] == 0)
+    got2 = sl.axpy(m, x, y0)
+    assert_values_close(got2, oracle.axpy(om, x, y0))
+    np.testing.assert_array_equal(got2[lens == 0], y0[lens == 0])
 
 
 def test_mulv_summation_order_matches_reference(sl):
@@ -122,6 +148,38 @@ def test_mulm_matches_oracle(sl, dtype, kind):
         got = sl.mulM(m, X)
         assert got.shape == (nr, k)
         np.testing.assert_array_equal(got, want)     # a thread owns (row, column): reference order
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_mulm_sell_plan_all_row_lengths(sl, dtype):
+    """The SELL-plan SpMM kernels (rows in registers up to 8 entries, rows staged in shared memory
+    above that, entries past the shared-memory capacity re-read from HBM): ragged rows, empty rows,
+    column counts that are not a multiple of the column tile."""
+    rng = np.random.default_rng(77)
+    for nr, nc, maxlen, k in [(70, 90, 3, 5), (300, 300, 8, 7), (500, 400, 13, 9), (257, 1000, 27, 17),
+                              (129, 3000, 150, 6), (64, 64, 40, 64)]:
+        lens = rng.integers(0, maxlen + 1, nr)
+        lens[rng.integers(0, nr)] = maxlen
+        lens = np.minimum(lens, nc)
+        rows = np.repeat(np.arange(nr), lens)
+        cols = np.concatenate([np.sort(rng.choice(nc, l, replace=False)) for l in lens])
+        om = oracle.compress(nr, nc, rows, cols, vec(rng, len(rows), dtype))
+        m = to_matrix(sl, om)
+        m.device().set_spmv_kernel(KINDS["sell"])
+        X = np.asfortranarray(np.stack([vec(rng, nc, dtype) for _ in range(k)], axis=1))
+        got = sl.mulM(m, X)
+        assert "sell32" in m.device().plan_info()
+        np.testing.assert_array_equal(got, oracle.mulm(om, X))
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_mulm_stencils_bit_exact(sl, dtype):
+    rng = np.random.default_rng(4)
+    for gm, k in ((g.laplace3d_7pt(9, dtype), 10), (g.stencil3d_27pt((9, 10, 11), dtype), 19),
+                  (g.stencil3d_27pt((12, 7, 8), dtype), 64)):
+        om, m = oracle.csc(*gm), to_matrix(sl, gm)
+        X = np.asfortranarray(np.stack([vec(rng, gm.ncols, dtype) for _ in range(k)], axis=1))
+        np.testing.assert_array_equal(sl.mulM(m, X), oracle.mulm(om, X))
 
 
 def test_mulm_stencil_block_and_column_range(sl):
