@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg5", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5", "cfg5mm"])
+    ap.add_argument("--workload", default="cfg5", choices=["cfg1", "cfg2", "cfg3", "cfg3t", "cfg3a", "cfg4", "cfg4t", "cfg5", "cfg5mm", "cfg5t"])
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"])
     ap.add_argument("--grid", type=int, default=0, help="override the stencil grid edge (debugging)")
     ap.add_argument("--kernel", type=int, default=0, help="force SpMV kernel family (slc_set_spmv_kernel)")
@@ -79,6 +79,21 @@ def build_workload(name, grid=0):
         n = grid or 128
         return dict(kind="spgemm", m=g.laplace3d_7pt(n), dtype=np.float64, k=1,
                     desc="cfg3: SpGEMM A*A, 3D 7-point Laplacian %d^3" % n)
+    if name in ("cfg3t", "cfg3a"):
+        n = grid or 128
+        what = "transpose" if name == "cfg3t" else "assemble"
+        return dict(kind=what, m=g.laplace3d_7pt(n), dtype=np.float64, k=1,
+                    desc="cfg3: %s, 3D 7-point Laplacian %d^3" % (
+                        "transpose" if name == "cfg3t" else
+                        "triplet assembly (every entry split in 0.25 v + 0.75 v, shuffled: 2x duplicates)", n))
+    if name == "cfg5t":
+        n = grid or 200
+        return dict(kind="transpose", m=g.stencil3d_27pt(n), dtype=np.float64, k=1,
+                    desc="cfg5: transpose, 3D 27-point stencil %d^3" % n)
+    if name == "cfg4t":
+        scale = grid or 24
+        return dict(kind="rmat", then="transpose", scale=scale, dtype=np.float64, k=1,
+                    desc="cfg4: R-MAT scale %d edge factor 16, transpose" % scale)
     if name == "cfg4":
         scale = grid or 24
         return dict(kind="rmat", scale=scale, dtype=np.float64, k=1,
@@ -90,6 +105,16 @@ def build_workload(name, grid=0):
     n = grid or 200
     return dict(kind="spmv", m=g.stencil3d_27pt(n), dtype=np.float64, k=1,
                 desc="cfg5: 3D 27-point stencil %d^3 (%d rows), Double SpMV (mulV)" % (n, n ** 3))
+
+
+def hot_kernel(plan, k, dm):
+    """Name of the kernel one step launches (what the roofline object describes)."""
+    if k == 1:
+        return "k_spmv_sell" if "sell" in plan else "k_spmv_merge + k_spmv_bal_fixup"
+    if "sell" not in plan:
+        return "k_spmm_rows"
+    maxlen = int(plan.split("max_rowlen=")[1].split()[0])
+    return "k_spmm_short" if maxlen <= 8 else "k_spmm_panel"
 
 
 def algorithmic_bytes(kind, nrows, ncols, nnz, k, dtype):
@@ -261,7 +286,7 @@ def main():
         sl.synchronize()
         assemble_s = time.perf_counter() - t0
         del r, c, v
-        wl["kind"] = "spmv"
+        wl["kind"] = wl.get("then", "spmv")
         wl["desc"] += " (%d nnz after duplicate merge; device assembly %.3f s incl. H2D)" % (sl.nonZero(m), assemble_s)
         host_m = None
     else:
@@ -277,6 +302,8 @@ def main():
 
     if wl["kind"] == "spgemm":
         return bench_spgemm(args, sl, m, wl, peak, peak_src)
+    if wl["kind"] in ("transpose", "assemble"):
+        return bench_structural(args, sl, m, host_m, wl, peak, peak_src)
 
     dm.prepare()
     sl.synchronize()
@@ -391,9 +418,76 @@ def main():
         "e2e": e2e,
         "roofline": {"bound": "hbm", "achieved": value, "peak": peak, "unit": "GB/s", "frac": value / peak,
                      "traffic": traffic, "peak_source": peak_src,
-                     "kernel": "k_spmv_sell" if "sell" in dm.plan_info() else "k_spmv_bal"},
+                     "kernel": hot_kernel(dm.plan_info(), k, dm)},
         "cpu_baseline": cpu,
     }
+    print(json.dumps(line), flush=True)
+
+
+def bench_structural(args, sl, m, host_m, wl, peak, peak_src):
+    """Transpose (handle -> handle) and triplet assembly (device triplets -> handle): throughput in
+    stored entries per second, algorithmic bytes as SURVEY.md section 8(d)."""
+    import torch
+    from sparse_linear_b200 import generators as g
+    steps = max(1, min(args.steps, 20))
+    warm = max(args.warmup, 3) if args.warmup < 10 else 3
+    nr, nc, nnz = m.device().dims()
+    if wl["kind"] == "transpose":
+        abytes = 2 * nnz * 12 + (nr + nc + 2) * 4
+        units, unit_name = nnz, "nnz/s"
+        metric = "transpose_nnz_per_s"
+        kernel = "k_radix_scatter"
+
+        def step():
+            t = sl.transpose(m)
+            del t
+        check = None
+    else:
+        r, c, v = g.split_duplicates(host_m, seed=0)
+        n_in = len(r)
+        dr = torch.from_numpy(r.astype(np.int32)).cuda()
+        dc = torch.from_numpy(c.astype(np.int32)).cuda()
+        dv = torch.from_numpy(v).cuda()
+        abytes = n_in * 16 + nnz * 12 + (nc + 1) * 4
+        units, unit_name = n_in, "triplets/s"
+        metric = "assembly_triplets_per_s"
+        kernel = "k_radix_scatter"
+
+        def step():
+            t = sl.compress_dev(nr, nc, n_in, dr.data_ptr(), dc.data_ptr(), dv.data_ptr(), np.float64)
+            del t
+        built = sl.compress_dev(nr, nc, n_in, dr.data_ptr(), dc.data_ptr(), dv.data_ptr(), np.float64)
+        check = bool(np.array_equal(built.pointers, host_m.colptr) and np.array_equal(built.indices, host_m.rowidx)
+                     and np.array_equal(built.values, host_m.values))   # 0.25 v + 0.75 v == v exactly
+        del built
+    for _ in range(warm):
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(torch.cuda.current_device())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = sl.launch_count()
+    sampler.start()
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1) / steps
+    gbs = abytes / (ms * 1e-3) / 1e9
+    line = {"metric": metric, "value": units / (ms * 1e-3), "unit": unit_name, "n_gpus": 1, "steps": steps,
+            "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": args.scaling,
+            "vs_baseline": None, "dtype": "u32 keys + f64 values", "data": "synthetic (seeded numpy PCG64)",
+            "config": {"workload": wl["desc"], "rows": nr, "cols": nc, "nnz": nnz, "units_per_step": units,
+                       "algorithmic_bytes_per_step": abytes,
+                       "l2": "inputs larger than L2" if abytes > 300e6 else "working set fits L2: warm-L2 number"},
+            "clocks": clocks, "gpu_launches": int(sl.launch_count() - l0),
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                         "traffic": None, "peak_source": peak_src, "kernel": kernel,
+                         "note": "algorithmic bytes are the one-pass floor; an LSD radix sort moves ~20 B per "
+                                 "key per 8-bit pass on top of it"}}
+    if check is not None:
+        line["config"]["result_equals_source_matrix_bit_exact"] = check
     print(json.dumps(line), flush=True)
 
 

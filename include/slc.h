@@ -165,6 +165,13 @@ int slc_d_compress(int32_t nrows, int32_t ncols, int64_t n, const int32_t *rows,
                    const int32_t *cols, const double *vals, slc_matrix **out, int64_t *bad_pos);
 int slc_z_compress(int32_t nrows, int32_t ncols, int64_t n, const int32_t *rows,
                    const int32_t *cols, const double *vals, slc_matrix **out, int64_t *bad_pos);
+/* Same, with the triplet arrays already in device memory (read in place, left intact). */
+int slc_d_compress_dev(int32_t nrows, int32_t ncols, int64_t n, const int32_t *rows_dev,
+                       const int32_t *cols_dev, const double *vals_dev, slc_matrix **out,
+                       int64_t *bad_pos);
+int slc_z_compress_dev(int32_t nrows, int32_t ncols, int64_t n, const int32_t *rows_dev,
+                       const int32_t *cols_dev, const double *vals_dev, slc_matrix **out,
+                       int64_t *bad_pos);
 
 /* ---- builders the configs and FEAST use: lin / glin, kronecker
         (Data/Matrix/Sparse.hs:401-431,597-638) ------------------------------------------- */
@@ -219,6 +226,17 @@ int slc_d_mulv_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const
                         const double *const *x_parts, double *y_dev, slc_peer_group *sync);
 int slc_z_mulv_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits,
                         const double *const *x_parts, double *y_dev, slc_peer_group *sync);
+
+/* Y_local <- A_local X, the block form (FEAST's multiplyWork over a row-partitioned subspace block).
+   X is partitioned by the same row blocks: X_parts[p] is the device address, as mapped in THIS process,
+   of part p's (splits[p+1]-splits[p]) x k column-major block with leading dimension ldx_parts[p].
+   Same ordering contract as slc_*_mulv_dist_dev.  Sliced-ELL plans only. */
+int slc_d_mulm_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits,
+                        const double *const *X_parts, const int64_t *ldx_parts, double *Y_dev,
+                        int64_t ldy, int32_t k, slc_peer_group *sync);
+int slc_z_mulm_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits,
+                        const double *const *X_parts, const int64_t *ldx_parts, double *Y_dev,
+                        int64_t ldy, int32_t k, slc_peer_group *sync);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -8,7 +8,7 @@ Import as `sparse_linear_b200` (see sparse_linear_b200.py at the repo root).
 from . import _capi, generators, sharded  # noqa: F401
 from .matrix import (  # noqa: F401
     DeviceMatrix, Matrix, SparseLinearError,
-    axpy, axpy_, cmap, compress, ctrans, decompress, device_count, diag, fromTriples, hermitian, ident,
+    axpy, axpy_, cmap, compress, compress_dev, ctrans, decompress, device_count, diag, fromTriples, hermitian, ident,
     kronecker, launch_count, lin, mm, mulM, mulM_dev, mulV, mulV_dev, nonZero, scale, set_device,
     set_stream, synchronize, transpose, zeros,
 )

@@ -59,6 +59,8 @@ for _p in ("d", "z"):
         "slc_%s_mulv_dev" % _p: (C.c_int, [_hp, _vp, _vp]),
         "slc_%s_axpy_dev" % _p: (C.c_int, [_hp, _vp, _vp]),
         "slc_%s_mulv_dist_dev" % _p: (C.c_int, [_hp, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp]),
+        "slc_%s_mulm_dist_dev" % _p: (C.c_int, [_hp, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp, C.c_int64,
+                                                C.c_int32, _vp]),
         "slc_%s_mulm" % _p: (C.c_int, [_hp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32]),
         "slc_%s_mulm_dev" % _p: (C.c_int, [_hp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32]),
         "slc_%s_mm" % _p: (C.c_int, [_hp, _hp, C.POINTER(_hp)]),
@@ -66,6 +68,8 @@ for _p in ("d", "z"):
         "slc_%s_hermitian" % _p: (C.c_int, [_hp, C.POINTER(C.c_int)]),
         "slc_%s_compress" % _p: (C.c_int, [C.c_int32, C.c_int32, C.c_int64, _vp, _vp, _vp,
                                            C.POINTER(_hp), C.POINTER(C.c_int64)]),
+        "slc_%s_compress_dev" % _p: (C.c_int, [C.c_int32, C.c_int32, C.c_int64, _vp, _vp, _vp,
+                                               C.POINTER(_hp), C.POINTER(C.c_int64)]),
         "slc_%s_lin" % _p: (C.c_int, [_vp, _hp, _vp, _hp, C.POINTER(_hp)]),
         "slc_%s_kronecker" % _p: (C.c_int, [_hp, _hp, C.POINTER(_hp)]),
     })

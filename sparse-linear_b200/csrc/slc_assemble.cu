@@ -65,7 +65,7 @@ __global__ void k_ptrs_from_sorted_u32(int64_t n, int32_t nkeys, const uint32_t 
 
 template <class T>
 static int compress_entry(int32_t nrows, int32_t ncols, int64_t n, const int32_t *rows, const int32_t *cols,
-                          const double *vals, slc_matrix **out, int64_t *bad_pos) {
+                          const double *vals, slc_matrix **out, int64_t *bad_pos, bool on_device) {
   if (!out) return fail(SLC_ERR_INVALID, "compress: null output handle");
   *out = nullptr;
   if (bad_pos) *bad_pos = -1;
@@ -83,25 +83,34 @@ static int compress_entry(int32_t nrows, int32_t ncols, int64_t n, const int32_t
   const int rowbits = bits_for((uint32_t)nrows);
   const int colbits = bits_for((uint32_t)ncols);
 
+  // triplets: lent host arrays are copied to the device first (Foreign.hs:33-37); device arrays
+  // (the *_compress_dev entry points) are read in place and left intact
   DevBuf<int32_t> drows, dcols, head, seg;
   DevBuf<T> dvals;
   DevBuf<uint64_t> k0, k1;
   DevBuf<uint32_t> p0, p1;
   DevBuf<unsigned long long> bad;
-  SLC_TRY(drows.alloc(n));
-  SLC_TRY(dcols.alloc(n));
-  SLC_TRY(dvals.alloc(n));
+  const int32_t *rows_d = rows, *cols_d = cols;
+  const T *vals_d = reinterpret_cast<const T *>(vals);
+  if (!on_device) {
+    SLC_TRY(drows.alloc(n));
+    SLC_TRY(dcols.alloc(n));
+    SLC_TRY(dvals.alloc(n));
+    SLC_CUDA(cudaMemcpyAsync(drows.p, rows, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+    SLC_CUDA(cudaMemcpyAsync(dcols.p, cols, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+    SLC_CUDA(cudaMemcpyAsync(dvals.p, vals, (size_t)n * sizeof(T), cudaMemcpyHostToDevice, s));
+    rows_d = drows.p;
+    cols_d = dcols.p;
+    vals_d = dvals.p;
+  }
   SLC_TRY(k0.alloc(n));
   SLC_TRY(k1.alloc(n));
   SLC_TRY(p0.alloc(n));
   SLC_TRY(p1.alloc(n));
   SLC_TRY(bad.alloc(2));
-  SLC_CUDA(cudaMemcpyAsync(drows.p, rows, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
-  SLC_CUDA(cudaMemcpyAsync(dcols.p, cols, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
-  SLC_CUDA(cudaMemcpyAsync(dvals.p, vals, (size_t)n * sizeof(T), cudaMemcpyHostToDevice, s));
   SLC_CUDA(cudaMemsetAsync(bad.p, 0xff, 2 * sizeof(unsigned long long), s));
   const unsigned nb = (unsigned)ceil_div(n, 256);
-  k_coo_check_pack<<<nb, 256, 0, s>>>(n, nrows, ncols, rowbits, drows.p, dcols.p, k0.p, bad.p);
+  k_coo_check_pack<<<nb, 256, 0, s>>>(n, nrows, ncols, rowbits, rows_d, cols_d, k0.p, bad.p);
   SLC_LAUNCHED();
   unsigned long long hbad[2];
   SLC_CUDA(cudaMemcpyAsync(hbad, bad.p, sizeof hbad, cudaMemcpyDeviceToHost, s));
@@ -138,7 +147,7 @@ static int compress_entry(int32_t nrows, int32_t ncols, int64_t n, const int32_t
   DevBuf<uint32_t> ocol;
   int rc = ocol.alloc((size_t)nnz_out);
   if (rc == SLC_OK) {
-    k_reduce_runs<T><<<nb, 256, 0, s>>>(n, rowbits, skey, sperm, head.p, seg.p, dvals.p, m->rowidx, ocol.p,
+    k_reduce_runs<T><<<nb, 256, 0, s>>>(n, rowbits, skey, sperm, head.p, seg.p, vals_d, m->rowidx, ocol.p,
                                         (T *)m->vals);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     k_ptrs_from_sorted_u32<<<(unsigned)ceil_div((int64_t)nnz_out + 1, 256), 256, 0, s>>>(nnz_out, ncols,
@@ -336,11 +345,19 @@ using namespace slc;
 extern "C" {
 int slc_d_compress(int32_t nrows, int32_t ncols, int64_t n, const int32_t *rows, const int32_t *cols,
                    const double *vals, slc_matrix **out, int64_t *bad_pos) {
-  return compress_entry<double>(nrows, ncols, n, rows, cols, vals, out, bad_pos);
+  return compress_entry<double>(nrows, ncols, n, rows, cols, vals, out, bad_pos, false);
 }
 int slc_z_compress(int32_t nrows, int32_t ncols, int64_t n, const int32_t *rows, const int32_t *cols,
                    const double *vals, slc_matrix **out, int64_t *bad_pos) {
-  return compress_entry<double2>(nrows, ncols, n, rows, cols, vals, out, bad_pos);
+  return compress_entry<double2>(nrows, ncols, n, rows, cols, vals, out, bad_pos, false);
+}
+int slc_d_compress_dev(int32_t nrows, int32_t ncols, int64_t n, const int32_t *rows, const int32_t *cols,
+                       const double *vals, slc_matrix **out, int64_t *bad_pos) {
+  return compress_entry<double>(nrows, ncols, n, rows, cols, vals, out, bad_pos, true);
+}
+int slc_z_compress_dev(int32_t nrows, int32_t ncols, int64_t n, const int32_t *rows, const int32_t *cols,
+                       const double *vals, slc_matrix **out, int64_t *bad_pos) {
+  return compress_entry<double2>(nrows, ncols, n, rows, cols, vals, out, bad_pos, true);
 }
 int slc_d_lin(const double *alpha, const slc_matrix *a, const double *beta, const slc_matrix *b,
               slc_matrix **c) {

@@ -157,7 +157,7 @@ struct slc_matrix {
   // partition table of the last distributed product (device copy + host shadow)
   void *dist_table = nullptr;
   bool dist_table_valid = false;
-  alignas(8) unsigned char dist_table_host[256];
+  alignas(8) unsigned char dist_table_host[384];
 };
 
 namespace slc {

@@ -59,6 +59,7 @@ struct DistTable {
   int32_t nparts;
   int32_t splits[MAX_PARTS + 1];
   const void *parts[MAX_PARTS];
+  int64_t ld[MAX_PARTS];  // SpMM: leading dimension of every part's block (0 for vectors)
 };
 
 template <class T>
@@ -76,6 +77,39 @@ struct DistX {
       p = static_cast<const T *>(tbl->parts[q]) + (c - tbl->splits[q]);
     }
     return ld_gather(p, pol);
+  }
+};
+
+// The same two accessors for a column-major block X (SpMM): col0(c, ld) is the address of X[c, 0] and
+// ld the distance to X[c, 1] -- every part keeps its own leading dimension.
+template <class T>
+struct LocalXM {
+  const T *X;
+  int64_t ldx;
+  __device__ __forceinline__ const T *col0(int32_t c, int64_t &ld) const {
+    ld = ldx;
+    return X + c;
+  }
+};
+
+template <class T>
+struct DistXM {
+  const T *self_X;  // this rank's own row block of X
+  int64_t self_ld;
+  int32_t self_lo, self_hi;
+  const DistTable *tbl;
+  __device__ __forceinline__ const T *col0(int32_t c, int64_t &ld) const {
+    ld = self_ld;
+    const T *p = self_X + (c - self_lo);
+    if (c < self_lo || c >= self_hi) {
+      int q = 0;
+      const int np = tbl->nparts;
+#pragma unroll 1
+      while (q + 1 < np && c >= tbl->splits[q + 1]) ++q;
+      p = static_cast<const T *>(tbl->parts[q]) + (c - tbl->splits[q]);
+      ld = tbl->ld[q];
+    }
+    return p;
   }
 };
 
@@ -884,7 +918,7 @@ k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, int32_t stride32, u
 // and half of the stall samples sat between an index load and the gather that needs it.
 template <class T, int JT, int KU>
 __global__ void __launch_bounds__(256)
-k_spmm_panel(int32_t nrows, int32_t kcap, uint32_t zmask, const int64_t *__restrict__ slice_ptr,
+k_spmm_panel(int32_t row_begin, int32_t row_end, int32_t kcap, uint32_t zmask, const int64_t *__restrict__ slice_ptr,
              const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
              const T *__restrict__ vals, const T *__restrict__ X, int64_t ldx, T *__restrict__ Y,
              int64_t ldy, int32_t k) {
@@ -892,8 +926,8 @@ k_spmm_panel(int32_t nrows, int32_t kcap, uint32_t zmask, const int64_t *__restr
   const int32_t nt = blockDim.x, tid = threadIdx.x;
   T *s_a = reinterpret_cast<T *>(panel_smem) + tid;                                       // [kcap][nt]
   int32_t *s_c = reinterpret_cast<int32_t *>(panel_smem + (size_t)kcap * nt * sizeof(T)) + tid;  // [kcap][nt]
-  const int32_t row = blockIdx.x * nt + tid;
-  if (row >= nrows) return;
+  const int32_t row = row_begin + blockIdx.x * nt + tid;  // row_begin % 32 == 0: lanes are slice rows
+  if (row >= row_end) return;
   const uint64_t pol_s = policy_evict_first();
   const uint64_t pol_x = policy_evict_last();
   const int64_t base = __ldg(slice_ptr + (row >> 5)) + (tid & 31);
@@ -959,6 +993,58 @@ k_spmm_panel(int32_t nrows, int32_t kcap, uint32_t zmask, const int64_t *__restr
 #pragma unroll
     for (int j = 0; j < JT; ++j)
       if (j0 + j < k) st_stream(Yrow + (int64_t)(j0 + j) * ldy, acc[j]);
+  }
+}
+
+// Boundary rows of a row-partitioned SpMM: rows [0, r0) and [r1, nrows) of the local block, whose
+// columns reach into a peer's rows of X.  One thread per row, JT columns per pass; the row's entries
+// are re-read through L1 for every pass (these rows are a few per cent of the block -- two planes
+// of a z-slab -- so the interior kernel's staging is not repeated here).  Remote entries are plain
+// loads from the owner's HBM over NVLink, each part with its own leading dimension (DistXM).
+template <class T, int JT>
+__global__ void __launch_bounds__(128)
+k_spmm_boundary(int32_t nrows, int32_t r0, int32_t r1, uint32_t zmask, const int64_t *__restrict__ slice_ptr,
+                const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
+                const T *__restrict__ vals, const DistXM<T> xa, T *__restrict__ Y, int64_t ldy, int32_t k) {
+  const int32_t nbl = (r0 + 127) >> 7;  // blocks below the interior
+  int32_t row, limit;
+  if ((int32_t)blockIdx.x < nbl) {
+    row = blockIdx.x * 128 + threadIdx.x;
+    limit = r0;
+  } else {
+    row = r1 + (blockIdx.x - nbl) * 128 + threadIdx.x;  // r1 % 32 == 0 unless r1 == nrows
+    limit = nrows;
+  }
+  if (row >= limit) return;
+  const uint64_t pol_x = policy_evict_last();
+  const int64_t base = __ldg(slice_ptr + (row >> 5)) + (row & 31);
+  const int32_t len = __ldg(rowlen + row);
+  const int32_t *ci = colidx + base;
+  const T *va = vals + base;
+  for (int32_t j0 = 0; j0 < k; j0 += JT) {
+    T acc[JT];
+#pragma unroll
+    for (int j = 0; j < JT; ++j) acc[j] = Num<T>::zero();
+    for (int32_t e = 0; e < len; ++e) {
+      const int32_t c = __ldg(ci + (int64_t)e * SELL_C);
+      const T a = __ldg(va + (int64_t)e * SELL_C);
+      int64_t ld;
+      const T *xp = xa.col0(c, ld) + (int64_t)j0 * ld;
+      T xv[JT];
+#pragma unroll
+      for (int j = 0; j < JT; ++j) xv[j] = (j0 + j < k) ? ld_gather(xp + (int64_t)j * ld, pol_x) : Num<T>::zero();
+      uint32_t r = 0;
+#pragma unroll
+      for (int j = 0; j < JT; ++j) r |= probe(xv[j]);
+      r &= zmask;
+#pragma unroll
+      for (int j = 0; j < JT; ++j) tie(xv[j], r);
+#pragma unroll
+      for (int j = 0; j < JT; ++j) acc[j] = Num<T>::add(Num<T>::mul(a, xv[j]), acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < JT; ++j)
+      if (j0 + j < k) st_stream(Y + (int64_t)(j0 + j) * ldy + row, acc[j]);
   }
 }
 
@@ -1145,14 +1231,14 @@ static int spmv_host_entry(slc_matrix *m, const double *x, double *y, const char
   return SLC_OK;
 }
 
-// y_local <- A_local x, x partitioned by column ranges over the GPUs of one box (see DistX)
+// Validate a partition, put its table (splits, part pointers, leading dimensions) in HBM next to the
+// matrix (refreshed only when it changes) and return the device copy.
 template <class T>
-static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits,
-                           const double *const *x_parts, double *y, slc_peer_group *sync, const char *fn) {
+static int dist_table_setup(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits,
+                            const double *const *parts, const int64_t *lds, const char *fn, const DistTable **out) {
   SLC_TRY(check_handle<T>(m, fn));
   if (nparts < 1 || nparts > MAX_PARTS) return fail(SLC_ERR_INVALID, "%s: 1..%d partitions supported", fn, MAX_PARTS);
-  if (self < 0 || self >= nparts || !splits || !x_parts || (m->nrows && !y))
-    return fail(SLC_ERR_INVALID, "%s: bad partition argument", fn);
+  if (self < 0 || self >= nparts || !splits || !parts) return fail(SLC_ERR_INVALID, "%s: bad partition argument", fn);
   if (splits[0] != 0 || splits[nparts] != m->ncols)
     return fail(SLC_ERR_DIM, "axpy_: column dimension %d does not match operand dimension %d", m->ncols,
                 splits[nparts]);
@@ -1161,13 +1247,16 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   for (int p = 0; p <= MAX_PARTS; ++p) t.splits[p] = m->ncols;
   for (int p = 0; p < nparts; ++p) {
     if (splits[p] > splits[p + 1]) return fail(SLC_ERR_INVALID, "%s: partition bounds decrease", fn);
-    if (splits[p + 1] > splits[p] && !x_parts[p]) return fail(SLC_ERR_INVALID, "%s: null slice %d", fn, p);
-    t.parts[p] = x_parts[p];
+    if (splits[p + 1] > splits[p] && !parts[p]) return fail(SLC_ERR_INVALID, "%s: null slice %d", fn, p);
+    if (lds && lds[p] < splits[p + 1] - splits[p])
+      return fail(SLC_ERR_DIM, "axpy_: column dimension %d does not match operand dimension %lld",
+                  splits[p + 1] - splits[p], (long long)lds[p]);
+    t.parts[p] = parts[p];
     t.splits[p] = splits[p];
+    t.ld[p] = lds ? lds[p] : 0;
   }
   t.splits[nparts] = splits[nparts];
   t.nparts = nparts;
-  // keep the table in HBM next to the matrix; refresh it only when the partition changes
   static_assert(sizeof(DistTable) <= sizeof(m->dist_table_host), "dist table cache too small");
   if (!m->dist_table) {
     DevBuf<char> buf;
@@ -1180,28 +1269,20 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
     SLC_CUDA(cudaMemcpyAsync(m->dist_table, m->dist_table_host, sizeof t, cudaMemcpyHostToDevice, cur_stream()));
     m->dist_table_valid = true;
   }
-  DistX<T> xa;
-  xa.self_x = (const T *)x_parts[self];
-  xa.self_lo = splits[self];
-  xa.self_hi = splits[self + 1];
-  xa.tbl = (const DistTable *)m->dist_table;
-  if (m->nnz > 0) SLC_TRY(ensure_plan<T>(m));
-  if (m->nrows == 0 || m->nnz == 0 || m->spmv_active != SPMV_SELL) {
-    if (sync) SLC_TRY(slc_peer_barrier(sync));  // separate barrier kernel, then the generic kernels
-    return spmv_run<T, false, DistX<T>>(m, xa, (T *)y);
-  }
+  *out = (const DistTable *)m->dist_table;
+  return SLC_OK;
+}
 
-  // Sliced-ELL plan: the slices whose columns all fall inside this rank's own slice of x (for a
-  // z-slab stencil: everything but the first and last plane) run the undistributed kernel on a
-  // shifted base pointer, at full single-GPU speed; only the boundary slices take the peer path.
+// Sliced-ELL plan: the longest run of consecutive slices whose columns all fall inside [lo, hi), this
+// rank's own slice of the operand (for a z-slab stencil: everything but the first and last plane).
+// Rows [r0, r1) need no peer; cached per (lo, hi).
+static int dist_interior(slc_matrix *m, int32_t lo, int32_t hi, int32_t *r0, int32_t *r1) {
   SellPlan &sp = m->sell;
-  if (sp.interior_lo != xa.self_lo || sp.interior_hi != xa.self_hi || sp.interior_s0 < 0) {
+  if (sp.interior_lo != lo || sp.interior_hi != hi || sp.interior_s0 < 0) {
     SLC_TRY(fetch_slice_ranges(m));
-    // longest run of consecutive all-local slices (empty slices count as local)
-    int32_t best0 = 0, best1 = 0, run0 = 0;
+    int32_t best0 = 0, best1 = 0, run0 = 0;  // empty slices count as local
     for (int32_t sl = 0; sl <= sp.nslices; ++sl) {
-      const bool local = sl < sp.nslices &&
-                         (sp.h_cmax[sl] < 0 || (sp.h_cmin[sl] >= xa.self_lo && sp.h_cmax[sl] < xa.self_hi));
+      const bool local = sl < sp.nslices && (sp.h_cmax[sl] < 0 || (sp.h_cmin[sl] >= lo && sp.h_cmax[sl] < hi));
       if (!local) {
         if (sl - run0 > best1 - best0) { best0 = run0; best1 = sl; }
         run0 = sl + 1;
@@ -1209,11 +1290,37 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
     }
     sp.interior_s0 = best0;
     sp.interior_s1 = best1;
-    sp.interior_lo = xa.self_lo;
-    sp.interior_hi = xa.self_hi;
+    sp.interior_lo = lo;
+    sp.interior_hi = hi;
   }
-  const int32_t r0 = sp.interior_s0 * SELL_C;
-  const int32_t r1 = min(m->nrows, sp.interior_s1 * SELL_C);
+  *r0 = sp.interior_s0 * SELL_C;
+  *r1 = std::min(m->nrows, sp.interior_s1 * SELL_C);
+  return SLC_OK;
+}
+
+// y_local <- A_local x, x partitioned by column ranges over the GPUs of one box (see DistX)
+template <class T>
+static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits,
+                           const double *const *x_parts, double *y, slc_peer_group *sync, const char *fn) {
+  const DistTable *tbl = nullptr;
+  SLC_TRY((dist_table_setup<T>(m, nparts, self, splits, x_parts, nullptr, fn, &tbl)));
+  if (m->nrows && !y) return fail(SLC_ERR_INVALID, "%s: bad partition argument", fn);
+  DistX<T> xa;
+  xa.self_x = (const T *)x_parts[self];
+  xa.self_lo = splits[self];
+  xa.self_hi = splits[self + 1];
+  xa.tbl = tbl;
+  if (m->nnz > 0) SLC_TRY(ensure_plan<T>(m));
+  if (m->nrows == 0 || m->nnz == 0 || m->spmv_active != SPMV_SELL) {
+    if (sync) SLC_TRY(slc_peer_barrier(sync));  // separate barrier kernel, then the generic kernels
+    return spmv_run<T, false, DistX<T>>(m, xa, (T *)y);
+  }
+
+  // the interior slices run the undistributed row body on a shifted base pointer, at full single-GPU
+  // speed; only the boundary slices take the peer path
+  SellPlan &sp = m->sell;
+  int32_t r0 = 0, r1 = 0;
+  SLC_TRY(dist_interior(m, xa.self_lo, xa.self_hi, &r0, &r1));
   // one launch: [boundary blocks | interior blocks], barrier fused in (see k_spmv_sell_dist)
   PeerSync ps;
   memset(&ps, 0, sizeof ps);
@@ -1236,7 +1343,7 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
 // the 27-point stencil; the environment variables exist for that sweep.
 template <class T, int JT, int KU>
 static int launch_panel_inst(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, int threads,
-                             int32_t kcap) {
+                             int32_t kcap, int32_t row_begin, int32_t row_end) {
   const SellPlan &sp = m->sell;
   const size_t smem = (size_t)kcap * threads * (sizeof(T) + sizeof(int32_t));
   static size_t smem_set = 0;  // per instantiation
@@ -1244,15 +1351,18 @@ static int launch_panel_inst(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64
     SLC_CUDA(cudaFuncSetAttribute(k_spmm_panel<T, JT, KU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     smem_set = smem;
   }
-  const int64_t nb = ceil_div(m->nrows, threads);
+  if (row_end <= row_begin) return SLC_OK;
+  const int64_t nb = ceil_div(row_end - row_begin, threads);
   k_spmm_panel<T, JT, KU><<<(unsigned)nb, threads, smem, cur_stream()>>>(
-      m->nrows, kcap, 0u, sp.slice_ptr, sp.rowlen, sp.colidx, (const T *)sp.vals, X, ldx, Y, ldy, k);
+      row_begin, row_end, kcap, 0u, sp.slice_ptr, sp.rowlen, sp.colidx, (const T *)sp.vals, X, ldx, Y, ldy, k);
   SLC_LAUNCHED();
   return SLC_OK;
 }
 
 template <class T>
-static int launch_panel(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k) {
+static int launch_panel(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k,
+                        int32_t row_begin = 0, int32_t row_end = -1) {
+  if (row_end < 0) row_end = m->nrows;
   static const int threads_env = env_int("SLC_PANEL_THREADS", 0);
   static const int smem_env = env_int("SLC_PANEL_SMEM_KB", 0);
   static const int jt_env = env_int("SLC_PANEL_JT", 0);
@@ -1266,7 +1376,8 @@ static int launch_panel(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ld
   int ku = ku_env ? ku_env : ((m->max_rowlen % 3) < (m->max_rowlen % 4) ? 3 : 4);
   if (m->max_rowlen < 3) ku = 2;
   const bool wide = jt_env ? jt_env >= 8 : sizeof(T) == 8;  // 8 columns per tile for Double, 4 for Complex
-#define SLC_PANEL(JT_, KU_) return launch_panel_inst<T, JT_, KU_>(m, X, ldx, Y, ldy, k, threads, kcap)
+#define SLC_PANEL(JT_, KU_) \
+  return launch_panel_inst<T, JT_, KU_>(m, X, ldx, Y, ldy, k, threads, kcap, row_begin, row_end)
   if (wide) {
     if (ku <= 2) SLC_PANEL(8, 2);
     if (ku == 3) SLC_PANEL(8, 3);
@@ -1347,6 +1458,59 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
                                                                  (const T *)m->rvals, X, ldx, Y, ldy, k);
   }
   SLC_LAUNCHED();
+  return SLC_OK;
+}
+
+// Y_local <- A_local X, X partitioned by row blocks over the GPUs of one box (column-major, every
+// part with its own leading dimension).  Sliced-ELL plans only (the stencils this is for): signal,
+// interior rows on the undistributed panel kernel, wait, boundary rows through the peers' memory.
+template <class T>
+static int spmm_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits,
+                           const double *const *X_parts, const int64_t *ldx_parts, double *Y, int64_t ldy,
+                           int32_t k, slc_peer_group *sync, const char *fn) {
+  const DistTable *tbl = nullptr;
+  if (!ldx_parts) return fail(SLC_ERR_INVALID, "%s: null leading dimensions", fn);
+  SLC_TRY((dist_table_setup<T>(m, nparts, self, splits, X_parts, ldx_parts, fn, &tbl)));
+  if (k < 0) return fail(SLC_ERR_INVALID, "%s: negative column count", fn);
+  if (k > 0 && m->nrows && !Y) return fail(SLC_ERR_INVALID, "%s: null block", fn);
+  if (ldy < m->nrows)
+    return fail(SLC_ERR_DIM, "axpy_: row dimension %d does not match result dimension %lld", m->nrows,
+                (long long)ldy);
+  cudaStream_t s = cur_stream();
+  if (k == 0 || m->nrows == 0 || m->nnz == 0) {
+    if (sync) SLC_TRY(slc_peer_barrier(sync));
+    if (k > 0 && m->nrows > 0)
+      SLC_CUDA(cudaMemset2DAsync(Y, (size_t)ldy * sizeof(T), 0, (size_t)m->nrows * sizeof(T), (size_t)k, s));
+    return SLC_OK;
+  }
+  SLC_TRY(ensure_plan<T>(m));
+  if (m->spmv_active != SPMV_SELL) {
+    // the distributed block product is written for the sliced layout only
+    if (m->sell.padded > 2 * m->nnz + 1024)
+      return fail(SLC_ERR_INVALID, "%s: the row-partitioned block product needs a sliced-ELL plan (padding %lld > nnz %lld)",
+                  fn, (long long)(m->sell.padded - m->nnz), (long long)m->nnz);
+    SLC_TRY(fill_sell<T>(m));
+  }
+  DistXM<T> xa;
+  xa.self_X = (const T *)X_parts[self];
+  xa.self_ld = ldx_parts[self];
+  xa.self_lo = splits[self];
+  xa.self_hi = splits[self + 1];
+  xa.tbl = tbl;
+  int32_t r0 = 0, r1 = 0;
+  SLC_TRY(dist_interior(m, xa.self_lo, xa.self_hi, &r0, &r1));
+  if (sync) SLC_TRY(slc_peer_signal(sync));  // "my rows of X are written" (stream order)
+  // interior rows: columns are global, so shift the local block's base by the first owned row
+  SLC_TRY(launch_panel<T>(m, xa.self_X - xa.self_lo, xa.self_ld, (T *)Y, ldy, k, r0, r1));
+  if (sync) SLC_TRY(slc_peer_wait(sync));
+  const int64_t nb = ceil_div(r0, 128) + ceil_div(m->nrows - r1, 128);
+  if (nb > 0) {
+    const SellPlan &sp = m->sell;
+    constexpr int JT = sizeof(T) == 16 ? 4 : 8;
+    k_spmm_boundary<T, JT><<<(unsigned)nb, 128, 0, s>>>(m->nrows, r0, r1, 0u, sp.slice_ptr, sp.rowlen, sp.colidx,
+                                                        (const T *)sp.vals, xa, (T *)Y, ldy, k);
+    SLC_LAUNCHED();
+  }
   return SLC_OK;
 }
 
@@ -1458,6 +1622,16 @@ int slc_z_mulv_dist_dev(slc_matrix *a, int32_t nparts, int32_t self, const int32
   return spmv_dist_entry<double2>(a, nparts, self, splits, x_parts, y_dev, sync, "mulV");
 }
 
+int slc_d_mulm_dist_dev(slc_matrix *a, int32_t nparts, int32_t self, const int32_t *splits,
+                        const double *const *X_parts, const int64_t *ldx_parts, double *Y, int64_t ldy, int32_t k,
+                        slc_peer_group *sync) {
+  return spmm_dist_entry<double>(a, nparts, self, splits, X_parts, ldx_parts, Y, ldy, k, sync, "mulM");
+}
+int slc_z_mulm_dist_dev(slc_matrix *a, int32_t nparts, int32_t self, const int32_t *splits,
+                        const double *const *X_parts, const int64_t *ldx_parts, double *Y, int64_t ldy, int32_t k,
+                        slc_peer_group *sync) {
+  return spmm_dist_entry<double2>(a, nparts, self, splits, X_parts, ldx_parts, Y, ldy, k, sync, "mulM");
+}
 int slc_d_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k) {
   return spmm_host_entry<double>(a, X, ldx, Y, ldy, k, "mulM");
 }

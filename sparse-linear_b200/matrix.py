@@ -258,6 +258,19 @@ def compress(nrows, ncols, rows, cols, vals):
     return Matrix._from_device(h)
 
 
+def compress_dev(nrows, ncols, n, rows_ptr, cols_ptr, vals_ptr, dtype=np.float64):
+    """compress over triplet arrays that already live in device memory (int32 rows / cols, values of
+    `dtype`), given as raw device addresses; the arrays are read in place and left intact."""
+    p = _prefix(np.dtype(dtype))
+    h = C.c_void_p()
+    bad = C.c_int64(-1)
+    rc = _fn(p, "compress_dev")(int(nrows), int(ncols), int(n), C.c_void_p(rows_ptr), C.c_void_p(cols_ptr),
+                                C.c_void_p(vals_ptr), C.byref(h), C.byref(bad))
+    if rc != _capi.OK:
+        raise SparseLinearError(_capi.last_error(), code=rc, pos=bad.value if bad.value >= 0 else None)
+    return Matrix._from_device(h)
+
+
 def fromTriples(nr, nc, triples, dtype=None):
     """Sparse.hs:357-363; triples are (row, col, value)."""
     triples = list(triples)

@@ -70,8 +70,10 @@ class ShardedSpMV:
     in a cudaMalloc'ed buffer that every other rank maps through CUDA IPC.
     """
 
-    def __init__(self, local, splits, rank, world, dist=None, cpu_group=None):
+    def __init__(self, local, splits, rank, world, dist=None, cpu_group=None, k=None):
         self.local, self.rank, self.world, self.dist = local, rank, world, dist
+        self.k = k                      # None: vectors (mulV); k >= 1: column-major blocks (mulM)
+        ncol = 1 if k is None else int(k)
         self.splits = np.ascontiguousarray(splits, dtype=np.int32)
         if len(self.splits) != world + 1 or self.splits[0] != 0 or self.splits[-1] != local.ncols:
             raise SparseLinearError("axpy_: column dimension %d does not match operand dimension %d"
@@ -81,9 +83,9 @@ class ShardedSpMV:
         lib = _capi.lib()
         self.nloc_x = int(self.splits[rank + 1] - self.splits[rank])
         self.x_ptr = C.c_void_p()
-        _check(lib.slc_dev_alloc(C.byref(self.x_ptr), max(self.nloc_x, 1) * self.el))
+        _check(lib.slc_dev_alloc(C.byref(self.x_ptr), max(self.nloc_x * ncol, 1) * self.el))
         self.y_ptr = C.c_void_p()
-        _check(lib.slc_dev_alloc(C.byref(self.y_ptr), max(local.nrows, 1) * self.el))
+        _check(lib.slc_dev_alloc(C.byref(self.y_ptr), max(local.nrows * ncol, 1) * self.el))
         handle = C.create_string_buffer(IPC_BYTES)
         _check(lib.slc_ipc_export(self.x_ptr, handle))
         self.group = C.c_void_p()
@@ -105,12 +107,19 @@ class ShardedSpMV:
                 self.parts[r] = ptr.value
                 self._imported.append(ptr)
         self.local.device().prepare()
-        self._fn = getattr(lib, "slc_%s_mulv_dist_dev" % self.p)
+        self._fn = getattr(lib, "slc_%s_%s_dist_dev" % (self.p, "mulv" if k is None else "mulm"))
+        # every part's block is packed: leading dimension = its own row count
+        self.lds = np.ascontiguousarray(np.diff(self.splits).astype(np.int64))
         self._flag = None
 
     def set_x(self, x_local):
-        x_local = np.ascontiguousarray(x_local, dtype=self.local.dtype)
-        assert len(x_local) == self.nloc_x
+        """This rank's slice of x (vector) or its row block of X (nloc x k, stored column-major)."""
+        if self.k is None:
+            x_local = np.ascontiguousarray(x_local, dtype=self.local.dtype)
+            assert len(x_local) == self.nloc_x
+        else:
+            x_local = np.asfortranarray(x_local, dtype=self.local.dtype)
+            assert x_local.shape == (self.nloc_x, self.k)
         _check(_capi.lib().slc_memcpy_h2d(self.x_ptr, C.c_void_p(x_local.ctypes.data), x_local.nbytes))
 
     def barrier(self):
@@ -133,9 +142,15 @@ class ShardedSpMV:
         return bool(f.value)
 
     def product(self, sync=None):
-        _check(self._fn(self.local.device().handle, self.world, self.rank,
-                        self.splits.ctypes.data_as(C.c_void_p), C.cast(self.parts, C.c_void_p), self.y_ptr,
-                        sync))
+        if self.k is None:
+            _check(self._fn(self.local.device().handle, self.world, self.rank,
+                            self.splits.ctypes.data_as(C.c_void_p), C.cast(self.parts, C.c_void_p), self.y_ptr,
+                            sync))
+        else:
+            _check(self._fn(self.local.device().handle, self.world, self.rank,
+                            self.splits.ctypes.data_as(C.c_void_p), C.cast(self.parts, C.c_void_p),
+                            self.lds.ctypes.data_as(C.c_void_p), self.y_ptr, max(self.local.nrows, 1), self.k,
+                            sync))
 
     def mulv(self):
         """One distributed product, ordered against the peers.  Default: the library signals, runs
@@ -147,8 +162,11 @@ class ShardedSpMV:
         else:
             self.product(self.group)
 
+    mulm = mulv   # the block form: same ordering, slc_*_mulm_dist_dev underneath
+
     def y(self):
-        out = np.empty(self.local.nrows, dtype=self.local.dtype)
+        shape = self.local.nrows if self.k is None else (self.local.nrows, self.k)
+        out = np.empty(shape, dtype=self.local.dtype, order="F")
         _check(_capi.lib().slc_memcpy_d2h(C.c_void_p(out.ctypes.data), self.y_ptr, out.nbytes))
         return out
 
@@ -196,11 +214,18 @@ def bench_main(args, rank, world, local_rank, dist):
     cb = Matrix(colblock.ncols, colblock.nrows, colblock.colptr, colblock.rowidx, colblock.values)
     local = sl.transpose(cb)                                 # (r1-r0) x ntot, on the device
     del cb
-    sh = ShardedSpMV(local, splits, rank, world, dist, cpu_group)
+    k = 64 if args.workload == "cfg5mm" else None
+    sh = ShardedSpMV(local, splits, rank, world, dist, cpu_group, k=k)
     xfull = g.uniform_vector(ntot, seed=0)
-    sh.set_x(xfull[r0:r1])
     nnz_local = int(colblock.colptr[-1])
-    abytes_local = g.spmv_bytes(r1 - r0, r1 - r0, nnz_local)   # every x entry is read from HBM once, by its owner
+    if k is None:
+        sh.set_x(xfull[r0:r1])
+        abytes_local = g.spmv_bytes(r1 - r0, r1 - r0, nnz_local)   # every x entry is read from HBM once, by its owner
+    else:
+        # column j of the block is x scaled by 1 + j/64, so one host SpMV checks all 64 columns
+        colscale = 1.0 + np.arange(k) / 64.0
+        sh.set_x(np.asfortranarray(xfull[r0:r1, None] * colscale[None, :]))
+        abytes_local = g.spmm_bytes(r1 - r0, r1 - r0, nnz_local, k)
     tot = torch.tensor([float(abytes_local), float(nnz_local)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tot)
@@ -212,6 +237,8 @@ def bench_main(args, rank, world, local_rank, dist):
     # parity on this rank's rows: y_local = (column block)^T x, summed on the host
     want = np.add.reduceat(colblock.values * xfull[colblock.rowidx], colblock.colptr[:-1].astype(np.int64))
     got = sh.y()
+    if k is not None:
+        want = want[:, None] * colscale[None, :]
     err = float(np.linalg.norm(got - want) / max(np.linalg.norm(want), 1e-300))
 
     sampler = B.ClockSampler(local_rank)
@@ -243,9 +270,13 @@ def bench_main(args, rank, world, local_rank, dist):
     e2e = None
     if not args.no_e2e:
         lib = _capi.lib()
-        xp = torch.from_numpy(np.ascontiguousarray(xfull[r0:r1])).pin_memory()
-        yp = torch.empty(r1 - r0, dtype=torch.float64).pin_memory()
-        steps_e2e = max(3, min(args.steps, 20))
+        ncol = 1 if k is None else k
+        if k is None:
+            xp = torch.from_numpy(np.ascontiguousarray(xfull[r0:r1])).pin_memory()
+        else:
+            xp = torch.from_numpy(np.ascontiguousarray((xfull[r0:r1, None] * colscale[None, :]).T)).pin_memory()
+        yp = torch.empty((r1 - r0) * ncol, dtype=torch.float64).pin_memory()
+        steps_e2e = max(3, min(args.steps, 20 if k is None else 5))
 
         def hstep():
             _check(lib.slc_memcpy_h2d(sh.x_ptr, C.c_void_p(xp.data_ptr()), xp.numel() * 8))
@@ -265,19 +296,24 @@ def bench_main(args, rank, world, local_rank, dist):
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         dt = float(dt.item())
         e2e = {"value": abytes / dt / 1e9, "unit": "GB/s", "ms_per_step": dt * 1e3, "steps": steps_e2e,
-               "h2d_bytes_per_step": int(ntot * 8), "d2h_bytes_per_step": int(ntot * 8),
-               "api": "ShardedSpMV (slc_memcpy_h2d + slc_d_mulv_dist_dev + slc_memcpy_d2h per rank)"}
+               "h2d_bytes_per_step": int(ntot * 8 * ncol), "d2h_bytes_per_step": int(ntot * 8 * ncol),
+               "api": "ShardedSpMV (slc_memcpy_h2d + slc_d_%s_dist_dev + slc_memcpy_d2h per rank)"
+                      % ("mulv" if k is None else "mulm")}
 
     if rank == 0:
         peak, peak_src = B.peaks()
         per_gpu = value / world
         line = {
-            "metric": B.METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+            "metric": B.METRIC if k is None else "spmm_effective_hbm_gbps", "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic (seeded numpy PCG64)",
-            "config": {"workload": "cfg5: 3D 27-point stencil %dx%dx%d, Double SpMV, row-partitioned in z-slabs over %d GPU(s); "
-                                   "halo entries gathered from peer HBM over NVLink inside the product kernel; "
-                                   "the inter-GPU barrier (peer-memory flags) is fused into the same launch" % (shape + (world,)),
+            "config": {"workload": ("cfg5: 3D 27-point stencil %dx%dx%d, Double SpMV, row-partitioned in z-slabs over %d GPU(s); "
+                                    "halo entries gathered from peer HBM over NVLink inside the product kernel; "
+                                    "the inter-GPU barrier (peer-memory flags) is fused into the same launch" % (shape + (world,)))
+                       if k is None else
+                       ("cfg5: 3D 27-point stencil %dx%dx%d, Double SpMM k=64, row-partitioned in z-slabs over %d GPU(s); "
+                        "signal, interior rows (k_spmm_panel), wait, boundary rows gathering the peers' rows of X "
+                        "over NVLink (k_spmm_boundary)" % (shape + (world,))),
                        "rows": ntot, "nnz": nnz, "algorithmic_bytes_per_step": abytes,
                        "plan": local.device().plan_info(),
                        "l2": "inputs larger than L2 (%.0f MB per GPU per step)" % (abytes / world / 1e6),
@@ -285,9 +321,11 @@ def bench_main(args, rank, world, local_rank, dist):
                        "max_rel_err_vs_host_sum": float(errt.item())},
             "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e,
             "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": "k_spmv_sell_dist",
+                         "traffic": None, "peak_source": peak_src,
+                         "kernel": "k_spmv_sell_dist" if k is None else "k_spmm_panel + k_spmm_boundary",
                          "note": "per-GPU figure; step time includes the inter-GPU barrier",
-                         "barrier": "nccl all-reduce" if sh.use_nccl_barrier else "peer-memory flags, fused in k_spmv_sell_dist",
+                         "barrier": "nccl all-reduce" if sh.use_nccl_barrier else
+                         ("peer-memory flags, fused in k_spmv_sell_dist" if k is None else "peer-memory flags (signal / wait kernels)"),
                          "barrier_timed_out": sh.timed_out()},
             "cpu_baseline": None,
         }

@@ -57,6 +57,48 @@ def test_partitioned_operand_matches_oracle(sl, dtype, kind):
             lib.slc_dev_free(p)
 
 
+@pytest.mark.parametrize("dtype", [np.float64, np.complex128])
+def test_partitioned_block_product_matches_oracle(sl, dtype):
+    """slc_*_mulm_dist_dev: X partitioned by row blocks, each part with its own leading dimension;
+    every (row, column) is owned by one thread, so the result is the oracle's bit for bit."""
+    lib = sl._capi.lib()
+    rng = np.random.default_rng(13)
+    pfx = "z" if np.dtype(dtype).kind == "c" else "d"
+    fn = getattr(lib, "slc_%s_mulm_dist_dev" % pfx)
+    for gm, nparts, k in ((g.stencil3d_27pt((8, 6, 7), dtype), 4, 11), (g.laplace2d_5pt(30, dtype), 3, 5),
+                          (g.stencil3d_27pt((12, 12, 10), dtype), 2, 64)):
+        om = oracle.csc(*gm)
+        X = rng.uniform(-1, 1, (gm.ncols, k)).astype(dtype)
+        if np.dtype(dtype).kind == "c":
+            X = X + 1j * rng.uniform(-1, 1, (gm.ncols, k))
+        X = np.asfortranarray(X)
+        want = oracle.mulm(om, X)
+        xs = sharded.uniform_splits(gm.ncols, nparts).astype(np.int32)
+        lds = np.array([int(xs[p + 1] - xs[p]) + 3 * p for p in range(nparts)], dtype=np.int64)   # padded blocks
+        parts = []
+        for p in range(nparts):
+            blk = np.zeros((lds[p], k), dtype=dtype, order="F")
+            blk[: xs[p + 1] - xs[p]] = X[xs[p]:xs[p + 1]]
+            parts.append(_dev_array(sl, blk))
+        table = (C.c_void_p * nparts)(*[p.value for p in parts])
+        rs = sharded.uniform_splits(gm.nrows, nparts)
+        out = []
+        for rank in range(nparts):
+            blk = sharded.row_block(gm, rs[rank], rs[rank + 1])
+            m = to_matrix(sl, blk)
+            Y = np.zeros((blk.nrows, k), dtype=dtype, order="F")
+            Yd = _dev_array(sl, Y)
+            rc = fn(m.device().handle, nparts, rank, xs.ctypes.data_as(C.c_void_p), C.cast(table, C.c_void_p),
+                    lds.ctypes.data_as(C.c_void_p), Yd, blk.nrows, k, None)
+            assert rc == 0, sl._capi.last_error()
+            assert lib.slc_memcpy_d2h(C.c_void_p(Y.ctypes.data), Yd, Y.nbytes) == 0
+            lib.slc_dev_free(Yd)
+            out.append(Y)
+        np.testing.assert_array_equal(np.concatenate(out, axis=0), want)
+        for p in parts:
+            lib.slc_dev_free(p)
+
+
 def test_sharded_wrapper_single_rank(sl):
     gm = g.stencil3d_27pt((10, 9, 8))
     m = to_matrix(sl, gm)
