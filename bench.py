@@ -110,7 +110,9 @@ def build_workload(name, grid=0):
 def hot_kernel(plan, k, dm):
     """Name of the kernel one step launches (what the roofline object describes)."""
     if k == 1:
-        return "k_spmv_sell" if "sell" in plan else "k_spmv_merge + k_spmv_bal_fixup"
+        if "sell" in plan:
+            return "k_spmv_sell"
+        return ("k_spmv_merge" if plan.startswith("csr-merge") else "k_spmv_bal") + " + k_spmv_bal_fixup"
     if "sell" not in plan:
         return "k_spmm_rows"
     maxlen = int(plan.split("max_rowlen=")[1].split()[0])

@@ -106,8 +106,9 @@ int slc_z_download(const slc_matrix *m, int32_t *colptr, int32_t *rowidx, double
 /* Build the row-major mirror and the product plan now instead of at the first product. */
 int slc_prepare(slc_matrix *m);
 /* Force the SpMV kernel family for this handle: 0 auto, 1 sliced-ELL (row per thread),
-   2 CSR row-per-warp, 3 CSR nnz-balanced (merge-style kernel), 4 CSR nnz-balanced with products
-   staged in shared memory.  For benchmarking; results are unchanged up to summation order. */
+   2 CSR row-per-warp, 3 CSR nnz-balanced with products staged in shared memory, 4 CSR nnz-balanced
+   merge-style (registers + segmented scan).  For benchmarking; results are unchanged up to
+   summation order. */
 int slc_set_spmv_kernel(slc_matrix *m, int kind);
 /* One-line description of the plan ("sell32 slices=... pad=...%"), for logs. */
 int slc_plan_info(const slc_matrix *m, char *buf, int32_t buflen);

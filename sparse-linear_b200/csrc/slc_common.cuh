@@ -98,8 +98,8 @@ enum SpmvKind : int {
   SPMV_AUTO = 0,
   SPMV_SELL = 1,
   SPMV_CSR_WARP = 2,
-  SPMV_CSR_BALANCED = 3,       // nnz chunks, merge-style kernel (k_spmv_merge)
-  SPMV_CSR_BALANCED_SMEM = 4,  // nnz chunks, products staged in shared memory (k_spmv_bal)
+  SPMV_CSR_BALANCED = 3,  // nnz chunks, products staged in shared memory (k_spmv_bal)
+  SPMV_CSR_MERGE = 4,     // nnz chunks, merge-style: registers + segmented scan (k_spmv_merge)
 };
 
 // Sliced-ELL plan (slices of 32 rows, column-major inside a slice, row per thread).

@@ -39,11 +39,48 @@ constexpr int MERGE_UB = 256;
 
 // ---- pass 0: products per column, classification ------------------------------------------------
 
-__global__ void k_mm_upper(int32_t bc, const int32_t *__restrict__ bp, const int32_t *__restrict__ bi,
-                           const int32_t *__restrict__ ap, int32_t *__restrict__ ub,
-                           int32_t *__restrict__ klass, int32_t *__restrict__ class_count, int merge_ok) {
+// Columns are bucketed by class with a STABLE split (block histograms, one scan, ranks inside the
+// block): inside a class the columns keep their ascending order, so the 32 columns a warp of the
+// product kernels takes are consecutive wherever the class does not change -- which is what lets
+// k_mm_merge stream a warp's slice of C out as one contiguous range.  Bin NCLASS collects the
+// columns with no product at all.
+constexpr int MM_BINS = NCLASS + 1;
+constexpr int MM_SPLIT_THREADS = 256;
+
+__device__ __forceinline__ int mm_class_of(int32_t nb, int64_t total, int merge_ok) {
+  if (total == 0) return NCLASS;
+  if (merge_ok && nb <= 4 && total <= MERGE_UB) return CLS_MERGE4;
+  if (merge_ok && nb <= 8 && total <= MERGE_UB) return CLS_MERGE8;
+  if (total <= CLASS_UB0) return CLS_HASH0;
+  if (total <= CLASS_UB1) return CLS_HASH1;
+  if (total <= CLASS_UB2) return CLS_HASH2;
+  return CLS_DENSE;
+}
+
+// rank of this thread among the threads of its block that hold the same bin, and the block's count
+// per bin (valid in counts[] after the call for threadIdx.x < MM_BINS)
+__device__ __forceinline__ int32_t mm_block_rank(int bin, int32_t (&wcount)[MM_SPLIT_THREADS / 32][MM_BINS]) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int32_t rank = 0;
+#pragma unroll
+  for (int c = 0; c < MM_BINS; ++c) {
+    const unsigned m = __ballot_sync(0xffffffffu, bin == c);
+    if (lane == 0) wcount[warp][c] = __popc(m);
+    if (bin == c) rank = __popc(m & ((1u << lane) - 1u));
+  }
+  __syncthreads();
+  if (bin >= 0)
+    for (int w = 0; w < warp; ++w) rank += wcount[w][bin];
+  return rank;
+}
+
+__global__ void __launch_bounds__(MM_SPLIT_THREADS)
+k_mm_upper(int32_t bc, int32_t nblocks, const int32_t *__restrict__ bp, const int32_t *__restrict__ bi,
+           const int32_t *__restrict__ ap, int32_t *__restrict__ ub, int32_t *__restrict__ klass,
+           int32_t *__restrict__ block_counts, int merge_ok) {
+  __shared__ int32_t wcount[MM_SPLIT_THREADS / 32][MM_BINS];
   const int32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-  int cls = -1;
+  int bin = -1;
   if (j < bc) {
     int64_t total = 0;
     const int32_t q0 = bp[j], q1 = bp[j + 1];
@@ -52,40 +89,25 @@ __global__ void k_mm_upper(int32_t bc, const int32_t *__restrict__ bp, const int
       total += ap[k + 1] - ap[k];
     }
     ub[j] = total > 0x7fffffffLL ? 0x7fffffff : (int32_t)total;
-    if (total == 0) cls = -1;
-    else if (merge_ok && q1 - q0 <= 4 && total <= MERGE_UB) cls = CLS_MERGE4;
-    else if (merge_ok && q1 - q0 <= 8 && total <= MERGE_UB) cls = CLS_MERGE8;
-    else if (total <= CLASS_UB0) cls = CLS_HASH0;
-    else if (total <= CLASS_UB1) cls = CLS_HASH1;
-    else if (total <= CLASS_UB2) cls = CLS_HASH2;
-    else cls = CLS_DENSE;
-    klass[j] = cls;
+    bin = mm_class_of(q1 - q0, total, merge_ok);
+    klass[j] = bin;
   }
-  // warp-aggregated class histogram
-  for (int c = 0; c < NCLASS; ++c) {
-    const unsigned m = __ballot_sync(0xffffffffu, cls == c);
-    if (m && (threadIdx.x & 31) == (__ffs(m) - 1)) atomicAdd(class_count + c, __popc(m));
+  (void)mm_block_rank(bin, wcount);
+  if (threadIdx.x < MM_BINS) {  // bin-major table: one scan turns it into output offsets
+    int32_t t = 0;
+    for (int w = 0; w < MM_SPLIT_THREADS / 32; ++w) t += wcount[w][threadIdx.x];
+    block_counts[(int64_t)threadIdx.x * nblocks + blockIdx.x] = t;
   }
 }
 
-// Bucket the column ids by class.  Order inside a class follows block scheduling (roughly
-// ascending, which keeps neighbouring groups on neighbouring columns of A); results do not
-// depend on it because every column writes to its own range of C.
-__global__ void k_mm_bucket(int32_t bc, const int32_t *__restrict__ klass,
-                            const int32_t *__restrict__ class_base, int32_t *__restrict__ cursor,
-                            int32_t *__restrict__ cols) {
+__global__ void __launch_bounds__(MM_SPLIT_THREADS)
+k_mm_bucket(int32_t bc, int32_t nblocks, const int32_t *__restrict__ klass,
+            const int32_t *__restrict__ block_offsets, int32_t *__restrict__ cols) {
+  __shared__ int32_t wcount[MM_SPLIT_THREADS / 32][MM_BINS];
   const int32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-  const int cls = j < bc ? klass[j] : -1;
-  for (int c = 0; c < NCLASS; ++c) {
-    const unsigned m = __ballot_sync(0xffffffffu, cls == c);
-    if (!m) continue;
-    const int lane = threadIdx.x & 31;
-    const int leader = __ffs(m) - 1;
-    int base = 0;
-    if (lane == leader) base = atomicAdd(cursor + c, __popc(m));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (cls == c) cols[class_base[c] + base + __popc(m & ((1u << lane) - 1))] = j;
-  }
+  const int bin = j < bc ? klass[j] : -1;
+  const int32_t rank = mm_block_rank(bin, wcount);
+  if (bin >= 0) cols[block_offsets[(int64_t)bin * nblocks + blockIdx.x] + rank] = j;
 }
 
 // ---- thread-per-column merge --------------------------------------------------------------------
@@ -96,17 +118,27 @@ __global__ void k_mm_bucket(int32_t bc, const int32_t *__restrict__ klass,
 // counts the distinct rows (symbolic pass).
 constexpr int32_t ROW_END = 0x7fffffff;  // past every valid row index
 
+// Output staging (numeric pass).  A thread emits its column one (row, value) at a time, so written
+// directly each store instruction of a warp touches 32 different sectors (launch list, round 1: the
+// numeric merge took 7x the symbolic one).  When the 32 columns of a warp are consecutive -- the
+// bucket order keeps them so except at class boundaries -- their slice of C is one contiguous range:
+// the lanes park their entries in the warp's shared-memory window at (position in C - start of the
+// range) and the warp then streams the window out with fully coalesced stores.
+constexpr int MERGE_STAGE = 1024;  // entries per warp window (12 or 20 KB per warp)
+
 template <class T, int NB, bool NUMERIC>
 __global__ void __launch_bounds__(128)
 k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32_t *__restrict__ ap,
            const int32_t *__restrict__ ai, const T *__restrict__ av, const int32_t *__restrict__ bp,
            const int32_t *__restrict__ bi, const T *__restrict__ bv, int32_t *__restrict__ cnt,
-           const int32_t *__restrict__ cp, int32_t *__restrict__ ci, T *__restrict__ cv) {
+           const int32_t *__restrict__ cp, int32_t *__restrict__ ci, T *__restrict__ cv, int stage) {
+  extern __shared__ __align__(16) unsigned char merge_smem[];
   const int32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
-  if (slot >= ncols_in_class) return;
-  const int32_t j = cols[slot];
-  const int32_t q0 = bp[j];
-  const int32_t nb = bp[j + 1] - q0;
+  const bool active = slot < ncols_in_class;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int32_t j = active ? cols[slot] : -1;
+  const int32_t q0 = active ? bp[j] : 0;
+  const int32_t nb = active ? bp[j + 1] - q0 : 0;
   int32_t p[NB], pe[NB], head[NB];
   T b[NB];
 #pragma unroll
@@ -126,10 +158,29 @@ k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32
   int32_t count = 0;
   int32_t *co = nullptr;
   T *vo = nullptr;
+  bool staged = false;
+  int32_t wbase = 0, wtotal = 0;
   if (NUMERIC) {
-    const int32_t base = cp[j];
+    const int32_t base = active ? cp[j] : 0;
+    const int32_t bend = active ? cp[j + 1] : 0;
     co = ci + base;
     vo = cv + base;
+    if (stage) {  // warp-uniform decision
+      const unsigned live = __ballot_sync(0xffffffffu, active);
+      const int32_t jfirst = __shfl_sync(0xffffffffu, j, 0);
+      const bool consecutive = __all_sync(0xffffffffu, !active || j == jfirst + lane);
+      const int last = 31 - __clz(live | 1u);
+      wbase = __shfl_sync(0xffffffffu, base, 0);
+      wtotal = __shfl_sync(0xffffffffu, bend, last) - wbase;
+      staged = live != 0 && consecutive && wtotal <= MERGE_STAGE;
+      if (staged) {
+        int32_t *s_i = reinterpret_cast<int32_t *>(merge_smem) + (size_t)warp * MERGE_STAGE;
+        T *s_v = reinterpret_cast<T *>(merge_smem + (size_t)(blockDim.x >> 5) * MERGE_STAGE * sizeof(int32_t)) +
+                 (size_t)warp * MERGE_STAGE;
+        co = s_i + (base - wbase);
+        vo = s_v + (base - wbase);
+      }
+    }
   }
   for (;;) {
     int32_t m = head[0];
@@ -151,16 +202,34 @@ k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32
     }
     ++count;
   }
-  if (!NUMERIC) cnt[j] = count;
+  if (!NUMERIC) {
+    if (active) cnt[j] = count;
+    return;
+  }
+  if (staged) {
+    __syncwarp();
+    const int32_t *s_i = reinterpret_cast<const int32_t *>(merge_smem) + (size_t)warp * MERGE_STAGE;
+    const T *s_v = reinterpret_cast<const T *>(merge_smem + (size_t)(blockDim.x >> 5) * MERGE_STAGE * sizeof(int32_t)) +
+                   (size_t)warp * MERGE_STAGE;
+    for (int32_t e = lane; e < wtotal; e += 32) {
+      ci[wbase + e] = s_i[e];
+      cv[wbase + e] = s_v[e];
+    }
+  }
 }
 
 template <class T, int NB, bool NUMERIC>
 static int run_merge(int32_t n, const int32_t *cols, const slc_matrix *a, const slc_matrix *b, int32_t *cnt,
                      slc_matrix *c) {
   if (n == 0) return SLC_OK;
-  k_mm_merge<T, NB, NUMERIC><<<(unsigned)ceil_div(n, 128), 128, 0, cur_stream()>>>(
+  static const char *stage_env = getenv("SLC_MM_STAGE");  // SLC_MM_STAGE=0: direct (uncoalesced) stores
+  const int stage = NUMERIC && !(stage_env && stage_env[0] == '0');
+  const size_t smem = stage ? (size_t)(128 / 32) * MERGE_STAGE * (sizeof(int32_t) + sizeof(T)) : 0;
+  auto kern = k_mm_merge<T, NB, NUMERIC>;
+  if (smem > 48 * 1024) SLC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(unsigned)ceil_div(n, 128), 128, smem, cur_stream()>>>(
       n, cols, a->colptr, a->rowidx, (const T *)a->vals, b->colptr, b->rowidx, (const T *)b->vals, cnt,
-      c ? c->colptr : nullptr, c ? c->rowidx : nullptr, c ? (T *)c->vals : nullptr);
+      c ? c->colptr : nullptr, c ? c->rowidx : nullptr, c ? (T *)c->vals : nullptr, stage);
   SLC_LAUNCHED();
   return SLC_OK;
 }
@@ -465,31 +534,31 @@ static int mm_entry(const slc_matrix *a, const slc_matrix *b, slc_matrix **out) 
   cudaStream_t s = cur_stream();
   const int32_t ar = a->nrows, bc = b->ncols;
 
-  // pass 0
-  DevBuf<int32_t> ub, klass, ccount, cols, cnt, cursor, cbase;
+  // pass 0: products per column, class, stable split of the column ids by class
+  DevBuf<int32_t> ub, klass, cols, cnt, btab;
   SLC_TRY(ub.alloc((size_t)bc));
   SLC_TRY(klass.alloc((size_t)bc));
-  SLC_TRY(ccount.alloc(NCLASS));
-  SLC_TRY(cursor.alloc(NCLASS));
-  SLC_TRY(cbase.alloc(NCLASS));
   SLC_TRY(cols.alloc((size_t)bc));
   SLC_TRY(cnt.alloc((size_t)bc + 1));
-  SLC_CUDA(cudaMemsetAsync(ccount.p, 0, NCLASS * sizeof(int32_t), s));
-  SLC_CUDA(cudaMemsetAsync(cursor.p, 0, NCLASS * sizeof(int32_t), s));
   SLC_CUDA(cudaMemsetAsync(cnt.p, 0, ((size_t)bc + 1) * sizeof(int32_t), s));
-  int32_t hcount[NCLASS] = {}, hbase[NCLASS] = {};
+  int32_t hcount[MM_BINS] = {}, hbase[MM_BINS + 1] = {};
   const char *merge_env = getenv("SLC_MM_MERGE");  // SLC_MM_MERGE=0: hash tables for every column
   const int merge_ok = !(merge_env && merge_env[0] == '0');
   if (bc > 0) {
-    const unsigned nb = (unsigned)ceil_div(bc, 256);
-    k_mm_upper<<<nb, 256, 0, s>>>(bc, b->colptr, b->rowidx, a->colptr, ub.p, klass.p, ccount.p, merge_ok);
+    const int32_t nb = (int32_t)ceil_div(bc, MM_SPLIT_THREADS);
+    SLC_TRY(btab.alloc((size_t)nb * MM_BINS));
+    k_mm_upper<<<(unsigned)nb, MM_SPLIT_THREADS, 0, s>>>(bc, nb, b->colptr, b->rowidx, a->colptr, ub.p, klass.p,
+                                                         btab.p, merge_ok);
     SLC_LAUNCHED();
-    SLC_CUDA(cudaMemcpyAsync(hcount, ccount.p, sizeof hcount, cudaMemcpyDeviceToHost, s));
+    SLC_TRY(exclusive_scan_i32(btab.p, btab.p, (int64_t)nb * MM_BINS));
+    // first offset of every bin = where its columns start in cols[]
+    SLC_CUDA(cudaMemcpy2DAsync(hbase, sizeof(int32_t), btab.p, (size_t)nb * sizeof(int32_t), sizeof(int32_t),
+                               MM_BINS, cudaMemcpyDeviceToHost, s));
+    k_mm_bucket<<<(unsigned)nb, MM_SPLIT_THREADS, 0, s>>>(bc, nb, klass.p, btab.p, cols.p);
+    SLC_LAUNCHED();
     SLC_CUDA(cudaStreamSynchronize(s));
-    for (int c = 1; c < NCLASS; ++c) hbase[c] = hbase[c - 1] + hcount[c - 1];
-    SLC_CUDA(cudaMemcpyAsync(cbase.p, hbase, sizeof hbase, cudaMemcpyHostToDevice, s));
-    k_mm_bucket<<<nb, 256, 0, s>>>(bc, klass.p, cbase.p, cursor.p, cols.p);
-    SLC_LAUNCHED();
+    hbase[MM_BINS] = bc;
+    for (int c = 0; c < MM_BINS; ++c) hcount[c] = hbase[c + 1] - hbase[c];
   }
 
   // dense-fallback workspace, bounded to ~4 GB

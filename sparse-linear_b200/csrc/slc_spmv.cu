@@ -284,7 +284,7 @@ static int ensure_plan(slc_matrix *m) {
     kind = regular ? SPMV_SELL : SPMV_CSR_BALANCED;
   }
   if (kind == SPMV_SELL) SLC_TRY(fill_sell<T>(m));
-  if (kind == SPMV_CSR_BALANCED || kind == SPMV_CSR_BALANCED_SMEM) SLC_TRY(build_balanced(m));
+  if (kind == SPMV_CSR_BALANCED || kind == SPMV_CSR_MERGE) SLC_TRY(build_balanced(m));
   m->spmv_active = kind;
   return SLC_OK;
 }
@@ -456,7 +456,7 @@ k_spmv_csr_warp(int32_t nrows, const int32_t *__restrict__ rowptr, const int32_t
 // chunk goes to part_tail[b].  k_spmv_bal_fixup then adds the pieces of each spanning row in order.
 template <class T, bool ACC, class XA>
 __global__ void __launch_bounds__(BAL_THREADS)
-k_spmv_bal(int32_t nrows, int64_t nnz, const int32_t *__restrict__ rowptr,
+k_spmv_bal(int32_t nrows, int64_t nnz, uint32_t zmask, int batch, const int32_t *__restrict__ rowptr,
            const int32_t *__restrict__ colidx, const T *__restrict__ vals,
            const int32_t *__restrict__ first_owned, const XA xa, T *__restrict__ y,
            T *__restrict__ part_head, T *__restrict__ part_tail) {
@@ -479,10 +479,22 @@ k_spmv_bal(int32_t nrows, int64_t nnz, const int32_t *__restrict__ rowptr,
       c[i] = ok ? ld_stream(colidx + start + e, pol_s) : 0;
       a[i] = ok ? ld_stream(vals + start + e, pol_s) : Num<T>::zero();
     }
+    if (batch && cnt == BAL_CHUNK) {  // full chunk: the 8 gathers of a thread are issued together (probe/tie)
+      T xv[BAL_ITEMS];
 #pragma unroll
-    for (int i = 0; i < BAL_ITEMS; ++i) {
-      const int32_t e = i * BAL_THREADS + tid;
-      if (e < cnt) prod[e] = Num<T>::mul(a[i], xa(c[i], pol_x));
+      for (int i = 0; i < BAL_ITEMS; ++i) xv[i] = xa(c[i], pol_x);
+      uint32_t r = 0;
+#pragma unroll
+      for (int i = 0; i < BAL_ITEMS; ++i) r |= probe(xv[i]);
+      tie(xv[0], r & zmask);
+#pragma unroll
+      for (int i = 0; i < BAL_ITEMS; ++i) prod[i * BAL_THREADS + tid] = Num<T>::mul(a[i], xv[i]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < BAL_ITEMS; ++i) {
+        const int32_t e = i * BAL_THREADS + tid;
+        if (e < cnt) prod[e] = Num<T>::mul(a[i], xa(c[i], pol_x));
+      }
     }
   }
   __syncthreads();
@@ -807,30 +819,31 @@ k_spmm_rows(int32_t nrows, int32_t ntiles, const int64_t *__restrict__ slice_ptr
 // instructions per (row, column) with LMAX = 8 on 5-entry rows), so LMAX is instantiated to the
 // matrix's exact longest row and a warp whose 32 rows are all full-length runs a branch-free,
 // predicate-free column loop; only boundary warps and the last partial column tile pay for predicates.
-template <class T, int JT, int LMAX, bool FULL>
+template <class T, int JT, int LMAX, bool FULL, bool PIPE>
 __device__ __forceinline__ void spmm_short_columns(const int32_t (&c)[LMAX], const T (&a)[LMAX], int32_t len,
                                                    const T *__restrict__ X, int64_t ldx, T *__restrict__ Yrow,
                                                    int64_t ldy, int32_t jbeg, int32_t jend, uint64_t pol_x,
                                                    uint32_t zmask) {
-  int32_t j0 = jbeg;
-  for (; j0 + JT <= jend; j0 += JT) {
+  // the LMAX*JT gathers of the column tile that starts at j0
+  auto load = [&](T (&xv)[LMAX][JT], int32_t j0) {
     const T *xb = X + (int64_t)j0 * ldx;
-    T xv[LMAX][JT];
 #pragma unroll
     for (int u = 0; u < LMAX; ++u)
 #pragma unroll
       for (int j = 0; j < JT; ++j)
         xv[u][j] = (FULL || u < len) ? ld_gather(xb + (int64_t)j * ldx + c[u], pol_x) : Num<T>::zero();
-    {  // all LMAX*JT gathers are issued before the first product (see probe/tie)
-      uint32_t r = 0;
+  };
+  // products of the tile, in the reference's order per column; no product issues before every gather
+  // of the tile has been issued (see probe/tie)
+  auto finish = [&](T (&xv)[LMAX][JT], int32_t j0) {
+    uint32_t r = 0;
 #pragma unroll
-      for (int u = 0; u < LMAX; ++u)
+    for (int u = 0; u < LMAX; ++u)
 #pragma unroll
-        for (int j = 0; j < JT; ++j) r |= probe(xv[u][j]);
-      r &= zmask;
+      for (int j = 0; j < JT; ++j) r |= probe(xv[u][j]);
+    r &= zmask;
 #pragma unroll
-      for (int j = 0; j < JT; ++j) tie(xv[0][j], r);
-    }
+    for (int j = 0; j < JT; ++j) tie(xv[0][j], r);
 #pragma unroll
     for (int j = 0; j < JT; ++j) {
       T acc = Num<T>::zero();
@@ -838,6 +851,33 @@ __device__ __forceinline__ void spmm_short_columns(const int32_t (&c)[LMAX], con
       for (int u = 0; u < LMAX; ++u)
         if (FULL || u < len) acc = Num<T>::add(Num<T>::mul(a[u], xv[u][j]), acc);
       st_stream(Yrow + (int64_t)(j0 + j) * ldy, acc);
+    }
+  };
+  int32_t j0 = jbeg;
+  if (PIPE) {
+    // two register buffers: the gathers of tile t+1 are issued before the products of tile t, so a
+    // warp always has a tile in flight while it computes (ptxas keeps that order: checked in SASS)
+    if (j0 + JT <= jend) {
+      T x0[LMAX][JT], x1[LMAX][JT];
+      load(x0, j0);
+      for (;;) {
+        const bool n1 = j0 + 2 * JT <= jend;
+        if (n1) load(x1, j0 + JT);
+        finish(x0, j0);
+        j0 += JT;
+        if (!n1) break;
+        const bool n2 = j0 + 2 * JT <= jend;
+        if (n2) load(x0, j0 + JT);
+        finish(x1, j0);
+        j0 += JT;
+        if (!n2) break;
+      }
+    }
+  } else {
+    for (; j0 + JT <= jend; j0 += JT) {
+      T xv[LMAX][JT];
+      load(xv, j0);
+      finish(xv, j0);
     }
   }
   for (; j0 < jend; ++j0) {  // last partial tile, one column at a time
@@ -856,7 +896,7 @@ __device__ __forceinline__ void spmm_short_columns(const int32_t (&c)[LMAX], con
 // 32-row slices S rows apart, block b of a chunk of W*S rows taking slices {b + w*S/32}.  The window
 // of X that warp w gathers around column r+S is then the window warp w+1 gathers around its own
 // diagonal, so it is fetched from L2 once per block (L1 hit for the others) instead of once per warp.
-template <class T, int JT, int LMAX, bool SELL>
+template <class T, int JT, int LMAX, bool SELL, bool PIPE>
 __global__ void __launch_bounds__(256)
 k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, int32_t stride32, uint32_t zmask,
              const int64_t *__restrict__ slice_ptr,
@@ -902,9 +942,9 @@ k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, int32_t stride32, u
   const int32_t jbeg = grp * jgroup;
   const int32_t jend = min(k, jbeg + jgroup);
   if (full)
-    spmm_short_columns<T, JT, LMAX, true>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x, zmask);
+    spmm_short_columns<T, JT, LMAX, true, PIPE>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x, zmask);
   else
-    spmm_short_columns<T, JT, LMAX, false>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x, zmask);
+    spmm_short_columns<T, JT, LMAX, false, false>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x, zmask);
 }
 
 // Longer rows (SELL plan, e.g. the 27-point stencil): a block owns blockDim.x consecutive rows and ALL
@@ -917,7 +957,7 @@ k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, int32_t stride32, u
 // this replaces (k_spmm_rows): A was streamed 16 times (11.4 GB DRAM reads for 6.7 GB compulsory)
 // and half of the stall samples sat between an index load and the gather that needs it.
 template <class T, int JT, int KU>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(512)
 k_spmm_panel(int32_t row_begin, int32_t row_end, int32_t kcap, uint32_t zmask, const int64_t *__restrict__ slice_ptr,
              const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
              const T *__restrict__ vals, const T *__restrict__ X, int64_t ldx, T *__restrict__ Y,
@@ -1102,10 +1142,13 @@ static int spmv_run(slc_matrix *m, const XA &xa, T *y) {
       DevBuf<T> ph, pt;
       SLC_TRY(ph.alloc((size_t)bp.nchunks));
       SLC_TRY(pt.alloc((size_t)bp.nchunks));
-      static const int smem_env = env_int("SLC_BAL_SMEM", 0);  // 1: the shared-memory kernel for kind 3 too
-      if (m->spmv_active == SPMV_CSR_BALANCED_SMEM || smem_env)
+      // measured on B200, R-MAT scale 24: shared-memory kernel 1.51 ms, merge-style kernel 1.95 ms
+      // (both bound by the number of random 32-byte gathers an SM keeps in flight)
+      static const int batch_env = env_int("SLC_BAL_BATCH", 0);
+      if (m->spmv_active == SPMV_CSR_BALANCED)
         k_spmv_bal<T, ACC, XA><<<(unsigned)bp.nchunks, BAL_THREADS, 0, s>>>(
-            m->nrows, m->nnz, m->rowptr, m->colidx, (const T *)m->rvals, bp.chunk_row, xa, y, ph.p, pt.p);
+            m->nrows, m->nnz, 0u, batch_env, m->rowptr, m->colidx, (const T *)m->rvals, bp.chunk_row, xa, y, ph.p,
+            pt.p);
       else
         k_spmv_merge<T, ACC, XA><<<(unsigned)bp.nchunks, BAL_THREADS, 0, s>>>(
             m->nrows, m->nnz, 0u, m->rowptr, m->colidx, (const T *)m->rvals, bp.chunk_row, xa, y, ph.p, pt.p);
@@ -1367,9 +1410,11 @@ static int launch_panel(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ld
   static const int smem_env = env_int("SLC_PANEL_SMEM_KB", 0);
   static const int jt_env = env_int("SLC_PANEL_JT", 0);
   static const int ku_env = env_int("SLC_PANEL_KU", 0);
-  int threads = threads_env ? threads_env : 128;
-  threads = std::max(32, std::min(256, threads / 32 * 32));
-  const int budget_kb = smem_env ? std::min(smem_env, 200) : (threads <= 128 ? 48 : 96);
+  // measured on B200, 27-point stencil 200^3, k = 64 Double: 256 threads / 96 KB 6.32 ms,
+  // 128 threads / 48 KB 8.69 ms, 64 threads 9.19 ms (a bigger row block re-fetches less of X from L2)
+  int threads = threads_env ? threads_env : 256;
+  threads = std::max(32, std::min(512, threads / 32 * 32));
+  const int budget_kb = smem_env ? std::min(smem_env, 200) : (threads <= 128 ? 48 : threads <= 256 ? 96 : 192);
   const int32_t kcap =
       std::max(1, std::min<int32_t>(m->max_rowlen, (int32_t)((size_t)budget_kb * 1024 / ((size_t)threads * (sizeof(T) + 4)))));
   // batch depth: the one that leaves fewer single-entry leftovers on the longest row
@@ -1415,16 +1460,21 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
     const bool sell = m->spmv_active == SPMV_SELL;
     const SellPlan &sp = m->sell;
     constexpr int JTS = sizeof(T) == 16 ? 2 : 4;
-#define SLC_SHORT(L_, SELL_)                                                                         \
-  k_spmm_short<T, JTS, L_, SELL_><<<(unsigned)nb, threads, 0, s>>>(                                   \
-      m->nrows, ngroups, jgroup, stride32, 0u, sp.slice_ptr, sp.rowlen, m->rowptr,                     \
+    // PIPE: two register buffers of gathers per thread (SELL plans, rows of at most 6 entries: one
+    // buffer is then at most 48 registers; see spmm_short_columns)
+    static const int pipe_env = env_int("SLC_SPMM_PIPE", 1);
+    const bool pipe = sell && pipe_env != 0;
+#define SLC_SHORT(L_, SELL_, PIPE_)                                                                  \
+  k_spmm_short<T, JTS, L_, SELL_, (PIPE_) && (L_ * JTS * sizeof(T) / 4 <= 48)><<<(unsigned)nb, threads, 0, s>>>( \
+      m->nrows, ngroups, jgroup, stride32, 0u, sp.slice_ptr, sp.rowlen, m->rowptr,                    \
       SELL_ ? sp.colidx : m->colidx, SELL_ ? (const T *)sp.vals : (const T *)m->rvals, X, ldx, Y, ldy, k)
 #define SLC_SHORT_L(L_)                                                                              \
   case L_:                                                                                           \
-    if (sell) SLC_SHORT(L_, true);                                                                   \
-    else SLC_SHORT(L_, false);                                                                       \
+    if (pipe) SLC_SHORT(L_, true, true);                                                             \
+    else if (sell) SLC_SHORT(L_, true, false);                                                       \
+    else SLC_SHORT(L_, false, false);                                                                \
     break
-    switch (m->max_rowlen) {
+    switch (m->max_rowlen < 8 ? m->max_rowlen : 8) {
       SLC_SHORT_L(1);
       SLC_SHORT_L(2);
       SLC_SHORT_L(3);
@@ -1432,9 +1482,7 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
       SLC_SHORT_L(5);
       SLC_SHORT_L(6);
       SLC_SHORT_L(7);
-      default:
-        if (sell) SLC_SHORT(8, true);
-        else SLC_SHORT(8, false);
+      SLC_SHORT_L(8);
     }
 #undef SLC_SHORT_L
 #undef SLC_SHORT
@@ -1572,7 +1620,7 @@ int slc_prepare(slc_matrix *m) {
 
 int slc_set_spmv_kernel(slc_matrix *m, int kind) {
   if (!m) return fail(SLC_ERR_INVALID, "slc_set_spmv_kernel: null handle");
-  if (kind < SPMV_AUTO || kind > SPMV_CSR_BALANCED_SMEM)
+  if (kind < SPMV_AUTO || kind > SPMV_CSR_MERGE)
     return fail(SLC_ERR_INVALID, "slc_set_spmv_kernel: unknown kernel %d", kind);
   m->spmv_kind = kind;
   return SLC_OK;
@@ -1580,7 +1628,7 @@ int slc_set_spmv_kernel(slc_matrix *m, int kind) {
 
 int slc_plan_info(const slc_matrix *m, char *buf, int32_t buflen) {
   if (!m || !buf || buflen <= 0) return fail(SLC_ERR_INVALID, "slc_plan_info: bad argument");
-  const char *names[] = {"unplanned", "sell32", "csr-warp", "csr-balanced", "csr-balanced-smem"};
+  const char *names[] = {"unplanned", "sell32", "csr-warp", "csr-balanced", "csr-merge"};
   const double pad = m->nnz ? 100.0 * (double)(m->sell.padded - m->nnz) / (double)m->nnz : 0.0;
   snprintf(buf, (size_t)buflen, "%s rows=%d cols=%d nnz=%lld max_rowlen=%d sell_padding=%.2f%% chunks=%d",
            names[m->spmv_active], m->nrows, m->ncols, (long long)m->nnz, m->max_rowlen, pad,

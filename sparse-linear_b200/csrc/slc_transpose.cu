@@ -13,14 +13,32 @@
 namespace slc {
 
 // ptr[r] = first sorted position whose key is >= r, for r in [0, nkeys]; each entry is written by
-// exactly one thread (the one sitting on the boundary that passes r).
-__global__ void k_ptrs_from_sorted(int64_t n, int32_t nkeys, const uint32_t *__restrict__ sorted,
-                                   int32_t *__restrict__ ptr) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i > n) return;
-  int64_t prev = (i == 0) ? -1 : (int64_t)sorted[i - 1];
-  int64_t cur = (i == n) ? (int64_t)nkeys : (int64_t)sorted[i];
-  for (int64_t r = prev + 1; r <= cur; ++r) ptr[r] = (int32_t)i;
+// exactly one thread (the one sitting on the boundary that passes r).  A thread takes 8 consecutive
+// keys (two 128-bit loads): with one key per thread the kernel was bound by thread turnover, not bytes.
+constexpr int PTR_ITEMS = 8;
+__global__ void __launch_bounds__(256)
+k_ptrs_from_sorted(int64_t n, int32_t nkeys, const uint32_t *__restrict__ sorted, int32_t *__restrict__ ptr) {
+  const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * PTR_ITEMS;
+  if (i0 > n) return;
+  uint32_t key[PTR_ITEMS];
+  if (i0 + PTR_ITEMS <= n) {
+    const uint4 a = *reinterpret_cast<const uint4 *>(sorted + i0);
+    const uint4 b = *reinterpret_cast<const uint4 *>(sorted + i0 + 4);
+    key[0] = a.x; key[1] = a.y; key[2] = a.z; key[3] = a.w;
+    key[4] = b.x; key[5] = b.y; key[6] = b.z; key[7] = b.w;
+  } else {
+#pragma unroll
+    for (int e = 0; e < PTR_ITEMS; ++e) key[e] = i0 + e < n ? sorted[i0 + e] : (uint32_t)nkeys;
+  }
+  int64_t prev = (i0 == 0) ? -1 : (int64_t)sorted[i0 - 1];
+#pragma unroll
+  for (int e = 0; e < PTR_ITEMS; ++e) {
+    const int64_t i = i0 + e;
+    if (i > n) break;
+    const int64_t cur = (i == n) ? (int64_t)nkeys : (int64_t)key[e];
+    for (int64_t r = prev + 1; r <= cur; ++r) ptr[r] = (int32_t)i;
+    prev = cur;
+  }
 }
 
 // column that owns stored position p: the c with colptr[c] <= p < colptr[c+1]
@@ -34,9 +52,9 @@ __device__ __forceinline__ int32_t owner_of(const int32_t *__restrict__ ptr, int
   return lo - 1;
 }
 
-// colid[p] = the column that owns stored position p.  A thread takes 8 consecutive positions: one
+// colid[p] = the column that owns stored position p.  A thread takes 16 consecutive positions: one
 // binary search for the first, then a walk along colptr (empty columns are stepped over).
-constexpr int EXPAND_ITEMS = 8;
+constexpr int EXPAND_ITEMS = 16;
 __global__ void k_expand_cols(int64_t nnz, int32_t ncols, const int32_t *__restrict__ colptr,
                               uint32_t *__restrict__ colid) {
   const int64_t p0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * EXPAND_ITEMS;
@@ -54,9 +72,10 @@ __global__ void k_expand_cols(int64_t nnz, int32_t ncols, const int32_t *__restr
     out[e] = (uint32_t)c;
   }
   if (p0 + EXPAND_ITEMS <= nnz) {
-    uint4 *dst = reinterpret_cast<uint4 *>(colid + p0);  // p0 is a multiple of 8: 32-byte aligned
-    dst[0] = make_uint4(out[0], out[1], out[2], out[3]);
-    dst[1] = make_uint4(out[4], out[5], out[6], out[7]);
+    uint4 *dst = reinterpret_cast<uint4 *>(colid + p0);  // p0 is a multiple of 16: 64-byte aligned
+#pragma unroll
+    for (int q = 0; q < EXPAND_ITEMS / 4; ++q)
+      dst[q] = make_uint4(out[4 * q], out[4 * q + 1], out[4 * q + 2], out[4 * q + 3]);
   } else {
     for (int e = 0; p0 + e < nnz; ++e) colid[p0 + e] = out[e];
   }
@@ -112,7 +131,7 @@ int transpose_csc(int32_t nrows, int32_t ncols, int64_t nnz, const int32_t *colp
   uint32_t *skey = nullptr, *sperm = nullptr;
   SLC_TRY(sort_pairs_u32(reinterpret_cast<const uint32_t *>(rowidx), k0.p, k1.p, p0.p, p1.p, nnz,
                          bits_for((uint32_t)nrows), true, &skey, &sperm));
-  k_ptrs_from_sorted<<<(unsigned)ceil_div(nnz + 1, 256), 256, 0, s>>>(nnz, nrows, skey, out_ptr);
+  k_ptrs_from_sorted<<<(unsigned)ceil_div(ceil_div(nnz + 1, PTR_ITEMS), 256), 256, 0, s>>>(nnz, nrows, skey, out_ptr);
   SLC_LAUNCHED();
   uint32_t *colid = (skey == k0.p) ? k1.p : k0.p;  // the key buffer the sort left free
   k_expand_cols<<<(unsigned)ceil_div(ceil_div(nnz, EXPAND_ITEMS), 256), 256, 0, s>>>(nnz, ncols, colptr, colid);

@@ -14,7 +14,7 @@ from sparse_linear_b200 import generators as g
 
 pytestmark = pytest.mark.gpu
 DTYPES = [np.float64, np.complex128]
-KINDS = {"auto": 0, "sell": 1, "csr-warp": 2, "csr-balanced": 3, "csr-balanced-smem": 4}
+KINDS = {"auto": 0, "sell": 1, "csr-warp": 2, "csr-balanced": 3, "csr-merge": 4}
 
 
 def vec(rng, n, dtype):
@@ -55,7 +55,7 @@ def test_mulv_and_axpy_match_oracle(sl, dtype, kind):
         np.testing.assert_array_equal(y, got2)
 
 
-@pytest.mark.parametrize("kind", ["csr-warp", "csr-balanced", "csr-balanced-smem"])
+@pytest.mark.parametrize("kind", ["csr-warp", "csr-balanced", "csr-merge"])
 @pytest.mark.parametrize("dtype", DTYPES)
 def test_mulv_irregular_rows(sl, dtype, kind):
     """Power-law-like rows: empty rows, rows spanning several nnz chunks, a dense row."""
@@ -77,7 +77,7 @@ def test_mulv_irregular_rows(sl, dtype, kind):
     assert_values_close(sl.axpy(m, x, y0), oracle.axpy(om, x, y0))
 
 
-@pytest.mark.parametrize("kind", ["csr-balanced", "csr-balanced-smem"])
+@pytest.mark.parametrize("kind", ["csr-balanced", "csr-merge"])
 @pytest.mark.parametrize("dtype", DTYPES)
 def test_mulv_balanced_chunk_edges(sl, dtype, kind):
     """Rows placed against the 2048-nonzero chunk grid of the balanced kernels: a row that is exactly
