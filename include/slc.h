@@ -140,6 +140,11 @@ int slc_d_mulm_dev(slc_matrix *a, const double *X_dev, int64_t ldx, double *Y_de
 int slc_z_mulm_dev(slc_matrix *a, const double *X_dev, int64_t ldx, double *Y_dev, int64_t ldy,
                    int32_t k);
 
+/* *flag <- nonzero if a launch of the TMA-staged block product (banded matrices with short rows) gave
+   up waiting on one of its shared-memory barriers or met a window wider than planned: its result
+   is then invalid.  A diagnostic for tests and benchmarks; 0 in normal operation. */
+int slc_spmm_window_error(int *flag);
+
 /* ---- SpGEMM: mm = (*) (Data/Matrix/Sparse.hs:691-702, ScatterGather.hs:37-147) -------- */
 
 /* C <- A B.  Structural product: an entry exists wherever a term landed, zeros are

@@ -10,7 +10,7 @@ from .matrix import (  # noqa: F401
     DeviceMatrix, Matrix, SparseLinearError,
     axpy, axpy_, cmap, compress, compress_dev, ctrans, decompress, device_count, diag, fromTriples, hermitian, ident,
     kronecker, launch_count, lin, mm, mulM, mulM_dev, mulV, mulV_dev, nonZero, scale, set_device,
-    set_stream, synchronize, transpose, zeros,
+    set_stream, spmm_window_error, synchronize, transpose, zeros,
 )
 
 __all__ = [n for n in dir() if not n.startswith("_")]

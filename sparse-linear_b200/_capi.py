@@ -37,6 +37,7 @@ SIGNATURES = {
     "slc_dims": (C.c_int, [_hp, _i32p, _i32p, C.POINTER(C.c_int64)]),
     "slc_elem_type": (C.c_int, [_hp]),
     "slc_prepare": (C.c_int, [_hp]),
+    "slc_spmm_window_error": (C.c_int, [C.POINTER(C.c_int)]),
     "slc_set_spmv_kernel": (C.c_int, [_hp, C.c_int]),
     "slc_plan_info": (C.c_int, [_hp, C.c_char_p, C.c_int32]),
     "slc_ipc_export": (C.c_int, [_vp, _vp]),

@@ -116,6 +116,8 @@ struct SellPlan {
   // distributed products: host copy of the slice ranges and the cached interior run
   std::vector<int32_t> h_cmin, h_cmax;
   int32_t interior_s0 = -1, interior_s1 = -1, interior_lo = 0, interior_hi = 0;
+  // widest column window of a 1024-row block (k_spmm_window), -1 = not measured yet
+  int32_t window_max = -1;
 };
 
 // nnz-balanced CSR plan: fixed-size chunks of nonzeros, first row of each chunk.
@@ -293,6 +295,10 @@ int transpose_csc(int32_t nrows, int32_t ncols, int64_t nnz, const int32_t *colp
                   const int32_t *rowidx, const T *vals, bool conj, int32_t *out_ptr,
                   int32_t *out_idx, T *out_vals);
 int ensure_csr(slc_matrix *m);
+
+// built in slc_spmm_window.cu: the TMA-staged SpMM for banded short-row matrices (*done = it ran)
+template <class T>
+int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, bool *done);
 
 inline int bits_for(uint32_t n) {  // bits needed to represent values in [0, n)
   int b = 1;

@@ -1,0 +1,321 @@
+// slc_spmm_window.cu -- SpMM for banded matrices with short rows (2-D stencils: the Complex Double
+// Laplacian times FEAST's 64-column subspace block): the window of X a row block needs is staged in
+// shared memory by the TMA engine, one column per pipeline stage.
+//
+// Reference: mulM / FEAST multiplyWork (Data/Matrix/Sparse.hs:473-498, Feast.hs:203-208): every
+// column of the block is an independent mulV, terms added in increasing column order.
+//
+// Why: a row block of R consecutive rows of a banded matrix gathers from ONE contiguous window
+// [wlo, whi) of a column of X (R + 2*bandwidth entries).  k_spmm_short fetches that window through
+// per-thread gathers: it needs registers for every load in flight (ncu, round 1: 94-156 registers,
+// 12-20 warps per SM, 10 exposed-latency loads per warp) and re-fetches the overlap from L2 once per
+// 128-row block (3.2x amplification on the 1024x1024 grid).  Here
+//   * one producer lane issues ONE cp.async.bulk per (row block, column): window bytes travel
+//     L2 -> shared memory with no register, no LSU instruction and no L1 allocation, arriving on an
+//     mbarrier (complete_tx); NSTAGE columns are in flight per SM whatever the consumers are doing;
+//   * 512 consumer threads own RPT = 2 rows each (a block is 1024 rows, so the window overlap is
+//     fetched once per 1024 rows), keep the rows' (column - wlo, value) pairs in registers for all k
+//     columns, read X from shared memory with conflict-free 64/128-bit loads, add in the
+//     reference's order (bit-identical) and stream Y out with coalesced stores;
+//   * full[] / empty[] mbarriers form the ring; no __syncthreads in the column loop.
+// Every mbarrier wait is bounded (WINDOW_SPIN_LIMIT probes): a protocol bug sets an error flag and
+// produces a wrong answer that the parity tests catch, it cannot hang the GPU.
+#include <cstdlib>
+
+#include "slc_common.cuh"
+
+namespace slc {
+
+constexpr int WIN_CONSUMERS = 512;             // consumer threads
+constexpr int WIN_THREADS = WIN_CONSUMERS + 32;  // + one producer warp
+constexpr int WIN_RPT = 2;                     // rows per consumer thread
+constexpr int WIN_ROWS = WIN_CONSUMERS * WIN_RPT;
+constexpr int WIN_SELL_C = 32;
+constexpr uint32_t WINDOW_SPIN_LIMIT = 1u << 22;
+
+// ---- mbarrier / bulk-copy primitives (PTX ISA 8.x, sm_90+) -------------------------------------------
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// bounded wait; returns false (and raises *err) if the phase never completed
+__device__ __forceinline__ bool mbar_wait(uint64_t *bar, uint32_t parity, int *err) {
+  for (uint32_t spin = 0; spin < WINDOW_SPIN_LIMIT; ++spin)
+    if (mbar_try_wait(bar, parity)) return true;
+  atomicExch(err, 1);
+  return false;
+}
+// global -> shared bulk copy by the TMA engine; completes `bytes` on the mbarrier.  src, dst and bytes
+// are multiples of 16.
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+__device__ __forceinline__ double lds_t(const double *p) { return *p; }
+__device__ __forceinline__ double2 lds_t(const double2 *p) { return *p; }
+
+// ---- the kernel -----------------------------------------------------------------------------------------
+
+// products of one column for this thread's rows, X read from the staged window
+template <class T, int LMAX, bool FULL>
+__device__ __forceinline__ void window_column(const int32_t (&c)[WIN_RPT][LMAX], const T (&a)[WIN_RPT][LMAX],
+                                              const int32_t (&len)[WIN_RPT], const bool (&live)[WIN_RPT],
+                                              const T *__restrict__ xs, T *__restrict__ ycol,
+                                              const int32_t (&row)[WIN_RPT]) {
+#pragma unroll
+  for (int i = 0; i < WIN_RPT; ++i) {
+    if (!FULL && !live[i]) continue;
+    T acc = Num<T>::zero();
+#pragma unroll
+    for (int u = 0; u < LMAX; ++u)
+      if (FULL || u < len[i]) acc = Num<T>::add(Num<T>::mul(a[i][u], lds_t(xs + c[i][u])), acc);
+    st_stream(ycol + row[i], acc);
+  }
+}
+
+template <class T, int LMAX>
+__global__ void __launch_bounds__(WIN_THREADS, 1)
+k_spmm_window(int32_t nrows, int32_t ncols, int32_t nslices, int32_t nstage, int32_t wcap,
+              const int64_t *__restrict__ slice_ptr, const int32_t *__restrict__ rowlen,
+              const int32_t *__restrict__ colidx, const T *__restrict__ vals,
+              const int32_t *__restrict__ slice_cmin, const int32_t *__restrict__ slice_cmax,
+              const T *__restrict__ X, int64_t ldx, T *__restrict__ Y, int64_t ldy, int32_t k,
+              int *__restrict__ err) {
+  extern __shared__ __align__(128) unsigned char win_smem[];
+  T *stage0 = reinterpret_cast<T *>(win_smem);                                              // [nstage][wcap]
+  uint64_t *full = reinterpret_cast<uint64_t *>(win_smem + (size_t)nstage * wcap * sizeof(T));  // [nstage]
+  uint64_t *empty = full + nstage;                                                          // [nstage]
+  int32_t *s_rng = reinterpret_cast<int32_t *>(empty + nstage);                             // lo, width
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int32_t row0 = blockIdx.x * WIN_ROWS;
+
+  // the block's window of columns = union of its 32 slices' ranges, 16-byte aligned in X
+  if (tid < 32) {
+    const int32_t s = row0 / WIN_SELL_C + tid;
+    int32_t lo = 0x7fffffff, hi = -1;
+    if (s < nslices) {
+      lo = __ldg(slice_cmin + s);
+      hi = __ldg(slice_cmax + s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+      hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    if (tid == 0) {
+      constexpr int32_t EPV = 16 / sizeof(T);  // elements per 16 bytes: 2 (Double) or 1 (Complex)
+      if (hi < lo) {                           // no entry in the whole block: stage one vector anyway
+        lo = 0;
+        hi = EPV - 1;
+      }
+      lo = lo / EPV * EPV;
+      int32_t end = (hi + EPV) / EPV * EPV;    // exclusive, rounded up; the host guarantees ncols % EPV == 0
+      end = min(end, ncols);
+      s_rng[0] = lo;
+      s_rng[1] = end - lo;
+      for (int st = 0; st < nstage; ++st) {
+        mbar_init(full + st, 1);
+        mbar_init(empty + st, WIN_CONSUMERS);
+      }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+  }
+  __syncthreads();
+  const int32_t wlo = s_rng[0], width = s_rng[1];
+  if (width > wcap || width <= 0) {  // cannot happen with the host's plan; never index past the stage
+    if (tid == 0) atomicExch(err, 2);
+    return;
+  }
+
+  if (tid >= WIN_CONSUMERS) {
+    // ---- producer: one lane feeds the ring -------------------------------------------------------
+    if (lane != 0) return;
+    const uint32_t bytes = (uint32_t)width * (uint32_t)sizeof(T);
+    int32_t st = 0, use = 0;  // stage index, how many times the ring has wrapped
+    for (int32_t j = 0; j < k; ++j) {
+      if (use > 0 && !mbar_wait(empty + st, (uint32_t)((use - 1) & 1), err)) return;
+      mbar_arrive_expect_tx(full + st, bytes);
+      bulk_g2s(stage0 + (size_t)st * wcap, X + (int64_t)j * ldx + wlo, bytes, full + st);
+      if (++st == nstage) {
+        st = 0;
+        ++use;
+      }
+    }
+    return;
+  }
+
+  // ---- consumers ---------------------------------------------------------------------------------------
+  const uint64_t pol_s = policy_evict_first();
+  int32_t row[WIN_RPT], len[WIN_RPT], c[WIN_RPT][LMAX];
+  bool live[WIN_RPT];
+  T a[WIN_RPT][LMAX];
+  bool mine_full = true;
+#pragma unroll
+  for (int i = 0; i < WIN_RPT; ++i) {
+    row[i] = row0 + i * WIN_CONSUMERS + tid;
+    live[i] = row[i] < nrows;
+    int64_t base = 0;
+    len[i] = 0;
+    if (live[i]) {
+      base = __ldg(slice_ptr + (row[i] >> 5)) + lane;
+      len[i] = __ldg(rowlen + row[i]);
+    }
+#pragma unroll
+    for (int u = 0; u < LMAX; ++u) {
+      const bool ok = u < len[i];
+      c[i][u] = ok ? ld_stream(colidx + base + (int64_t)u * WIN_SELL_C, pol_s) - wlo : 0;
+      a[i][u] = ok ? ld_stream(vals + base + (int64_t)u * WIN_SELL_C, pol_s) : Num<T>::zero();
+    }
+    mine_full = mine_full && live[i] && len[i] == LMAX;
+  }
+  const bool full_warp = __all_sync(0xffffffffu, mine_full);
+  int32_t st = 0;
+  uint32_t parity = 0;
+  for (int32_t j = 0; j < k; ++j) {
+    if (!mbar_wait(full + st, parity, err)) return;
+    const T *xs = stage0 + (size_t)st * wcap;
+    T *ycol = Y + (int64_t)j * ldy;
+    if (full_warp) window_column<T, LMAX, true>(c, a, len, live, xs, ycol, row);
+    else window_column<T, LMAX, false>(c, a, len, live, xs, ycol, row);
+    mbar_arrive(empty + st);  // this thread is done reading the stage
+    if (++st == nstage) {
+      st = 0;
+      parity ^= 1u;
+    }
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------------------------
+
+// widest window over the row blocks of WIN_ROWS rows (one thread per block)
+__global__ void k_window_max(int32_t nslices, const int32_t *__restrict__ slice_cmin,
+                             const int32_t *__restrict__ slice_cmax, int32_t *__restrict__ out) {
+  const int32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+  constexpr int SPB = WIN_ROWS / WIN_SELL_C;
+  if ((int64_t)b * SPB >= nslices) return;
+  int32_t lo = 0x7fffffff, hi = -1;
+  for (int s = b * SPB; s < min(nslices, (b + 1) * SPB); ++s) {
+    lo = min(lo, slice_cmin[s]);
+    hi = max(hi, slice_cmax[s]);
+  }
+  if (hi >= lo) atomicMax(out, hi - lo + 1);
+}
+
+static int *g_window_err = nullptr;  // device flag shared by every launch of this process
+
+int spmm_window_error(int *flag) {
+  *flag = 0;
+  if (!g_window_err) return SLC_OK;
+  SLC_CUDA(cudaMemcpyAsync(flag, g_window_err, sizeof(int), cudaMemcpyDeviceToHost, cur_stream()));
+  SLC_CUDA(cudaStreamSynchronize(cur_stream()));
+  return SLC_OK;
+}
+
+template <class T, int LMAX>
+static int launch_window(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, int32_t nstage,
+                         int32_t wcap) {
+  const SellPlan &sp = m->sell;
+  const size_t smem = (size_t)nstage * wcap * sizeof(T) + (size_t)nstage * 2 * sizeof(uint64_t) + 16;
+  auto kern = k_spmm_window<T, LMAX>;
+  static size_t smem_set = 0;  // per instantiation
+  if (smem > smem_set) {
+    SLC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set = smem;
+  }
+  const unsigned nb = (unsigned)ceil_div(m->nrows, WIN_ROWS);
+  kern<<<nb, WIN_THREADS, smem, cur_stream()>>>(m->nrows, m->ncols, sp.nslices, nstage, wcap, sp.slice_ptr, sp.rowlen,
+                                                sp.colidx, (const T *)sp.vals, sp.slice_cmin, sp.slice_cmax, X, ldx, Y,
+                                                ldy, k, g_window_err);
+  SLC_LAUNCHED();
+  return SLC_OK;
+}
+
+// Runs the product on the window kernel when the matrix and the operands qualify: sliced-ELL plan,
+// rows of at most 8 entries, every 1024-row block's window of X fits a pipeline stage (at least 3
+// stages in 200 KB of shared memory), X 16-byte aligned with an even column stride for Double.
+// *done says whether it did.
+template <class T>
+int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, bool *done) {
+  *done = false;
+  static const char *env = getenv("SLC_SPMM_WINDOW");
+  if (env && env[0] == '0') return SLC_OK;
+  SellPlan &sp = m->sell;
+  if (m->spmv_active != SPMV_SELL || !sp.slice_cmin || m->max_rowlen < 1 || m->max_rowlen > 8 || k < 1)
+    return SLC_OK;
+  constexpr int EPV = 16 / (int)sizeof(T);
+  if (((uintptr_t)X & 15) != 0 || m->ncols % EPV != 0 || ldx % EPV != 0) return SLC_OK;
+  cudaStream_t s = cur_stream();
+  if (sp.window_max < 0) {  // once per matrix
+    DevBuf<int32_t> w;
+    SLC_TRY(w.alloc(1));
+    SLC_CUDA(cudaMemsetAsync(w.p, 0, sizeof(int32_t), s));
+    const int32_t nblocks = (int32_t)ceil_div(sp.nslices, WIN_ROWS / WIN_SELL_C);
+    k_window_max<<<(unsigned)ceil_div(nblocks, 128), 128, 0, s>>>(sp.nslices, sp.slice_cmin, sp.slice_cmax, w.p);
+    SLC_LAUNCHED();
+    int32_t h = 0;
+    SLC_CUDA(cudaMemcpyAsync(&h, w.p, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    SLC_CUDA(cudaStreamSynchronize(s));
+    sp.window_max = h;
+  }
+  // the kernel aligns the window start down and its end up to 16 bytes: up to 2*(EPV-1) extra elements
+  const int32_t wcap = (int32_t)ceil_div((int64_t)sp.window_max + 2 * (EPV - 1), 16) * 16;
+  const size_t stage_bytes = (size_t)wcap * sizeof(T);
+  const size_t budget = 200 * 1024;
+  int32_t nstage = (int32_t)std::min<size_t>(8, budget / stage_bytes);
+  if (sp.window_max <= 0 || nstage < 3) return SLC_OK;
+  nstage = std::min(nstage, std::max(k, 2));
+  if (!g_window_err) {
+    SLC_CUDA(cudaMalloc((void **)&g_window_err, sizeof(int)));
+    SLC_CUDA(cudaMemsetAsync(g_window_err, 0, sizeof(int), s));
+  }
+  switch (m->max_rowlen) {
+#define SLC_WIN_CASE(L_) \
+  case L_:               \
+    SLC_TRY((launch_window<T, L_>(m, X, ldx, Y, ldy, k, nstage, wcap))); \
+    break
+    SLC_WIN_CASE(1);
+    SLC_WIN_CASE(2);
+    SLC_WIN_CASE(3);
+    SLC_WIN_CASE(4);
+    SLC_WIN_CASE(5);
+    SLC_WIN_CASE(6);
+    SLC_WIN_CASE(7);
+    SLC_WIN_CASE(8);
+#undef SLC_WIN_CASE
+    default:
+      return SLC_OK;
+  }
+  *done = true;
+  return SLC_OK;
+}
+
+template int spmm_window_try<double>(slc_matrix *, const double *, int64_t, double *, int64_t, int32_t, bool *);
+template int spmm_window_try<double2>(slc_matrix *, const double2 *, int64_t, double2 *, int64_t, int32_t, bool *);
+
+}  // namespace slc
+
+extern "C" int slc_spmm_window_error(int *flag) {
+  if (!flag) return slc::fail(SLC_ERR_INVALID, "slc_spmm_window_error: null argument");
+  return slc::spmm_window_error(flag);
+}

@@ -1444,7 +1444,10 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
     return SLC_OK;
   }
   SLC_TRY(ensure_plan<T>(m));
-  if (m->max_rowlen >= 1 && m->max_rowlen <= 8) {  // short rows: registers hold the row, see k_spmm_short
+  if (m->max_rowlen >= 1 && m->max_rowlen <= 8) {  // short rows: registers hold the row
+    bool done = false;  // banded: X windows staged by TMA (slc_spmm_window.cu); else per-thread gathers
+    SLC_TRY(spmm_window_try<T>(m, X, ldx, Y, ldy, k, &done));
+    if (done) return SLC_OK;
     static const int jg_env = env_int("SLC_SPMM_JG", 0);
     static const int stride_env = env_int("SLC_SPMM_STRIDE", -1);
     static const int threads_env = env_int("SLC_SPMM_THREADS", 0);
@@ -1462,7 +1465,7 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
     constexpr int JTS = sizeof(T) == 16 ? 2 : 4;
     // PIPE: two register buffers of gathers per thread (SELL plans, rows of at most 6 entries: one
     // buffer is then at most 48 registers; see spmm_short_columns)
-    static const int pipe_env = env_int("SLC_SPMM_PIPE", 1);
+    static const int pipe_env = env_int("SLC_SPMM_PIPE", 0);  // measured: 0.535 ms with, 0.473 without (cfg 2)
     const bool pipe = sell && pipe_env != 0;
 #define SLC_SHORT(L_, SELL_, PIPE_)                                                                  \
   k_spmm_short<T, JTS, L_, SELL_, (PIPE_) && (L_ * JTS * sizeof(T) / 4 <= 48)><<<(unsigned)nb, threads, 0, s>>>( \

@@ -423,6 +423,13 @@ def launch_count():
     return int(_capi.lib().slc_launch_count())
 
 
+def spmm_window_error():
+    """Nonzero if a launch of the TMA-staged block product gave up on a barrier (diagnostic)."""
+    f = C.c_int(0)
+    _check(_capi.lib().slc_spmm_window_error(C.byref(f)))
+    return f.value
+
+
 def device_count():
     n = C.c_int(0)
     rc = _capi.lib().slc_device_count(C.byref(n))

@@ -182,6 +182,21 @@ def test_mulm_stencils_bit_exact(sl, dtype):
         np.testing.assert_array_equal(sl.mulM(m, X), oracle.mulm(om, X))
 
 
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_mulm_banded_window_kernel(sl, dtype):
+    """Banded matrices with short rows take the TMA-staged kernel (k_spmm_window): 1024-row blocks, so
+    use sizes around one and several blocks, a ragged last block, fewer columns than pipeline stages,
+    and a band wide enough that the stage count drops to the minimum."""
+    rng = np.random.default_rng(31)
+    cases = [(g.laplace2d_5pt(32, dtype), 3), (g.laplace2d_5pt(46, dtype), 9), (g.laplace2d_5pt(90, dtype), 20),
+             (g.tridiag(5000, dtype=dtype), 1), (g.laplace2d_5pt(300, dtype), 2)]
+    for gm, k in cases:
+        om, m = oracle.csc(*gm), to_matrix(sl, gm)
+        X = np.asfortranarray(np.stack([vec(rng, gm.ncols, dtype) for _ in range(k)], axis=1))
+        np.testing.assert_array_equal(sl.mulM(m, X), oracle.mulm(om, X))
+    assert sl.spmm_window_error() == 0
+
+
 def test_mulm_stencil_block_and_column_range(sl):
     """FEAST's multiplyWork: only an active column range is multiplied (Feast.hs:203-208)."""
     rng = np.random.default_rng(2)
