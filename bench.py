@@ -403,6 +403,7 @@ def main():
     if os.path.exists(tpath):
         try:
             traffic = json.load(open(tpath)).get(args.workload)
+            traffic = traffic if isinstance(traffic, (int, float)) else None
         except Exception:
             traffic = None
 
