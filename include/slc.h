@@ -233,6 +233,17 @@ int slc_d_mulv_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const
 int slc_z_mulv_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits,
                         const double *const *x_parts, double *y_dev, slc_peer_group *sync);
 
+/* The same product with the operand all-gathered first: barrier (when sync != NULL), one kernel
+   that pulls every part's slice over NVLink into x_full_dev[ncols] (this rank's scratch copy of x),
+   then the undistributed product.  For matrices whose rows touch columns all over the operand
+   (power-law graphs, BASELINE.json config 4), where the halo is the whole vector. */
+int slc_d_mulv_allgather_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits,
+                             const double *const *x_parts, double *x_full_dev, double *y_dev,
+                             slc_peer_group *sync);
+int slc_z_mulv_allgather_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits,
+                             const double *const *x_parts, double *x_full_dev, double *y_dev,
+                             slc_peer_group *sync);
+
 /* Y_local <- A_local X, the block form (FEAST's multiplyWork over a row-partitioned subspace block).
    X is partitioned by the same row blocks: X_parts[p] is the device address, as mapped in THIS process,
    of part p's (splits[p+1]-splits[p]) x k column-major block with leading dimension ldx_parts[p].

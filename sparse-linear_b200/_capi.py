@@ -60,6 +60,7 @@ for _p in ("d", "z"):
         "slc_%s_mulv_dev" % _p: (C.c_int, [_hp, _vp, _vp]),
         "slc_%s_axpy_dev" % _p: (C.c_int, [_hp, _vp, _vp]),
         "slc_%s_mulv_dist_dev" % _p: (C.c_int, [_hp, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp]),
+        "slc_%s_mulv_allgather_dev" % _p: (C.c_int, [_hp, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp, _vp]),
         "slc_%s_mulm_dist_dev" % _p: (C.c_int, [_hp, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp, C.c_int64,
                                                 C.c_int32, _vp]),
         "slc_%s_mulm" % _p: (C.c_int, [_hp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32]),

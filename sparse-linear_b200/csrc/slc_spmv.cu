@@ -1382,6 +1382,55 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   return SLC_OK;
 }
 
+// All-gather of the operand over peer memory: every block pulls 16-byte words of one part's slice
+// (its own included) into this rank's full-length copy of x.  blockIdx.y = part.  Used when the rows
+// of a rank touch columns all over the matrix (power-law graphs: SURVEY.md section 8e, config 4), where
+// per-entry loads across NVLink would be one 32-byte sector per nonzero.
+template <class T>
+__global__ void __launch_bounds__(256) k_allgather_pull(const DistTable *tbl, T *xfull) {
+  const int p = blockIdx.y;
+  if (p >= tbl->nparts) return;
+  const int64_t lo = tbl->splits[p], n = (int64_t)tbl->splits[p + 1] - lo;
+  const T *src = static_cast<const T *>(tbl->parts[p]);
+  T *dst = xfull + lo;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  constexpr int PER = 16 / sizeof(T) > 0 ? 16 / sizeof(T) : 1;  // elements per 16-byte word
+  if (PER > 1 && (((uintptr_t)src | (uintptr_t)dst) & 15) == 0) {
+    const int64_t nw = n / PER;
+    const double2 *s2 = reinterpret_cast<const double2 *>(src);
+    double2 *d2 = reinterpret_cast<double2 *>(dst);
+    int64_t i = tid;
+    for (; i + 3 * nth < nw; i += 4 * nth) {  // four loads in flight per thread
+      const double2 a = s2[i], b = s2[i + nth], c = s2[i + 2 * nth], d = s2[i + 3 * nth];
+      d2[i] = a; d2[i + nth] = b; d2[i + 2 * nth] = c; d2[i + 3 * nth] = d;
+    }
+    for (; i < nw; i += nth) d2[i] = s2[i];
+    for (int64_t e = nw * PER + tid; e < n; e += nth) dst[e] = src[e];
+  } else {
+    for (int64_t e = tid; e < n; e += nth) dst[e] = src[e];
+  }
+}
+
+// y_local <- A_local x with x all-gathered first: barrier, pull kernel, then the undistributed product
+// (merge-path balanced kernels for irregular rows) on the full local copy.
+template <class T>
+static int spmv_allgather_entry(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits,
+                                const double *const *x_parts, double *x_full, double *y, slc_peer_group *sync,
+                                const char *fn) {
+  const DistTable *tbl = nullptr;
+  SLC_TRY((dist_table_setup<T>(m, nparts, self, splits, x_parts, nullptr, fn, &tbl)));
+  if ((m->ncols && !x_full) || (m->nrows && !y)) return fail(SLC_ERR_INVALID, "%s: null vector", fn);
+  if (sync) SLC_TRY(slc_peer_barrier(sync));
+  if (m->ncols) {
+    int64_t longest = 0;
+    for (int p = 0; p < nparts; ++p) longest = std::max<int64_t>(longest, splits[p + 1] - splits[p]);
+    const unsigned bx = (unsigned)std::max<int64_t>(1, std::min<int64_t>(ceil_div(longest, 256 * 8), 148 * 4));
+    k_allgather_pull<T><<<dim3(bx, (unsigned)nparts), 256, 0, cur_stream()>>>(tbl, (T *)x_full);
+    SLC_LAUNCHED();
+  }
+  return spmv_dev<T, false>(m, (const T *)x_full, (T *)y);
+}
+
 // k_spmm_panel: block size, shared-memory budget and batch shape.  Defaults from the round-1 sweep on
 // the 27-point stencil; the environment variables exist for that sweep.
 template <class T, int JT, int KU>
@@ -1598,6 +1647,50 @@ static int spmm_host_entry(slc_matrix *m, const double *X, int64_t ldx, double *
   DevBuf<T> dX, dY;
   SLC_TRY(dX.alloc((size_t)m->ncols * k));
   SLC_TRY(dY.alloc((size_t)m->nrows * k));
+  // Columns are independent products (FE:203-208 serves them one by one), so the block is cut into
+  // column groups: group g+1 goes up on one stream while group g is multiplied on the caller's
+  // stream and group g-1 comes back on a third -- PCIe is full duplex, so the upload and the
+  // download overlap instead of running back to back.
+  static const int groups_env = env_int("SLC_E2E_COLGROUPS", 8);
+  const size_t bytes_total = ((size_t)m->ncols + (size_t)m->nrows) * (size_t)k * sizeof(T);
+  int ngroups = std::max(1, std::min<int>(std::min(groups_env, PIPE_MAX_CHUNKS), k));
+  if (bytes_total < ((size_t)8 << 20) || m->ncols == 0 || m->nrows == 0) ngroups = 1;
+  if (ngroups > 1) {
+    if (m->nnz > 0) SLC_TRY(ensure_plan<T>(m));
+    if (!m->pipe_in) {
+      SLC_CUDA(cudaStreamCreateWithFlags(&m->pipe_in, cudaStreamNonBlocking));
+      SLC_CUDA(cudaStreamCreateWithFlags(&m->pipe_out, cudaStreamNonBlocking));
+      m->pipe_events.resize(2 * PIPE_MAX_CHUNKS + 1);
+      for (auto &e : m->pipe_events) SLC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    cudaEvent_t ev_start = m->pipe_events[2 * PIPE_MAX_CHUNKS];
+    SLC_CUDA(cudaEventRecord(ev_start, s));
+    SLC_CUDA(cudaStreamWaitEvent(m->pipe_in, ev_start, 0));
+    SLC_CUDA(cudaStreamWaitEvent(m->pipe_out, ev_start, 0));
+    const int32_t per = (int32_t)ceil_div(k, ngroups);
+    int rc = SLC_OK;
+    for (int g = 0; g * per < k && rc == SLC_OK; ++g) {
+      const int32_t j0 = g * per, kk = std::min<int32_t>(per, k - j0);
+      const T *Xg = (const T *)X + (size_t)j0 * ldx;
+      T *Yg = (T *)Y + (size_t)j0 * ldy;
+      T *dXg = dX.p + (size_t)j0 * m->ncols, *dYg = dY.p + (size_t)j0 * m->nrows;
+      cudaEvent_t ev_in = m->pipe_events[g], ev_k = m->pipe_events[PIPE_MAX_CHUNKS + g];
+      SLC_CUDA(cudaMemcpy2DAsync(dXg, (size_t)m->ncols * sizeof(T), Xg, (size_t)ldx * sizeof(T),
+                                 (size_t)m->ncols * sizeof(T), (size_t)kk, cudaMemcpyHostToDevice, m->pipe_in));
+      SLC_CUDA(cudaEventRecord(ev_in, m->pipe_in));
+      SLC_CUDA(cudaStreamWaitEvent(s, ev_in, 0));
+      rc = spmm_dev<T>(m, dXg, m->ncols, dYg, m->nrows, kk);
+      if (rc != SLC_OK) break;
+      SLC_CUDA(cudaEventRecord(ev_k, s));
+      SLC_CUDA(cudaStreamWaitEvent(m->pipe_out, ev_k, 0));
+      SLC_CUDA(cudaMemcpy2DAsync(Yg, (size_t)ldy * sizeof(T), dYg, (size_t)m->nrows * sizeof(T),
+                                 (size_t)m->nrows * sizeof(T), (size_t)kk, cudaMemcpyDeviceToHost, m->pipe_out));
+    }
+    SLC_CUDA(cudaStreamSynchronize(m->pipe_out));
+    SLC_CUDA(cudaStreamSynchronize(m->pipe_in));
+    SLC_CUDA(cudaStreamSynchronize(s));
+    return rc;
+  }
   if (m->ncols)
     SLC_CUDA(cudaMemcpy2DAsync(dX.p, (size_t)m->ncols * sizeof(T), X, (size_t)ldx * sizeof(T),
                                (size_t)m->ncols * sizeof(T), (size_t)k, cudaMemcpyHostToDevice, s));
@@ -1671,6 +1764,17 @@ int slc_d_mulv_dist_dev(slc_matrix *a, int32_t nparts, int32_t self, const int32
 int slc_z_mulv_dist_dev(slc_matrix *a, int32_t nparts, int32_t self, const int32_t *splits,
                         const double *const *x_parts, double *y_dev, slc_peer_group *sync) {
   return spmv_dist_entry<double2>(a, nparts, self, splits, x_parts, y_dev, sync, "mulV");
+}
+
+int slc_d_mulv_allgather_dev(slc_matrix *a, int32_t nparts, int32_t self, const int32_t *splits,
+                             const double *const *x_parts, double *x_full_dev, double *y_dev,
+                             slc_peer_group *sync) {
+  return spmv_allgather_entry<double>(a, nparts, self, splits, x_parts, x_full_dev, y_dev, sync, "mulV");
+}
+int slc_z_mulv_allgather_dev(slc_matrix *a, int32_t nparts, int32_t self, const int32_t *splits,
+                             const double *const *x_parts, double *x_full_dev, double *y_dev,
+                             slc_peer_group *sync) {
+  return spmv_allgather_entry<double2>(a, nparts, self, splits, x_parts, x_full_dev, y_dev, sync, "mulV");
 }
 
 int slc_d_mulm_dist_dev(slc_matrix *a, int32_t nparts, int32_t self, const int32_t *splits,

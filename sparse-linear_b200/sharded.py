@@ -61,6 +61,50 @@ def exchange_objects(obj, dist, group=None):
     return out
 
 
+def vstack_blocks(blocks):
+    """Row blocks of one matrix (CSC, same ncols, listed top to bottom) put back together: column j of
+    the result is the blocks' columns j one after the other, row indices shifted by the rows above.
+    This is how the row-partitioned SpGEMM's outputs concatenate."""
+    ncols = blocks[0].ncols
+    counts = [np.diff(np.asarray(b.colptr, dtype=np.int64)) for b in blocks]
+    colptr = np.concatenate([[0], np.cumsum(np.sum(counts, axis=0))])
+    nnz = int(colptr[-1])
+    rowidx = np.empty(nnz, dtype=np.int32)
+    values = np.empty(nnz, dtype=np.asarray(blocks[0].values).dtype)
+    before = np.zeros(ncols, dtype=np.int64)     # entries of column j already placed by the blocks above
+    row0 = 0
+    for b, cnt in zip(blocks, counts):
+        n = int(cnt.sum())
+        if n:
+            src_col = np.repeat(np.arange(ncols, dtype=np.int64), cnt)
+            within = np.arange(n, dtype=np.int64) - np.repeat(np.asarray(b.colptr[:-1], dtype=np.int64), cnt)
+            dst = colptr[:-1][src_col] + before[src_col] + within
+            rowidx[dst] = np.asarray(b.rowidx, dtype=np.int64) + row0
+            values[dst] = b.values
+        before += cnt
+        row0 += b.nrows
+    return CSC(row0, ncols, colptr.astype(np.int32), rowidx, values)
+
+
+def mm_row_block(a, b, rank, world, splits=None):
+    """This rank's share of C = A B (mm, Data/Matrix/Sparse.hs:691-702): rows [r0, r1) of A against a
+    replicated B, no exchange while computing.  a: host CSC of the whole A (every rank can build or
+    load it) -- only the block is uploaded; b: Matrix.  Returns (C block as Matrix, r0, r1)."""
+    from .matrix import mm
+    if splits is None:
+        splits = uniform_splits(a.nrows, world)
+    r0, r1 = int(splits[rank]), int(splits[rank + 1])
+    blk = row_block(a, r0, r1)
+    local = Matrix(blk.ncols, blk.nrows, blk.colptr, blk.rowidx, blk.values)
+    return mm(local, b), r0, r1
+
+
+def gather_blocks(c_local, dist, group=None):
+    """One gather of the C blocks when a single result is wanted (host side, rank order)."""
+    blk = CSC(c_local.nrows, c_local.ncols, c_local.pointers, c_local.indices, c_local.values)
+    return vstack_blocks(exchange_objects(blk, dist, group))
+
+
 # ---- device side --------------------------------------------------------------------------------------
 
 class ShardedSpMV:
@@ -70,9 +114,14 @@ class ShardedSpMV:
     in a cudaMalloc'ed buffer that every other rank maps through CUDA IPC.
     """
 
-    def __init__(self, local, splits, rank, world, dist=None, cpu_group=None, k=None):
+    def __init__(self, local, splits, rank, world, dist=None, cpu_group=None, k=None, mode="halo"):
         self.local, self.rank, self.world, self.dist = local, rank, world, dist
         self.k = k                      # None: vectors (mulV); k >= 1: column-major blocks (mulM)
+        # "halo": remote entries are gathered by the product kernel itself (banded matrices);
+        # "allgather": every slice is pulled over NVLink into a full local copy first (power-law)
+        if mode not in ("halo", "allgather") or (mode == "allgather" and k is not None):
+            raise SparseLinearError("ShardedSpMV: unsupported mode %r" % (mode,))
+        self.mode = mode
         ncol = 1 if k is None else int(k)
         self.splits = np.ascontiguousarray(splits, dtype=np.int32)
         if len(self.splits) != world + 1 or self.splits[0] != 0 or self.splits[-1] != local.ncols:
@@ -86,6 +135,9 @@ class ShardedSpMV:
         _check(lib.slc_dev_alloc(C.byref(self.x_ptr), max(self.nloc_x * ncol, 1) * self.el))
         self.y_ptr = C.c_void_p()
         _check(lib.slc_dev_alloc(C.byref(self.y_ptr), max(local.nrows * ncol, 1) * self.el))
+        self.xfull_ptr = C.c_void_p()
+        if mode == "allgather":
+            _check(lib.slc_dev_alloc(C.byref(self.xfull_ptr), max(local.ncols, 1) * self.el))
         handle = C.create_string_buffer(IPC_BYTES)
         _check(lib.slc_ipc_export(self.x_ptr, handle))
         self.group = C.c_void_p()
@@ -108,6 +160,7 @@ class ShardedSpMV:
                 self._imported.append(ptr)
         self.local.device().prepare()
         self._fn = getattr(lib, "slc_%s_%s_dist_dev" % (self.p, "mulv" if k is None else "mulm"))
+        self._fn_ag = getattr(lib, "slc_%s_mulv_allgather_dev" % self.p)
         # every part's block is packed: leading dimension = its own row count
         self.lds = np.ascontiguousarray(np.diff(self.splits).astype(np.int64))
         self._flag = None
@@ -142,7 +195,11 @@ class ShardedSpMV:
         return bool(f.value)
 
     def product(self, sync=None):
-        if self.k is None:
+        if self.mode == "allgather":
+            _check(self._fn_ag(self.local.device().handle, self.world, self.rank,
+                               self.splits.ctypes.data_as(C.c_void_p), C.cast(self.parts, C.c_void_p),
+                               self.xfull_ptr, self.y_ptr, sync))
+        elif self.k is None:
             _check(self._fn(self.local.device().handle, self.world, self.rank,
                             self.splits.ctypes.data_as(C.c_void_p), C.cast(self.parts, C.c_void_p), self.y_ptr,
                             sync))
@@ -184,6 +241,9 @@ class ShardedSpMV:
         if self.y_ptr:
             lib.slc_dev_free(self.y_ptr)
             self.y_ptr = None
+        if self.xfull_ptr:
+            lib.slc_dev_free(self.xfull_ptr)
+            self.xfull_ptr = None
 
 
 # ---- bench.py --gpus N ------------------------------------------------------------------------------------
@@ -196,6 +256,10 @@ def bench_main(args, rank, world, local_rank, dist):
     from . import generators as g
     import bench as B
 
+    if args.workload == "cfg3":
+        return bench_spgemm_sharded(args, rank, world, local_rank, dist)
+    if args.workload == "cfg4":
+        return bench_powerlaw_sharded(args, rank, world, local_rank, dist)
     n = args.grid or 200
     if args.scaling == "weak":
         shape = (n * world, n, n)
@@ -329,6 +393,168 @@ def bench_main(args, rank, world, local_rank, dist):
                          "barrier_timed_out": sh.timed_out()},
             "cpu_baseline": None,
         }
+        print(json.dumps(line), flush=True)
+    sh.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def _max_over_ranks(ms, dist, world):
+    import torch
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _sum_over_ranks(vals, dist, world):
+    import torch
+    t = torch.tensor([float(v) for v in vals], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t)
+    return [float(v) for v in t.tolist()]
+
+
+def bench_spgemm_sharded(args, rank, world, local_rank, dist):
+    """cfg 3, C = A A, strong-scaled: A cut into row blocks, B = A replicated, no exchange while
+    computing; value = output nnz of all blocks / slowest rank's time (symbolic + numeric)."""
+    import torch
+    import sparse_linear_b200 as sl
+    from . import generators as g
+    import bench as B
+    n = args.grid or 128
+    a = g.laplace3d_7pt(n)
+    stream = torch.cuda.current_stream()
+    sl.set_stream(stream.cuda_stream)
+    bm = Matrix(a.ncols, a.nrows, a.colptr, a.rowidx, a.values)
+    splits = uniform_splits(n, world) * (n * n)           # z-slabs: equal work per rank
+    r0, r1 = int(splits[rank]), int(splits[rank + 1])
+    blk = row_block(a, r0, r1)
+    local = Matrix(blk.ncols, blk.nrows, blk.colptr, blk.rowidx, blk.values)
+    c = sl.mm(local, bm)
+    sl.synchronize()
+    nnzc_local = sl.nonZero(c)
+    # parity of this rank's block against the closed form of the whole product and, on a small
+    # grid, the structure of a host product (scipy is a second opinion only; tests use the oracle)
+    del c
+    steps = max(1, min(args.steps, 10))
+    for _ in range(2):
+        c = sl.mm(local, bm)
+        del c
+    sampler = B.ClockSampler(local_rank)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    l0 = sl.launch_count()
+    sampler.start()
+    e0.record(stream)
+    for _ in range(steps):
+        c = sl.mm(local, bm)
+        del c
+    e1.record(stream)
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    launches = sl.launch_count() - l0
+    ms = _max_over_ranks(e0.elapsed_time(e1) / steps, dist, world)
+    nnzc, nnza = _sum_over_ranks([nnzc_local, blk.colptr[-1]], dist, world)
+    if rank == 0:
+        peak, peak_src = B.peaks()
+        nnzb = int(a.colptr[-1])
+        floor_bytes = (nnza + nnzb * world + nnzc) * 12 + 3 * (a.ncols + 1) * 4 * world
+        gbs = floor_bytes / (ms * 1e-3) / 1e9 / world
+        expect = None
+        if n >= 5:   # nnz(A A) of the 7-point Laplacian on an n^3 grid: the 25-point radius-2 diamond, clipped
+            import itertools
+            offs = {(dx + ex, dy + ey, dz + ez) for (dx, dy, dz) in [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0), (0, 0, 1), (0, 0, -1)]
+                    for (ex, ey, ez) in [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0), (0, 0, 1), (0, 0, -1)]}
+            expect = sum((n - abs(dx)) * (n - abs(dy)) * (n - abs(dz)) for dx, dy, dz in offs)
+        line = {"metric": "spgemm_output_nnz_per_s", "value": nnzc / (ms * 1e-3), "unit": "nnz/s", "n_gpus": world,
+                "steps": steps, "warmup": 2, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "cfg3: SpGEMM A*A, 3D 7-point Laplacian %d^3, A in %d row blocks (z-slabs), "
+                                       "B replicated, no exchange during the product" % (n, world),
+                           "nnz_in": int(nnzb), "nnz_out": int(nnzc), "nnz_out_closed_form": expect,
+                           "structure_count_matches_closed_form": (int(nnzc) == expect) if expect else None},
+                "clocks": clocks, "gpu_launches": int(launches),
+                "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                             "traffic": None, "peak_source": peak_src, "kernel": "k_mm_merge (numeric)",
+                             "note": "per-GPU share of the one-pass byte floor (B counted once per rank)"}}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def bench_powerlaw_sharded(args, rank, world, local_rank, dist):
+    """cfg 4 over `world` GPUs: R-MAT rows cut into blocks of equal nonzeros, x sliced by the same
+    bounds; every product all-gathers x over NVLink (k_allgather_pull) and runs the balanced kernel."""
+    import torch
+    import sparse_linear_b200 as sl
+    from . import generators as g
+    import bench as B
+    scale = args.grid or 24
+    stream = torch.cuda.current_stream()
+    sl.set_stream(stream.cuda_stream)
+    cpu_group = dist.new_group(backend="gloo") if world > 1 else None
+    n, r, c, v = g.rmat_triplets(scale, 16, seed=0)          # every rank generates the same edge list
+    splits = balanced_splits(np.bincount(r, minlength=n), world)
+    r0, r1 = int(splits[rank]), int(splits[rank + 1])
+    keep = (r >= r0) & (r < r1)
+    rl, cl, vl = (r[keep] - r0).astype(np.int32), c[keep], v[keep]
+    del r, c, v, keep
+    local = sl.compress(r1 - r0, n, rl, cl, vl)               # device assembly, duplicates summed
+    nnz_local = sl.nonZero(local)
+    sh = ShardedSpMV(local, splits, rank, world, dist, cpu_group, mode="allgather")
+    xfull = g.uniform_vector(n, seed=0)
+    sh.set_x(xfull[r0:r1])
+    for _ in range(max(args.warmup, 3)):
+        sh.mulv()
+    torch.cuda.synchronize()
+    want = np.bincount(rl, weights=vl * xfull[cl], minlength=r1 - r0)
+    got = sh.y()
+    err = float(np.linalg.norm(got - want) / max(np.linalg.norm(want), 1e-300))
+    del rl, cl, vl
+    sampler = B.ClockSampler(local_rank)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    l0 = sl.launch_count()
+    sampler.start()
+    e0.record(stream)
+    for _ in range(args.steps):
+        sh.mulv()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop()
+    launches = sl.launch_count() - l0
+    ms = _max_over_ranks(e0.elapsed_time(e1) / args.steps, dist, world)
+    nnz, errsq = _sum_over_ranks([nnz_local, err * err], dist, world)
+    abytes = g.spmv_bytes(n, n, int(nnz))
+    value = abytes / (ms * 1e-3) / 1e9
+    if rank == 0:
+        peak, peak_src = B.peaks()
+        per_gpu = value / world
+        line = {"metric": B.METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic (seeded numpy PCG64)",
+                "config": {"workload": "cfg4: R-MAT scale %d edge factor 16, Double SpMV, rows in %d blocks of equal "
+                                       "nonzeros; x all-gathered over NVLink peer memory every product (%.0f MB inbound "
+                                       "per GPU), then the balanced kernel" % (scale, world, n * 8 * (world - 1) / world / 1e6),
+                           "rows": n, "nnz": int(nnz), "algorithmic_bytes_per_step": abytes,
+                           "plan": local.device().plan_info(), "splits": [int(x) for x in splits],
+                           "rel_err_vs_host_sum_rms_over_ranks": float(np.sqrt(errsq / world))},
+                "clocks": clocks, "gpu_launches": int(launches), "e2e": None,
+                "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
+                             "traffic": None, "peak_source": peak_src,
+                             "kernel": "k_allgather_pull + k_spmv_bal",
+                             "note": "per-GPU figure; the step includes the barrier and the all-gather of x",
+                             "barrier_timed_out": sh.timed_out()},
+                "cpu_baseline": None}
         print(json.dumps(line), flush=True)
     sh.close()
     if world > 1:

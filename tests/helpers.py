@@ -44,6 +44,13 @@ def random_csc(rng, nr, nc, density, dtype=np.float64, integer=False):
     return oracle.csc(nr, nc, colptr, rows, vals.astype(dtype))
 
 
+def rmat_csc(scale, edge_factor=8, seed=0, dtype=np.float64):
+    """Small power-law matrix: R-MAT triplets assembled by the oracle (duplicates summed)."""
+    from sparse_linear_b200 import generators as g
+    n, r, c, v = g.rmat_triplets(scale, edge_factor, seed=seed, dtype=dtype)
+    return oracle.compress(n, n, r, c, v)
+
+
 def to_matrix(sl, m):
     """oracle.CSC (or generators.CSC) -> product Matrix"""
     return sl.Matrix(m.ncols, m.nrows, m.colptr, m.rowidx, m.values)

@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 import oracle
-from helpers import random_csc, to_matrix
+from helpers import random_csc, rmat_csc, to_matrix
 from sparse_linear_b200 import generators as g
 from sparse_linear_b200 import sharded
 
@@ -97,6 +97,78 @@ def test_partitioned_block_product_matches_oracle(sl, dtype):
         np.testing.assert_array_equal(np.concatenate(out, axis=0), want)
         for p in parts:
             lib.slc_dev_free(p)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.complex128])
+def test_allgather_operand_matches_oracle(sl, dtype):
+    """slc_*_mulv_allgather_dev: the slices (odd sizes, so some destinations are not 16-byte aligned)
+    are pulled into a full copy of x, then the undistributed kernels run."""
+    lib = sl._capi.lib()
+    rng = np.random.default_rng(21)
+    pfx = "z" if np.dtype(dtype).kind == "c" else "d"
+    fn = getattr(lib, "slc_%s_mulv_allgather_dev" % pfx)
+    for gm, xs in ((random_csc(rng, 400, 777, 0.03, dtype), [0, 101, 101, 400, 777]),
+                   (rmat_csc(10, 8, seed=3, dtype=dtype), None),
+                   (g.stencil3d_27pt((7, 6, 5), dtype), [0, 33, 210])):
+        om = oracle.csc(*gm)
+        x = rng.uniform(-1, 1, gm.ncols).astype(dtype)
+        want = oracle.mulv(om, x)
+        xs = (sharded.uniform_splits(gm.ncols, 5) if xs is None else np.asarray(xs)).astype(np.int32)
+        nparts = len(xs) - 1
+        xparts = [_dev_array(sl, np.ascontiguousarray(x[xs[p]:xs[p + 1]])) for p in range(nparts)]
+        table = (C.c_void_p * nparts)(*[p.value for p in xparts])
+        rownnz = np.bincount(gm.rowidx, minlength=gm.nrows)
+        rs = sharded.balanced_splits(rownnz, nparts)
+        out = []
+        for rank in range(nparts):
+            blk = sharded.row_block(gm, rs[rank], rs[rank + 1])
+            m = to_matrix(sl, blk)
+            m.device().set_spmv_kernel(1)     # row per thread: the reference's summation order
+            y = np.zeros(blk.nrows, dtype=dtype)
+            yd, xf = _dev_array(sl, y), _dev_array(sl, np.full(gm.ncols, np.nan, dtype=dtype))
+            rc = fn(m.device().handle, nparts, rank, xs.ctypes.data_as(C.c_void_p), C.cast(table, C.c_void_p),
+                    xf, yd, None)
+            assert rc == 0, sl._capi.last_error()
+            assert lib.slc_memcpy_d2h(C.c_void_p(y.ctypes.data), yd, y.nbytes) == 0
+            lib.slc_dev_free(yd)
+            lib.slc_dev_free(xf)
+            out.append(y)
+        np.testing.assert_array_equal(np.concatenate(out), want)
+        for p in xparts:
+            lib.slc_dev_free(p)
+
+
+def test_row_partitioned_spgemm_concatenates_to_the_oracle(sl):
+    """C = A B with A cut into row blocks and B replicated: the blocks stacked
+    top to bottom are the undistributed product, structure and values bit for bit."""
+    rng = np.random.default_rng(5)
+    for a, b, world in ((g.laplace3d_7pt(9), g.laplace3d_7pt(9), 4),
+                        (random_csc(rng, 120, 90, 0.08), random_csc(rng, 90, 150, 0.06), 3),
+                        (rmat_csc(9, 6, seed=1), rmat_csc(9, 6, seed=2), 8)):
+        want = oracle.mm(oracle.csc(*a), oracle.csc(*b))
+        bm = to_matrix(sl, b)
+        blocks = []
+        for rank in range(world):
+            c, r0, r1 = sharded.mm_row_block(a, bm, rank, world)
+            assert c.nrows == r1 - r0 and c.ncols == b.ncols
+            blocks.append(g.CSC(c.nrows, c.ncols, c.pointers, c.indices, c.values))
+        got = sharded.vstack_blocks(blocks)
+        assert got.nrows == a.nrows
+        assert np.array_equal(got.colptr, want.colptr) and np.array_equal(got.rowidx, want.rowidx)
+        assert np.array_equal(got.values, want.values)
+
+
+def test_sharded_wrapper_allgather_single_rank(sl):
+    gm = rmat_csc(9, 8, seed=4)
+    m = to_matrix(sl, gm)
+    sh = sharded.ShardedSpMV(m, np.array([0, gm.ncols]), 0, 1, mode="allgather")
+    x = g.uniform_vector(gm.ncols, seed=2)
+    sh.set_x(x)
+    sh.mulv()
+    sl.synchronize()
+    want = oracle.mulv(oracle.csc(*gm), x)
+    assert np.linalg.norm(sh.y() - want) <= 1e-12 * np.linalg.norm(want)
+    sh.close()
 
 
 def test_sharded_wrapper_single_rank(sl):

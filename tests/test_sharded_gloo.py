@@ -56,6 +56,35 @@ def test_symmetric_row_block_is_transposed_column_block():
     assert np.array_equal(t.values, rb.values)
 
 
+def test_vstack_blocks_inverts_row_block():
+    """Row blocks of C concatenate back to C (what the row-partitioned SpGEMM's gather does)."""
+    rng = np.random.default_rng(3)
+    for m, nparts in ((random_csc(rng, 60, 45, 0.15), 4), (random_csc(rng, 7, 9, 0.5, np.complex128), 7),
+                      (g.laplace3d_7pt(5), 3), (random_csc(rng, 10, 10, 0.0), 2)):
+        splits = sharded.uniform_splits(m.nrows, nparts)
+        blocks = [sharded.row_block(m, splits[p], splits[p + 1]) for p in range(nparts)]
+        back = sharded.vstack_blocks(blocks)
+        assert back.nrows == m.nrows and back.ncols == m.ncols
+        assert np.array_equal(back.colptr, m.colptr) and np.array_equal(back.rowidx, m.rowidx)
+        assert np.array_equal(back.values, m.values)
+        assert oracle.check_format(oracle.csc(*back)) == 0
+
+
+def test_row_partitioned_product_of_matrices_is_the_product():
+    """mm on row blocks of A against all of B, stacked, equals mm(A, B) (oracle on both sides)."""
+    rng = np.random.default_rng(8)
+    a, b = random_csc(rng, 40, 30, 0.2), random_csc(rng, 30, 50, 0.2)
+    want = oracle.mm(oracle.csc(*a), oracle.csc(*b))
+    splits = sharded.uniform_splits(a.nrows, 3)
+    blocks = []
+    for p in range(3):
+        c = oracle.mm(oracle.csc(*sharded.row_block(a, splits[p], splits[p + 1])), oracle.csc(*b))
+        blocks.append(g.CSC(c.nrows, c.ncols, c.colptr, c.rowidx, c.values))
+    got = sharded.vstack_blocks(blocks)
+    assert np.array_equal(got.colptr, want.colptr) and np.array_equal(got.rowidx, want.rowidx)
+    assert np.array_equal(got.values, want.values)
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
