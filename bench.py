@@ -116,7 +116,10 @@ def hot_kernel(plan, k, dm):
     if "sell" not in plan:
         return "k_spmm_rows"
     maxlen = int(plan.split("max_rowlen=")[1].split()[0])
-    return "k_spmm_short" if maxlen <= 8 else "k_spmm_panel"
+    if maxlen > 8:
+        return "k_spmm_panel"
+    # rows of <= 8 entries: banded matrices take the TMA-staged window kernel unless it is switched off
+    return "k_spmm_short" if os.environ.get("SLC_SPMM_WINDOW", "1") == "0" else "k_spmm_window (banded) / k_spmm_short"
 
 
 def algorithmic_bytes(kind, nrows, ncols, nnz, k, dtype):

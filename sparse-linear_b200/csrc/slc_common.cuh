@@ -87,6 +87,11 @@ struct DevBuf {
   U *take() { U *q = p; p = nullptr; n = 0; return q; }
 };
 
+inline int env_int(const char *name, int dflt) {
+  const char *v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
+
 inline void dev_free(void *p) {
   if (p) cudaFreeAsync(p, cur_stream());
 }
@@ -118,6 +123,12 @@ struct SellPlan {
   int32_t interior_s0 = -1, interior_s1 = -1, interior_lo = 0, interior_hi = 0;
   // widest column window of a 1024-row block (k_spmm_window), -1 = not measured yet
   int32_t window_max = -1;
+  // k_spmm_panel: distance in rows between grid lines (the near off-diagonal band of a stencil),
+  // -1 = not measured yet, 0 = none; and the cached slice order that tiles blocks over lines
+  int32_t line_stride = -1;
+  int32_t *panel_order = nullptr;   // [panel_blocks * warps] slice of every warp, -1 = idle
+  int64_t panel_blocks = 0;
+  int32_t panel_key[4] = {-1, -1, -1, -1};   // (first slice, last slice, stride, warps << 8 | width)
 };
 
 // nnz-balanced CSR plan: fixed-size chunks of nonzeros, first row of each chunk.

@@ -133,26 +133,44 @@ k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32
            const int32_t *__restrict__ bi, const T *__restrict__ bv, int32_t *__restrict__ cnt,
            const int32_t *__restrict__ cp, int32_t *__restrict__ ci, T *__restrict__ cv, int stage) {
   extern __shared__ __align__(16) unsigned char merge_smem[];
-  const int32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  // grid-stride over tiles of blockDim.x columns: a grid of a few blocks per SM (run_merge) keeps the
+  // number of resident warps, and with it the L1 working set of A columns, bounded
+  for (int32_t tile = blockIdx.x; (int64_t)tile * blockDim.x < ncols_in_class; tile += gridDim.x) {
+  const int32_t slot = tile * blockDim.x + threadIdx.x;
   const bool active = slot < ncols_in_class;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int32_t j = active ? cols[slot] : -1;
   const int32_t q0 = active ? bp[j] : 0;
   const int32_t nb = active ? bp[j + 1] - q0 : 0;
-  int32_t p[NB], pe[NB], head[NB];
-  T b[NB];
+  // Every list keeps its next two (row, value) pairs in registers: head/hval is the entry at p, nxt/nval
+  // the one at p + 1.  Consuming an entry shifts nxt into head and issues the loads for p + 2, so the
+  // load a merge step starts is not needed before the same list advances again -- the chain of a step
+  // holds no L2 round trip (the launch list of round 1 had this kernel at 4x the symbolic pass with 16
+  // warps per SM waiting on the head loads).
+  int32_t p[NB], pe[NB], head[NB], nxt[NB];
+  T b[NB], hval[NB], nval[NB];
 #pragma unroll
   for (int u = 0; u < NB; ++u) {
     p[u] = 0;
     pe[u] = 0;
     head[u] = ROW_END;
+    nxt[u] = ROW_END;
     b[u] = Num<T>::zero();
+    hval[u] = Num<T>::zero();
+    nval[u] = Num<T>::zero();
     if (u < nb) {
       const int32_t k = __ldg(bi + q0 + u);
       p[u] = __ldg(ap + k);
       pe[u] = __ldg(ap + k + 1);
       if (NUMERIC) b[u] = __ldg(bv + q0 + u);
-      if (p[u] < pe[u]) head[u] = __ldg(ai + p[u]);
+      if (p[u] < pe[u]) {
+        head[u] = __ldg(ai + p[u]);
+        if (NUMERIC) hval[u] = __ldg(av + p[u]);
+      }
+      if (p[u] + 1 < pe[u]) {
+        nxt[u] = __ldg(ai + p[u] + 1);
+        if (NUMERIC) nval[u] = __ldg(av + p[u] + 1);
+      }
     }
   }
   int32_t count = 0;
@@ -191,9 +209,13 @@ k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32
 #pragma unroll
     for (int u = 0; u < NB; ++u) {
       if (head[u] == m) {
-        if (NUMERIC) acc = Num<T>::add(acc, Num<T>::mul(__ldg(av + p[u]), b[u]));
+        if (NUMERIC) acc = Num<T>::add(acc, Num<T>::mul(hval[u], b[u]));
         ++p[u];
-        head[u] = p[u] < pe[u] ? __ldg(ai + p[u]) : ROW_END;
+        head[u] = nxt[u];
+        if (NUMERIC) hval[u] = nval[u];
+        const bool more = p[u] + 1 < pe[u];
+        nxt[u] = more ? __ldg(ai + p[u] + 1) : ROW_END;
+        if (NUMERIC) nval[u] = more ? __ldg(av + p[u] + 1) : Num<T>::zero();
       }
     }
     if (NUMERIC) {
@@ -204,7 +226,7 @@ k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32
   }
   if (!NUMERIC) {
     if (active) cnt[j] = count;
-    return;
+    continue;
   }
   if (staged) {
     __syncwarp();
@@ -215,6 +237,8 @@ k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32
       ci[wbase + e] = s_i[e];
       cv[wbase + e] = s_v[e];
     }
+    __syncwarp();  // the window is reused by the next tile
+  }
   }
 }
 
@@ -227,7 +251,12 @@ static int run_merge(int32_t n, const int32_t *cols, const slc_matrix *a, const 
   const size_t smem = stage ? (size_t)(128 / 32) * MERGE_STAGE * (sizeof(int32_t) + sizeof(T)) : 0;
   auto kern = k_mm_merge<T, NB, NUMERIC>;
   if (smem > 48 * 1024) SLC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<(unsigned)ceil_div(n, 128), 128, smem, cur_stream()>>>(
+  // SLC_MM_RESIDENT=B: at most B blocks per SM (0 = one block per tile)
+  static const int resident_env = env_int("SLC_MM_RESIDENT", 0);
+  const int resident = NUMERIC ? resident_env : 0;
+  const int64_t tiles = ceil_div(n, 128);
+  const int64_t grid = resident > 0 ? std::min<int64_t>(tiles, (int64_t)resident * 148) : tiles;
+  kern<<<(unsigned)grid, 128, smem, cur_stream()>>>(
       n, cols, a->colptr, a->rowidx, (const T *)a->vals, b->colptr, b->rowidx, (const T *)b->vals, cnt,
       c ? c->colptr : nullptr, c ? c->rowidx : nullptr, c ? (T *)c->vals : nullptr, stage);
   SLC_LAUNCHED();

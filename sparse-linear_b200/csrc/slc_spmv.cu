@@ -961,12 +961,17 @@ __global__ void __launch_bounds__(512)
 k_spmm_panel(int32_t row_begin, int32_t row_end, int32_t kcap, uint32_t zmask, const int64_t *__restrict__ slice_ptr,
              const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
              const T *__restrict__ vals, const T *__restrict__ X, int64_t ldx, T *__restrict__ Y,
-             int64_t ldy, int32_t k) {
+             int64_t ldy, int32_t k, const int32_t *__restrict__ order) {
   extern __shared__ __align__(16) unsigned char panel_smem[];
   const int32_t nt = blockDim.x, tid = threadIdx.x;
   T *s_a = reinterpret_cast<T *>(panel_smem) + tid;                                       // [kcap][nt]
   int32_t *s_c = reinterpret_cast<int32_t *>(panel_smem + (size_t)kcap * nt * sizeof(T)) + tid;  // [kcap][nt]
-  const int32_t row = row_begin + blockIdx.x * nt + tid;  // row_begin % 32 == 0: lanes are slice rows
+  int32_t row = row_begin + blockIdx.x * nt + tid;  // row_begin % 32 == 0: lanes are slice rows
+  if (order) {  // line-tiled blocks: every warp is told its slice (see panel_tiling)
+    const int32_t sl = __ldg(order + (int64_t)blockIdx.x * (nt >> 5) + (tid >> 5));
+    if (sl < 0) return;
+    row = sl * SELL_C + (tid & 31);
+  }
   if (row >= row_end) return;
   const uint64_t pol_s = policy_evict_first();
   const uint64_t pol_x = policy_evict_last();
@@ -1091,11 +1096,6 @@ k_spmm_boundary(int32_t nrows, int32_t r0, int32_t r1, uint32_t zmask, const int
 // =================================================================================================
 // dispatch
 // =================================================================================================
-
-static int env_int(const char *name, int dflt) {
-  const char *v = getenv(name);
-  return v && *v ? atoi(v) : dflt;
-}
 
 template <class T, bool ACC, class XA>
 static int launch_sell(slc_matrix *m, const XA &xa, T *y, int32_t row_begin = 0, int32_t row_end = -1) {
@@ -1433,10 +1433,77 @@ static int spmv_allgather_entry(slc_matrix *m, int32_t nparts, int32_t self, con
 
 // k_spmm_panel: block size, shared-memory budget and batch shape.  Defaults from the round-1 sweep on
 // the 27-point stencil; the environment variables exist for that sweep.
+// Line stride of a stencil-like matrix: the distance in rows between neighbouring grid lines, read off
+// the middle row of the row-major mirror.
+static int detect_line_stride(slc_matrix *m) {
+  SellPlan &sp = m->sell;
+  if (sp.line_stride >= 0) return SLC_OK;
+  sp.line_stride = 0;
+  if (!m->has_csr || m->nrows < 4096) return SLC_OK;
+  const int32_t r = m->nrows / 2;
+  int32_t rp[2];
+  cudaStream_t s = cur_stream();
+  SLC_CUDA(cudaMemcpyAsync(rp, m->rowptr + r, sizeof rp, cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  const int32_t len = rp[1] - rp[0];
+  if (len < 3 || len > 4096) return SLC_OK;
+  std::vector<int32_t> cols((size_t)len);
+  SLC_CUDA(cudaMemcpyAsync(cols.data(), m->colidx + rp[0], (size_t)len * 4, cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  // runs of consecutive columns; the stride is the smallest distance between the centres of two
+  // neighbouring runs (independent of where the row block starts in a partitioned matrix)
+  int64_t best = 0, prev_centre = -1;
+  for (size_t i = 0; i < cols.size();) {
+    size_t j = i;
+    while (j + 1 < cols.size() && cols[j + 1] == cols[j] + 1) ++j;
+    const int64_t centre = ((int64_t)cols[i] + cols[j]) / 2;
+    if (prev_centre >= 0 && (best == 0 || centre - prev_centre < best)) best = centre - prev_centre;
+    prev_centre = centre;
+    i = j + 1;
+  }
+  if (best >= 32 && best <= m->nrows / 64) sp.line_stride = (int32_t)best;
+  return SLC_OK;
+}
+
+// Slice order of k_spmm_panel for a matrix with grid lines `stride` rows apart: a block takes `width`
+// neighbouring slices from each of `warps / width` consecutive lines, so the rows of X that one warp
+// fetches for the lines above and below it are the rows its neighbours in the block need too (a block
+// of consecutive rows re-fetches every line three times from L2).  Line i is the slices
+// [ceil(i stride / 32), ceil((i+1) stride / 32)); warps without a slice idle.  Any order is correct:
+// the table only decides which rows share an SM.
+static int panel_tiling(slc_matrix *m, int32_t s_begin, int32_t s_end, int32_t stride, int warps, int width) {
+  SellPlan &sp = m->sell;
+  const int32_t key[4] = {s_begin, s_end, stride, (warps << 8) | width};
+  if (sp.panel_order && memcmp(key, sp.panel_key, sizeof key) == 0) return SLC_OK;
+  const int lines_per = warps / width;
+  auto line_first = [&](int64_t i) { return (int32_t)std::min<int64_t>(s_end, std::max<int64_t>(s_begin, ceil_div(i * stride, (int64_t)SELL_C))); };
+  const int64_t line0 = ((int64_t)s_begin * SELL_C) / stride, line1 = ceil_div((int64_t)s_end * SELL_C, (int64_t)stride);
+  std::vector<int32_t> order;
+  for (int64_t l = line0; l < line1; l += lines_per) {
+    int32_t widest = 0;
+    for (int i = 0; i < lines_per; ++i) widest = std::max(widest, line_first(l + i + 1) - line_first(l + i));
+    for (int32_t q = 0; q < widest; q += width)
+      for (int i = 0; i < lines_per; ++i) {
+        const int32_t a = line_first(l + i), b = line_first(l + i + 1);
+        for (int w = 0; w < width; ++w) order.push_back(a + q + w < b ? a + q + w : -1);
+      }
+  }
+  if (sp.panel_order) { dev_free(sp.panel_order); sp.panel_order = nullptr; }
+  DevBuf<int32_t> buf;
+  SLC_TRY(buf.alloc(order.size()));
+  cudaStream_t s = cur_stream();
+  SLC_CUDA(cudaMemcpyAsync(buf.p, order.data(), order.size() * 4, cudaMemcpyHostToDevice, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  sp.panel_order = buf.take();
+  sp.panel_blocks = (int64_t)(order.size() / (size_t)warps);
+  memcpy(sp.panel_key, key, sizeof key);
+  return SLC_OK;
+}
+
 template <class T, int JT, int KU>
 static int launch_panel_inst(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, int threads,
                              int32_t kcap, int32_t row_begin, int32_t row_end) {
-  const SellPlan &sp = m->sell;
+  SellPlan &sp = m->sell;
   const size_t smem = (size_t)kcap * threads * (sizeof(T) + sizeof(int32_t));
   static size_t smem_set = 0;  // per instantiation
   if (smem > smem_set) {
@@ -1444,9 +1511,24 @@ static int launch_panel_inst(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64
     smem_set = smem;
   }
   if (row_end <= row_begin) return SLC_OK;
-  const int64_t nb = ceil_div(row_end - row_begin, threads);
+  int64_t nb = ceil_div(row_end - row_begin, threads);
+  const int32_t *order = nullptr;
+  // Line tiling lost its A/B on the 27-point stencil (7.25 ms against 6.29 ms for consecutive rows,
+  // DESIGN.md 4.3), so it is opt-in: SLC_PANEL_STRIDE=-1 detects the stride, > 0 sets it.  Read on
+  // every call (not cached) so a test can switch it on.
+  const int stride_env = env_int("SLC_PANEL_STRIDE", 0);
+  const int width_env = env_int("SLC_PANEL_WIDTH", 1);
+  if (stride_env < 0) SLC_TRY(detect_line_stride(m));
+  const int32_t stride = stride_env >= 0 ? stride_env : sp.line_stride;
+  const int warps = threads / 32;
+  const int width = (width_env >= 1 && warps % width_env == 0) ? width_env : 1;
+  if (stride >= 32 && warps / width >= 2 && row_begin % SELL_C == 0) {
+    SLC_TRY(panel_tiling(m, row_begin / SELL_C, (int32_t)ceil_div(row_end, SELL_C), stride, warps, width));
+    order = sp.panel_order;
+    nb = sp.panel_blocks;
+  }
   k_spmm_panel<T, JT, KU><<<(unsigned)nb, threads, smem, cur_stream()>>>(
-      row_begin, row_end, kcap, 0u, sp.slice_ptr, sp.rowlen, sp.colidx, (const T *)sp.vals, X, ldx, Y, ldy, k);
+      row_begin, row_end, kcap, 0u, sp.slice_ptr, sp.rowlen, sp.colidx, (const T *)sp.vals, X, ldx, Y, ldy, k, order);
   SLC_LAUNCHED();
   return SLC_OK;
 }

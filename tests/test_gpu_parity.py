@@ -4,6 +4,8 @@ Bar (BASELINE.json north_star): bit-exact sparsity structure for SpGEMM, transpo
 values within 1e-12 relative norm-wise error; transpose values bit-identical.  Where the kernel
 keeps the reference's summation order (row per thread) the test also demands bit-identical values.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -195,6 +197,27 @@ def test_mulm_banded_window_kernel(sl, dtype):
         X = np.asfortranarray(np.stack([vec(rng, gm.ncols, dtype) for _ in range(k)], axis=1))
         np.testing.assert_array_equal(sl.mulM(m, X), oracle.mulm(om, X))
     assert sl.spmm_window_error() == 0
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_mulm_panel_line_tiling(sl, dtype):
+    """Stencils large enough that k_spmm_panel tiles its blocks over grid lines (the slice-order
+    table): line strides that are and are not multiples of 32, a ragged last slice, a 2-D 9-point
+    grid (one level of lines only).  Any slice order must give the reference's rows bit for bit."""
+    rng = np.random.default_rng(8)
+    nine = g._stencil((70, 90), [(dy, dx) for dy in (-1, 0, 1) for dx in (-1, 0, 1)],
+                      [8.0 if (dy, dx) == (0, 0) else -1.0 for dy in (-1, 0, 1) for dx in (-1, 0, 1)], dtype)
+    for gm, k in ((g.stencil3d_27pt((12, 40, 48), dtype), 9), (g.stencil3d_27pt((10, 30, 50), dtype), 16),
+                  (g.stencil3d_27pt((7, 19, 33), dtype), 3), (nine, 8)):
+        om = oracle.csc(*gm)
+        X = np.asfortranarray(np.stack([vec(rng, gm.ncols, dtype) for _ in range(k)], axis=1))
+        want = oracle.mulm(om, X)
+        for stride, width in (("-1", "1"), ("-1", "2"), ("64", "1"), ("0", "1")):
+            os.environ["SLC_PANEL_STRIDE"], os.environ["SLC_PANEL_WIDTH"] = stride, width
+            try:
+                np.testing.assert_array_equal(sl.mulM(to_matrix(sl, gm), X), want)
+            finally:
+                del os.environ["SLC_PANEL_STRIDE"], os.environ["SLC_PANEL_WIDTH"]
 
 
 def test_mulm_stencil_block_and_column_range(sl):
