@@ -136,6 +136,11 @@ struct BalancedPlan {
   bool built = false;
   int32_t nchunks = 0;
   int32_t *chunk_row = nullptr;  // [nchunks+1] first row touching each chunk
+  // hot columns (k_spmv_bal_hot): -1 = not looked at yet, 0 = not worth it
+  int32_t hot_k = -1;
+  int32_t *hot_cols = nullptr;    // [hot_k] column of every shared-memory slot, ascending
+  int32_t *colidx_hot = nullptr;  // [nnz] mirror's column indices, hot ones as 0x80000000 | slot
+  double hot_share = 0.0;         // fraction of the nonzeros that sit in hot columns
 };
 
 }  // namespace slc

@@ -94,6 +94,8 @@ void matrix_release(slc_matrix *m) {
   dev_free(m->sell.slice_cmin);
   dev_free(m->sell.slice_cmax);
   dev_free(m->bal.chunk_row);
+  dev_free(m->bal.hot_cols);
+  dev_free(m->bal.colidx_hot);
   dev_free(m->dist_table);
   if (m->pipe_in) {
     cudaStreamSynchronize(m->pipe_in);

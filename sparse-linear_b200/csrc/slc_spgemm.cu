@@ -124,7 +124,7 @@ constexpr int32_t ROW_END = 0x7fffffff;  // past every valid row index
 // bucket order keeps them so except at class boundaries -- their slice of C is one contiguous range:
 // the lanes park their entries in the warp's shared-memory window at (position in C - start of the
 // range) and the warp then streams the window out with fully coalesced stores.
-constexpr int MERGE_STAGE = 1024;  // entries per warp window (12 or 20 KB per warp)
+constexpr int MERGE_STAGE = 1024;  // default entries per warp window (12 or 20 KB per warp); the kernel takes it as `stage`
 
 template <class T, int NB, bool NUMERIC>
 __global__ void __launch_bounds__(128)
@@ -190,11 +190,11 @@ k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32
       const int last = 31 - __clz(live | 1u);
       wbase = __shfl_sync(0xffffffffu, base, 0);
       wtotal = __shfl_sync(0xffffffffu, bend, last) - wbase;
-      staged = live != 0 && consecutive && wtotal <= MERGE_STAGE;
+      staged = live != 0 && consecutive && wtotal <= stage;
       if (staged) {
-        int32_t *s_i = reinterpret_cast<int32_t *>(merge_smem) + (size_t)warp * MERGE_STAGE;
-        T *s_v = reinterpret_cast<T *>(merge_smem + (size_t)(blockDim.x >> 5) * MERGE_STAGE * sizeof(int32_t)) +
-                 (size_t)warp * MERGE_STAGE;
+        int32_t *s_i = reinterpret_cast<int32_t *>(merge_smem) + (size_t)warp * stage;
+        T *s_v = reinterpret_cast<T *>(merge_smem + (size_t)(blockDim.x >> 5) * stage * sizeof(int32_t)) +
+                 (size_t)warp * stage;
         co = s_i + (base - wbase);
         vo = s_v + (base - wbase);
       }
@@ -230,9 +230,9 @@ k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32
   }
   if (staged) {
     __syncwarp();
-    const int32_t *s_i = reinterpret_cast<const int32_t *>(merge_smem) + (size_t)warp * MERGE_STAGE;
-    const T *s_v = reinterpret_cast<const T *>(merge_smem + (size_t)(blockDim.x >> 5) * MERGE_STAGE * sizeof(int32_t)) +
-                   (size_t)warp * MERGE_STAGE;
+    const int32_t *s_i = reinterpret_cast<const int32_t *>(merge_smem) + (size_t)warp * stage;
+    const T *s_v = reinterpret_cast<const T *>(merge_smem + (size_t)(blockDim.x >> 5) * stage * sizeof(int32_t)) +
+                   (size_t)warp * stage;
     for (int32_t e = lane; e < wtotal; e += 32) {
       ci[wbase + e] = s_i[e];
       cv[wbase + e] = s_v[e];
@@ -247,10 +247,15 @@ static int run_merge(int32_t n, const int32_t *cols, const slc_matrix *a, const 
                      slc_matrix *c) {
   if (n == 0) return SLC_OK;
   static const char *stage_env = getenv("SLC_MM_STAGE");  // SLC_MM_STAGE=0: direct (uncoalesced) stores
-  const int stage = NUMERIC && !(stage_env && stage_env[0] == '0');
-  const size_t smem = stage ? (size_t)(128 / 32) * MERGE_STAGE * (sizeof(int32_t) + sizeof(T)) : 0;
+  static const int cap_env = env_int("SLC_MM_STAGE_CAP", MERGE_STAGE);
+  static const int carve_env = env_int("SLC_MM_CARVEOUT", -1);  // preferred shared-memory carve-out, per cent
+  const int cap = std::max(32, std::min(cap_env, 2048)) / 4 * 4;
+  const int stage = (NUMERIC && !(stage_env && stage_env[0] == '0')) ? cap : 0;
+  const size_t smem = stage ? (size_t)(128 / 32) * stage * (sizeof(int32_t) + sizeof(T)) : 0;
   auto kern = k_mm_merge<T, NB, NUMERIC>;
   if (smem > 48 * 1024) SLC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (NUMERIC && carve_env >= 0)
+    SLC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve_env));
   // SLC_MM_RESIDENT=B: at most B blocks per SM (0 = one block per tile)
   static const int resident_env = env_int("SLC_MM_RESIDENT", 0);
   const int resident = NUMERIC ? resident_env : 0;

@@ -19,6 +19,7 @@
 //   CSR warp/row   one warp per row with a shuffle tree; kept as a simple cross-check.
 #include <algorithm>
 #include <cstdlib>
+#include <type_traits>
 
 #include "slc_common.cuh"
 
@@ -79,6 +80,10 @@ struct DistX {
     return ld_gather(p, pol);
   }
 };
+
+// plain pointer behind an accessor (null when the operand is partitioned)
+template <class T> static inline const T *local_ptr(const LocalX<T> &xa) { return xa.x; }
+template <class T> static inline const T *local_ptr(const DistX<T> &) { return nullptr; }
 
 // The same two accessors for a column-major block X (SpMM): col0(c, ld) is the address of X[c, 0] and
 // ld the distance to X[c, 1] -- every part keeps its own leading dimension.
@@ -272,6 +277,63 @@ static int build_balanced(slc_matrix *m) {
   return SLC_OK;
 }
 
+__global__ void k_hot_remap(int64_t nnz, const int32_t *__restrict__ colidx, const int32_t *__restrict__ slot_of,
+                            int32_t *__restrict__ out) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= nnz) return;
+  const int32_t c = colidx[e];
+  const int32_t sl = __ldg(slot_of + c);
+  out[e] = sl >= 0 ? (int32_t)(0x80000000u | (uint32_t)sl) : c;
+}
+
+// Hot columns of a balanced plan: the `cap` columns with the most entries (degrees come from the
+// canonical CSC pointers; selection on the host, once per matrix).  Kept only when they hold at
+// least a tenth of the nonzeros and x is much longer than the table.
+static int build_hot(slc_matrix *m, int32_t cap) {
+  BalancedPlan &bp = m->bal;
+  if (bp.hot_k >= 0) return SLC_OK;
+  bp.hot_k = 0;
+  // read when the plan is built (not cached): SLC_BAL_HOT=0 switches the table off, SLC_BAL_HOT_K=n
+  // caps it at n slots and drops the size thresholds (tests use it on small matrices)
+  const int hot_env = env_int("SLC_BAL_HOT", 1);
+  const int cap_env = env_int("SLC_BAL_HOT_K", 0);
+  if (cap_env > 0) cap = std::min(cap, cap_env);
+  if (!hot_env || cap < 1 || m->ncols <= cap) return SLC_OK;
+  if (cap_env <= 0 && ((int64_t)m->ncols < (int64_t)cap * 16 || m->nnz < (1 << 20))) return SLC_OK;
+  cudaStream_t s = cur_stream();
+  std::vector<int32_t> cp((size_t)m->ncols + 1);
+  SLC_CUDA(cudaMemcpyAsync(cp.data(), m->colptr, cp.size() * 4, cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  std::vector<int32_t> order((size_t)m->ncols);
+  for (int32_t c = 0; c < m->ncols; ++c) order[(size_t)c] = c;
+  auto denser = [&](int32_t a, int32_t b) {
+    const int32_t da = cp[(size_t)a + 1] - cp[(size_t)a], db = cp[(size_t)b + 1] - cp[(size_t)b];
+    return da != db ? da > db : a < b;
+  };
+  std::nth_element(order.begin(), order.begin() + cap, order.end(), denser);
+  order.resize((size_t)cap);
+  std::sort(order.begin(), order.end());
+  int64_t covered = 0;
+  for (int32_t c : order) covered += cp[(size_t)c + 1] - cp[(size_t)c];
+  bp.hot_share = (double)covered / (double)m->nnz;
+  if (bp.hot_share < 0.10 && cap_env <= 0) return SLC_OK;
+  std::vector<int32_t> slot_of((size_t)m->ncols, -1);
+  for (int32_t i = 0; i < cap; ++i) slot_of[(size_t)order[(size_t)i]] = i;
+  DevBuf<int32_t> d_slot, d_hot, d_idx;
+  SLC_TRY(d_slot.alloc(slot_of.size()));
+  SLC_TRY(d_hot.alloc((size_t)cap));
+  SLC_TRY(d_idx.alloc((size_t)m->nnz));
+  SLC_CUDA(cudaMemcpyAsync(d_slot.p, slot_of.data(), slot_of.size() * 4, cudaMemcpyHostToDevice, s));
+  SLC_CUDA(cudaMemcpyAsync(d_hot.p, order.data(), (size_t)cap * 4, cudaMemcpyHostToDevice, s));
+  k_hot_remap<<<(unsigned)ceil_div(m->nnz, 256), 256, 0, s>>>(m->nnz, m->colidx, d_slot.p, d_idx.p);
+  SLC_LAUNCHED();
+  SLC_CUDA(cudaStreamSynchronize(s));  // the host vectors go out of scope
+  bp.hot_cols = d_hot.take();
+  bp.colidx_hot = d_idx.take();
+  bp.hot_k = cap;
+  return SLC_OK;
+}
+
 // Build the mirror, measure the rows and settle on a kernel family.
 template <class T>
 static int ensure_plan(slc_matrix *m) {
@@ -454,15 +516,12 @@ k_spmv_csr_warp(int32_t nrows, const int32_t *__restrict__ rowptr, const int32_t
 // per row when the chunk holds many rows, a warp per row when it holds few); the piece of a row
 // that started in an earlier chunk goes to part_head[b], the piece of a row that runs past the
 // chunk goes to part_tail[b].  k_spmv_bal_fixup then adds the pieces of each spanning row in order.
-template <class T, bool ACC, class XA>
-__global__ void __launch_bounds__(BAL_THREADS)
-k_spmv_bal(int32_t nrows, int64_t nnz, uint32_t zmask, int batch, const int32_t *__restrict__ rowptr,
-           const int32_t *__restrict__ colidx, const T *__restrict__ vals,
-           const int32_t *__restrict__ first_owned, const XA xa, T *__restrict__ y,
-           T *__restrict__ part_head, T *__restrict__ part_tail) {
-  __shared__ T prod[BAL_CHUNK];
-  const int32_t b = blockIdx.x;
-  const int tid = threadIdx.x;
+// The two phases of a chunk, shared by k_spmv_bal (one chunk per block) and k_spmv_bal_hot (a
+// resident block walks many chunks).  tid = thread within the BAL_THREADS-wide group that owns chunk b.
+template <class T, class XA>
+__device__ __forceinline__ void bal_products(int32_t b, int tid, int64_t nnz, uint32_t zmask, int batch,
+                                             const int32_t *__restrict__ colidx, const T *__restrict__ vals,
+                                             const XA &xa, T *prod) {
   const int64_t start = (int64_t)b * BAL_CHUNK;
   const int64_t end = min(nnz, start + BAL_CHUNK);
   const int32_t cnt = (int32_t)(end - start);
@@ -497,7 +556,14 @@ k_spmv_bal(int32_t nrows, int64_t nnz, uint32_t zmask, int batch, const int32_t 
       }
     }
   }
-  __syncthreads();
+}
+
+template <class T, bool ACC>
+__device__ __forceinline__ void bal_reduce(int32_t b, int tid, int64_t nnz, const int32_t *__restrict__ rowptr,
+                                           const int32_t *__restrict__ first_owned, const T *prod,
+                                           T *__restrict__ y, T *__restrict__ part_head, T *__restrict__ part_tail) {
+  const int64_t start = (int64_t)b * BAL_CHUNK;
+  const int64_t end = min(nnz, start + BAL_CHUNK);
 
   const int32_t fo = first_owned[b];
   const int32_t fo_next = first_owned[b + 1];
@@ -546,6 +612,86 @@ k_spmv_bal(int32_t nrows, int64_t nnz, uint32_t zmask, int batch, const int32_t 
         else part_tail[b] = acc;
       }
     }
+  }
+}
+
+template <class T, bool ACC, class XA>
+__global__ void __launch_bounds__(BAL_THREADS)
+k_spmv_bal(int32_t nrows, int64_t nnz, uint32_t zmask, int batch, const int32_t *__restrict__ rowptr,
+           const int32_t *__restrict__ colidx, const T *__restrict__ vals,
+           const int32_t *__restrict__ first_owned, const XA xa, T *__restrict__ y,
+           T *__restrict__ part_head, T *__restrict__ part_tail) {
+  __shared__ T prod[BAL_CHUNK];
+  bal_products<T, XA>(blockIdx.x, threadIdx.x, nnz, zmask, batch, colidx, vals, xa, prod);
+  __syncthreads();
+  bal_reduce<T, ACC>(blockIdx.x, threadIdx.x, nnz, rowptr, first_owned, prod, y, part_head, part_tail);
+}
+
+// Power-law matrices: a few thousand columns carry a large share of the nonzeros (R-MAT scale 24: the
+// 16384 densest columns hold about a third), but they are scattered over x, so each one costs a whole
+// 32-byte sector of L1 and the gathers miss (ncu, round 1: 4.6 % L1 hits, one L2 sector request per
+// nonzero -- the request rate, not HBM, bounds k_spmv_bal).  Here a resident block of HOT_GROUPS x
+// BAL_THREADS threads copies x at the plan's hot columns into shared memory once and then walks its
+// chunks; colidx_hot holds (0x80000000 | slot) for a hot column, so those gathers are shared-memory
+// reads.  Arithmetic and summation order are k_spmv_bal's.
+// groups (chunks in flight) per resident block: 4 for Double; 3 for Complex Double, whose chunk body
+// needs more than the 64 registers a 1024-thread block leaves
+template <class T> struct HotGroups { static constexpr int value = sizeof(T) == 8 ? 4 : 3; };
+
+template <class T>
+struct HotX {
+  const T *x;
+  const T *hot;  // shared memory
+  __device__ __forceinline__ T operator()(int32_t c, uint64_t pol) const {
+    if (c < 0) return hot[c & 0x7fffffff];
+    return ld_gather(x + c, pol);
+  }
+};
+
+// The same table kept in global memory instead (mode 2): x at the hot columns is packed into a small
+// contiguous array before the product, so the hot gathers share a few hundred L1 lines instead of one
+// sector each; the product kernel is the ordinary k_spmv_bal.
+template <class T>
+struct HotPackedX {
+  const T *x;
+  const T *xhot;  // [hot_k], global
+  __device__ __forceinline__ T operator()(int32_t c, uint64_t pol) const {
+    if (c < 0) return __ldg(xhot + (c & 0x7fffffff));
+    return ld_gather(x + c, pol);
+  }
+};
+
+template <class T>
+__global__ void k_hot_pack(int32_t hot_k, const int32_t *__restrict__ hot_cols, const T *__restrict__ x,
+                           T *__restrict__ xhot) {
+  const int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < hot_k) xhot[i] = x[hot_cols[i]];
+}
+
+template <class T, bool ACC>
+__global__ void __launch_bounds__(HotGroups<T>::value *BAL_THREADS, 1)
+k_spmv_bal_hot(int32_t nrows, int64_t nnz, int32_t nchunks, uint32_t zmask, int batch,
+               const int32_t *__restrict__ rowptr, const int32_t *__restrict__ colidx_hot,
+               const T *__restrict__ vals, const int32_t *__restrict__ first_owned, const T *__restrict__ x,
+               const int32_t *__restrict__ hot_cols, int32_t hot_k, T *__restrict__ y, T *__restrict__ part_head,
+               T *__restrict__ part_tail) {
+  extern __shared__ __align__(16) unsigned char hot_smem[];
+  const int HOT_GROUPS = blockDim.x / BAL_THREADS;  // <= HotGroups<T>::value
+  T *prod_all = reinterpret_cast<T *>(hot_smem);               // [HOT_GROUPS][BAL_CHUNK]
+  T *hot = prod_all + (size_t)HOT_GROUPS * BAL_CHUNK;         // [hot_k]
+  const uint64_t pol_x = policy_evict_last();
+  for (int32_t i = threadIdx.x; i < hot_k; i += blockDim.x) hot[i] = ld_gather(x + __ldg(hot_cols + i), pol_x);
+  __syncthreads();
+  const int grp = threadIdx.x / BAL_THREADS, tid = threadIdx.x % BAL_THREADS;
+  T *prod = prod_all + (size_t)grp * BAL_CHUNK;
+  const HotX<T> xa{x, hot};
+  for (int64_t base = (int64_t)blockIdx.x * HOT_GROUPS; base < nchunks; base += (int64_t)gridDim.x * HOT_GROUPS) {
+    const int32_t b = (int32_t)base + grp;
+    const bool live = b < nchunks;
+    if (live) bal_products<T, HotX<T>>(b, tid, nnz, zmask, batch, colidx_hot, vals, xa, prod);
+    __syncthreads();
+    if (live) bal_reduce<T, ACC>(b, tid, nnz, rowptr, first_owned, prod, y, part_head, part_tail);
+    __syncthreads();  // prod is rewritten by the next chunk
   }
 }
 
@@ -1145,6 +1291,46 @@ static int spmv_run(slc_matrix *m, const XA &xa, T *y) {
       // measured on B200, R-MAT scale 24: shared-memory kernel 1.51 ms, merge-style kernel 1.95 ms
       // (both bound by the number of random 32-byte gathers an SM keeps in flight)
       static const int batch_env = env_int("SLC_BAL_BATCH", 0);
+      if (m->spmv_active == SPMV_CSR_BALANCED && std::is_same<XA, LocalX<T>>::value) {
+        // hot columns of x in shared memory: 128 KB of slots beside the four product buffers
+        const int32_t cap = (int32_t)(((size_t)128 << 10) / sizeof(T));
+        SLC_TRY(build_hot(m, cap));
+        static const int mode_env = env_int("SLC_BAL_HOT_MODE", 2);  // 2 = packed table in global memory (default, -10 % on R-MAT scale 24), 1 = shared-memory table in resident blocks (lost its A/B)
+        if (bp.hot_k > 0 && mode_env == 2) {
+          DevBuf<T> xhot;
+          SLC_TRY(xhot.alloc((size_t)bp.hot_k));
+          k_hot_pack<T><<<(unsigned)ceil_div(bp.hot_k, 256), 256, 0, s>>>(bp.hot_k, bp.hot_cols, local_ptr(xa), xhot.p);
+          SLC_LAUNCHED();
+          k_spmv_bal<T, ACC, HotPackedX<T>><<<(unsigned)bp.nchunks, BAL_THREADS, 0, s>>>(
+              m->nrows, m->nnz, 0u, batch_env, m->rowptr, bp.colidx_hot, (const T *)m->rvals, bp.chunk_row,
+              HotPackedX<T>{local_ptr(xa), xhot.p}, y, ph.p, pt.p);
+          SLC_LAUNCHED();
+          k_spmv_bal_fixup<T, ACC><<<(unsigned)ceil_div(bp.nchunks, 256), 256, 0, s>>>(
+              bp.nchunks, m->nnz, m->rowptr, bp.chunk_row, ph.p, pt.p, y);
+          SLC_LAUNCHED();
+          return SLC_OK;
+        }
+        if (bp.hot_k > 0) {
+          static const int groups_env = env_int("SLC_BAL_HOT_GROUPS", 0);
+          const int HOT_GROUPS = groups_env > 0 ? std::min(groups_env, HotGroups<T>::value) : HotGroups<T>::value;
+          const size_t smem = ((size_t)HOT_GROUPS * BAL_CHUNK + (size_t)bp.hot_k) * sizeof(T);
+          static size_t smem_set = 0;
+          if (smem > smem_set) {
+            SLC_CUDA(cudaFuncSetAttribute(k_spmv_bal_hot<T, ACC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            smem_set = smem;
+          }
+          const int per_sm = std::max<int>(1, (int)(((size_t)227 << 10) / (smem + 1024)));
+          const int64_t grid = std::min<int64_t>(ceil_div(bp.nchunks, HOT_GROUPS), (int64_t)sm_count() * per_sm);
+          k_spmv_bal_hot<T, ACC><<<(unsigned)grid, HOT_GROUPS * BAL_THREADS, smem, s>>>(
+              m->nrows, m->nnz, bp.nchunks, 0u, batch_env, m->rowptr, bp.colidx_hot, (const T *)m->rvals, bp.chunk_row,
+              local_ptr(xa), bp.hot_cols, bp.hot_k, y, ph.p, pt.p);
+          SLC_LAUNCHED();
+          k_spmv_bal_fixup<T, ACC><<<(unsigned)ceil_div(bp.nchunks, 256), 256, 0, s>>>(
+              bp.nchunks, m->nnz, m->rowptr, bp.chunk_row, ph.p, pt.p, y);
+          SLC_LAUNCHED();
+          return SLC_OK;
+        }
+      }
       if (m->spmv_active == SPMV_CSR_BALANCED)
         k_spmv_bal<T, ACC, XA><<<(unsigned)bp.nchunks, BAL_THREADS, 0, s>>>(
             m->nrows, m->nnz, 0u, batch_env, m->rowptr, m->colidx, (const T *)m->rvals, bp.chunk_row, xa, y, ph.p,

@@ -105,6 +105,107 @@ def gather_blocks(c_local, dist, group=None):
     return vstack_blocks(exchange_objects(blk, dist, group))
 
 
+# ---- transpose and assembly over ranks: one exchange step, local kernels ----------
+# Both are written as "make the pieces for every destination" / "combine what arrived", so a test can
+# run the ranks one after the other in one process; exchange_pieces is the only collective.
+
+def col_block(m, c0, c1):
+    """A[:, c0:c1] of a CSC matrix (a slice of the arrays, pointers rebased)."""
+    p0, p1 = int(m.colptr[c0]), int(m.colptr[c1])
+    return CSC(m.nrows, int(c1 - c0), (np.asarray(m.colptr[c0:c1 + 1], dtype=np.int64) - p0).astype(np.int32),
+               np.ascontiguousarray(m.rowidx[p0:p1]), np.ascontiguousarray(m.values[p0:p1]))
+
+
+def exchange_pieces(send, dist, group=None):
+    """All-to-all-v of picklable pieces: send[p] goes to rank p; returns recv with recv[q] = the piece
+    rank q sent here.  Numpy arrays inside the pieces travel as NCCL all_to_all_single payloads when
+    the default backend is NCCL (sizes first, then one flat byte buffer per pair); on gloo (the CPU
+    tests) the pieces are gathered as objects."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return [send[0]]
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    if dist.get_backend(group) != "nccl":
+        everything = exchange_objects(send, dist, group)
+        return [everything[q][rank] for q in range(world)]
+    import pickle
+    import torch
+    blobs = [np.frombuffer(pickle.dumps(x, protocol=pickle.HIGHEST_PROTOCOL), dtype=np.uint8) for x in send]
+    out_sizes = torch.tensor([len(b) for b in blobs], dtype=torch.int64, device="cuda")
+    in_sizes = torch.empty(world, dtype=torch.int64, device="cuda")
+    dist.all_to_all_single(in_sizes, out_sizes, group=group)
+    in_sizes = [int(v) for v in in_sizes.tolist()]
+    flat = torch.from_numpy(np.concatenate(blobs)).cuda()
+    got = torch.empty(sum(in_sizes), dtype=torch.uint8, device="cuda")
+    dist.all_to_all_single(got, flat, output_split_sizes=in_sizes, input_split_sizes=[len(b) for b in blobs],
+                           group=group)
+    got = got.cpu().numpy()
+    recv, at = [], 0
+    for n in in_sizes:
+        recv.append(pickle.loads(got[at:at + n].tobytes()))
+        at += n
+    return recv
+
+
+def transpose_pieces(local_t, row_splits):
+    """local_t: the transpose of this rank's column block A[:, c0:c1], i.e. a (c1-c0) x nrows CSC whose
+    column r is row r of the block.  Piece p = its columns [row_splits[p], row_splits[p+1])."""
+    return [col_block(local_t, int(row_splits[p]), int(row_splits[p + 1])) for p in range(len(row_splits) - 1)]
+
+
+def transpose_combine(received):
+    """received[q] = piece from rank q (its rows are A's columns [c_q0, c_q1)); stacked in rank order they
+    are this rank's column block of the transpose, A^T[:, r0:r1] -- stable, because rank order is column
+    order of A (Sparse.hs:301-329 keeps equal keys in input order)."""
+    return vstack_blocks(received)
+
+
+def sharded_transpose(local_block, row_splits, dist=None, group=None, local_transpose=None):
+    """Transpose of a matrix held as column blocks (rank q: A[:, c_q0:c_q1], all nrows rows).  Returns
+    this rank's column block of A^T as a CSC of shape ncols x (r1-r0).  The local transpose runs on
+    the GPU (slc_*_transpose); one all-to-all-v moves every entry to the rank that owns its row."""
+    if local_transpose is None:
+        def local_transpose(blk):
+            from .matrix import transpose
+            t = transpose(Matrix(blk.ncols, blk.nrows, blk.colptr, blk.rowidx, blk.values))
+            return CSC(t.nrows, t.ncols, t.pointers, t.indices, t.values)
+    pieces = transpose_pieces(local_transpose(local_block), row_splits)
+    return transpose_combine(exchange_pieces(pieces, dist, group))
+
+
+def compress_pieces(rows, cols, vals, col_splits):
+    """Triplets bucketed by the rank that owns their column, input order kept inside a bucket, columns
+    rebased to the owner's block.  Out-of-range columns go to the nearest block so that the owner's
+    compress reports them (Sparse.hs:192-212)."""
+    rows, cols, vals = np.asarray(rows), np.asarray(cols), np.asarray(vals)
+    nparts = len(col_splits) - 1
+    owner = np.clip(np.searchsorted(np.asarray(col_splits[1:-1]), cols, side="right"), 0, nparts - 1)
+    out = []
+    for p in range(nparts):
+        keep = owner == p
+        out.append((np.ascontiguousarray(rows[keep]), np.ascontiguousarray(cols[keep] - int(col_splits[p])),
+                    np.ascontiguousarray(vals[keep])))
+    return out
+
+
+def compress_combine(nrows, width, received, local_compress=None):
+    """Triplets from every rank, concatenated in rank order, assembled locally (slc_*_compress on the
+    GPU): duplicates are summed in (source rank, input position) order."""
+    if local_compress is None:
+        from .matrix import compress as local_compress
+    r = np.concatenate([x[0] for x in received])
+    c = np.concatenate([x[1] for x in received])
+    v = np.concatenate([x[2] for x in received])
+    return local_compress(nrows, width, r, c, v)
+
+
+def sharded_compress(nrows, rows, cols, vals, col_splits, rank, dist=None, group=None, local_compress=None):
+    """compress (Sparse.hs:184-255) of triplets spread over the ranks: returns this rank's column block
+    A[:, c0:c1] (nrows x (c1-c0)).  One all-to-all-v, then the local device assembly."""
+    pieces = compress_pieces(rows, cols, vals, col_splits)
+    width = int(col_splits[rank + 1] - col_splits[rank])
+    return compress_combine(nrows, width, exchange_pieces(pieces, dist, group), local_compress)
+
+
 # ---- device side --------------------------------------------------------------------------------------
 
 class ShardedSpMV:
@@ -260,6 +361,8 @@ def bench_main(args, rank, world, local_rank, dist):
         return bench_spgemm_sharded(args, rank, world, local_rank, dist)
     if args.workload == "cfg4":
         return bench_powerlaw_sharded(args, rank, world, local_rank, dist)
+    if args.workload in ("cfg3t", "cfg3a"):
+        return bench_structural_sharded(args, rank, world, local_rank, dist)
     n = args.grid or 200
     if args.scaling == "weak":
         shape = (n * world, n, n)
@@ -557,6 +660,66 @@ def bench_powerlaw_sharded(args, rank, world, local_rank, dist):
                 "cpu_baseline": None}
         print(json.dumps(line), flush=True)
     sh.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def bench_structural_sharded(args, rank, world, local_rank, dist):
+    """cfg 3 transpose / assembly over `world` GPUs: column blocks in, column blocks out, one
+    all-to-all-v (NCCL), local kernels on each GPU.  The pieces are cut, shipped and stacked through
+    host memory this round, so the figure is the whole step (device kernels + PCIe + host stacking),
+    wall clock, max over ranks."""
+    import torch
+    import sparse_linear_b200 as sl
+    from . import generators as g
+    import bench as B
+    n = args.grid or 128
+    a = g.laplace3d_7pt(n)
+    sl.set_stream(torch.cuda.current_stream().cuda_stream)
+    cs = uniform_splits(n, world) * (n * n)
+    c0, c1 = int(cs[rank]), int(cs[rank + 1])
+    blk = col_block(a, c0, c1)
+    steps = max(1, min(args.steps, 5))
+    if args.workload == "cfg3t":
+        def step():
+            return sharded_transpose(blk, cs, dist)
+        ref = blk          # the Laplacian is symmetric: block c of the transpose is block c of A
+        units, unit, metric = int(a.colptr[-1]), "nnz/s", "transpose_nnz_per_s"
+    else:
+        r, c, v = g.split_duplicates(a, seed=0)       # every rank generates the same shuffled triplets
+        lo, hi = (len(r) * rank) // world, (len(r) * (rank + 1)) // world
+        r, c, v = r[lo:hi], c[lo:hi], v[lo:hi]
+
+        def step():
+            m = sharded_compress(a.nrows, r, c, v, cs, rank, dist)
+            return CSC(m.nrows, m.ncols, m.pointers, m.indices, m.values)
+        ref = blk          # 0.25 v + 0.75 v == v exactly
+        units, unit, metric = 2 * int(a.colptr[-1]), "triplets/s", "assembly_triplets_per_s"
+    got = step()
+    ok = bool(np.array_equal(got.colptr, ref.colptr) and np.array_equal(got.rowidx, ref.rowidx)
+              and np.array_equal(got.values, ref.values))
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    l0 = sl.launch_count()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    torch.cuda.synchronize()
+    ms = _max_over_ranks((time.perf_counter() - t0) / steps * 1e3, dist, world)
+    oks = _sum_over_ranks([1.0 if ok else 0.0], dist, world)[0]
+    if rank == 0:
+        line = {"metric": metric, "value": units / (ms * 1e-3), "unit": unit, "n_gpus": world, "steps": steps, "warmup": 1,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "u32 keys + f64 values", "data": "synthetic (seeded numpy PCG64)",
+                "config": {"workload": "cfg3: %s of the 3D 7-point Laplacian %d^3 held as %d column blocks; local %s on each GPU, "
+                                       "one all-to-all-v over NCCL, pieces cut and stacked on the host"
+                                       % ("transpose" if args.workload == "cfg3t" else "triplet assembly (2x duplicates)", n, world,
+                                          "slc_d_transpose" if args.workload == "cfg3t" else "slc_d_compress"),
+                           "blocks_equal_expected_bit_exact_on_ranks": int(oks), "timing": "wall clock, max over ranks"},
+                "gpu_launches": int(sl.launch_count() - l0), "roofline": None}
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -11,7 +11,7 @@ import pytest
 
 import oracle
 from helpers import (TOL, arbitrary_matrix, arbitrary_triples, assert_same_structure, assert_values_close,
-                     random_csc, to_matrix)
+                     random_csc, rmat_csc, to_matrix)
 from sparse_linear_b200 import generators as g
 
 pytestmark = pytest.mark.gpu
@@ -150,6 +150,36 @@ def test_mulm_matches_oracle(sl, dtype, kind):
         got = sl.mulM(m, X)
         assert got.shape == (nr, k)
         np.testing.assert_array_equal(got, want)     # a thread owns (row, column): reference order
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_mulv_balanced_hot_columns(sl, dtype):
+    """Power-law matrices on the balanced plan keep x at their densest columns in shared memory
+    (k_spmv_bal_hot, resident blocks walking the chunks).  Small tables force hot and cold gathers in
+    the same warp, a table larger than the chunk count exercises idle groups, axpy exercises ACC."""
+    rng = np.random.default_rng(41)
+    for scale, ef, cap in ((12, 8, "64"), (14, 6, "1000"), (10, 40, "7"), (15, 3, "4096")):
+        om = rmat_csc(scale, ef, seed=scale, dtype=dtype)
+        x = vec(rng, om.ncols, dtype)
+        y0 = vec(rng, om.nrows, dtype)
+        want, want_acc = oracle.mulv(om, x), oracle.axpy(om, x, y0)
+        os.environ["SLC_BAL_HOT_K"] = cap
+        try:
+            m = to_matrix(sl, om)
+            m.device().set_spmv_kernel(KINDS["csr-balanced"])
+            got, got_acc = sl.mulV(m, x), sl.axpy(m, x, y0)
+        finally:
+            del os.environ["SLC_BAL_HOT_K"]
+        assert_values_close(got, want)
+        assert_values_close(got_acc, want_acc)
+        # the table changes where x is read from, not the arithmetic: same bits as the plain kernel
+        os.environ["SLC_BAL_HOT"] = "0"
+        try:
+            m2 = to_matrix(sl, om)
+            m2.device().set_spmv_kernel(KINDS["csr-balanced"])
+            np.testing.assert_array_equal(sl.mulV(m2, x), got)
+        finally:
+            del os.environ["SLC_BAL_HOT"]
 
 
 @pytest.mark.parametrize("dtype", DTYPES)

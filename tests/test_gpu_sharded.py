@@ -158,6 +158,43 @@ def test_row_partitioned_spgemm_concatenates_to_the_oracle(sl):
         assert np.array_equal(got.values, want.values)
 
 
+@pytest.mark.parametrize("dtype", [np.float64, np.complex128])
+def test_sharded_transpose_and_assembly_device_ops(sl, dtype):
+    """The ranks of sharded_transpose / sharded_compress run one after the other in this process, the
+    local steps on the GPU (slc_*_transpose, slc_*_compress); blocks must equal the oracle's."""
+    rng = np.random.default_rng(17)
+    m = random_csc(rng, 230, 170, 0.06, dtype)
+    world = 3
+    cs, rs = sharded.uniform_splits(m.ncols, world), sharded.uniform_splits(m.nrows, world)
+
+    def dev_transpose(blk):
+        t = sl.transpose(to_matrix(sl, blk))
+        return g.CSC(t.nrows, t.ncols, t.pointers, t.indices, t.values)
+    sent = [sharded.transpose_pieces(dev_transpose(sharded.col_block(m, cs[q], cs[q + 1])), rs) for q in range(world)]
+    want = oracle.transpose(oracle.csc(*m))
+    for p in range(world):
+        got = sharded.transpose_combine([sent[q][p] for q in range(world)])
+        ref = sharded.col_block(want, rs[p], rs[p + 1])
+        assert np.array_equal(got.colptr, ref.colptr) and np.array_equal(got.rowidx, ref.rowidx)
+        assert np.array_equal(got.values, ref.values)
+    # single rank through the public wrapper (no collective)
+    whole = sharded.sharded_transpose(m, np.array([0, m.nrows]))
+    assert np.array_equal(whole.colptr, want.colptr) and np.array_equal(whole.rowidx, want.rowidx)
+
+    n = 3000
+    r, c = rng.integers(0, 230, n), rng.integers(0, 170, n)
+    v = rng.integers(-5, 6, n).astype(dtype)      # integers: sums are exact in any order
+    full = oracle.compress(230, 170, r, c, v)
+    cuts = [0, 1100, 1900, n]
+    sent = [sharded.compress_pieces(r[cuts[q]:cuts[q + 1]], c[cuts[q]:cuts[q + 1]], v[cuts[q]:cuts[q + 1]], cs)
+            for q in range(world)]
+    for p in range(world):
+        got = sharded.compress_combine(230, int(cs[p + 1] - cs[p]), [sent[q][p] for q in range(world)])
+        ref = sharded.col_block(full, cs[p], cs[p + 1])
+        assert np.array_equal(got.pointers, ref.colptr) and np.array_equal(got.indices, ref.rowidx)
+        assert np.array_equal(got.values, ref.values)
+
+
 def test_sharded_wrapper_allgather_single_rank(sl):
     gm = rmat_csc(9, 8, seed=4)
     m = to_matrix(sl, gm)

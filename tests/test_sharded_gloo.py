@@ -85,6 +85,89 @@ def test_row_partitioned_product_of_matrices_is_the_product():
     assert np.array_equal(got.values, want.values)
 
 
+def _oracle_transpose(blk):
+    t = oracle.transpose(oracle.csc(*blk))
+    return g.CSC(t.nrows, t.ncols, t.colptr, t.rowidx, t.values)
+
+
+def test_sharded_transpose_pieces_single_process():
+    """Ranks run one after the other: column blocks in, column blocks of the transpose out."""
+    rng = np.random.default_rng(12)
+    for m, world in ((random_csc(rng, 37, 53, 0.2), 4), (random_csc(rng, 20, 9, 0.4, np.complex128), 3),
+                     (g.laplace3d_7pt(4), 2), (random_csc(rng, 8, 8, 0.0), 3)):
+        want = oracle.transpose(oracle.csc(*m))
+        cs, rs = sharded.uniform_splits(m.ncols, world), sharded.uniform_splits(m.nrows, world)
+        sent = [sharded.transpose_pieces(_oracle_transpose(sharded.col_block(m, cs[q], cs[q + 1])), rs)
+                for q in range(world)]
+        for p in range(world):
+            got = sharded.transpose_combine([sent[q][p] for q in range(world)])
+            ref = sharded.col_block(want, rs[p], rs[p + 1])
+            assert got.nrows == m.ncols and got.ncols == rs[p + 1] - rs[p]
+            assert np.array_equal(got.colptr, ref.colptr) and np.array_equal(got.rowidx, ref.rowidx)
+            assert np.array_equal(got.values, ref.values)
+
+
+def test_sharded_compress_pieces_single_process():
+    """Triplets with duplicates spread over ranks: every rank's block equals the block of the whole
+    assembly; sums run in (rank, input position) order = the order of the concatenated input."""
+    rng = np.random.default_rng(14)
+    nr, nc, world = 23, 31, 3
+    n = 400
+    r, c = rng.integers(0, nr, n), rng.integers(0, nc, n)
+    v = rng.integers(-5, 6, n).astype(np.float64)
+    want = oracle.compress(nr, nc, r, c, v)
+    cs = sharded.uniform_splits(nc, world)
+    cuts = [0, 150, 150, n]          # rank 1 holds no triplets
+    sent = [sharded.compress_pieces(r[cuts[q]:cuts[q + 1]], c[cuts[q]:cuts[q + 1]], v[cuts[q]:cuts[q + 1]], cs)
+            for q in range(world)]
+    for p in range(world):
+        got = sharded.compress_combine(nr, int(cs[p + 1] - cs[p]), [sent[q][p] for q in range(world)], oracle.compress)
+        ref = sharded.col_block(want, cs[p], cs[p + 1])
+        assert np.array_equal(got.colptr, ref.colptr) and np.array_equal(got.rowidx, ref.rowidx)
+        assert np.array_equal(got.values, ref.values)
+    # an out-of-range column is reported by the owner's compress, as the reference does (Sparse.hs:192-212)
+    bad = sharded.compress_pieces([0], [nc + 5], [1.0], cs)
+    with pytest.raises(oracle.OracleError):
+        sharded.compress_combine(nr, int(cs[-1] - cs[-2]), [bad[world - 1]], oracle.compress)
+
+
+def _worker_structural(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(30)            # same matrix on every rank
+        m = random_csc(rng, 41, 29, 0.25)
+        cs, rs = sharded.uniform_splits(m.ncols, world), sharded.uniform_splits(m.nrows, world)
+        got = sharded.sharded_transpose(sharded.col_block(m, cs[rank], cs[rank + 1]), rs, dist,
+                                        local_transpose=_oracle_transpose)
+        want = sharded.col_block(oracle.transpose(oracle.csc(*m)), rs[rank], rs[rank + 1])
+        ok = (np.array_equal(got.colptr, want.colptr) and np.array_equal(got.rowidx, want.rowidx)
+              and np.array_equal(got.values, want.values))
+        # assembly: this rank's share of the triplets (with duplicates)
+        n = 300
+        r, c = rng.integers(0, 41, n), rng.integers(0, 29, n)
+        v = rng.integers(-5, 6, n).astype(np.float64)
+        lo, hi = (0, 170) if rank == 0 else (170, n)
+        blk = sharded.sharded_compress(41, r[lo:hi], c[lo:hi], v[lo:hi], cs, rank, dist, local_compress=oracle.compress)
+        ref = sharded.col_block(oracle.compress(41, 29, r, c, v), cs[rank], cs[rank + 1])
+        ok = ok and (np.array_equal(blk.colptr, ref.colptr) and np.array_equal(blk.rowidx, ref.rowidx)
+                     and np.array_equal(blk.values, ref.values))
+        oks = [None] * world
+        dist.all_gather_object(oks, bool(ok))
+        if rank == 0:
+            ret["ok"] = all(oks)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_transpose_and_assembly_gloo():
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker_structural, args=(2, _free_port(), ret), nprocs=2, join=True)
+    assert ret.get("ok") is True
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
