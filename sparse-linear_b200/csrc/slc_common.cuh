@@ -116,6 +116,12 @@ struct SellPlan {
   int32_t *rowlen = nullptr;     // [nrows]
   int32_t *colidx = nullptr;     // [padded]
   void *vals = nullptr;          // [padded]
+  // Index compression: kbase[slice_ptr[s] / 32 + k] = c - lane when entry k of every row of slice s
+  // that has one sits at column (that value + lane) -- a stencil away from the grid boundary -- so
+  // the warp needs 4 bytes instead of 128 for those indices; SELL_IRREGULAR otherwise.  nullptr when
+  // fewer than a quarter of the entries qualify.
+  int32_t *kbase = nullptr;
+  int64_t unit_entries = 0;       // stored entries covered by a unit-stride base
   int32_t *slice_cmin = nullptr;  // [nslices] smallest / largest column of each slice
   int32_t *slice_cmax = nullptr;
   // distributed products: host copy of the slice ranges and the cached interior run

@@ -87,6 +87,7 @@ void matrix_release(slc_matrix *m) {
   dev_free(m->colidx);
   dev_free(m->rvals);
   dev_free(m->sell.slice_ptr);
+  dev_free(m->sell.kbase);
   dev_free(m->sell.panel_order);
   dev_free(m->sell.rowlen);
   dev_free(m->sell.colidx);

@@ -34,6 +34,7 @@ int peer_sync_args(slc_peer_group *g, unsigned long long *const **flags, int **t
 // =================================================================================================
 
 constexpr int SELL_C = 32;
+constexpr int32_t SELL_IRREGULAR = (int32_t)0x80000000;  // kbase: this (slice, k) keeps per-lane indices
 constexpr int BAL_THREADS = 256;
 constexpr int BAL_ITEMS = 8;
 constexpr int BAL_CHUNK = BAL_THREADS * BAL_ITEMS;  // nonzeros per block
@@ -146,7 +147,8 @@ __global__ void k_sell_fill(int32_t nrows, int32_t nslices, const int32_t *__res
                             const int32_t *__restrict__ colidx, const T *__restrict__ vals,
                             const int64_t *__restrict__ slice_ptr, int32_t *__restrict__ s_col,
                             T *__restrict__ s_val, int32_t *__restrict__ slice_cmin,
-                            int32_t *__restrict__ slice_cmax) {
+                            int32_t *__restrict__ slice_cmax, int32_t *__restrict__ kbase,
+                            unsigned long long *__restrict__ unit_entries) {
   const int32_t slice = (int32_t)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   const int lane = threadIdx.x & 31;
   if (slice >= nslices) return;
@@ -159,10 +161,12 @@ __global__ void k_sell_fill(int32_t nrows, int32_t nslices, const int32_t *__res
     len = rowptr[row + 1] - start;
   }
   int32_t cmin = 0x7fffffff, cmax = -1;
+  unsigned long long units = 0;
   for (int32_t k = 0; k < width; ++k) {
     const int64_t at = base + (int64_t)k * SELL_C + lane;
+    int32_t c = 0;
     if (k < len) {
-      const int32_t c = colidx[start + k];
+      c = colidx[start + k];
       s_col[at] = c;
       s_val[at] = vals[start + k];
       cmin = min(cmin, c);
@@ -171,7 +175,19 @@ __global__ void k_sell_fill(int32_t nrows, int32_t nslices, const int32_t *__res
       s_col[at] = 0;
       s_val[at] = Num<T>::zero();
     }
+    // unit stride: every lane that has an entry k sits at column (common base) + lane
+    const unsigned have = __ballot_sync(0xffffffffu, k < len);
+    int32_t kb = 0;
+    if (have) {
+      const int32_t mine = c - lane;
+      const int32_t first = __shfl_sync(0xffffffffu, mine, __ffs(have) - 1);
+      const bool same = __all_sync(0xffffffffu, k >= len || mine == first);
+      kb = same ? first : SELL_IRREGULAR;
+      if (same) units += __popc(have);
+    }
+    if (lane == 0) kbase[base / SELL_C + k] = kb;
   }
+  if (lane == 0 && units) atomicAdd(unit_entries, units);
   // column range of the slice: lets a distributed product find the rows that need no peer
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -249,11 +265,27 @@ static int fill_sell(slc_matrix *m) {
   SLC_TRY(sv.alloc((size_t)sp.padded));
   SLC_TRY(cmin.alloc((size_t)sp.nslices));
   SLC_TRY(cmax.alloc((size_t)sp.nslices));
+  DevBuf<int32_t> kb;
+  DevBuf<unsigned long long> units;
+  SLC_TRY(kb.alloc((size_t)(sp.padded / SELL_C) + 16));  // + 16: a batch may look past the last slice
+  SLC_TRY(units.alloc(1));
+  SLC_CUDA(cudaMemsetAsync(kb.p, 0, ((size_t)(sp.padded / SELL_C) + 16) * sizeof(int32_t), s));
+  SLC_CUDA(cudaMemsetAsync(units.p, 0, sizeof(unsigned long long), s));
   if (sp.nslices) {
     k_sell_fill<T><<<(unsigned)ceil_div((int64_t)sp.nslices * 32, 256), 256, 0, s>>>(
         m->nrows, sp.nslices, m->rowptr, m->colidx, (const T *)m->rvals, sp.slice_ptr, sc.p, sv.p, cmin.p,
-        cmax.p);
+        cmax.p, kb.p, units.p);
     SLC_LAUNCHED();
+    unsigned long long h_units = 0;
+    SLC_CUDA(cudaMemcpyAsync(&h_units, units.p, sizeof h_units, cudaMemcpyDeviceToHost, s));
+    SLC_CUDA(cudaStreamSynchronize(s));
+    sp.unit_entries = (int64_t)h_units;
+    // Used when at least a quarter of the entries qualify and the matrix streams from HBM; a matrix
+    // that stays in L2 gains nothing from fewer bytes and pays for the extra words (cfg 1: 16.7 µs with,
+    // 14.5 µs without).  SLC_SELL_KBASE=0 keeps the per-entry indices, =2 compresses at any size (tests).
+    const int kb_env = env_int("SLC_SELL_KBASE", 1);
+    const bool streams = (size_t)sp.padded * (sizeof(T) + sizeof(int32_t)) > ((size_t)96 << 20);
+    if (kb_env && (streams || kb_env == 2) && sp.unit_entries * 4 >= m->nnz) sp.kbase = kb.take();
   }
   sp.colidx = sc.take();
   sp.vals = sv.take();
@@ -359,26 +391,53 @@ static int ensure_plan(slc_matrix *m) {
 // Per k the 32 lanes of a warp read 32 consecutive indices (128 B) and 32 consecutive values
 // (256/512 B); on a stencil the gathered x entries are consecutive too.  U entries are fetched
 // before any is used, so each thread keeps U index + U value loads in flight.
-template <class T, int U, bool ACC, class XA>
+template <class T, int U, bool ACC, class XA, bool KB = false>
 __device__ __forceinline__ void sell_row(int32_t row, const int64_t *__restrict__ slice_ptr,
                                          const int32_t *__restrict__ rowlen,
                                          const int32_t *__restrict__ colidx, const T *__restrict__ vals,
-                                         const XA &xa, T *__restrict__ y) {
+                                         const XA &xa, T *__restrict__ y, const int32_t *__restrict__ kbase = nullptr) {
   const uint64_t pol_s = policy_evict_first();
   const uint64_t pol_x = policy_evict_last();
-  const int64_t base = __ldg(slice_ptr + (row >> 5)) + (threadIdx.x & 31);
+  const int lane = threadIdx.x & 31;
+  const int64_t sbase = __ldg(slice_ptr + (row >> 5));
+  const int64_t base = sbase + lane;
   const int32_t len = __ldg(rowlen + row);
   const int32_t *ci = colidx + base;
   const T *va = vals + base;
+  const int32_t *kb = KB ? kbase + (sbase >> 5) : nullptr;  // one word per (slice, k): same address for the warp
   T acc = ACC ? y[row] : Num<T>::zero();
   for (int32_t k = 0; k < len; k += U) {
     int32_t c[U];
     T a[U], xv[U];
+    bool regular = false;
+    if (KB) {
+      // Compressed indices: one word per (slice, k) says "column = word + lane" for every row of the
+      // slice, so a regular batch reads 4 U bytes of indices per warp instead of 128 U.  A batch with
+      // an irregular (slice, k) in it reads its per-lane indices like the uncompressed kernel (the
+      // branch is warp-uniform: every lane loads the same words).  Handing the words round by shuffle
+      // from one coalesced load per slice measured slower (0.417 against 0.379 ms on cfg 5).
+      int32_t b[U];
+      regular = true;
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const bool ok = k + u < len;
-      c[u] = ok ? ld_stream(ci + (int64_t)(k + u) * SELL_C, pol_s) : 0;
-      a[u] = ok ? ld_stream(va + (int64_t)(k + u) * SELL_C, pol_s) : Num<T>::zero();
+      for (int u = 0; u < U; ++u) {
+        b[u] = __ldg(kb + k + u);  // the array is padded by 16 words past the last slice
+        regular = regular && b[u] != SELL_IRREGULAR;
+      }
+      if (regular) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          a[u] = (k + u < len) ? ld_stream(va + (int64_t)(k + u) * SELL_C, pol_s) : Num<T>::zero();
+          c[u] = b[u] + lane;
+        }
+      }
+    }
+    if (!regular) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const bool ok = k + u < len;
+        c[u] = ok ? ld_stream(ci + (int64_t)(k + u) * SELL_C, pol_s) : 0;
+        a[u] = ok ? ld_stream(va + (int64_t)(k + u) * SELL_C, pol_s) : Num<T>::zero();
+      }
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) xv[u] = (k + u < len) ? xa(c[u], pol_x) : Num<T>::zero();
@@ -389,14 +448,14 @@ __device__ __forceinline__ void sell_row(int32_t row, const int64_t *__restrict_
   st_stream(y + row, acc);
 }
 
-template <class T, int U, bool ACC, class XA>
+template <class T, int U, bool ACC, class XA, bool KB = false>
 __global__ void __launch_bounds__(256)
 k_spmv_sell(int32_t row_begin, int32_t row_end, const int64_t *__restrict__ slice_ptr,
             const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
-            const T *__restrict__ vals, const XA xa, T *__restrict__ y) {
+            const T *__restrict__ vals, const XA xa, T *__restrict__ y, const int32_t *__restrict__ kbase = nullptr) {
   const int32_t row = row_begin + blockIdx.x * blockDim.x + threadIdx.x;  // row_begin % 32 == 0
   if (row >= row_end) return;
-  sell_row<T, U, ACC, XA>(row, slice_ptr, rowlen, colidx, vals, xa, y);
+  sell_row<T, U, ACC, XA, KB>(row, slice_ptr, rowlen, colidx, vals, xa, y, kbase);
 }
 
 // ---- SELL-32, row-partitioned over the GPUs of one box: ONE launch per product ---------------------
@@ -425,7 +484,8 @@ template <class T, int U>
 __global__ void __launch_bounds__(256, sizeof(T) == 8 ? 6 : 4)
 k_spmv_sell_dist(int32_t nrows, int32_t r0, int32_t r1, const int64_t *__restrict__ slice_ptr,
                  const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
-                 const T *__restrict__ vals, const DistX<T> xa, T *__restrict__ y, const PeerSync ps) {
+                 const T *__restrict__ vals, const DistX<T> xa, T *__restrict__ y, const PeerSync ps,
+                 const int32_t *__restrict__ kbase) {
   const int32_t nbl = (r0 + 255) >> 8;            // boundary blocks below the interior
   const int32_t nbh = (nrows - r1 + 255) >> 8;    // and above it
   const int32_t b = blockIdx.x;
@@ -466,8 +526,13 @@ k_spmv_sell_dist(int32_t nrows, int32_t r0, int32_t r1, const int64_t *__restric
     if (row < limit) sell_row<T, 4, false, DistX<T>>(row, slice_ptr, rowlen, colidx, vals, xa, y);
   } else {
     const int32_t row = r0 + (b - nbl - nbh) * 256 + threadIdx.x;
-    if (row < r1)
-      sell_row<T, U, false, LocalX<T>>(row, slice_ptr, rowlen, colidx, vals, LocalX<T>{xa.self_x - xa.self_lo}, y);
+    if (row < r1) {
+      if (kbase)
+        sell_row<T, U, false, LocalX<T>, true>(row, slice_ptr, rowlen, colidx, vals,
+                                               LocalX<T>{xa.self_x - xa.self_lo}, y, kbase);
+      else
+        sell_row<T, U, false, LocalX<T>>(row, slice_ptr, rowlen, colidx, vals, LocalX<T>{xa.self_x - xa.self_lo}, y);
+    }
   }
 }
 
@@ -1253,10 +1318,17 @@ static int launch_sell(slc_matrix *m, const XA &xa, T *y, int32_t row_begin = 0,
   static const int u_env = env_int("SLC_SELL_U", 0);
   int u = u_env;
   // measured on B200, 27-point stencil: U=8 6690 GB/s, U=4 6464, U=16 5425 (register pressure)
-  if (u == 0) u = m->max_rowlen <= 4 ? 4 : 8;
+  // with compressed indices: U=4 0.371 ms (40 registers), U=8 0.471 ms (64 registers), off 0.430 ms
+  if (u == 0) u = (m->max_rowlen <= 4 || sp.kbase) ? 4 : 8;
 #define SLC_SELL_CASE(UU)                                                                          \
-  k_spmv_sell<T, UU, ACC, XA><<<nb, 256, 0, s>>>(row_begin, row_end, sp.slice_ptr, sp.rowlen,      \
-                                                 sp.colidx, (const T *)sp.vals, xa, y)
+  do {                                                                                             \
+    if (sp.kbase)                                                                                  \
+      k_spmv_sell<T, UU, ACC, XA, true><<<nb, 256, 0, s>>>(row_begin, row_end, sp.slice_ptr, sp.rowlen, \
+                                                           sp.colidx, (const T *)sp.vals, xa, y, sp.kbase); \
+    else                                                                                           \
+      k_spmv_sell<T, UU, ACC, XA><<<nb, 256, 0, s>>>(row_begin, row_end, sp.slice_ptr, sp.rowlen,  \
+                                                     sp.colidx, (const T *)sp.vals, xa, y);        \
+  } while (0)
   if (u <= 4) SLC_SELL_CASE(4);
   else if (u <= 8) SLC_SELL_CASE(8);
   else SLC_SELL_CASE(16);
@@ -1557,13 +1629,13 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   const int64_t nblocks = ceil_div(r0, 256) + ceil_div(m->nrows - r1, 256) + ceil_div(r1 - r0, 256);
   cudaStream_t s = cur_stream();
   static const int u_env = env_int("SLC_SELL_U", 0);
-  const int u = u_env ? u_env : (m->max_rowlen <= 4 ? 4 : 8);
+  const int u = u_env ? u_env : ((m->max_rowlen <= 4 || sp.kbase) ? 4 : 8);
   if (u <= 4)
     k_spmv_sell_dist<T, 4><<<(unsigned)nblocks, 256, 0, s>>>(m->nrows, r0, r1, sp.slice_ptr, sp.rowlen, sp.colidx,
-                                                             (const T *)sp.vals, xa, (T *)y, ps);
+                                                             (const T *)sp.vals, xa, (T *)y, ps, sp.kbase);
   else
     k_spmv_sell_dist<T, 8><<<(unsigned)nblocks, 256, 0, s>>>(m->nrows, r0, r1, sp.slice_ptr, sp.rowlen, sp.colidx,
-                                                             (const T *)sp.vals, xa, (T *)y, ps);
+                                                             (const T *)sp.vals, xa, (T *)y, ps, sp.kbase);
   SLC_LAUNCHED();
   return SLC_OK;
 }
@@ -1994,9 +2066,11 @@ int slc_plan_info(const slc_matrix *m, char *buf, int32_t buflen) {
   if (!m || !buf || buflen <= 0) return fail(SLC_ERR_INVALID, "slc_plan_info: bad argument");
   const char *names[] = {"unplanned", "sell32", "csr-warp", "csr-balanced", "csr-merge"};
   const double pad = m->nnz ? 100.0 * (double)(m->sell.padded - m->nnz) / (double)m->nnz : 0.0;
-  snprintf(buf, (size_t)buflen, "%s rows=%d cols=%d nnz=%lld max_rowlen=%d sell_padding=%.2f%% chunks=%d",
-           names[m->spmv_active], m->nrows, m->ncols, (long long)m->nnz, m->max_rowlen, pad,
-           m->bal.nchunks);
+  const double unit = (m->sell.kbase && m->nnz) ? 100.0 * (double)m->sell.unit_entries / (double)m->nnz : 0.0;
+  snprintf(buf, (size_t)buflen,
+           "%s rows=%d cols=%d nnz=%lld max_rowlen=%d sell_padding=%.2f%% chunks=%d unit_stride=%.2f%% hot_cols=%d",
+           names[m->spmv_active], m->nrows, m->ncols, (long long)m->nnz, m->max_rowlen, pad, m->bal.nchunks, unit,
+           m->bal.hot_k > 0 ? m->bal.hot_k : 0);
   return SLC_OK;
 }
 

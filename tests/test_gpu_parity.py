@@ -153,6 +153,34 @@ def test_mulm_matches_oracle(sl, dtype, kind):
 
 
 @pytest.mark.parametrize("dtype", DTYPES)
+def test_mulv_sell_compressed_indices(sl, dtype):
+    """Sliced-ELL plans replace the 32 indices of a (slice, k) by one base when they are base + lane
+    (stencils away from grid boundaries).  Same rows, same order: bit-identical to the oracle, with
+    and without the compression, for grids whose lines do and do not align with slices, a band
+    matrix whose every slice qualifies, and axpy."""
+    rng = np.random.default_rng(55)
+    for gm in (g.stencil3d_27pt((9, 10, 11), dtype), g.stencil3d_27pt((4, 32, 64), dtype), g.laplace2d_5pt(37, dtype),
+               g.tridiag(1000, dtype=dtype), g.laplace3d_7pt(12, dtype)):
+        om = oracle.csc(*gm)
+        x, y0 = vec(rng, gm.ncols, dtype), vec(rng, gm.nrows, dtype)
+        want, want_acc = oracle.mulv(om, x), oracle.axpy(om, x, y0)
+        infos = []
+        for flag in ("2", "0"):      # 2 = compress whatever the size
+            os.environ["SLC_SELL_KBASE"] = flag
+            try:
+                m = to_matrix(sl, gm)
+                m.device().set_spmv_kernel(KINDS["sell"])
+                np.testing.assert_array_equal(sl.mulV(m, x), want)
+                np.testing.assert_array_equal(sl.axpy(m, x, y0), want_acc)
+                infos.append(m.device().plan_info())
+            finally:
+                del os.environ["SLC_SELL_KBASE"]
+        assert "unit_stride=0.00%" in infos[1]
+        if gm.nrows in (1000, 4 * 32 * 64):   # the band matrix and the grid whose lines are whole slices compress
+            assert "unit_stride=0.00%" not in infos[0], infos[0]
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
 def test_mulv_balanced_hot_columns(sl, dtype):
     """Power-law matrices on the balanced plan keep x at their densest columns in shared memory
     (k_spmv_bal_hot, resident blocks walking the chunks).  Small tables force hot and cold gathers in

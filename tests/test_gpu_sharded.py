@@ -100,6 +100,41 @@ def test_partitioned_block_product_matches_oracle(sl, dtype):
 
 
 @pytest.mark.parametrize("dtype", [np.float64, np.complex128])
+def test_partitioned_operand_compressed_indices(sl, dtype, monkeypatch):
+    """The one-launch distributed kernel runs its interior rows on the compressed-index row body
+    (one base per (slice, k)); forced on here at test size.  z-slabs of a grid whose lines are whole
+    slices, so interior slices compress and boundary slices take the peer path."""
+    monkeypatch.setenv("SLC_SELL_KBASE", "2")
+    lib = sl._capi.lib()
+    rng = np.random.default_rng(10)
+    gm = g.stencil3d_27pt((8, 8, 64), dtype)
+    nparts, plane = 4, 8 * 64
+    om = oracle.csc(*gm)
+    x = rng.uniform(-1, 1, gm.ncols).astype(dtype)
+    want = oracle.mulv(om, x)
+    xs = (sharded.uniform_splits(8, nparts) * plane).astype(np.int32)
+    xparts = [_dev_array(sl, np.ascontiguousarray(x[xs[p]:xs[p + 1]])) for p in range(nparts)]
+    table = (C.c_void_p * nparts)(*[p.value for p in xparts])
+    fn = getattr(lib, "slc_%s_mulv_dist_dev" % ("z" if np.dtype(dtype).kind == "c" else "d"))
+    out = []
+    for rank in range(nparts):
+        blk = sharded.row_block(gm, xs[rank], xs[rank + 1])
+        m = to_matrix(sl, blk)
+        m.device().set_spmv_kernel(1)
+        y = np.zeros(blk.nrows, dtype=dtype)
+        yd = _dev_array(sl, y)
+        rc = fn(m.device().handle, nparts, rank, xs.ctypes.data_as(C.c_void_p), C.cast(table, C.c_void_p), yd, None)
+        assert rc == 0, sl._capi.last_error()
+        assert "unit_stride=0.00%" not in m.device().plan_info()
+        assert lib.slc_memcpy_d2h(C.c_void_p(y.ctypes.data), yd, y.nbytes) == 0
+        lib.slc_dev_free(yd)
+        out.append(y)
+    np.testing.assert_array_equal(np.concatenate(out), want)
+    for p in xparts:
+        lib.slc_dev_free(p)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.complex128])
 def test_allgather_operand_matches_oracle(sl, dtype):
     """slc_*_mulv_allgather_dev: the slices (odd sizes, so some destinations are not 16-byte aligned)
     are pulled into a full copy of x, then the undistributed kernels run."""
