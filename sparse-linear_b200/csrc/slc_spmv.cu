@@ -395,7 +395,8 @@ template <class T, int U, bool ACC, class XA, bool KB = false>
 __device__ __forceinline__ void sell_row(int32_t row, const int64_t *__restrict__ slice_ptr,
                                          const int32_t *__restrict__ rowlen,
                                          const int32_t *__restrict__ colidx, const T *__restrict__ vals,
-                                         const XA &xa, T *__restrict__ y, const int32_t *__restrict__ kbase = nullptr) {
+                                         const XA &xa, T *__restrict__ y, const int32_t *__restrict__ kbase = nullptr,
+                                         int pf = 0) {
   const uint64_t pol_s = policy_evict_first();
   const uint64_t pol_x = policy_evict_last();
   const int lane = threadIdx.x & 31;
@@ -418,6 +419,12 @@ __device__ __forceinline__ void sell_row(int32_t row, const int64_t *__restrict_
       // from one coalesced load per slice measured slower (0.417 against 0.379 ms on cfg 5).
       int32_t b[U];
       regular = true;
+      if (pf > 0) {  // pull the values `pf` batches ahead into L2 (the stream is perfectly predictable)
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (k + pf * U + u < len)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(va + (int64_t)(k + pf * U + u) * SELL_C));
+      }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         b[u] = __ldg(kb + k + u);  // the array is padded by 16 words past the last slice
@@ -448,14 +455,15 @@ __device__ __forceinline__ void sell_row(int32_t row, const int64_t *__restrict_
   st_stream(y + row, acc);
 }
 
-template <class T, int U, bool ACC, class XA, bool KB = false>
-__global__ void __launch_bounds__(256)
+template <class T, int U, bool ACC, class XA, bool KB = false, int MINB = 1>
+__global__ void __launch_bounds__(256, MINB)
 k_spmv_sell(int32_t row_begin, int32_t row_end, const int64_t *__restrict__ slice_ptr,
             const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
-            const T *__restrict__ vals, const XA xa, T *__restrict__ y, const int32_t *__restrict__ kbase = nullptr) {
+            const T *__restrict__ vals, const XA xa, T *__restrict__ y, const int32_t *__restrict__ kbase = nullptr,
+            int pf = 0) {
   const int32_t row = row_begin + blockIdx.x * blockDim.x + threadIdx.x;  // row_begin % 32 == 0
   if (row >= row_end) return;
-  sell_row<T, U, ACC, XA, KB>(row, slice_ptr, rowlen, colidx, vals, xa, y, kbase);
+  sell_row<T, U, ACC, XA, KB>(row, slice_ptr, rowlen, colidx, vals, xa, y, kbase, pf);
 }
 
 // ---- SELL-32, row-partitioned over the GPUs of one box: ONE launch per product ---------------------
@@ -480,8 +488,8 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   return t;
 }
 
-template <class T, int U>
-__global__ void __launch_bounds__(256, sizeof(T) == 8 ? 6 : 4)
+template <class T, int U, bool KB>
+__global__ void __launch_bounds__(256, sizeof(T) == 8 ? (KB ? 8 : 6) : 4)
 k_spmv_sell_dist(int32_t nrows, int32_t r0, int32_t r1, const int64_t *__restrict__ slice_ptr,
                  const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
                  const T *__restrict__ vals, const DistX<T> xa, T *__restrict__ y, const PeerSync ps,
@@ -526,13 +534,9 @@ k_spmv_sell_dist(int32_t nrows, int32_t r0, int32_t r1, const int64_t *__restric
     if (row < limit) sell_row<T, 4, false, DistX<T>>(row, slice_ptr, rowlen, colidx, vals, xa, y);
   } else {
     const int32_t row = r0 + (b - nbl - nbh) * 256 + threadIdx.x;
-    if (row < r1) {
-      if (kbase)
-        sell_row<T, U, false, LocalX<T>, true>(row, slice_ptr, rowlen, colidx, vals,
-                                               LocalX<T>{xa.self_x - xa.self_lo}, y, kbase);
-      else
-        sell_row<T, U, false, LocalX<T>>(row, slice_ptr, rowlen, colidx, vals, LocalX<T>{xa.self_x - xa.self_lo}, y);
-    }
+    if (row < r1)
+      sell_row<T, U, false, LocalX<T>, KB>(row, slice_ptr, rowlen, colidx, vals, LocalX<T>{xa.self_x - xa.self_lo}, y,
+                                           kbase, 1);
   }
 }
 
@@ -1316,15 +1320,21 @@ static int launch_sell(slc_matrix *m, const XA &xa, T *y, int32_t row_begin = 0,
   if (row_end <= row_begin) return SLC_OK;
   const unsigned nb = (unsigned)ceil_div(row_end - row_begin, 256);
   static const int u_env = env_int("SLC_SELL_U", 0);
+  static const int pf_env = env_int("SLC_SELL_PREFETCH", 1);  // L2 prefetch distance in batches (compressed kernel)
+  static const int cap_env = env_int("SLC_SELL_CAP32", 1);  // compressed U = 4 kernel held to 32 registers (8 blocks per SM)
   int u = u_env;
   // measured on B200, 27-point stencil: U=8 6690 GB/s, U=4 6464, U=16 5425 (register pressure)
-  // with compressed indices: U=4 0.371 ms (40 registers), U=8 0.471 ms (64 registers), off 0.430 ms
+  // with compressed indices: U=4 0.379 ms (40 registers, 6 blocks per SM), held to 32 registers (8 blocks)
+  // 0.338 ms, plus an L2 prefetch one batch ahead 0.326 ms (two: 0.330, three: 0.334, five: 0.340); U=8 0.471 ms (64 registers); off 0.430 ms
   if (u == 0) u = (m->max_rowlen <= 4 || sp.kbase) ? 4 : 8;
 #define SLC_SELL_CASE(UU)                                                                          \
   do {                                                                                             \
-    if (sp.kbase)                                                                                  \
+    if (sp.kbase && cap_env && UU == 4 && sizeof(T) == 8)                                          \
+      k_spmv_sell<T, 4, ACC, XA, true, 8><<<nb, 256, 0, s>>>(row_begin, row_end, sp.slice_ptr, sp.rowlen, \
+                                                             sp.colidx, (const T *)sp.vals, xa, y, sp.kbase, pf_env); \
+    else if (sp.kbase)                                                                             \
       k_spmv_sell<T, UU, ACC, XA, true><<<nb, 256, 0, s>>>(row_begin, row_end, sp.slice_ptr, sp.rowlen, \
-                                                           sp.colidx, (const T *)sp.vals, xa, y, sp.kbase); \
+                                                           sp.colidx, (const T *)sp.vals, xa, y, sp.kbase, pf_env); \
     else                                                                                           \
       k_spmv_sell<T, UU, ACC, XA><<<nb, 256, 0, s>>>(row_begin, row_end, sp.slice_ptr, sp.rowlen,  \
                                                      sp.colidx, (const T *)sp.vals, xa, y);        \
@@ -1630,12 +1640,17 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   cudaStream_t s = cur_stream();
   static const int u_env = env_int("SLC_SELL_U", 0);
   const int u = u_env ? u_env : ((m->max_rowlen <= 4 || sp.kbase) ? 4 : 8);
-  if (u <= 4)
-    k_spmv_sell_dist<T, 4><<<(unsigned)nblocks, 256, 0, s>>>(m->nrows, r0, r1, sp.slice_ptr, sp.rowlen, sp.colidx,
-                                                             (const T *)sp.vals, xa, (T *)y, ps, sp.kbase);
-  else
-    k_spmv_sell_dist<T, 8><<<(unsigned)nblocks, 256, 0, s>>>(m->nrows, r0, r1, sp.slice_ptr, sp.rowlen, sp.colidx,
-                                                             (const T *)sp.vals, xa, (T *)y, ps, sp.kbase);
+#define SLC_DIST_CASE(UU, KB_)                                                                                  \
+  k_spmv_sell_dist<T, UU, KB_><<<(unsigned)nblocks, 256, 0, s>>>(m->nrows, r0, r1, sp.slice_ptr, sp.rowlen, sp.colidx, \
+                                                                 (const T *)sp.vals, xa, (T *)y, ps, sp.kbase)
+  if (sp.kbase) {
+    if (u <= 4) SLC_DIST_CASE(4, true);
+    else SLC_DIST_CASE(8, true);
+  } else {
+    if (u <= 4) SLC_DIST_CASE(4, false);
+    else SLC_DIST_CASE(8, false);
+  }
+#undef SLC_DIST_CASE
   SLC_LAUNCHED();
   return SLC_OK;
 }
