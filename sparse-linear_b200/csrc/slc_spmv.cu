@@ -455,7 +455,7 @@ __device__ __forceinline__ void sell_row(int32_t row, const int64_t *__restrict_
   st_stream(y + row, acc);
 }
 
-template <class T, int U, bool ACC, class XA, bool KB = false, int MINB = 1>
+template <class T, int U, bool ACC, class XA, bool KB = false, int MINB = 0>
 __global__ void __launch_bounds__(256, MINB)
 k_spmv_sell(int32_t row_begin, int32_t row_end, const int64_t *__restrict__ slice_ptr,
             const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
@@ -684,8 +684,8 @@ __device__ __forceinline__ void bal_reduce(int32_t b, int tid, int64_t nnz, cons
   }
 }
 
-template <class T, bool ACC, class XA>
-__global__ void __launch_bounds__(BAL_THREADS)
+template <class T, bool ACC, class XA, int MINB = 0>
+__global__ void __launch_bounds__(BAL_THREADS, MINB)
 k_spmv_bal(int32_t nrows, int64_t nnz, uint32_t zmask, int batch, const int32_t *__restrict__ rowptr,
            const int32_t *__restrict__ colidx, const T *__restrict__ vals,
            const int32_t *__restrict__ first_owned, const XA xa, T *__restrict__ y,
@@ -1383,9 +1383,15 @@ static int spmv_run(slc_matrix *m, const XA &xa, T *y) {
           SLC_TRY(xhot.alloc((size_t)bp.hot_k));
           k_hot_pack<T><<<(unsigned)ceil_div(bp.hot_k, 256), 256, 0, s>>>(bp.hot_k, bp.hot_cols, local_ptr(xa), xhot.p);
           SLC_LAUNCHED();
-          k_spmv_bal<T, ACC, HotPackedX<T>><<<(unsigned)bp.nchunks, BAL_THREADS, 0, s>>>(
-              m->nrows, m->nnz, 0u, batch_env, m->rowptr, bp.colidx_hot, (const T *)m->rvals, bp.chunk_row,
-              HotPackedX<T>{local_ptr(xa), xhot.p}, y, ph.p, pt.p);
+          static const int minb_env = env_int("SLC_BAL_MINB8", 0);  // hold the kernel to 32 registers (8 blocks per SM)
+          if (minb_env && sizeof(T) == 8)
+            k_spmv_bal<T, ACC, HotPackedX<T>, 8><<<(unsigned)bp.nchunks, BAL_THREADS, 0, s>>>(
+                m->nrows, m->nnz, 0u, batch_env, m->rowptr, bp.colidx_hot, (const T *)m->rvals, bp.chunk_row,
+                HotPackedX<T>{local_ptr(xa), xhot.p}, y, ph.p, pt.p);
+          else
+            k_spmv_bal<T, ACC, HotPackedX<T>><<<(unsigned)bp.nchunks, BAL_THREADS, 0, s>>>(
+                m->nrows, m->nnz, 0u, batch_env, m->rowptr, bp.colidx_hot, (const T *)m->rvals, bp.chunk_row,
+                HotPackedX<T>{local_ptr(xa), xhot.p}, y, ph.p, pt.p);
           SLC_LAUNCHED();
           k_spmv_bal_fixup<T, ACC><<<(unsigned)ceil_div(bp.nchunks, 256), 256, 0, s>>>(
               bp.nchunks, m->nnz, m->rowptr, bp.chunk_row, ph.p, pt.p, y);
