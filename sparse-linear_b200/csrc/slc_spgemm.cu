@@ -126,8 +126,8 @@ constexpr int32_t ROW_END = 0x7fffffff;  // past every valid row index
 // range) and the warp then streams the window out with fully coalesced stores.
 constexpr int MERGE_STAGE = 1024;  // default entries per warp window (12 or 20 KB per warp); the kernel takes it as `stage`
 
-template <class T, int NB, bool NUMERIC>
-__global__ void __launch_bounds__(128)
+template <class T, int NB, bool NUMERIC, int MINB = 0>
+__global__ void __launch_bounds__(128, MINB)
 k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32_t *__restrict__ ap,
            const int32_t *__restrict__ ai, const T *__restrict__ av, const int32_t *__restrict__ bp,
            const int32_t *__restrict__ bi, const T *__restrict__ bv, int32_t *__restrict__ cnt,
@@ -252,7 +252,11 @@ static int run_merge(int32_t n, const int32_t *cols, const slc_matrix *a, const 
   const int cap = std::max(32, std::min(cap_env, 2048)) / 4 * 4;
   const int stage = (NUMERIC && !(stage_env && stage_env[0] == '0')) ? cap : 0;
   const size_t smem = stage ? (size_t)(128 / 32) * stage * (sizeof(int32_t) + sizeof(T)) : 0;
+  // SLC_MM_MINB=5/6: numeric 8-list merge for Double held to 96 / 80 registers (5 / 6 blocks per SM)
+  static const int minb_env = env_int("SLC_MM_MINB", 0);
   auto kern = k_mm_merge<T, NB, NUMERIC>;
+  if (NUMERIC && NB == 8 && sizeof(T) == 8 && minb_env == 5) kern = k_mm_merge<T, NB, NUMERIC, 5>;
+  if (NUMERIC && NB == 8 && sizeof(T) == 8 && minb_env == 6) kern = k_mm_merge<T, NB, NUMERIC, 6>;
   if (smem > 48 * 1024) SLC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (NUMERIC && carve_env >= 0)
     SLC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve_env));
