@@ -1699,14 +1699,16 @@ static int spmv_allgather_entry(slc_matrix *m, int32_t nparts, int32_t self, con
   const DistTable *tbl = nullptr;
   SLC_TRY((dist_table_setup<T>(m, nparts, self, splits, x_parts, nullptr, fn, &tbl)));
   if ((m->ncols && !x_full) || (m->nrows && !y)) return fail(SLC_ERR_INVALID, "%s: null vector", fn);
-  if (sync) SLC_TRY(slc_peer_barrier(sync));
-  if (m->ncols) {
+  static const int diag_env = env_int("SLC_AG_DIAG", 0);  // timing diagnosis: 1 = no pull, 2 = no product, 3 = no barrier
+  if (sync && diag_env != 3) SLC_TRY(slc_peer_barrier(sync));
+  if (m->ncols && diag_env != 1) {
     int64_t longest = 0;
     for (int p = 0; p < nparts; ++p) longest = std::max<int64_t>(longest, splits[p + 1] - splits[p]);
     const unsigned bx = (unsigned)std::max<int64_t>(1, std::min<int64_t>(ceil_div(longest, 256 * 8), 148 * 4));
     k_allgather_pull<T><<<dim3(bx, (unsigned)nparts), 256, 0, cur_stream()>>>(tbl, (T *)x_full);
     SLC_LAUNCHED();
   }
+  if (diag_env == 2) return SLC_OK;
   return spmv_dev<T, false>(m, (const T *)x_full, (T *)y);
 }
 
