@@ -1476,7 +1476,10 @@ constexpr int PIPE_MAX_CHUNKS = 32;
 template <class T, bool ACC>
 static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
   *done = false;
-  static const int chunks_env = env_int("SLC_E2E_CHUNKS", 8);
+  const int chunks_env = env_int("SLC_E2E_CHUNKS", 8);  // read per call: scripts/e2e_probe.py sweeps it in one process
+  const int diag = env_int("SLC_E2E_DIAG", 0);          // timing diagnosis: 1 = no download, 2 = no upload, 4 = no kernels
+  const int align_env = env_int("SLC_E2E_ALIGN", 512);
+  const int mode = env_int("SLC_E2E_MODE", 0);          // 0 = three streams chained by events, 1 = downloads follow their kernels
   const int want = chunks_env < 1 ? 1 : (chunks_env > PIPE_MAX_CHUNKS ? PIPE_MAX_CHUNKS : chunks_env);
   if (want == 1 || m->nnz == 0 || m->nrows < (1 << 18)) return SLC_OK;
   SLC_TRY(ensure_plan<T>(m));
@@ -1504,20 +1507,42 @@ static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
     const int32_t r0 = i * rows_per, r1 = (int32_t)std::min<int64_t>(m->nrows, (int64_t)(i + 1) * rows_per);
     int32_t need = sent;
     for (int32_t sl = r0 / SELL_C; sl < (int32_t)ceil_div(r1, SELL_C); ++sl) need = std::max(need, sp.h_cmax[sl] + 1);
+    // piece boundaries on 512-element (4 KB) multiples: both ends of every copy stay page-aligned
+    if (align_env > 0) need = (int32_t)std::min<int64_t>(m->ncols, ceil_div(need, align_env) * (int64_t)align_env);
     if (need > sent) {
-      SLC_CUDA(cudaMemcpyAsync(dx.p + sent, x + sent, (size_t)(need - sent) * sizeof(T), cudaMemcpyHostToDevice,
-                               m->pipe_in));
+      if (!(diag & 2))
+        SLC_CUDA(cudaMemcpyAsync(dx.p + sent, x + sent, (size_t)(need - sent) * sizeof(T), cudaMemcpyHostToDevice,
+                                 m->pipe_in));
       sent = need;
     }
     if (ACC)
       SLC_CUDA(cudaMemcpyAsync(dy.p + r0, y + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyHostToDevice, m->pipe_in));
     cudaEvent_t ev_in = m->pipe_events[i], ev_k = m->pipe_events[PIPE_MAX_CHUNKS + i];
     SLC_CUDA(cudaEventRecord(ev_in, m->pipe_in));
+    if (mode == 1) {
+      // chunk kernels alternate between the caller's stream and the side stream, and each chunk's
+      // download follows its kernel on the same stream: one cross-stream dependency per chunk (upload
+      // -> kernel) instead of two.  A dependency between copy-engine work on different streams costs
+      // tens of microseconds (scripts/e2e_probe.py: upload + download alone ran 1.78 ms through the
+      // event chain, 1.32 ms as two plain copies).
+      cudaStream_t cs = (i & 1) ? m->pipe_out : main_s;
+      SLC_CUDA(cudaStreamWaitEvent(cs, ev_in, 0));
+      if (!(diag & 4)) {
+        tls().stream = cs;
+        const int rc = launch_sell<T, ACC, LocalX<T>>(m, LocalX<T>{dx.p}, dy.p, r0, r1);
+        tls().stream = main_s;
+        SLC_TRY(rc);
+      }
+      if (!(diag & 1))
+        SLC_CUDA(cudaMemcpyAsync(y + r0, dy.p + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyDeviceToHost, cs));
+      continue;
+    }
     SLC_CUDA(cudaStreamWaitEvent(main_s, ev_in, 0));
-    SLC_TRY((launch_sell<T, ACC, LocalX<T>>(m, LocalX<T>{dx.p}, dy.p, r0, r1)));
+    if (!(diag & 4)) SLC_TRY((launch_sell<T, ACC, LocalX<T>>(m, LocalX<T>{dx.p}, dy.p, r0, r1)));
     SLC_CUDA(cudaEventRecord(ev_k, main_s));
     SLC_CUDA(cudaStreamWaitEvent(m->pipe_out, ev_k, 0));
-    SLC_CUDA(cudaMemcpyAsync(y + r0, dy.p + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyDeviceToHost, m->pipe_out));
+    if (!(diag & 1))
+      SLC_CUDA(cudaMemcpyAsync(y + r0, dy.p + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyDeviceToHost, m->pipe_out));
   }
   SLC_CUDA(cudaStreamSynchronize(m->pipe_out));
   SLC_CUDA(cudaStreamSynchronize(m->pipe_in));
