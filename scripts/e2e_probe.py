@@ -40,16 +40,7 @@ def timed(reps=20):
     return (time.perf_counter() - t0) / reps * 1e3
 
 
-ref = None
-side = torch.cuda.Stream()
-for name, stream in (("legacy default stream", torch.cuda.default_stream()), ("a non-blocking stream", side)):
-    sl.set_stream(stream.cuda_stream)
-    for mode in (0, 1):
-        os.environ["SLC_E2E_MODE"] = str(mode)
-        for diag in (0, 4):
-            os.environ["SLC_E2E_DIAG"] = str(diag)
-            t = timed()
-            if ref is None:
-                ref = yp.clone()
-            print("caller on %s, mode=%d, %s: %.3f ms  same_result=%s" % (name, mode, "no kernels" if diag else "full", t, bool(torch.equal(ref, yp)) if not diag else None), flush=True)
+for diag, what in ((0, "full"), (8, "downloads read a buffer no kernel wrote"), (4, "no kernels"), (12, "no kernels, cold buffer")):
+    os.environ["SLC_E2E_DIAG"] = str(diag)
+    print("%s: %.3f ms" % (what, timed()), flush=True)
 os.environ["SLC_E2E_DIAG"] = "0"

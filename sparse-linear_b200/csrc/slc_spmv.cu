@@ -1495,9 +1495,11 @@ static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
     for (auto &e : m->pipe_events) SLC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
   cudaStream_t main_s = cur_stream();
-  DevBuf<T> dx, dy;
+  DevBuf<T> dx, dy, dcold;
   SLC_TRY(dx.alloc((size_t)m->ncols));
   SLC_TRY(dy.alloc((size_t)m->nrows));
+  if (diag & 8) SLC_TRY(dcold.alloc((size_t)m->nrows));  // diagnosis: downloads read memory no kernel has written
+  const T *dsrc = (diag & 8) ? dcold.p : dy.p;
   cudaEvent_t ev_start = m->pipe_events[2 * PIPE_MAX_CHUNKS];
   SLC_CUDA(cudaEventRecord(ev_start, main_s));
   SLC_CUDA(cudaStreamWaitEvent(m->pipe_in, ev_start, 0));
@@ -1534,7 +1536,7 @@ static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
         SLC_TRY(rc);
       }
       if (!(diag & 1))
-        SLC_CUDA(cudaMemcpyAsync(y + r0, dy.p + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyDeviceToHost, cs));
+        SLC_CUDA(cudaMemcpyAsync(y + r0, dsrc + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyDeviceToHost, cs));
       continue;
     }
     SLC_CUDA(cudaStreamWaitEvent(main_s, ev_in, 0));
@@ -1542,7 +1544,7 @@ static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
     SLC_CUDA(cudaEventRecord(ev_k, main_s));
     SLC_CUDA(cudaStreamWaitEvent(m->pipe_out, ev_k, 0));
     if (!(diag & 1))
-      SLC_CUDA(cudaMemcpyAsync(y + r0, dy.p + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyDeviceToHost, m->pipe_out));
+      SLC_CUDA(cudaMemcpyAsync(y + r0, dsrc + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyDeviceToHost, m->pipe_out));
   }
   SLC_CUDA(cudaStreamSynchronize(m->pipe_out));
   SLC_CUDA(cudaStreamSynchronize(m->pipe_in));
