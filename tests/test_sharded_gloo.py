@@ -168,6 +168,39 @@ def test_two_rank_transpose_and_assembly_gloo():
     assert ret.get("ok") is True
 
 
+def test_sharding_helpers_edge_cases():
+    """Empty blocks, more ranks than rows or columns, triplets on one rank only, a matrix without entries."""
+    rng = np.random.default_rng(99)
+    m = random_csc(rng, 5, 3, 0.6)
+    want_t = oracle.transpose(oracle.csc(*m))
+    world = 7                                   # more ranks than rows and than columns
+    cs, rs = sharded.uniform_splits(m.ncols, world), sharded.uniform_splits(m.nrows, world)
+    assert cs[0] == 0 and cs[-1] == m.ncols and rs[-1] == m.nrows
+    sent = [sharded.transpose_pieces(_oracle_transpose(sharded.col_block(m, cs[q], cs[q + 1])), rs) for q in range(world)]
+    cols = []
+    for p in range(world):
+        got = sharded.transpose_combine([sent[q][p] for q in range(world)])
+        assert got.nrows == m.ncols and got.ncols == rs[p + 1] - rs[p]
+        cols.append(got)
+    # the column blocks of the transpose, side by side, are the transpose
+    assert np.array_equal(np.concatenate([c.rowidx for c in cols]), want_t.rowidx)
+    assert np.array_equal(np.concatenate([c.values for c in cols]), want_t.values)
+    # assembly where every triplet sits on the last rank
+    r, c, v = np.array([4, 0, 4, 2]), np.array([2, 0, 2, 1]), np.array([1.0, 2.0, 3.0, 4.0])
+    empty = (np.zeros(0, np.int64), np.zeros(0, np.int64), np.zeros(0))
+    sent = [sharded.compress_pieces(*empty, cs) for _ in range(world - 1)] + [sharded.compress_pieces(r, c, v, cs)]
+    full = oracle.compress(5, 3, r, c, v)
+    for p in range(world):
+        got = sharded.compress_combine(5, int(cs[p + 1] - cs[p]), [sent[q][p] for q in range(world)], oracle.compress)
+        ref = sharded.col_block(full, cs[p], cs[p + 1])
+        assert np.array_equal(got.colptr, ref.colptr) and np.array_equal(got.rowidx, ref.rowidx)
+        assert np.array_equal(got.values, ref.values)
+    # a matrix with no entries at all
+    z = random_csc(rng, 6, 4, 0.0)
+    assert sharded.vstack_blocks([sharded.row_block(z, 0, 2), sharded.row_block(z, 2, 6)]).colptr.tolist() == [0] * 5
+    assert sharded.balanced_splits(np.zeros(6), 4)[-1] == 6
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
