@@ -83,6 +83,8 @@ int slc_dev_alloc(void **ptr, int64_t bytes);
 int slc_dev_free(void *ptr);
 int slc_memcpy_h2d(void *dst_dev, const void *src_host, int64_t bytes);
 int slc_memcpy_d2h(void *dst_host, const void *src_dev, int64_t bytes);
+/* device to device on the current stream, asynchronous */
+int slc_memcpy_d2d(void *dst_dev, const void *src_dev, int64_t bytes);
 
 /* ---- handles: Matrix (Data/Matrix/Sparse.hs:67-76), withConstMatrix / fromForeign
         (Data/Matrix/Sparse/Foreign.hs:24-88) ------------------------------------------- */
@@ -130,15 +132,21 @@ int slc_z_axpy_dev(slc_matrix *a, const double *x_dev, double *y_dev);
 /* ---- SpMM: FEAST's multiplyWork (feast/src/Numeric/LinearAlgebra/Feast.hs:203-208) and
         the unexported mulM (Data/Matrix/Sparse.hs:473-498) ------------------------------- */
 
-/* Y[:, j] <- A X[:, j] for j in [0, k); X and Y column-major with leading dimensions
+/* Y[:, j] <- A X[:, j] + beta Y[:, j] for j in [0, k); X and Y column-major with leading dimensions
    ldx >= ncols and ldy >= nrows (in elements).  A column range is chosen by offsetting
-   the pointers, as sliceMat does (Feast.hs:189-192). */
-int slc_d_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k);
-int slc_z_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k);
+   the pointers, as sliceMat does (Feast.hs:189-192).
+   beta points at one element (1 double for d, 2 for z); NULL or 0 is mulM / multiplyWork proper (Y is
+   written, never read: the reference zeroes the destination first, Sparse.hs:482-484); 1 is the
+   reference's axpy_ into a block the caller filled (Sparse.hs:485-488: every entry starts from y and
+   adds its row's terms in column order, bit for bit); any other value starts from beta * y. */
+int slc_d_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
+               const double *beta);
+int slc_z_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
+               const double *beta);
 int slc_d_mulm_dev(slc_matrix *a, const double *X_dev, int64_t ldx, double *Y_dev, int64_t ldy,
-                   int32_t k);
+                   int32_t k, const double *beta);
 int slc_z_mulm_dev(slc_matrix *a, const double *X_dev, int64_t ldx, double *Y_dev, int64_t ldy,
-                   int32_t k);
+                   int32_t k, const double *beta);
 
 /* *flag <- nonzero if a launch of the TMA-staged block product (banded matrices with short rows) gave
    up waiting on one of its shared-memory barriers or met a window wider than planned: its result
@@ -198,8 +206,18 @@ int slc_z_kronecker(const slc_matrix *a, const slc_matrix *b, slc_matrix **c);
    block A[r0:r1, :] as an ordinary handle of shape (r1-r0) x ncols and the slice
    x[splits[self]:splits[self+1]] in its own HBM; every rank maps the other ranks' slices with CUDA
    IPC.  The product kernel gathers local columns from HBM and remote ("halo") columns straight from
-   the peer's memory over NVLink, so there is no separate exchange step.  The caller orders the
-   product after the peers have written their slices (one barrier per iteration). */
+   the peer's memory over NVLink, so there is no separate exchange step.
+
+   Ordering contract.  With sync != NULL a product orders itself: it tells the peers "my slice is
+   written" (true by stream order when the product starts) and its boundary rows wait until the peers
+   they depend on have said the same.  What the caller owns is the opposite hazard: a rank must not
+   overwrite a slice that a peer may still be reading.  The rule that closes it without any extra
+   exchange is DOUBLE BUFFERING: keep two exported buffers per rank and alternate them product by
+   product (pass the table of the buffers that hold the operand of THIS product).  Rank r writes
+   buffer b again only after its own next product -- which waited for its dependency set's next
+   signal, sent after they finished reading b -- so the write cannot overtake a reader.  A caller that
+   keeps one buffer must separate "all peers done reading" from "I overwrite" itself
+   (slc_peer_barrier after the product). */
 
 typedef struct slc_peer_group slc_peer_group;
 
@@ -217,13 +235,29 @@ int slc_ipc_close(void *dev_ptr);
 int slc_peer_group_create(int32_t nparts, int32_t self, slc_peer_group **out, void *handle72);
 int slc_peer_group_connect(slc_peer_group *g, const void *handles72);
 int slc_peer_barrier(slc_peer_group *g);
-/* The two halves of the barrier: signal = "my slice of x is written" (starts a new epoch),
-   wait = "every peer has signalled this epoch". */
+/* The two halves of the barrier: signal = "my slice of x is written",
+   wait = "every rank of my dependency set has signalled this epoch" (and closes the epoch).  The epoch
+   counter lives in device memory and is advanced by the kernels, so barriers and products can be
+   captured in a CUDA graph and the graph relaunched. */
 int slc_peer_signal(slc_peer_group *g);
 int slc_peer_wait(slc_peer_group *g);
-/* *flag <- 1 if a barrier gave up waiting for a peer (bounded spin), else 0 */
+/* The same group for ndev devices driven by ONE process (devices == NULL: 0..ndev-1): peer access is
+   enabled both ways, no IPC.  groups[ndev] receives one group per device, already connected. */
+int slc_peer_group_create_local(int32_t ndev, const int32_t *devices, slc_peer_group **groups);
+/* Dependency set of this rank, bit p = rank p: the ranks whose slices it reads OR that read its
+   slice (slc_*_dist_needs of every rank, exchanged and symmetrised by the caller).  Products and
+   barriers wait for exactly these; the default is every peer. */
+int slc_peer_group_set_deps(slc_peer_group *g, uint32_t mask);
+/* *flag <- 1 if a wait gave up on a peer (5 s bound).  The rows that depended on it were filled with
+   NaN, and every later call on the group fails with SLC_ERR_CUDA. */
 int slc_peer_group_timed_out(slc_peer_group *g, int *flag);
+/* out4 <- {epochs completed, timed waits, nanoseconds waited in total, longest wait in ns};
+   reset != 0 clears the wait statistics.  Synchronises the device. */
+int slc_peer_group_stats(slc_peer_group *g, int64_t *out4, int reset);
 void slc_peer_group_free(slc_peer_group *g);
+/* *mask <- the parts (bit p) whose slices the rows of a_local read, given the partition. */
+int slc_d_dist_needs(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits, uint32_t *mask);
+int slc_z_dist_needs(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits, uint32_t *mask);
 /* y_local <- A_local x.  splits[nparts+1] (host) are the column bounds of the slices, x_parts[nparts]
    (host array) the device addresses of the slices as mapped in THIS process; 1 <= nparts <= 16.
    With sync != NULL the call orders itself against the peers: signal, the rows that need no peer,
@@ -254,6 +288,74 @@ int slc_d_mulm_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const
 int slc_z_mulm_dist_dev(slc_matrix *a_local, int32_t nparts, int32_t self, const int32_t *splits,
                         const double *const *X_parts, const int64_t *ldx_parts, double *Y_dev,
                         int64_t ldy, int32_t k, slc_peer_group *sync);
+
+/* ---- one process, several GPUs: the same row-partitioned products behind one handle ------------------
+   SURVEY.md section 8(b): slc_T_upload_sharded / slc_T_mulv_sharded / slc_T_mulm_sharded.  The
+   reference's host is one Haskell process, so this is the form its shim binds.  upload cuts the
+   matrix into ndev contiguous row blocks with (almost) equal numbers of stored entries (bounds on
+   multiples of 32 rows), one per device; a square matrix partitions x like its rows.  The products
+   take whole host vectors / column-major blocks (each device moves its own slice over its own PCIe
+   link, the slices are double-buffered inside the handle) and return when y is complete.  Regular
+   matrices (sliced-ELL plans) read halo entries from the peers' HBM inside the product kernel;
+   irregular ones all-gather x over NVLink first (mulv only).  Not re-entrant per handle (a mutex
+   serialises callers). */
+typedef struct slc_sharded slc_sharded;
+/* devices == NULL: devices 0 .. ndev-1 */
+int slc_d_upload_sharded(int32_t ndev, const int32_t *devices, int32_t nrows, int32_t ncols,
+                         const int32_t *colptr, const int32_t *rowidx, const double *vals, slc_sharded **out);
+int slc_z_upload_sharded(int32_t ndev, const int32_t *devices, int32_t nrows, int32_t ncols,
+                         const int32_t *colptr, const int32_t *rowidx, const double *vals, slc_sharded **out);
+/* Finalizer ("&slc_sharded_free").  NULL is ignored. */
+void slc_sharded_free(slc_sharded *a);
+int slc_sharded_dims(const slc_sharded *a, int32_t *ndev, int32_t *nrows, int32_t *ncols, int64_t *nnz);
+/* row_splits[ndev+1], col_splits[ndev+1]: block p holds rows [row_splits[p], row_splits[p+1]) and owns
+   x[col_splits[p] : col_splits[p+1]]; either pointer may be NULL */
+int slc_sharded_splits(const slc_sharded *a, int32_t *row_splits, int32_t *col_splits);
+/* block p as an ordinary handle ((r1-r0) x ncols, owned by the sharded handle), its device ordinal and
+   the cudaStream_t its products run on; any output pointer may be NULL */
+int slc_sharded_block(const slc_sharded *a, int32_t part, slc_matrix **block, int32_t *device, void **stream);
+/* y <- A x (mulV), Y[:, j] <- A X[:, j] (multiplyWork): host operands, synchronous */
+int slc_d_mulv_sharded(slc_sharded *a, const double *x, double *y);
+int slc_z_mulv_sharded(slc_sharded *a, const double *x, double *y);
+int slc_d_mulm_sharded(slc_sharded *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k);
+int slc_z_mulm_sharded(slc_sharded *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k);
+/* Device-resident form.  slc_sharded_operand gives, for block `part`, the buffer (on that block's
+   device) that the NEXT product reads as its slice of x / its (slice x k) column-major rows of X with
+   leading dimension *ldx; fill it on the block's stream (or synchronise your own stream first), then
+   call slc_*_mul{v,m}_sharded_dev: asynchronous, one launch sequence per device.  The result of block
+   `part` is at slc_sharded_result; slc_sharded_synchronize waits for every device and reports a barrier
+   that gave up.  Two operand buffers alternate per product, so refilling right after the call is safe. */
+int slc_sharded_operand(slc_sharded *a, int32_t part, int32_t k, void **x_dev, int64_t *ldx);
+int slc_sharded_result(slc_sharded *a, int32_t part, void **y_dev, int64_t *ldy);
+int slc_d_mulv_sharded_dev(slc_sharded *a);
+int slc_z_mulv_sharded_dev(slc_sharded *a);
+int slc_d_mulm_sharded_dev(slc_sharded *a, int32_t k);
+int slc_z_mulm_sharded_dev(slc_sharded *a, int32_t k);
+int slc_sharded_synchronize(slc_sharded *a);
+
+/* ---- pieces of the transpose / assembly of a matrix spread over several GPUs --------
+   The exchange itself (one all-to-all-v of raw device arrays) is the caller's: NCCL between processes,
+   peer copies inside one.  These are the device-side steps around it. */
+/* The CSC arrays of a handle as device pointers (valid while the handle lives; read-only).  A column
+   range [c0, c1) of the matrix is the slice colptr[c0..c1], rowidx/vals[colptr[c0] .. colptr[c1]). */
+int slc_device_arrays(const slc_matrix *m, const int32_t **colptr_dev, const int32_t **rowidx_dev,
+                      const void **vals_dev);
+/* Row blocks of one matrix, listed top to bottom as device CSC arrays (pointers starting at 0, ncols+1
+   each), stacked into one handle: column j of the result is the blocks' columns j one after the other,
+   row indices shifted by the rows above.  1 <= nblocks <= 16; the arrays are read, not adopted. */
+int slc_d_vstack_dev(int32_t nblocks, const int32_t *block_rows, int32_t ncols, const int32_t *const *colptr_dev,
+                     const int32_t *const *rowidx_dev, const double *const *vals_dev, slc_matrix **out);
+int slc_z_vstack_dev(int32_t nblocks, const int32_t *block_rows, int32_t ncols, const int32_t *const *colptr_dev,
+                     const int32_t *const *rowidx_dev, const double *const *vals_dev, slc_matrix **out);
+/* Triplets in HBM bucketed by the part that owns their column (col_splits[nparts+1], host): bucket p
+   occupies counts[0]+..+counts[p-1] onwards in the output arrays, input order kept inside a bucket,
+   columns rebased to the owner's block.  counts[nparts] is a host array; synchronises the stream. */
+int slc_d_coo_bucket_dev(int64_t n, const int32_t *rows_dev, const int32_t *cols_dev, const double *vals_dev,
+                         int32_t nparts, const int32_t *col_splits, int32_t *out_rows_dev, int32_t *out_cols_dev,
+                         double *out_vals_dev, int64_t *counts);
+int slc_z_coo_bucket_dev(int64_t n, const int32_t *rows_dev, const int32_t *cols_dev, const double *vals_dev,
+                         int32_t nparts, const int32_t *col_splits, int32_t *out_rows_dev, int32_t *out_cols_dev,
+                         double *out_vals_dev, int64_t *counts);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

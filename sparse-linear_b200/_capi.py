@@ -33,6 +33,7 @@ SIGNATURES = {
     "slc_dev_free": (C.c_int, [_vp]),
     "slc_memcpy_h2d": (C.c_int, [_vp, _vp, C.c_int64]),
     "slc_memcpy_d2h": (C.c_int, [_vp, _vp, C.c_int64]),
+    "slc_memcpy_d2d": (C.c_int, [_vp, _vp, C.c_int64]),
     "slc_free": (None, [_hp]),
     "slc_dims": (C.c_int, [_hp, _i32p, _i32p, C.POINTER(C.c_int64)]),
     "slc_elem_type": (C.c_int, [_hp]),
@@ -50,6 +51,17 @@ SIGNATURES = {
     "slc_peer_wait": (C.c_int, [_vp]),
     "slc_peer_group_timed_out": (C.c_int, [_vp, C.POINTER(C.c_int)]),
     "slc_peer_group_free": (None, [_vp]),
+    "slc_peer_group_create_local": (C.c_int, [C.c_int32, _vp, C.POINTER(_vp)]),
+    "slc_peer_group_set_deps": (C.c_int, [_vp, C.c_uint32]),
+    "slc_peer_group_stats": (C.c_int, [_vp, C.POINTER(C.c_int64), C.c_int]),
+    "slc_sharded_free": (None, [_vp]),
+    "slc_sharded_dims": (C.c_int, [_vp, _i32p, _i32p, _i32p, C.POINTER(C.c_int64)]),
+    "slc_sharded_splits": (C.c_int, [_vp, _vp, _vp]),
+    "slc_sharded_block": (C.c_int, [_vp, C.c_int32, C.POINTER(_hp), _i32p, C.POINTER(_vp)]),
+    "slc_sharded_operand": (C.c_int, [_vp, C.c_int32, C.c_int32, C.POINTER(_vp), C.POINTER(C.c_int64)]),
+    "slc_sharded_result": (C.c_int, [_vp, C.c_int32, C.POINTER(_vp), C.POINTER(C.c_int64)]),
+    "slc_sharded_synchronize": (C.c_int, [_vp]),
+    "slc_device_arrays": (C.c_int, [_hp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)]),
 }
 for _p in ("d", "z"):
     SIGNATURES.update({
@@ -63,8 +75,16 @@ for _p in ("d", "z"):
         "slc_%s_mulv_allgather_dev" % _p: (C.c_int, [_hp, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp, _vp]),
         "slc_%s_mulm_dist_dev" % _p: (C.c_int, [_hp, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp, C.c_int64,
                                                 C.c_int32, _vp]),
-        "slc_%s_mulm" % _p: (C.c_int, [_hp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32]),
-        "slc_%s_mulm_dev" % _p: (C.c_int, [_hp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32]),
+        "slc_%s_mulm" % _p: (C.c_int, [_hp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32, _vp]),
+        "slc_%s_mulm_dev" % _p: (C.c_int, [_hp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32, _vp]),
+        "slc_%s_dist_needs" % _p: (C.c_int, [_hp, C.c_int32, C.c_int32, _vp, C.POINTER(C.c_uint32)]),
+        "slc_%s_upload_sharded" % _p: (C.c_int, [C.c_int32, _vp, C.c_int32, C.c_int32, _vp, _vp, _vp, C.POINTER(_vp)]),
+        "slc_%s_mulv_sharded" % _p: (C.c_int, [_vp, _vp, _vp]),
+        "slc_%s_mulm_sharded" % _p: (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int64, C.c_int32]),
+        "slc_%s_vstack_dev" % _p: (C.c_int, [C.c_int32, _vp, C.c_int32, _vp, _vp, _vp, C.POINTER(_hp)]),
+        "slc_%s_coo_bucket_dev" % _p: (C.c_int, [C.c_int64, _vp, _vp, _vp, C.c_int32, _vp, _vp, _vp, _vp, _vp]),
+        "slc_%s_mulv_sharded_dev" % _p: (C.c_int, [_vp]),
+        "slc_%s_mulm_sharded_dev" % _p: (C.c_int, [_vp, C.c_int32]),
         "slc_%s_mm" % _p: (C.c_int, [_hp, _hp, C.POINTER(_hp)]),
         "slc_%s_transpose" % _p: (C.c_int, [_hp, C.c_int, C.POINTER(_hp)]),
         "slc_%s_hermitian" % _p: (C.c_int, [_hp, C.POINTER(C.c_int)]),

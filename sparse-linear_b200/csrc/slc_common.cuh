@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstring>
 #include <atomic>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -96,6 +97,32 @@ inline void dev_free(void *p) {
   if (p) cudaFreeAsync(p, cur_stream());
 }
 
+// Per-device cache of a value that CUDA keeps per device (e.g. the dynamic shared-memory limit set with
+// cudaFuncSetAttribute): one slot per device ordinal, indexed by the calling thread's current device.
+// A process-wide static would be wrong as soon as one process drives two GPUs (slc_set_device,
+// slc_*_upload_sharded).  Slots are atomics, so two host threads may race to raise the same limit safely.
+constexpr int MAX_DEVICES = 64;
+template <class V>
+struct PerDevice {
+  std::atomic<V> slot[MAX_DEVICES];
+  PerDevice() { for (auto &s : slot) s.store(V(), std::memory_order_relaxed); }
+  std::atomic<V> &cur() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) dev = 0;
+    return slot[dev];
+  }
+};
+
+// Raise a kernel's dynamic shared-memory limit on the current device if it is below `bytes`.
+template <class K>
+inline cudaError_t ensure_dyn_smem(K kernel, PerDevice<size_t> &cache, size_t bytes) {
+  std::atomic<size_t> &have = cache.cur();
+  if (bytes <= have.load(std::memory_order_acquire)) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e == cudaSuccess) have.store(bytes, std::memory_order_release);
+  return e;
+}
+
 // ---- the handle ---------------------------------------------------------------------------------
 
 enum ElemType : int { ELEM_D = 'd', ELEM_Z = 'z' };
@@ -127,6 +154,7 @@ struct SellPlan {
   // distributed products: host copy of the slice ranges and the cached interior run
   std::vector<int32_t> h_cmin, h_cmax;
   int32_t interior_s0 = -1, interior_s1 = -1, interior_lo = 0, interior_hi = 0;
+  int32_t side_cmin[2] = {0x7fffffff, 0x7fffffff}, side_cmax[2] = {-1, -1};  // columns the rows below / above the interior reach
   // widest column window of a 1024-row block (k_spmm_window), -1 = not measured yet
   int32_t window_max = -1;
   // k_spmm_panel: distance in rows between grid lines (the near off-diagonal band of a stencil),
@@ -152,6 +180,10 @@ struct BalancedPlan {
 }  // namespace slc
 
 struct slc_matrix {
+  // Serialises every call that may build a plan, touch the per-handle pipeline streams or refresh the
+  // partition tables: two host threads (two Haskell sparks forcing `mulV a x` and `mulV a y`) may share
+  // one handle.  Recursive because entry points nest (mulm_dist -> ensure_plan -> ensure_csr).
+  std::recursive_mutex mu;
   int elem = slc::ELEM_D;
   int device = 0;
   int32_t nrows = 0, ncols = 0;
@@ -178,13 +210,27 @@ struct slc_matrix {
   // streams and events of the pipelined host-operand product (upload / compute / download overlap)
   cudaStream_t pipe_in = nullptr, pipe_out = nullptr;
   std::vector<cudaEvent_t> pipe_events;
-  // partition table of the last distributed product (device copy + host shadow)
-  void *dist_table = nullptr;
-  bool dist_table_valid = false;
-  alignas(8) unsigned char dist_table_host[384];
+  // partition tables of the recent distributed products (device copies + host shadows).  A caller that
+  // double-buffers its operand alternates between two tables; with a few cached slots neither costs a
+  // host-to-device copy per product, and the device addresses stay fixed (CUDA-graph friendly).
+  static constexpr int DIST_SLOTS = 4;
+  void *dist_table = nullptr;                     // DIST_SLOTS tables of DIST_TABLE_BYTES each
+  static constexpr int DIST_TABLE_BYTES = 384;
+  bool dist_slot_valid[DIST_SLOTS] = {};
+  int dist_next = 0;
+  alignas(8) unsigned char dist_table_host[DIST_SLOTS][DIST_TABLE_BYTES];
 };
 
 namespace slc {
+
+// lock a handle for the rest of the scope (null-safe; const handles are locked too: plans are caches)
+struct HandleLock {
+  std::recursive_mutex *mu;
+  explicit HandleLock(const slc_matrix *m) : mu(m ? &const_cast<slc_matrix *>(m)->mu : nullptr) { if (mu) mu->lock(); }
+  ~HandleLock() { if (mu) mu->unlock(); }
+  HandleLock(const HandleLock &) = delete;
+  HandleLock &operator=(const HandleLock &) = delete;
+};
 
 inline size_t elem_size(int elem) { return elem == ELEM_Z ? 16 : 8; }
 
@@ -221,6 +267,21 @@ template <> struct Num<double2> {
   static __device__ __forceinline__ double2 conj(double2 a) { return double2{a.x, -a.y}; }
   static __device__ __forceinline__ bool eq(double2 a, double2 b) { return a.x == b.x && a.y == b.y; }
 };
+
+// Start value of an output entry of the block product: 0 (mulM), y (the reference's axpy_ into a block
+// the caller filled, Sparse.hs:482-488) or beta * y.  A runtime mode, warp-uniform: one template
+// instantiation serves all three.
+template <class T>
+struct YInit {
+  int mode;  // 0: zero, 1: y, 2: beta * y
+  T beta;
+  __device__ __forceinline__ T operator()(const T *yp) const {
+    if (mode == 0) return Num<T>::zero();
+    const T y = *yp;
+    return mode == 1 ? y : Num<T>::mul(beta, y);
+  }
+};
+template <class T> inline YInit<T> yinit_zero() { YInit<T> yi; yi.mode = 0; yi.beta = Num<T>::zero(); return yi; }
 
 // ---- cache-hinted memory access -----------------------------------------------------------------
 // Matrix streams (indices, values) are read exactly once per product: keep them out of L1
@@ -272,6 +333,19 @@ __device__ __forceinline__ double2 ld_gather(const double2 *p, uint64_t pol) {
                : "=d"(v.x), "=d"(v.y) : "l"(p), "l"(pol));
   return v;
 }
+// operand entry that lives in a peer GPU's HBM and is rewritten between products: a plain (coherent) load,
+// not the read-only .nc path -- the data changes during the kernel's lifetime only before the acquire
+// that orders this load, but .nc makes no promise at all for memory another GPU writes
+__device__ __forceinline__ double ld_peer(const double *p) {
+  double v;
+  asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ double2 ld_peer(const double2 *p) {
+  double2 v;
+  asm volatile("ld.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+  return v;
+}
 // streaming store of a result that is not read again by this kernel
 __device__ __forceinline__ void st_stream(double *p, double v) {
   asm volatile("st.global.cs.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
@@ -320,7 +394,7 @@ int ensure_csr(slc_matrix *m);
 
 // built in slc_spmm_window.cu: the TMA-staged SpMM for banded short-row matrices (*done = it ran)
 template <class T>
-int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, bool *done);
+int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, YInit<T> yi, bool *done);
 
 inline int bits_for(uint32_t n) {  // bits needed to represent values in [0, n)
   int b = 1;

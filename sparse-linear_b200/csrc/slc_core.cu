@@ -283,6 +283,12 @@ int slc_memcpy_d2h(void *dst_host, const void *src_dev, int64_t bytes) {
   return SLC_OK;
 }
 
+int slc_memcpy_d2d(void *dst_dev, const void *src_dev, int64_t bytes) {
+  if (bytes < 0) return fail(SLC_ERR_INVALID, "slc_memcpy_d2d: negative size");
+  if (bytes) SLC_CUDA(cudaMemcpyAsync(dst_dev, src_dev, (size_t)bytes, cudaMemcpyDeviceToDevice, cur_stream()));
+  return SLC_OK;
+}
+
 // ---- CUDA IPC: one process per GPU, peers map each other's x slices -------------------------------
 // An IPC handle names a whole driver allocation, and small cudaMalloc requests are carved out of
 // larger ones, so the exported blob is the 64-byte handle of the containing allocation followed by

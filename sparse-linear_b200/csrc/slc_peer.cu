@@ -1,68 +1,120 @@
-// slc_peer.cu -- a barrier between the GPUs of one NVSwitch domain, written over peer memory.
+// slc_peer.cu -- ordering between the GPUs of one NVSwitch domain, written over peer memory.
 //
-// The row-partitioned SpMV gathers remote operand entries directly from the peers' HBM (DistX in
-// slc_spmv.cu), so the only communication step left is ordering: rank r may start its product once
-// every peer has finished writing its slice of x.  An NCCL all-reduce does that but costs tens of
-// microseconds per step, comparable to the product itself at 8 GPUs (~55 us).  This barrier is one
-// small kernel: every rank stores its epoch into its slot of every peer's flag array (release,
-// system scope, over NVLink) and then spins on its own array (acquire) until all slots reached the
-// epoch.  The spin is bounded (SLC_PEER_TIMEOUT_NS): a missing peer raises an error flag instead of
-// hanging the GPU.
-#include "slc_common.cuh"
-
-namespace slc {
-constexpr int MAX_PEERS = 16;
-constexpr unsigned long long PEER_TIMEOUT_NS = 5ull * 1000 * 1000 * 1000;
-}  // namespace slc
-
-struct slc_peer_group {
-  int32_t nparts = 0, self = 0;
-  unsigned long long epoch = 0;
-  unsigned long long *flags = nullptr;             // this rank's array: slot p is written by rank p
-  unsigned long long *peer_flags[slc::MAX_PEERS];  // every rank's array as mapped here
-  int *timeout_flag = nullptr;                     // device: set when a spin gave up
-  unsigned long long **table_dev = nullptr;        // device copy of peer_flags (for fused kernels)
-  bool connected = false;
-};
+// The row-partitioned products gather remote operand entries directly from the peers' HBM (DistX in
+// slc_spmv.cu), so the only communication step left is ordering: rank r may read a peer's slice of x
+// once that peer has finished writing it.  An NCCL all-reduce does that but costs tens of
+// microseconds per step, comparable to the product itself at 8 GPUs (~45 us).  Here every rank owns a
+// small flag array in its HBM that every peer maps (CUDA IPC between processes, plain peer access
+// inside one process); "signal" stores this rank's epoch into its slot of the peers' arrays (release,
+// system scope, over NVLink) and "wait" spins on the rank's own array (acquire) until the slots of
+// the peers it depends on reached the epoch.
+//
+// Round 2 changes, from the round-1 review:
+//   * the epoch lives in device memory and is advanced by the kernels themselves (the last block of
+//     a fused product, or the wait kernel), so a product is a pure function of device state: K
+//     products can be captured in one CUDA graph and the graph relaunched;
+//   * a rank waits only for the peers it reads from or is read by (PeerDeps: for a z-slab stencil the
+//     two neighbours), not for all N-1 -- a step is no longer a global rendezvous;
+//   * the spin is bounded (PEER_TIMEOUT_NS) and a timeout is sticky in a word of mapped host memory
+//     that every later call checks, so a product that gave up is reported, not silently wrong;
+//   * waits are timed (globaltimer) into a small statistics block (slc_peer_group_stats).
+#include "slc_peer.cuh"
 
 namespace slc {
 
-struct PeerTable {
-  unsigned long long *flags[MAX_PEERS];
-};
-
-__device__ __forceinline__ unsigned long long global_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
+__global__ void k_peer_barrier(PeerSync ps, uint32_t wait_mask, int mode) {
+  const int p = threadIdx.x;
+  const unsigned long long epoch = peer_epoch(ps);
+  if (p < ps.nparts && p != ps.self) {
+    if ((mode & 1) && ((ps.signal_mask >> p) & 1u)) peer_signal_one(ps, p, epoch);
+    if ((mode & 2) && ((wait_mask >> p) & 1u)) peer_wait_one(ps, p, epoch);
+  }
+  if (mode & 2) {
+    __syncthreads();
+    if (p == 0) peer_advance(ps, epoch);
+  }
 }
 
-// mode bit 0: signal (store my epoch into every peer's array); bit 1: wait (until every slot of my
-// own array reached the epoch).  Split in two, the signal goes out before the interior rows of a
-// product and the wait sits just before its boundary rows, so the peers' latency hides behind work.
-__global__ void k_peer_barrier(PeerTable peers, int32_t nparts, int32_t self, unsigned long long epoch,
-                               int mode, int *__restrict__ timeout_flag) {
-  const int p = threadIdx.x;
-  if (p >= nparts) return;
-  if (mode & 1) {
-    // everything this GPU wrote before the barrier (earlier in stream order) is visible to a peer
-    // that observes the epoch
-    __threadfence_system();
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peers.flags[p] + self), "l"(epoch) : "memory");
+static int enable_peer(int from_dev, int to_dev) {
+  if (from_dev == to_dev) return SLC_OK;
+  int can = 0;
+  SLC_CUDA(cudaDeviceCanAccessPeer(&can, from_dev, to_dev));
+  if (!can) return fail(SLC_ERR_CUDA, "device %d cannot map device %d's memory", from_dev, to_dev);
+  int prev = 0;
+  SLC_CUDA(cudaGetDevice(&prev));
+  SLC_CUDA(cudaSetDevice(from_dev));
+  cudaError_t e = cudaDeviceEnablePeerAccess(to_dev, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) { (void)cudaGetLastError(); e = cudaSuccess; }
+  cudaSetDevice(prev);
+  SLC_CUDA(e);
+  return SLC_OK;
+}
+
+static int group_alloc(int32_t nparts, int32_t self, slc_peer_group **out) {
+  slc_peer_group *g = new (std::nothrow) slc_peer_group();
+  if (!g) return fail(SLC_ERR_NOMEM, "out of host memory");
+  g->nparts = nparts;
+  g->self = self;
+  cudaGetDevice(&g->device);
+  for (int p = 0; p < MAX_PEERS; ++p) g->peer_flags[p] = nullptr;
+  g->deps_mask = nparts >= 32 ? 0xffffffffu : ((1u << nparts) - 1u);
+  g->deps_mask &= ~(1u << self);
+  // cudaMalloc (not the stream-ordered pool): pool memory cannot be exported through legacy IPC
+  cudaError_t e = cudaMalloc((void **)&g->flags, MAX_PEERS * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMalloc((void **)&g->state, PEER_STATE_WORDS * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMalloc((void **)&g->table_dev, MAX_PEERS * sizeof(unsigned long long *));
+  if (e == cudaSuccess) e = cudaHostAlloc((void **)&g->timeout_host, sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable);
+  if (e == cudaSuccess) e = cudaMemset(g->flags, 0, MAX_PEERS * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMemset(g->state, 0, PEER_STATE_WORDS * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    cudaFree(g->flags);
+    cudaFree(g->state);
+    cudaFree(g->table_dev);
+    if (g->timeout_host) cudaFreeHost(g->timeout_host);
+    delete g;
+    return fail(SLC_ERR_CUDA, "slc_peer_group_create: %s", cudaGetErrorString(e));
   }
-  if (!(mode & 2)) return;
-  const unsigned long long *mine = peers.flags[self] + p;
-  const unsigned long long t0 = global_ns();
-  for (;;) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mine) : "memory");
-    if (v >= epoch) break;
-    if (global_ns() - t0 > PEER_TIMEOUT_NS) {
-      atomicExch(timeout_flag, 1);
-      break;
-    }
-    __nanosleep(100);
-  }
+  *g->timeout_host = 0;
+  g->peer_flags[self] = g->flags;
+  *out = g;
+  return SLC_OK;
+}
+
+static int group_publish_table(slc_peer_group *g) {
+  SLC_CUDA(cudaMemcpy(g->table_dev, g->peer_flags, MAX_PEERS * sizeof(unsigned long long *), cudaMemcpyHostToDevice));
+  g->connected = true;
+  return SLC_OK;
+}
+
+int peer_check(slc_peer_group *g, const char *fn) {
+  if (!g) return fail(SLC_ERR_INVALID, "%s: null group", fn);
+  if (g->nparts > 1 && !g->connected) return fail(SLC_ERR_INVALID, "%s: group is not connected", fn);
+  const int t = *(volatile int *)g->timeout_host;
+  if (t) return fail(SLC_ERR_CUDA, "%s: a peer did not signal epoch %d within %.1f s; the rows that needed it were "
+                     "filled with NaN", fn, t, (double)PEER_TIMEOUT_NS * 1e-9);
+  return SLC_OK;
+}
+
+PeerSync peer_sync_of(slc_peer_group *g) {
+  PeerSync ps;
+  ps.flags = g->table_dev;
+  ps.state = g->state;
+  ps.timeout_host = g->timeout_host;
+  ps.nparts = g->nparts;
+  ps.self = g->self;
+  ps.signal_mask = g->nparts >= 32 ? 0xffffffffu : ((1u << g->nparts) - 1u);
+  ps.signal_mask &= ~(1u << g->self);
+  return ps;
+}
+
+static int peer_launch(slc_peer_group *g, int mode, const char *fn) {
+  SLC_TRY(peer_check(g, fn));
+  if (g->nparts == 1) return SLC_OK;
+  k_peer_barrier<<<1, 32, 0, cur_stream()>>>(peer_sync_of(g), g->deps_mask, mode);
+  SLC_LAUNCHED();
+  return SLC_OK;
 }
 
 }  // namespace slc
@@ -76,31 +128,13 @@ int slc_peer_group_create(int32_t nparts, int32_t self, slc_peer_group **out, vo
   *out = nullptr;
   if (nparts < 1 || nparts > MAX_PEERS || self < 0 || self >= nparts)
     return fail(SLC_ERR_INVALID, "slc_peer_group_create: 1..%d ranks supported", MAX_PEERS);
-  slc_peer_group *g = new (std::nothrow) slc_peer_group();
-  if (!g) return fail(SLC_ERR_NOMEM, "out of host memory");
-  g->nparts = nparts;
-  g->self = self;
-  for (int p = 0; p < MAX_PEERS; ++p) g->peer_flags[p] = nullptr;
-  // cudaMalloc (not the stream-ordered pool): pool memory cannot be exported through legacy IPC
-  cudaError_t e = cudaMalloc((void **)&g->flags, MAX_PEERS * sizeof(unsigned long long));
-  if (e == cudaSuccess) e = cudaMalloc((void **)&g->timeout_flag, sizeof(int));
-  if (e == cudaSuccess) e = cudaMemset(g->flags, 0, MAX_PEERS * sizeof(unsigned long long));
-  if (e == cudaSuccess) e = cudaMemset(g->timeout_flag, 0, sizeof(int));
-  if (e == cudaSuccess) e = cudaDeviceSynchronize();
-  if (e != cudaSuccess) {
-    cudaFree(g->flags);
-    cudaFree(g->timeout_flag);
-    delete g;
-    return fail(SLC_ERR_CUDA, "slc_peer_group_create: %s", cudaGetErrorString(e));
-  }
+  slc_peer_group *g = nullptr;
+  SLC_TRY(group_alloc(nparts, self, &g));
   int rc = slc_ipc_export(g->flags, handle72);
   if (rc != SLC_OK) {
-    cudaFree(g->flags);
-    cudaFree(g->timeout_flag);
-    delete g;
+    slc_peer_group_free(g);
     return rc;
   }
-  g->peer_flags[self] = g->flags;
   *out = g;
   return SLC_OK;
 }
@@ -112,24 +146,41 @@ int slc_peer_group_connect(slc_peer_group *g, const void *handles72) {
     void *ptr = nullptr;
     SLC_TRY(slc_ipc_import((const char *)handles72 + (size_t)p * 72, &ptr));
     g->peer_flags[p] = (unsigned long long *)ptr;
+    g->imported[p] = true;
   }
-  cudaError_t e = cudaMalloc((void **)&g->table_dev, MAX_PEERS * sizeof(unsigned long long *));
-  if (e == cudaSuccess)
-    e = cudaMemcpy(g->table_dev, g->peer_flags, MAX_PEERS * sizeof(unsigned long long *), cudaMemcpyHostToDevice);
-  if (e != cudaSuccess) return fail(SLC_ERR_CUDA, "slc_peer_group_connect: %s", cudaGetErrorString(e));
-  g->connected = true;
-  return SLC_OK;
+  return group_publish_table(g);
 }
 
-static int peer_launch(slc_peer_group *g, int mode, const char *fn) {
-  if (!g) return fail(SLC_ERR_INVALID, "%s: null group", fn);
-  if (g->nparts == 1) return SLC_OK;
-  if (!g->connected) return fail(SLC_ERR_INVALID, "%s: group is not connected", fn);
-  PeerTable t;
-  for (int p = 0; p < MAX_PEERS; ++p) t.flags[p] = g->peer_flags[p];
-  if (mode & 1) g->epoch += 1;
-  k_peer_barrier<<<1, 32, 0, cur_stream()>>>(t, g->nparts, g->self, g->epoch, mode, g->timeout_flag);
-  SLC_LAUNCHED();
+int slc_peer_group_create_local(int32_t ndev, const int32_t *devices, slc_peer_group **groups) {
+  if (!groups) return fail(SLC_ERR_INVALID, "slc_peer_group_create_local: null argument");
+  if (ndev < 1 || ndev > MAX_PEERS) return fail(SLC_ERR_INVALID, "slc_peer_group_create_local: 1..%d devices supported", MAX_PEERS);
+  int prev = 0;
+  SLC_CUDA(cudaGetDevice(&prev));
+  for (int p = 0; p < ndev; ++p) groups[p] = nullptr;
+  int rc = SLC_OK;
+  for (int p = 0; p < ndev && rc == SLC_OK; ++p) {
+    const int dev = devices ? devices[p] : p;
+    if (cudaSetDevice(dev) != cudaSuccess) { (void)cudaGetLastError(); rc = fail(SLC_ERR_CUDA, "slc_peer_group_create_local: no device %d", dev); break; }
+    rc = group_alloc(ndev, p, &groups[p]);
+  }
+  for (int p = 0; p < ndev && rc == SLC_OK; ++p)
+    for (int q = 0; q < ndev && rc == SLC_OK; ++q)
+      if (p != q) rc = enable_peer(groups[p]->device, groups[q]->device);
+  for (int p = 0; p < ndev && rc == SLC_OK; ++p) {
+    for (int q = 0; q < ndev; ++q) groups[p]->peer_flags[q] = groups[q]->flags;
+    cudaSetDevice(groups[p]->device);
+    rc = group_publish_table(groups[p]);
+  }
+  cudaSetDevice(prev);
+  if (rc != SLC_OK)
+    for (int p = 0; p < ndev; ++p) { slc_peer_group_free(groups[p]); groups[p] = nullptr; }
+  return rc;
+}
+
+int slc_peer_group_set_deps(slc_peer_group *g, uint32_t mask) {
+  if (!g) return fail(SLC_ERR_INVALID, "slc_peer_group_set_deps: null group");
+  const uint32_t all = g->nparts >= 32 ? 0xffffffffu : ((1u << g->nparts) - 1u);
+  g->deps_mask = mask & all & ~(1u << g->self);
   return SLC_OK;
 }
 
@@ -139,36 +190,40 @@ int slc_peer_wait(slc_peer_group *g) { return peer_launch(g, 2, "slc_peer_wait")
 
 int slc_peer_group_timed_out(slc_peer_group *g, int *flag) {
   if (!g || !flag) return fail(SLC_ERR_INVALID, "slc_peer_group_timed_out: null argument");
-  SLC_CUDA(cudaMemcpy(flag, g->timeout_flag, sizeof(int), cudaMemcpyDeviceToHost));
+  *flag = *(volatile int *)g->timeout_host != 0;
+  return SLC_OK;
+}
+
+int slc_peer_group_stats(slc_peer_group *g, int64_t *out4, int reset) {
+  if (!g || !out4) return fail(SLC_ERR_INVALID, "slc_peer_group_stats: null argument");
+  int prev = 0;
+  cudaGetDevice(&prev);
+  if (prev != g->device) cudaSetDevice(g->device);
+  unsigned long long h[PEER_STATE_WORDS];
+  cudaError_t e = cudaMemcpy(h, g->state, sizeof h, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess && reset) e = cudaMemset(g->state + PEER_STAT_WAIT_SUM, 0, 3 * sizeof(unsigned long long));
+  if (prev != g->device) cudaSetDevice(prev);
+  SLC_CUDA(e);
+  out4[0] = (int64_t)h[PEER_EPOCH];
+  out4[1] = (int64_t)h[PEER_STAT_WAITS];
+  out4[2] = (int64_t)h[PEER_STAT_WAIT_SUM];
+  out4[3] = (int64_t)h[PEER_STAT_WAIT_MAX];
   return SLC_OK;
 }
 
 void slc_peer_group_free(slc_peer_group *g) {
   if (!g) return;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  if (prev != g->device) cudaSetDevice(g->device);
   for (int p = 0; p < g->nparts; ++p)
-    if (p != g->self && g->peer_flags[p]) slc_ipc_close(g->peer_flags[p]);
+    if (g->imported[p] && g->peer_flags[p]) slc_ipc_close(g->peer_flags[p]);
   cudaFree(g->flags);
-  cudaFree(g->timeout_flag);
+  cudaFree(g->state);
   cudaFree(g->table_dev);
+  if (g->timeout_host) cudaFreeHost(g->timeout_host);
+  if (prev != g->device) cudaSetDevice(prev);
   delete g;
 }
 
 }  // extern "C"
-
-namespace slc {
-// For kernels that fuse the barrier (k_spmv_sell_dist): start a new epoch and expose the tables.
-int peer_sync_args(slc_peer_group *g, unsigned long long *const **flags, int **timeout_flag,
-                   unsigned long long *epoch, int32_t *nparts, int32_t *self) {
-  if (!g) return fail(SLC_ERR_INVALID, "peer sync: null group");
-  *flags = nullptr;
-  if (g->nparts == 1) return SLC_OK;
-  if (!g->connected) return fail(SLC_ERR_INVALID, "peer sync: group is not connected");
-  g->epoch += 1;
-  *flags = g->table_dev;
-  *timeout_flag = g->timeout_flag;
-  *epoch = g->epoch;
-  *nparts = g->nparts;
-  *self = g->self;
-  return SLC_OK;
-}
-}  // namespace slc

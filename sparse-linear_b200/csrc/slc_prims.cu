@@ -332,14 +332,9 @@ static int sort_pairs_impl(const K *src, K *ka, K *kb, uint32_t *va, uint32_t *v
   const int64_t ntiles = ceil_div(n, RS_TILE);
   DevBuf<int32_t> hist;
   SLC_TRY(hist.alloc((size_t)ntiles * RS_BINS));
-  static bool attr_set = false;  // per instantiation (K)
-  if (!attr_set) {
-    SLC_CUDA(cudaFuncSetAttribute(k_radix_scatter<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)radix_scatter_smem<K>()));
-    SLC_CUDA(cudaFuncSetAttribute(k_radix_scatter<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)radix_scatter_smem<K>()));
-    attr_set = true;
-  }
+  static PerDevice<size_t> smem_a, smem_b;  // per instantiation (K), per device
+  SLC_CUDA(ensure_dyn_smem(k_radix_scatter<K, false>, smem_a, radix_scatter_smem<K>()));
+  SLC_CUDA(ensure_dyn_smem(k_radix_scatter<K, true>, smem_b, radix_scatter_smem<K>()));
   const K *kin = src ? src : ka;
   const uint32_t *vin = va;
   K *kout = src ? ka : kb;

@@ -646,6 +646,10 @@ static int mm_entry(const slc_matrix *a, const slc_matrix *b, slc_matrix **out) 
   SLC_TRY(matrix_alloc(a->elem, ar, bc, nnzc, &c));
   k_narrow<<<(unsigned)ceil_div((int64_t)bc + 1, 256), 256, 0, s>>>((int64_t)bc + 1, ptr64.p, c->colptr);
   g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (cudaError_t e = cudaGetLastError(); e != cudaSuccess) {
+    matrix_release(c);
+    return fail(SLC_ERR_CUDA, "mm: pointer pass launch failed: %s", cudaGetErrorString(e));
+  }
 
   // pass 2: numeric
   int rc = run_merge<T, 4, true>(hcount[CLS_MERGE4], cols.p + hbase[CLS_MERGE4], a, b, nullptr, c);
@@ -659,7 +663,8 @@ static int mm_entry(const slc_matrix *a, const slc_matrix *b, slc_matrix **out) 
                                                      (const T *)b->vals, stamp.p, work.p, cnt.p, c->colptr,
                                                      c->rowidx, (T *)c->vals);
     g_launches.fetch_add(1, std::memory_order_relaxed);
-    if (cudaGetLastError() != cudaSuccess) rc = fail(SLC_ERR_CUDA, "mm: dense pass launch failed");
+    if (cudaError_t e = cudaGetLastError(); e != cudaSuccess)
+      rc = fail(SLC_ERR_CUDA, "mm: dense pass launch failed: %s", cudaGetErrorString(e));
   }
   if (rc != SLC_OK) {
     matrix_release(c);

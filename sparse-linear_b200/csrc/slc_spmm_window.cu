@@ -61,7 +61,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
 __device__ __forceinline__ bool mbar_wait(uint64_t *bar, uint32_t parity, int *err) {
   for (uint32_t spin = 0; spin < WINDOW_SPIN_LIMIT; ++spin)
     if (mbar_try_wait(bar, parity)) return true;
-  atomicExch(err, 1);
+  *(volatile int *)err = 1;  // mapped host word: a plain store, no PCIe atomic
   return false;
 }
 // global -> shared bulk copy by the TMA engine; completes `bytes` on the mbarrier.  src, dst and bytes
@@ -82,11 +82,11 @@ template <class T, int LMAX, bool FULL>
 __device__ __forceinline__ void window_column(const int32_t (&c)[WIN_RPT][LMAX], const T (&a)[WIN_RPT][LMAX],
                                               const int32_t (&len)[WIN_RPT], const bool (&live)[WIN_RPT],
                                               const T *__restrict__ xs, T *__restrict__ ycol,
-                                              const int32_t (&row)[WIN_RPT]) {
+                                              const int32_t (&row)[WIN_RPT], const YInit<T> &yi) {
 #pragma unroll
   for (int i = 0; i < WIN_RPT; ++i) {
     if (!FULL && !live[i]) continue;
-    T acc = Num<T>::zero();
+    T acc = yi(ycol + row[i]);
 #pragma unroll
     for (int u = 0; u < LMAX; ++u)
       if (FULL || u < len[i]) acc = Num<T>::add(Num<T>::mul(a[i][u], lds_t(xs + c[i][u])), acc);
@@ -101,7 +101,7 @@ k_spmm_window(int32_t nrows, int32_t ncols, int32_t nslices, int32_t nstage, int
               const int32_t *__restrict__ colidx, const T *__restrict__ vals,
               const int32_t *__restrict__ slice_cmin, const int32_t *__restrict__ slice_cmax,
               const T *__restrict__ X, int64_t ldx, T *__restrict__ Y, int64_t ldy, int32_t k,
-              int *__restrict__ err) {
+              const YInit<T> yi, int *__restrict__ err) {
   extern __shared__ __align__(128) unsigned char win_smem[];
   T *stage0 = reinterpret_cast<T *>(win_smem);                                              // [nstage][wcap]
   uint64_t *full = reinterpret_cast<uint64_t *>(win_smem + (size_t)nstage * wcap * sizeof(T));  // [nstage]
@@ -144,7 +144,7 @@ k_spmm_window(int32_t nrows, int32_t ncols, int32_t nslices, int32_t nstage, int
   __syncthreads();
   const int32_t wlo = s_rng[0], width = s_rng[1];
   if (width > wcap || width <= 0) {  // cannot happen with the host's plan; never index past the stage
-    if (tid == 0) atomicExch(err, 2);
+    if (tid == 0) *(volatile int *)err = 2;
     return;
   }
 
@@ -196,8 +196,8 @@ k_spmm_window(int32_t nrows, int32_t ncols, int32_t nslices, int32_t nstage, int
     if (!mbar_wait(full + st, parity, err)) return;
     const T *xs = stage0 + (size_t)st * wcap;
     T *ycol = Y + (int64_t)j * ldy;
-    if (full_warp) window_column<T, LMAX, true>(c, a, len, live, xs, ycol, row);
-    else window_column<T, LMAX, false>(c, a, len, live, xs, ycol, row);
+    if (full_warp) window_column<T, LMAX, true>(c, a, len, live, xs, ycol, row, yi);
+    else window_column<T, LMAX, false>(c, a, len, live, xs, ycol, row, yi);
     mbar_arrive(empty + st);  // this thread is done reading the stage
     if (++st == nstage) {
       st = 0;
@@ -222,31 +222,48 @@ __global__ void k_window_max(int32_t nslices, const int32_t *__restrict__ slice_
   if (hi >= lo) atomicMax(out, hi - lo + 1);
 }
 
-static int *g_window_err = nullptr;  // device flag shared by every launch of this process
+// Error flag of the window kernel: one word of mapped pinned host memory shared by every launch of this
+// process on any device (a kernel writes it over PCIe only when a barrier wait gives up), so reading it
+// needs neither a device of its own nor a synchronising copy.
+static std::atomic<int *> g_window_err{nullptr};
+
+static int window_err_flag(int **out) {
+  int *p = g_window_err.load(std::memory_order_acquire);
+  if (!p) {
+    int *fresh = nullptr;
+    SLC_CUDA(cudaHostAlloc((void **)&fresh, sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable));
+    *fresh = 0;
+    int *expected = nullptr;
+    if (g_window_err.compare_exchange_strong(expected, fresh, std::memory_order_acq_rel)) p = fresh;
+    else { cudaFreeHost(fresh); p = expected; }
+  }
+  *out = p;
+  return SLC_OK;
+}
 
 int spmm_window_error(int *flag) {
   *flag = 0;
-  if (!g_window_err) return SLC_OK;
-  SLC_CUDA(cudaMemcpyAsync(flag, g_window_err, sizeof(int), cudaMemcpyDeviceToHost, cur_stream()));
+  int *p = g_window_err.load(std::memory_order_acquire);
+  if (!p) return SLC_OK;
   SLC_CUDA(cudaStreamSynchronize(cur_stream()));
+  *flag = *(volatile int *)p;
   return SLC_OK;
 }
 
 template <class T, int LMAX>
 static int launch_window(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, int32_t nstage,
-                         int32_t wcap) {
+                         int32_t wcap, const YInit<T> &yi) {
   const SellPlan &sp = m->sell;
   const size_t smem = (size_t)nstage * wcap * sizeof(T) + (size_t)nstage * 2 * sizeof(uint64_t) + 16;
   auto kern = k_spmm_window<T, LMAX>;
-  static size_t smem_set = 0;  // per instantiation
-  if (smem > smem_set) {
-    SLC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
-  }
+  static PerDevice<size_t> smem_set;  // per instantiation, per device
+  SLC_CUDA(ensure_dyn_smem(kern, smem_set, smem));
+  int *err_flag = nullptr;
+  SLC_TRY(window_err_flag(&err_flag));
   const unsigned nb = (unsigned)ceil_div(m->nrows, WIN_ROWS);
   kern<<<nb, WIN_THREADS, smem, cur_stream()>>>(m->nrows, m->ncols, sp.nslices, nstage, wcap, sp.slice_ptr, sp.rowlen,
                                                 sp.colidx, (const T *)sp.vals, sp.slice_cmin, sp.slice_cmax, X, ldx, Y,
-                                                ldy, k, g_window_err);
+                                                ldy, k, yi, err_flag);
   SLC_LAUNCHED();
   return SLC_OK;
 }
@@ -256,7 +273,7 @@ static int launch_window(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t l
 // stages in 200 KB of shared memory), X 16-byte aligned with an even column stride for Double.
 // *done says whether it did.
 template <class T>
-int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, bool *done) {
+int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, YInit<T> yi, bool *done) {
   *done = false;
   static const char *env = getenv("SLC_SPMM_WINDOW");
   if (env && env[0] == '0') return SLC_OK;
@@ -285,14 +302,10 @@ int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
   int32_t nstage = (int32_t)std::min<size_t>(8, budget / stage_bytes);
   if (sp.window_max <= 0 || nstage < 3) return SLC_OK;
   nstage = std::min(nstage, std::max(k, 2));
-  if (!g_window_err) {
-    SLC_CUDA(cudaMalloc((void **)&g_window_err, sizeof(int)));
-    SLC_CUDA(cudaMemsetAsync(g_window_err, 0, sizeof(int), s));
-  }
   switch (m->max_rowlen) {
 #define SLC_WIN_CASE(L_) \
   case L_:               \
-    SLC_TRY((launch_window<T, L_>(m, X, ldx, Y, ldy, k, nstage, wcap))); \
+    SLC_TRY((launch_window<T, L_>(m, X, ldx, Y, ldy, k, nstage, wcap, yi))); \
     break
     SLC_WIN_CASE(1);
     SLC_WIN_CASE(2);
@@ -310,8 +323,8 @@ int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
   return SLC_OK;
 }
 
-template int spmm_window_try<double>(slc_matrix *, const double *, int64_t, double *, int64_t, int32_t, bool *);
-template int spmm_window_try<double2>(slc_matrix *, const double2 *, int64_t, double2 *, int64_t, int32_t, bool *);
+template int spmm_window_try<double>(slc_matrix *, const double *, int64_t, double *, int64_t, int32_t, YInit<double>, bool *);
+template int spmm_window_try<double2>(slc_matrix *, const double2 *, int64_t, double2 *, int64_t, int32_t, YInit<double2>, bool *);
 
 }  // namespace slc
 

@@ -22,12 +22,9 @@
 #include <type_traits>
 
 #include "slc_common.cuh"
+#include "slc_peer.cuh"
 
 namespace slc {
-
-// implemented in slc_peer.cu: starts a new epoch and hands out what a fused kernel needs
-int peer_sync_args(slc_peer_group *g, unsigned long long *const **flags, int **timeout_flag,
-                   unsigned long long *epoch, int32_t *nparts, int32_t *self);
 
 // =================================================================================================
 // plans
@@ -70,15 +67,12 @@ struct DistX {
   int32_t self_lo, self_hi;
   const DistTable *tbl;
   __device__ __forceinline__ T operator()(int32_t c, uint64_t pol) const {
-    const T *p = self_x + (c - self_lo);
-    if (c < self_lo || c >= self_hi) {
-      int q = 0;
-      const int np = tbl->nparts;
+    if (c >= self_lo && c < self_hi) return ld_gather(self_x + (c - self_lo), pol);
+    int q = 0;
+    const int np = tbl->nparts;
 #pragma unroll 1
-      while (q + 1 < np && c >= tbl->splits[q + 1]) ++q;
-      p = static_cast<const T *>(tbl->parts[q]) + (c - tbl->splits[q]);
-    }
-    return ld_gather(p, pol);
+    while (q + 1 < np && c >= tbl->splits[q + 1]) ++q;
+    return ld_peer(static_cast<const T *>(tbl->parts[q]) + (c - tbl->splits[q]));
   }
 };
 
@@ -104,10 +98,12 @@ struct DistXM {
   int64_t self_ld;
   int32_t self_lo, self_hi;
   const DistTable *tbl;
-  __device__ __forceinline__ const T *col0(int32_t c, int64_t &ld) const {
+  // remote: the entry lives in a peer's HBM (read it with ld_peer, not through the read-only path)
+  __device__ __forceinline__ const T *col0(int32_t c, int64_t &ld, bool &remote) const {
     ld = self_ld;
     const T *p = self_X + (c - self_lo);
-    if (c < self_lo || c >= self_hi) {
+    remote = c < self_lo || c >= self_hi;
+    if (remote) {
       int q = 0;
       const int np = tbl->nparts;
 #pragma unroll 1
@@ -467,59 +463,51 @@ k_spmv_sell(int32_t row_begin, int32_t row_end, const int64_t *__restrict__ slic
 }
 
 // ---- SELL-32, row-partitioned over the GPUs of one box: ONE launch per product ---------------------
-// The grid is  [boundary blocks | interior blocks].  Interior rows (all columns inside this rank's
-// slice of x) run the undistributed row body on a shifted base pointer.  Boundary rows gather some
-// columns from a peer's HBM over NVLink (DistX).  The ordering between ranks is fused in:
-//   * block 0 publishes this rank's epoch into every peer's flag array (release, system scope):
+// The grid is  [low boundary blocks | high boundary blocks | interior blocks].  Interior rows (all
+// columns inside this rank's slice of x) run the undistributed row body on a shifted base pointer.
+// Boundary rows gather some columns from a peer's HBM over NVLink (DistX).  The ordering between
+// ranks is fused in (slc_peer.cuh):
+//   * block 0 publishes this rank's epoch into the peers' flag arrays (release, system scope):
 //     "my slice of x is written" -- true when the kernel starts, by stream order;
-//   * every boundary block first waits (acquire, bounded spin) until all peers published the epoch.
+//   * a boundary block first waits (acquire, bounded spin) until the peers ITS rows read from have
+//     published the epoch: the rows below the interior wait for `wait_lo` (for a z-slab: rank-1), the
+//     rows above it for `wait_hi` (rank+1).  Round 1 made every boundary block wait for all N-1 peers,
+//     which turned each product into a global rendezvous (8 GPUs: 4.4x instead of 6x);
+//   * the last block to finish advances the device-resident epoch, so the launch carries no
+//     per-product host state and K products can sit in one CUDA graph.
 // Boundary blocks have the lowest block indices, so they are resident from the start: their wait
 // and their long-latency peer gathers overlap the interior blocks that fill the rest of the GPU.
-struct PeerSync {
-  unsigned long long *const *flags;  // device array [nparts]: every rank's flag array as mapped here
-  int *timeout_flag;
-  unsigned long long epoch;
-  int32_t nparts, self;
-};
-
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
+// A wait that gives up (5 s) records the epoch in a host-visible word and its rows are filled with
+// NaN: the next call on the group reports it (peer_check).
+template <class T> __device__ __forceinline__ T poison();
+template <> __device__ __forceinline__ double poison<double>() { return __longlong_as_double(0x7ff8000000000000ll); }
+template <> __device__ __forceinline__ double2 poison<double2>() { return double2{poison<double>(), poison<double>()}; }
 
 template <class T, int U, bool KB>
 __global__ void __launch_bounds__(256, sizeof(T) == 8 ? (KB ? 8 : 6) : 4)
 k_spmv_sell_dist(int32_t nrows, int32_t r0, int32_t r1, const int64_t *__restrict__ slice_ptr,
                  const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
                  const T *__restrict__ vals, const DistX<T> xa, T *__restrict__ y, const PeerSync ps,
-                 const int32_t *__restrict__ kbase) {
+                 const uint32_t wait_lo, const uint32_t wait_hi, const int32_t *__restrict__ kbase) {
   const int32_t nbl = (r0 + 255) >> 8;            // boundary blocks below the interior
   const int32_t nbh = (nrows - r1 + 255) >> 8;    // and above it
   const int32_t b = blockIdx.x;
   const bool boundary = b < nbl + nbh;
+  __shared__ int s_timed_out;
+  bool dead = false;
   if (ps.flags != nullptr) {
-    if (b == 0 && (int)threadIdx.x < ps.nparts) {
-      __threadfence_system();
-      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(ps.flags[threadIdx.x] + ps.self), "l"(ps.epoch)
-                   : "memory");
-    }
-    if (boundary) {
-      if ((int)threadIdx.x < ps.nparts) {
-        const unsigned long long *mine = ps.flags[ps.self] + threadIdx.x;
-        const unsigned long long t0 = globaltimer_ns();
-        for (;;) {
-          unsigned long long v;
-          asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mine) : "memory");
-          if (v >= ps.epoch) break;
-          if (globaltimer_ns() - t0 > 5000000000ull) {
-            atomicExch(ps.timeout_flag, 1);
-            break;
-          }
-          __nanosleep(64);
-        }
+    if (b == 0 || boundary) {
+      const unsigned long long epoch = peer_epoch(ps);
+      const int p = threadIdx.x;
+      if (threadIdx.x == 0) s_timed_out = 0;
+      __syncthreads();
+      if (p < ps.nparts && p != ps.self) {
+        if (b == 0 && ((ps.signal_mask >> p) & 1u)) peer_signal_one(ps, p, epoch);
+        const uint32_t wm = boundary ? (b < nbl ? wait_lo : wait_hi) : 0u;
+        if (((wm >> p) & 1u) && !peer_wait_one(ps, p, epoch)) s_timed_out = 1;
       }
       __syncthreads();
+      dead = s_timed_out != 0;
     }
   }
   if (boundary) {
@@ -531,13 +519,17 @@ k_spmv_sell_dist(int32_t nrows, int32_t r0, int32_t r1, const int64_t *__restric
       row = r1 + (b - nbl) * 256 + threadIdx.x;
       limit = nrows;
     }
-    if (row < limit) sell_row<T, 4, false, DistX<T>>(row, slice_ptr, rowlen, colidx, vals, xa, y);
+    if (row < limit) {
+      if (dead) y[row] = poison<T>();
+      else sell_row<T, 4, false, DistX<T>, KB>(row, slice_ptr, rowlen, colidx, vals, xa, y, kbase, 0);
+    }
   } else {
     const int32_t row = r0 + (b - nbl - nbh) * 256 + threadIdx.x;
     if (row < r1)
       sell_row<T, U, false, LocalX<T>, KB>(row, slice_ptr, rowlen, colidx, vals, LocalX<T>{xa.self_x - xa.self_lo}, y,
                                            kbase, 1);
   }
+  if (ps.flags != nullptr) peer_block_done(ps, gridDim.x);
 }
 
 // ---- CSR, one warp per row ----------------------------------------------------------------------
@@ -988,7 +980,7 @@ __global__ void __launch_bounds__(128)
 k_spmm_rows(int32_t nrows, int32_t ntiles, const int64_t *__restrict__ slice_ptr,
             const int32_t *__restrict__ rowlen, const int32_t *__restrict__ rowptr,
             const int32_t *__restrict__ colidx, const T *__restrict__ vals, const T *__restrict__ X,
-            int64_t ldx, T *__restrict__ Y, int64_t ldy, int32_t k) {
+            int64_t ldx, T *__restrict__ Y, int64_t ldy, int32_t k, const YInit<T> yi) {
   const int32_t rb = blockIdx.x / ntiles;
   const int32_t tile = blockIdx.x - rb * ntiles;
   const int32_t row = rb * blockDim.x + threadIdx.x;
@@ -1009,7 +1001,7 @@ k_spmm_rows(int32_t nrows, int32_t ntiles, const int64_t *__restrict__ slice_ptr
   }
   T acc[JT];
 #pragma unroll
-  for (int j = 0; j < JT; ++j) acc[j] = Num<T>::zero();
+  for (int j = 0; j < JT; ++j) acc[j] = (j0 + j < k) ? yi(Y + (int64_t)(j0 + j) * ldy + row) : Num<T>::zero();
   const T *xb = X + (int64_t)j0 * ldx;
   for (int32_t kk = 0; kk < len; ++kk) {
     const int32_t c = __ldg(colidx + base + (int64_t)kk * stride);
@@ -1038,7 +1030,7 @@ template <class T, int JT, int LMAX, bool FULL, bool PIPE>
 __device__ __forceinline__ void spmm_short_columns(const int32_t (&c)[LMAX], const T (&a)[LMAX], int32_t len,
                                                    const T *__restrict__ X, int64_t ldx, T *__restrict__ Yrow,
                                                    int64_t ldy, int32_t jbeg, int32_t jend, uint64_t pol_x,
-                                                   uint32_t zmask) {
+                                                   uint32_t zmask, const YInit<T> &yi) {
   // the LMAX*JT gathers of the column tile that starts at j0
   auto load = [&](T (&xv)[LMAX][JT], int32_t j0) {
     const T *xb = X + (int64_t)j0 * ldx;
@@ -1061,7 +1053,7 @@ __device__ __forceinline__ void spmm_short_columns(const int32_t (&c)[LMAX], con
     for (int j = 0; j < JT; ++j) tie(xv[0][j], r);
 #pragma unroll
     for (int j = 0; j < JT; ++j) {
-      T acc = Num<T>::zero();
+      T acc = yi(Yrow + (int64_t)(j0 + j) * ldy);
 #pragma unroll
       for (int u = 0; u < LMAX; ++u)
         if (FULL || u < len) acc = Num<T>::add(Num<T>::mul(a[u], xv[u][j]), acc);
@@ -1097,7 +1089,7 @@ __device__ __forceinline__ void spmm_short_columns(const int32_t (&c)[LMAX], con
   }
   for (; j0 < jend; ++j0) {  // last partial tile, one column at a time
     const T *xb = X + (int64_t)j0 * ldx;
-    T acc = Num<T>::zero();
+    T acc = yi(Yrow + (int64_t)j0 * ldy);
 #pragma unroll
     for (int u = 0; u < LMAX; ++u)
       if (FULL || u < len) acc = Num<T>::add(Num<T>::mul(a[u], ld_gather(xb + c[u], pol_x)), acc);
@@ -1117,7 +1109,7 @@ k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, int32_t stride32, u
              const int64_t *__restrict__ slice_ptr,
              const int32_t *__restrict__ rowlen, const int32_t *__restrict__ rowptr,
              const int32_t *__restrict__ colidx, const T *__restrict__ vals, const T *__restrict__ X,
-             int64_t ldx, T *__restrict__ Y, int64_t ldy, int32_t k) {
+             int64_t ldx, T *__restrict__ Y, int64_t ldy, int32_t k, const YInit<T> yi) {
   const int32_t rb = blockIdx.x / ngroups;
   const int32_t grp = blockIdx.x - rb * ngroups;
   int32_t row;
@@ -1157,9 +1149,9 @@ k_spmm_short(int32_t nrows, int32_t ngroups, int32_t jgroup, int32_t stride32, u
   const int32_t jbeg = grp * jgroup;
   const int32_t jend = min(k, jbeg + jgroup);
   if (full)
-    spmm_short_columns<T, JT, LMAX, true, PIPE>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x, zmask);
+    spmm_short_columns<T, JT, LMAX, true, PIPE>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x, zmask, yi);
   else
-    spmm_short_columns<T, JT, LMAX, false, false>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x, zmask);
+    spmm_short_columns<T, JT, LMAX, false, false>(c, a, len, X, ldx, Y + row, ldy, jbeg, jend, pol_x, zmask, yi);
 }
 
 // Longer rows (SELL plan, e.g. the 27-point stencil): a block owns blockDim.x consecutive rows and ALL
@@ -1176,7 +1168,7 @@ __global__ void __launch_bounds__(512)
 k_spmm_panel(int32_t row_begin, int32_t row_end, int32_t kcap, uint32_t zmask, const int64_t *__restrict__ slice_ptr,
              const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
              const T *__restrict__ vals, const T *__restrict__ X, int64_t ldx, T *__restrict__ Y,
-             int64_t ldy, int32_t k, const int32_t *__restrict__ order) {
+             int64_t ldy, int32_t k, const int32_t *__restrict__ order, const YInit<T> yi) {
   extern __shared__ __align__(16) unsigned char panel_smem[];
   const int32_t nt = blockDim.x, tid = threadIdx.x;
   T *s_a = reinterpret_cast<T *>(panel_smem) + tid;                                       // [kcap][nt]
@@ -1204,7 +1196,7 @@ k_spmm_panel(int32_t row_begin, int32_t row_end, int32_t kcap, uint32_t zmask, c
     const T *xb = X + (int64_t)j0 * ldx;
     T acc[JT];
 #pragma unroll
-    for (int j = 0; j < JT; ++j) acc[j] = Num<T>::zero();
+    for (int j = 0; j < JT; ++j) acc[j] = (j0 + j < k) ? yi(Yrow + (int64_t)(j0 + j) * ldy) : Num<T>::zero();
     int32_t e = 0;
     if (j0 + JT <= k) {  // full column tile: batches of KU staged entries, no predicates
       for (; e + KU <= nst; e += KU) {
@@ -1265,7 +1257,8 @@ template <class T, int JT>
 __global__ void __launch_bounds__(128)
 k_spmm_boundary(int32_t nrows, int32_t r0, int32_t r1, uint32_t zmask, const int64_t *__restrict__ slice_ptr,
                 const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
-                const T *__restrict__ vals, const DistXM<T> xa, T *__restrict__ Y, int64_t ldy, int32_t k) {
+                const T *__restrict__ vals, const DistXM<T> xa, T *__restrict__ Y, int64_t ldy, int32_t k,
+                const YInit<T> yi) {
   const int32_t nbl = (r0 + 127) >> 7;  // blocks below the interior
   int32_t row, limit;
   if ((int32_t)blockIdx.x < nbl) {
@@ -1284,15 +1277,22 @@ k_spmm_boundary(int32_t nrows, int32_t r0, int32_t r1, uint32_t zmask, const int
   for (int32_t j0 = 0; j0 < k; j0 += JT) {
     T acc[JT];
 #pragma unroll
-    for (int j = 0; j < JT; ++j) acc[j] = Num<T>::zero();
+    for (int j = 0; j < JT; ++j) acc[j] = (j0 + j < k) ? yi(Y + (int64_t)(j0 + j) * ldy + row) : Num<T>::zero();
     for (int32_t e = 0; e < len; ++e) {
       const int32_t c = __ldg(ci + (int64_t)e * SELL_C);
       const T a = __ldg(va + (int64_t)e * SELL_C);
       int64_t ld;
-      const T *xp = xa.col0(c, ld) + (int64_t)j0 * ld;
+      bool remote;
+      const T *xp = xa.col0(c, ld, remote);
+      xp += (int64_t)j0 * ld;
       T xv[JT];
+      if (remote) {
 #pragma unroll
-      for (int j = 0; j < JT; ++j) xv[j] = (j0 + j < k) ? ld_gather(xp + (int64_t)j * ld, pol_x) : Num<T>::zero();
+        for (int j = 0; j < JT; ++j) xv[j] = (j0 + j < k) ? ld_peer(xp + (int64_t)j * ld) : Num<T>::zero();
+      } else {
+#pragma unroll
+        for (int j = 0; j < JT; ++j) xv[j] = (j0 + j < k) ? ld_gather(xp + (int64_t)j * ld, pol_x) : Num<T>::zero();
+      }
       uint32_t r = 0;
 #pragma unroll
       for (int j = 0; j < JT; ++j) r |= probe(xv[j]);
@@ -1402,11 +1402,8 @@ static int spmv_run(slc_matrix *m, const XA &xa, T *y) {
           static const int groups_env = env_int("SLC_BAL_HOT_GROUPS", 0);
           const int HOT_GROUPS = groups_env > 0 ? std::min(groups_env, HotGroups<T>::value) : HotGroups<T>::value;
           const size_t smem = ((size_t)HOT_GROUPS * BAL_CHUNK + (size_t)bp.hot_k) * sizeof(T);
-          static size_t smem_set = 0;
-          if (smem > smem_set) {
-            SLC_CUDA(cudaFuncSetAttribute(k_spmv_bal_hot<T, ACC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            smem_set = smem;
-          }
+          static PerDevice<size_t> smem_set;
+          SLC_CUDA(ensure_dyn_smem(k_spmv_bal_hot<T, ACC>, smem_set, smem));
           const int per_sm = std::max<int>(1, (int)(((size_t)227 << 10) / (smem + 1024)));
           const int64_t grid = std::min<int64_t>(ceil_div(bp.nchunks, HOT_GROUPS), (int64_t)sm_count() * per_sm);
           k_spmv_bal_hot<T, ACC><<<(unsigned)grid, HOT_GROUPS * BAL_THREADS, smem, s>>>(
@@ -1463,6 +1460,7 @@ static int check_handle(const slc_matrix *m, const char *fn) {
 template <class T, bool ACC>
 static int spmv_dev_entry(slc_matrix *m, const double *x, double *y, const char *fn) {
   SLC_TRY(check_handle<T>(m, fn));
+  HandleLock lock(m);
   if ((m->ncols && !x) || (m->nrows && !y)) return fail(SLC_ERR_INVALID, "%s: null vector", fn);
   return spmv_dev<T, ACC>(m, (const T *)x, (T *)y);
 }
@@ -1556,6 +1554,7 @@ static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
 template <class T, bool ACC>
 static int spmv_host_entry(slc_matrix *m, const double *x, double *y, const char *fn) {
   SLC_TRY(check_handle<T>(m, fn));
+  HandleLock lock(m);
   if ((m->ncols && !x) || (m->nrows && !y)) return fail(SLC_ERR_INVALID, "%s: null vector", fn);
   bool done = false;
   SLC_TRY((spmv_host_pipelined<T, ACC>(m, (const T *)x, (T *)y, &done)));
@@ -1580,7 +1579,7 @@ static int spmv_host_entry(slc_matrix *m, const double *x, double *y, const char
 template <class T>
 static int dist_table_setup(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits,
                             const double *const *parts, const int64_t *lds, const char *fn, const DistTable **out) {
-  SLC_TRY(check_handle<T>(m, fn));
+  SLC_TRY(check_handle<T>(m, fn));  // callers hold the handle lock
   if (nparts < 1 || nparts > MAX_PARTS) return fail(SLC_ERR_INVALID, "%s: 1..%d partitions supported", fn, MAX_PARTS);
   if (self < 0 || self >= nparts || !splits || !parts) return fail(SLC_ERR_INVALID, "%s: bad partition argument", fn);
   if (splits[0] != 0 || splits[nparts] != m->ncols)
@@ -1601,19 +1600,25 @@ static int dist_table_setup(slc_matrix *m, int32_t nparts, int32_t self, const i
   }
   t.splits[nparts] = splits[nparts];
   t.nparts = nparts;
-  static_assert(sizeof(DistTable) <= sizeof(m->dist_table_host), "dist table cache too small");
+  static_assert(sizeof(DistTable) <= slc_matrix::DIST_TABLE_BYTES, "dist table cache too small");
   if (!m->dist_table) {
     DevBuf<char> buf;
-    SLC_TRY(buf.alloc(sizeof(DistTable)));
+    SLC_TRY(buf.alloc((size_t)slc_matrix::DIST_SLOTS * slc_matrix::DIST_TABLE_BYTES));
     m->dist_table = buf.take();
-    m->dist_table_valid = false;
+    for (bool &v : m->dist_slot_valid) v = false;
   }
-  if (!m->dist_table_valid || memcmp(m->dist_table_host, &t, sizeof t) != 0) {
-    memcpy(m->dist_table_host, &t, sizeof t);
-    SLC_CUDA(cudaMemcpyAsync(m->dist_table, m->dist_table_host, sizeof t, cudaMemcpyHostToDevice, cur_stream()));
-    m->dist_table_valid = true;
+  int slot = -1;
+  for (int i = 0; i < slc_matrix::DIST_SLOTS; ++i)
+    if (m->dist_slot_valid[i] && memcmp(m->dist_table_host[i], &t, sizeof t) == 0) slot = i;
+  if (slot < 0) {  // not cached: take the next slot round-robin (stream order protects a table still in use)
+    slot = m->dist_next;
+    m->dist_next = (m->dist_next + 1) % slc_matrix::DIST_SLOTS;
+    memcpy(m->dist_table_host[slot], &t, sizeof t);
+    SLC_CUDA(cudaMemcpyAsync((char *)m->dist_table + (size_t)slot * slc_matrix::DIST_TABLE_BYTES,
+                             m->dist_table_host[slot], sizeof t, cudaMemcpyHostToDevice, cur_stream()));
+    m->dist_slot_valid[slot] = true;
   }
-  *out = (const DistTable *)m->dist_table;
+  *out = (const DistTable *)((char *)m->dist_table + (size_t)slot * slc_matrix::DIST_TABLE_BYTES);
   return SLC_OK;
 }
 
@@ -1636,16 +1641,35 @@ static int dist_interior(slc_matrix *m, int32_t lo, int32_t hi, int32_t *r0, int
     sp.interior_s1 = best1;
     sp.interior_lo = lo;
     sp.interior_hi = hi;
+    // column ranges the rows below / above the interior reach: which peers each side has to wait for
+    for (int side = 0; side < 2; ++side) {
+      int32_t cmin = 0x7fffffff, cmax = -1;
+      const int32_t a = side == 0 ? 0 : best1, b = side == 0 ? best0 : sp.nslices;
+      for (int32_t sl = a; sl < b; ++sl)
+        if (sp.h_cmax[sl] >= 0) { cmin = std::min(cmin, sp.h_cmin[sl]); cmax = std::max(cmax, sp.h_cmax[sl]); }
+      sp.side_cmin[side] = cmin;
+      sp.side_cmax[side] = cmax;
+    }
   }
   *r0 = sp.interior_s0 * SELL_C;
   *r1 = std::min(m->nrows, sp.interior_s1 * SELL_C);
   return SLC_OK;
 }
 
+// parts other than `self` whose slice overlaps the column range [cmin, cmax]
+static uint32_t parts_overlapping(int32_t nparts, int32_t self, const int32_t *splits, int32_t cmin, int32_t cmax) {
+  uint32_t mask = 0;
+  if (cmax < cmin) return 0;
+  for (int p = 0; p < nparts; ++p)
+    if (p != self && splits[p + 1] > splits[p] && splits[p] <= cmax && splits[p + 1] > cmin) mask |= 1u << p;
+  return mask;
+}
+
 // y_local <- A_local x, x partitioned by column ranges over the GPUs of one box (see DistX)
 template <class T>
 static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits,
                            const double *const *x_parts, double *y, slc_peer_group *sync, const char *fn) {
+  HandleLock lock(m);
   const DistTable *tbl = nullptr;
   SLC_TRY((dist_table_setup<T>(m, nparts, self, splits, x_parts, nullptr, fn, &tbl)));
   if (m->nrows && !y) return fail(SLC_ERR_INVALID, "%s: bad partition argument", fn);
@@ -1655,6 +1679,7 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   xa.self_hi = splits[self + 1];
   xa.tbl = tbl;
   if (m->nnz > 0) SLC_TRY(ensure_plan<T>(m));
+  if (sync) SLC_TRY(peer_check(sync, fn));
   if (m->nrows == 0 || m->nnz == 0 || m->spmv_active != SPMV_SELL) {
     if (sync) SLC_TRY(slc_peer_barrier(sync));  // separate barrier kernel, then the generic kernels
     return spmv_run<T, false, DistX<T>>(m, xa, (T *)y);
@@ -1665,17 +1690,33 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   SellPlan &sp = m->sell;
   int32_t r0 = 0, r1 = 0;
   SLC_TRY(dist_interior(m, xa.self_lo, xa.self_hi, &r0, &r1));
-  // one launch: [boundary blocks | interior blocks], barrier fused in (see k_spmv_sell_dist)
+  // one launch: [boundary blocks | interior blocks], signal and waits fused in (see k_spmv_sell_dist)
   PeerSync ps;
   memset(&ps, 0, sizeof ps);
-  if (sync) SLC_TRY(peer_sync_args(sync, &ps.flags, &ps.timeout_flag, &ps.epoch, &ps.nparts, &ps.self));
-  const int64_t nblocks = ceil_div(r0, 256) + ceil_div(m->nrows - r1, 256) + ceil_div(r1 - r0, 256);
+  uint32_t wait_lo = 0, wait_hi = 0;
+  const int64_t nboundary = ceil_div(r0, 256) + ceil_div(m->nrows - r1, 256);
+  if (sync && nparts > 1) {
+    ps = peer_sync_of(sync);
+    // each side waits for the peers its rows read, plus the ranks that only READ this rank's slice
+    // (deps without a need): their signal of this epoch says they are done with the previous one,
+    // which is what lets the caller rewrite the other operand buffer (see slc.h, "double buffering")
+    const uint32_t need_lo = parts_overlapping(nparts, self, splits, sp.side_cmin[0], sp.side_cmax[0]);
+    const uint32_t need_hi = parts_overlapping(nparts, self, splits, sp.side_cmin[1], sp.side_cmax[1]);
+    const uint32_t extra = sync->deps_mask & ~(need_lo | need_hi);
+    wait_lo = need_lo | extra;
+    wait_hi = need_hi | extra;
+    if (nboundary == 0 && extra) {  // nothing here reads a peer, but peers read this rank: plain barrier
+      SLC_TRY(slc_peer_barrier(sync));
+      ps.flags = nullptr;
+    }
+  }
+  const int64_t nblocks = nboundary + ceil_div(r1 - r0, 256);
   cudaStream_t s = cur_stream();
   static const int u_env = env_int("SLC_SELL_U", 0);
   const int u = u_env ? u_env : ((m->max_rowlen <= 4 || sp.kbase) ? 4 : 8);
 #define SLC_DIST_CASE(UU, KB_)                                                                                  \
   k_spmv_sell_dist<T, UU, KB_><<<(unsigned)nblocks, 256, 0, s>>>(m->nrows, r0, r1, sp.slice_ptr, sp.rowlen, sp.colidx, \
-                                                                 (const T *)sp.vals, xa, (T *)y, ps, sp.kbase)
+                                                                 (const T *)sp.vals, xa, (T *)y, ps, wait_lo, wait_hi, sp.kbase)
   if (sp.kbase) {
     if (u <= 4) SLC_DIST_CASE(4, true);
     else SLC_DIST_CASE(8, true);
@@ -1685,6 +1726,31 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   }
 #undef SLC_DIST_CASE
   SLC_LAUNCHED();
+  return SLC_OK;
+}
+
+// Which peers the rows of this block read operand entries from (bit p = part p), for the caller that
+// wants neighbour-only waits: every rank computes its mask, the masks are exchanged, and rank r's
+// dependency set is  need(r) | {q : r in need(q)}  (slc_peer_group_set_deps).
+template <class T>
+static int dist_needs_entry(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits, uint32_t *mask,
+                            const char *fn) {
+  SLC_TRY(check_handle<T>(m, fn));
+  if (!mask || !splits || nparts < 1 || nparts > MAX_PARTS || self < 0 || self >= nparts)
+    return fail(SLC_ERR_INVALID, "%s: bad partition argument", fn);
+  *mask = 0;
+  if (m->nnz == 0 || m->nrows == 0) return SLC_OK;
+  SLC_TRY(ensure_plan<T>(m));
+  if (m->spmv_active != SPMV_SELL) {  // irregular rows: the whole operand is gathered
+    for (int p = 0; p < nparts; ++p)
+      if (p != self && splits[p + 1] > splits[p]) *mask |= 1u << p;
+    return SLC_OK;
+  }
+  int32_t r0 = 0, r1 = 0;
+  SLC_TRY(dist_interior(m, splits[self], splits[self + 1], &r0, &r1));
+  const SellPlan &sp = m->sell;
+  *mask = parts_overlapping(nparts, self, splits, sp.side_cmin[0], sp.side_cmax[0]) |
+          parts_overlapping(nparts, self, splits, sp.side_cmin[1], sp.side_cmax[1]);
   return SLC_OK;
 }
 
@@ -1723,9 +1789,11 @@ template <class T>
 static int spmv_allgather_entry(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits,
                                 const double *const *x_parts, double *x_full, double *y, slc_peer_group *sync,
                                 const char *fn) {
+  HandleLock lock(m);
   const DistTable *tbl = nullptr;
   SLC_TRY((dist_table_setup<T>(m, nparts, self, splits, x_parts, nullptr, fn, &tbl)));
   if ((m->ncols && !x_full) || (m->nrows && !y)) return fail(SLC_ERR_INVALID, "%s: null vector", fn);
+  if (sync) SLC_TRY(peer_check(sync, fn));
   static const int diag_env = env_int("SLC_AG_DIAG", 0);  // timing diagnosis: 1 = no pull, 2 = no product, 3 = no barrier
   if (sync && diag_env != 3) SLC_TRY(slc_peer_barrier(sync));
   if (m->ncols && diag_env != 1) {
@@ -1810,14 +1878,11 @@ static int panel_tiling(slc_matrix *m, int32_t s_begin, int32_t s_end, int32_t s
 
 template <class T, int JT, int KU>
 static int launch_panel_inst(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, int threads,
-                             int32_t kcap, int32_t row_begin, int32_t row_end) {
+                             int32_t kcap, int32_t row_begin, int32_t row_end, const YInit<T> &yi) {
   SellPlan &sp = m->sell;
   const size_t smem = (size_t)kcap * threads * (sizeof(T) + sizeof(int32_t));
-  static size_t smem_set = 0;  // per instantiation
-  if (smem > smem_set) {
-    SLC_CUDA(cudaFuncSetAttribute(k_spmm_panel<T, JT, KU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
-  }
+  static PerDevice<size_t> smem_set;  // per instantiation, per device
+  SLC_CUDA(ensure_dyn_smem(k_spmm_panel<T, JT, KU>, smem_set, smem));
   if (row_end <= row_begin) return SLC_OK;
   int64_t nb = ceil_div(row_end - row_begin, threads);
   const int32_t *order = nullptr;
@@ -1836,13 +1901,13 @@ static int launch_panel_inst(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64
     nb = sp.panel_blocks;
   }
   k_spmm_panel<T, JT, KU><<<(unsigned)nb, threads, smem, cur_stream()>>>(
-      row_begin, row_end, kcap, 0u, sp.slice_ptr, sp.rowlen, sp.colidx, (const T *)sp.vals, X, ldx, Y, ldy, k, order);
+      row_begin, row_end, kcap, 0u, sp.slice_ptr, sp.rowlen, sp.colidx, (const T *)sp.vals, X, ldx, Y, ldy, k, order, yi);
   SLC_LAUNCHED();
   return SLC_OK;
 }
 
 template <class T>
-static int launch_panel(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k,
+static int launch_panel(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, const YInit<T> &yi,
                         int32_t row_begin = 0, int32_t row_end = -1) {
   if (row_end < 0) row_end = m->nrows;
   static const int threads_env = env_int("SLC_PANEL_THREADS", 0);
@@ -1861,7 +1926,7 @@ static int launch_panel(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ld
   if (m->max_rowlen < 3) ku = 2;
   const bool wide = jt_env ? jt_env >= 8 : sizeof(T) == 8;  // 8 columns per tile for Double, 4 for Complex
 #define SLC_PANEL(JT_, KU_) \
-  return launch_panel_inst<T, JT_, KU_>(m, X, ldx, Y, ldy, k, threads, kcap, row_begin, row_end)
+  return launch_panel_inst<T, JT_, KU_>(m, X, ldx, Y, ldy, k, threads, kcap, row_begin, row_end, yi)
   if (wide) {
     if (ku <= 2) SLC_PANEL(8, 2);
     if (ku == 3) SLC_PANEL(8, 3);
@@ -1874,18 +1939,34 @@ static int launch_panel(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ld
 #undef SLC_PANEL
 }
 
+// Y[:, 0:k] <- beta Y (an operand with no stored entry: the product term vanishes)
 template <class T>
-static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k) {
+__global__ void k_scale_block(int32_t nrows, int32_t k, T *__restrict__ Y, int64_t ldy, T beta) {
+  const int64_t n = (int64_t)nrows * k;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    T *p = Y + (i / nrows) * ldy + (i % nrows);
+    *p = Num<T>::mul(beta, *p);
+  }
+}
+
+template <class T>
+static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, const YInit<T> &yi) {
   if (k == 0 || m->nrows == 0) return SLC_OK;
   cudaStream_t s = cur_stream();
   if (m->nnz == 0) {
-    SLC_CUDA(cudaMemset2DAsync(Y, (size_t)ldy * sizeof(T), 0, (size_t)m->nrows * sizeof(T), (size_t)k, s));
+    if (yi.mode == 0)
+      SLC_CUDA(cudaMemset2DAsync(Y, (size_t)ldy * sizeof(T), 0, (size_t)m->nrows * sizeof(T), (size_t)k, s));
+    else if (yi.mode == 2) {
+      k_scale_block<T><<<(unsigned)std::min<int64_t>(ceil_div((int64_t)m->nrows * k, 256), 148 * 16), 256, 0, s>>>(
+          m->nrows, k, Y, ldy, yi.beta);
+      SLC_LAUNCHED();
+    }
     return SLC_OK;
   }
   SLC_TRY(ensure_plan<T>(m));
   if (m->max_rowlen >= 1 && m->max_rowlen <= 8) {  // short rows: registers hold the row
     bool done = false;  // banded: X windows staged by TMA (slc_spmm_window.cu); else per-thread gathers
-    SLC_TRY(spmm_window_try<T>(m, X, ldx, Y, ldy, k, &done));
+    SLC_TRY(spmm_window_try<T>(m, X, ldx, Y, ldy, k, yi, &done));
     if (done) return SLC_OK;
     static const int jg_env = env_int("SLC_SPMM_JG", 0);
     static const int stride_env = env_int("SLC_SPMM_STRIDE", -1);
@@ -1909,7 +1990,7 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
 #define SLC_SHORT(L_, SELL_, PIPE_)                                                                  \
   k_spmm_short<T, JTS, L_, SELL_, (PIPE_) && (L_ * JTS * sizeof(T) / 4 <= 48)><<<(unsigned)nb, threads, 0, s>>>( \
       m->nrows, ngroups, jgroup, stride32, 0u, sp.slice_ptr, sp.rowlen, m->rowptr,                    \
-      SELL_ ? sp.colidx : m->colidx, SELL_ ? (const T *)sp.vals : (const T *)m->rvals, X, ldx, Y, ldy, k)
+      SELL_ ? sp.colidx : m->colidx, SELL_ ? (const T *)sp.vals : (const T *)m->rvals, X, ldx, Y, ldy, k, yi)
 #define SLC_SHORT_L(L_)                                                                              \
   case L_:                                                                                           \
     if (pipe) SLC_SHORT(L_, true, true);                                                             \
@@ -1932,7 +2013,7 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
     return SLC_OK;
   }
   static const int panel_env = env_int("SLC_SPMM_PANEL", 1);
-  if (m->spmv_active == SPMV_SELL && panel_env) return launch_panel<T>(m, X, ldx, Y, ldy, k);
+  if (m->spmv_active == SPMV_SELL && panel_env) return launch_panel<T>(m, X, ldx, Y, ldy, k, yi);
   constexpr int JT = sizeof(T) == 16 ? 4 : 8;
   const int32_t ntiles = (int32_t)ceil_div(k, JT);
   const int64_t nblocks = ceil_div(m->nrows, 128) * ntiles;
@@ -1941,11 +2022,11 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
     const SellPlan &sp = m->sell;
     k_spmm_rows<T, JT, true><<<(unsigned)nblocks, 128, 0, s>>>(m->nrows, ntiles, sp.slice_ptr, sp.rowlen,
                                                                 nullptr, sp.colidx, (const T *)sp.vals, X,
-                                                                ldx, Y, ldy, k);
+                                                                ldx, Y, ldy, k, yi);
   } else {
     k_spmm_rows<T, JT, false><<<(unsigned)nblocks, 128, 0, s>>>(m->nrows, ntiles, nullptr, nullptr,
                                                                  m->rowptr, m->colidx,
-                                                                 (const T *)m->rvals, X, ldx, Y, ldy, k);
+                                                                 (const T *)m->rvals, X, ldx, Y, ldy, k, yi);
   }
   SLC_LAUNCHED();
   return SLC_OK;
@@ -1958,8 +2039,10 @@ template <class T>
 static int spmm_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits,
                            const double *const *X_parts, const int64_t *ldx_parts, double *Y, int64_t ldy,
                            int32_t k, slc_peer_group *sync, const char *fn) {
+  HandleLock lock(m);
   const DistTable *tbl = nullptr;
   if (!ldx_parts) return fail(SLC_ERR_INVALID, "%s: null leading dimensions", fn);
+  if (sync) SLC_TRY(peer_check(sync, fn));
   SLC_TRY((dist_table_setup<T>(m, nparts, self, splits, X_parts, ldx_parts, fn, &tbl)));
   if (k < 0) return fail(SLC_ERR_INVALID, "%s: negative column count", fn);
   if (k > 0 && m->nrows && !Y) return fail(SLC_ERR_INVALID, "%s: null block", fn);
@@ -1991,14 +2074,14 @@ static int spmm_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   SLC_TRY(dist_interior(m, xa.self_lo, xa.self_hi, &r0, &r1));
   if (sync) SLC_TRY(slc_peer_signal(sync));  // "my rows of X are written" (stream order)
   // interior rows: columns are global, so shift the local block's base by the first owned row
-  SLC_TRY(launch_panel<T>(m, xa.self_X - xa.self_lo, xa.self_ld, (T *)Y, ldy, k, r0, r1));
+  SLC_TRY(launch_panel<T>(m, xa.self_X - xa.self_lo, xa.self_ld, (T *)Y, ldy, k, yinit_zero<T>(), r0, r1));
   if (sync) SLC_TRY(slc_peer_wait(sync));
   const int64_t nb = ceil_div(r0, 128) + ceil_div(m->nrows - r1, 128);
   if (nb > 0) {
     const SellPlan &sp = m->sell;
     constexpr int JT = sizeof(T) == 16 ? 4 : 8;
     k_spmm_boundary<T, JT><<<(unsigned)nb, 128, 0, s>>>(m->nrows, r0, r1, 0u, sp.slice_ptr, sp.rowlen, sp.colidx,
-                                                        (const T *)sp.vals, xa, (T *)Y, ldy, k);
+                                                        (const T *)sp.vals, xa, (T *)Y, ldy, k, yinit_zero<T>());
     SLC_LAUNCHED();
   }
   return SLC_OK;
@@ -2019,18 +2102,37 @@ static int spmm_check(slc_matrix *m, const double *X, int64_t ldx, double *Y, in
   return SLC_OK;
 }
 
+// beta of the C ABI -> start value of the accumulators: NULL or 0 -> mulM (Y is not read), 1 -> the
+// reference's axpy_ into a block the caller filled (exact: y itself starts the sum), else beta * y
+static YInit<double> yinit_of(const double *beta, double) {
+  YInit<double> yi = yinit_zero<double>();
+  if (beta && beta[0] != 0.0) { yi.mode = beta[0] == 1.0 ? 1 : 2; yi.beta = beta[0]; }
+  return yi;
+}
+static YInit<double2> yinit_of(const double *beta, double2) {
+  YInit<double2> yi = yinit_zero<double2>();
+  if (beta && (beta[0] != 0.0 || beta[1] != 0.0)) {
+    yi.mode = (beta[0] == 1.0 && beta[1] == 0.0) ? 1 : 2;
+    yi.beta = double2{beta[0], beta[1]};
+  }
+  return yi;
+}
+
 template <class T>
 static int spmm_dev_entry(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
-                          const char *fn) {
+                          const double *beta, const char *fn) {
   SLC_TRY(spmm_check<T>(m, X, ldx, Y, ldy, k, fn));
-  return spmm_dev<T>(m, (const T *)X, ldx, (T *)Y, ldy, k);
+  HandleLock lock(m);
+  return spmm_dev<T>(m, (const T *)X, ldx, (T *)Y, ldy, k, yinit_of(beta, T()));
 }
 
 template <class T>
 static int spmm_host_entry(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
-                           const char *fn) {
+                           const double *beta, const char *fn) {
   SLC_TRY(spmm_check<T>(m, X, ldx, Y, ldy, k, fn));
   if (k == 0) return SLC_OK;
+  HandleLock lock(m);
+  const YInit<T> yi = yinit_of(beta, T());
   cudaStream_t s = cur_stream();
   // Device blocks are packed (leading dimension = ncols / nrows); the strided host blocks are
   // moved with 2-D copies so only the active columns cross PCIe.
@@ -2067,9 +2169,12 @@ static int spmm_host_entry(slc_matrix *m, const double *X, int64_t ldx, double *
       cudaEvent_t ev_in = m->pipe_events[g], ev_k = m->pipe_events[PIPE_MAX_CHUNKS + g];
       SLC_CUDA(cudaMemcpy2DAsync(dXg, (size_t)m->ncols * sizeof(T), Xg, (size_t)ldx * sizeof(T),
                                  (size_t)m->ncols * sizeof(T), (size_t)kk, cudaMemcpyHostToDevice, m->pipe_in));
+      if (yi.mode != 0)
+        SLC_CUDA(cudaMemcpy2DAsync(dYg, (size_t)m->nrows * sizeof(T), Yg, (size_t)ldy * sizeof(T),
+                                   (size_t)m->nrows * sizeof(T), (size_t)kk, cudaMemcpyHostToDevice, m->pipe_in));
       SLC_CUDA(cudaEventRecord(ev_in, m->pipe_in));
       SLC_CUDA(cudaStreamWaitEvent(s, ev_in, 0));
-      rc = spmm_dev<T>(m, dXg, m->ncols, dYg, m->nrows, kk);
+      rc = spmm_dev<T>(m, dXg, m->ncols, dYg, m->nrows, kk, yi);
       if (rc != SLC_OK) break;
       SLC_CUDA(cudaEventRecord(ev_k, s));
       SLC_CUDA(cudaStreamWaitEvent(m->pipe_out, ev_k, 0));
@@ -2084,7 +2189,10 @@ static int spmm_host_entry(slc_matrix *m, const double *X, int64_t ldx, double *
   if (m->ncols)
     SLC_CUDA(cudaMemcpy2DAsync(dX.p, (size_t)m->ncols * sizeof(T), X, (size_t)ldx * sizeof(T),
                                (size_t)m->ncols * sizeof(T), (size_t)k, cudaMemcpyHostToDevice, s));
-  SLC_TRY(spmm_dev<T>(m, dX.p, m->ncols, dY.p, m->nrows, k));
+  if (yi.mode != 0 && m->nrows)
+    SLC_CUDA(cudaMemcpy2DAsync(dY.p, (size_t)m->nrows * sizeof(T), Y, (size_t)ldy * sizeof(T),
+                               (size_t)m->nrows * sizeof(T), (size_t)k, cudaMemcpyHostToDevice, s));
+  SLC_TRY(spmm_dev<T>(m, dX.p, m->ncols, dY.p, m->nrows, k, yi));
   if (m->nrows)
     SLC_CUDA(cudaMemcpy2DAsync(Y, (size_t)ldy * sizeof(T), dY.p, (size_t)m->nrows * sizeof(T),
                                (size_t)m->nrows * sizeof(T), (size_t)k, cudaMemcpyDeviceToHost, s));
@@ -2100,6 +2208,7 @@ extern "C" {
 
 int slc_prepare(slc_matrix *m) {
   if (!m) return fail(SLC_ERR_INVALID, "slc_prepare: null handle");
+  HandleLock lock(m);
   if (m->nnz == 0) return SLC_OK;
   return m->elem == ELEM_D ? ensure_plan<double>(m) : ensure_plan<double2>(m);
 }
@@ -2179,17 +2288,27 @@ int slc_z_mulm_dist_dev(slc_matrix *a, int32_t nparts, int32_t self, const int32
                         slc_peer_group *sync) {
   return spmm_dist_entry<double2>(a, nparts, self, splits, X_parts, ldx_parts, Y, ldy, k, sync, "mulM");
 }
-int slc_d_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k) {
-  return spmm_host_entry<double>(a, X, ldx, Y, ldy, k, "mulM");
+int slc_d_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k, const double *beta) {
+  return spmm_host_entry<double>(a, X, ldx, Y, ldy, k, beta, "mulM");
 }
-int slc_z_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k) {
-  return spmm_host_entry<double2>(a, X, ldx, Y, ldy, k, "mulM");
+int slc_z_mulm(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k, const double *beta) {
+  return spmm_host_entry<double2>(a, X, ldx, Y, ldy, k, beta, "mulM");
 }
-int slc_d_mulm_dev(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k) {
-  return spmm_dev_entry<double>(a, X, ldx, Y, ldy, k, "mulM");
+int slc_d_mulm_dev(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
+                   const double *beta) {
+  return spmm_dev_entry<double>(a, X, ldx, Y, ldy, k, beta, "mulM");
 }
-int slc_z_mulm_dev(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k) {
-  return spmm_dev_entry<double2>(a, X, ldx, Y, ldy, k, "mulM");
+int slc_z_mulm_dev(slc_matrix *a, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
+                   const double *beta) {
+  return spmm_dev_entry<double2>(a, X, ldx, Y, ldy, k, beta, "mulM");
+}
+int slc_d_dist_needs(slc_matrix *a, int32_t nparts, int32_t self, const int32_t *splits, uint32_t *mask) {
+  HandleLock lock(a);
+  return dist_needs_entry<double>(a, nparts, self, splits, mask, "slc_d_dist_needs");
+}
+int slc_z_dist_needs(slc_matrix *a, int32_t nparts, int32_t self, const int32_t *splits, uint32_t *mask) {
+  HandleLock lock(a);
+  return dist_needs_entry<double2>(a, nparts, self, splits, mask, "slc_z_dist_needs");
 }
 
 }  // extern "C"

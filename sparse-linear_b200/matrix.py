@@ -344,16 +344,27 @@ def mulV(m, x):
     return y
 
 
-def mulM(m, X):
+def mulM(m, X, Y0=None, beta=None):
     """A X for a dense (ncols, k) block (mulM, Sparse.hs:473-498; FEAST's multiplyWork,
-    feast/src/Numeric/LinearAlgebra/Feast.hs:203-208).  Returns an (nrows, k) Fortran-order array."""
+    feast/src/Numeric/LinearAlgebra/Feast.hs:203-208).  Returns an (nrows, k) Fortran-order array.
+    With Y0 (and beta, default 1) the result is A X + beta Y0: beta = 1 is the reference's axpy_ into a
+    block the caller filled (Sparse.hs:485-488)."""
     X = np.asarray(X)
     if X.ndim != 2 or X.shape[0] != m.ncols:
         raise SparseLinearError("mulM: inner dimension mismatch")
     Xf = np.asfortranarray(X, dtype=m.dtype)
     k = Xf.shape[1]
-    Y = np.empty((m.nrows, k), dtype=m.dtype, order="F")
-    _check(_fn(m._p, "mulm")(m.device().handle, _ptr(Xf), max(m.ncols, 1), _ptr(Y), max(m.nrows, 1), k))
+    bptr = None
+    if Y0 is None:
+        Y = np.empty((m.nrows, k), dtype=m.dtype, order="F")
+    else:
+        Y0 = np.asarray(Y0)
+        if Y0.shape != (m.nrows, k):
+            raise SparseLinearError("axpy_: row dimension %d does not match result dimension %d" % (m.nrows, Y0.shape[0]))
+        Y = np.array(Y0, dtype=m.dtype, order="F", copy=True)
+        b = np.array([1 if beta is None else beta], dtype=m.dtype)
+        bptr = _ptr(b)
+    _check(_fn(m._p, "mulm")(m.device().handle, _ptr(Xf), max(m.ncols, 1), _ptr(Y), max(m.nrows, 1), k, bptr))
     return Y
 
 
@@ -363,9 +374,13 @@ def mulV_dev(m, x_ptr, y_ptr, accumulate=False):
                                                               C.c_void_p(y_ptr)))
 
 
-def mulM_dev(m, X_ptr, ldx, Y_ptr, ldy, k):
+def mulM_dev(m, X_ptr, ldx, Y_ptr, ldy, k, beta=None):
+    bptr = None
+    if beta is not None:
+        b = np.array([beta], dtype=m.dtype)
+        bptr = _ptr(b)
     _check(_fn(m._p, "mulm_dev")(m.device().handle, C.c_void_p(X_ptr), int(ldx), C.c_void_p(Y_ptr), int(ldy),
-                                 int(k)))
+                                 int(k), bptr))
 
 
 def _same(a, b, fn):

@@ -9,9 +9,7 @@ Host-side pieces (partitioning, row blocks, handle exchange) are plain numpy / t
 are covered by world_size-2 gloo tests on the CPU (tests/test_sharded_gloo.py).
 """
 import ctypes as C
-import json
 import os
-import time
 
 import numpy as np
 
@@ -206,13 +204,141 @@ def sharded_compress(nrows, rows, cols, vals, col_splits, rank, dist=None, group
     return compress_combine(nrows, width, exchange_pieces(pieces, dist, group), local_compress)
 
 
+# ---- the same two operations with every entry staying on the GPUs -----------------------------------------
+# Local kernels (slc_*_transpose, slc_*_coo_bucket_dev, slc_*_compress_dev, slc_*_vstack_dev), pieces cut by
+# slicing the handle's device arrays, ONE all-to-all-v of raw device buffers (NCCL all_to_all_single with
+# split sizes; sizes first).  torch is plumbing here: views of device memory and the collective.
+
+class _DevArray:
+    """A raw device pointer as something torch.as_tensor can wrap without copying."""
+
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+def _view(ptr, n, typestr):
+    import torch
+    if n == 0 or not ptr:
+        return torch.empty(0, dtype={"<i4": torch.int32, "<f8": torch.float64}[typestr], device="cuda")
+    return torch.as_tensor(_DevArray(ptr, n, typestr), device="cuda")
+
+
+def device_arrays(m):
+    """(colptr, rowidx, vals) of a Matrix's device handle as torch tensors viewing the handle's memory
+    (Complex Double values come back as 2 float64 per entry).  The handle must outlive the views."""
+    cp, ri, va = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    dm = m.device()
+    _check(_capi.lib().slc_device_arrays(dm.handle, C.byref(cp), C.byref(ri), C.byref(va)))
+    nr, nc, nnz = dm.dims()
+    w = 2 if m._p == "z" else 1
+    return _view(cp.value, nc + 1, "<i4"), _view(ri.value, nnz, "<i4"), _view(va.value, nnz * w, "<f8")
+
+
+def _all_to_all_v(send, send_counts, dist, group, width=1):
+    """send: 1-D device tensor laid out bucket after bucket; send_counts[p] elements (x width) go to rank p.
+    Returns (received tensor, recv_counts)."""
+    import torch
+    world = len(send_counts)
+    if dist is None or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return send, list(send_counts)
+    sc = torch.tensor(send_counts, dtype=torch.int64, device="cuda")
+    rc = torch.empty(world, dtype=torch.int64, device="cuda")
+    dist.all_to_all_single(rc, sc, group=group)
+    recv_counts = [int(v) for v in rc.tolist()]
+    out = torch.empty(sum(recv_counts) * width, dtype=send.dtype, device="cuda")
+    dist.all_to_all_single(out, send, output_split_sizes=[c * width for c in recv_counts],
+                           input_split_sizes=[c * width for c in send_counts], group=group)
+    return out, recv_counts
+
+
+def vstack_device(p, block_rows, ncols, ptrs, idxs, vals):
+    """slc_*_vstack_dev over lists of device tensors (one CSC block each, top to bottom)."""
+    n = len(block_rows)
+    br = np.ascontiguousarray(block_rows, dtype=np.int32)
+    pp = (C.c_void_p * n)(*[t.data_ptr() for t in ptrs])
+    ii = (C.c_void_p * n)(*[t.data_ptr() if t.numel() else None for t in idxs])
+    vv = (C.c_void_p * n)(*[t.data_ptr() if t.numel() else None for t in vals])
+    h = C.c_void_p()
+    _check(getattr(_capi.lib(), "slc_%s_vstack_dev" % p)(n, br.ctypes.data_as(C.c_void_p), int(ncols), C.cast(pp, C.c_void_p),
+                                                        C.cast(ii, C.c_void_p), C.cast(vv, C.c_void_p), C.byref(h)))
+    return Matrix._from_device(h)
+
+
+def sharded_transpose_device(local, row_splits, dist=None, group=None, col_splits=None):
+    """Transpose of a matrix held as column blocks (this rank: `local` = A[:, c0:c1] as a Matrix), entries
+    never leaving the GPUs.  Returns this rank's column block of A^T, ncols(A) x (r1-r0), as a Matrix.
+    Stable (Sparse.hs:301-329): the pieces are stacked in rank order = A's column order."""
+    import torch
+    from .matrix import transpose
+    world = len(row_splits) - 1
+    rank = dist.get_rank(group) if (dist is not None and dist.is_initialized() and world > 1) else 0
+    if col_splits is None:
+        col_splits = row_splits
+    w = 2 if local._p == "z" else 1
+    lt = transpose(local)                                   # (c1-c0) x nrows: column r = row r of the block
+    cp, ri, va = device_arrays(lt)
+    cuts = torch.as_tensor(np.asarray(row_splits, dtype=np.int64), device="cuda")
+    bounds = [int(v) for v in cp[cuts].tolist()]            # world+1 pointer values: the only D2H of the step
+    send_counts = [bounds[q + 1] - bounds[q] for q in range(world)]
+    colcnt = cp[1:] - cp[:-1]                               # entries per column of local^T, laid out piece after piece
+    widths = [int(row_splits[q + 1] - row_splits[q]) for q in range(world)]
+    np_cols = widths[rank]
+    if world == 1:
+        rcnt, ridx, rval, recv_counts = colcnt, ri, va, send_counts
+    else:
+        rcnt = torch.empty(np_cols * world, dtype=torch.int32, device="cuda")
+        dist.all_to_all_single(rcnt, colcnt.contiguous(), output_split_sizes=[np_cols] * world, input_split_sizes=widths, group=group)
+        ridx, recv_counts = _all_to_all_v(ri, send_counts, dist, group)
+        rval, _ = _all_to_all_v(va, send_counts, dist, group, width=w)
+    # per-piece pointers: exclusive scan of the per-column counts of each piece
+    ptr = torch.zeros((world, np_cols + 1), dtype=torch.int32, device="cuda")
+    ptr[:, 1:] = torch.cumsum(rcnt.view(world, np_cols), dim=1)
+    offs = np.concatenate([[0], np.cumsum(recv_counts)]).astype(np.int64)
+    out = vstack_device(local._p, [int(col_splits[q + 1] - col_splits[q]) for q in range(world)], np_cols,
+                        [ptr[q] for q in range(world)], [ridx[offs[q]:offs[q + 1]] for q in range(world)],
+                        [rval[offs[q] * w:offs[q + 1] * w] for q in range(world)])
+    del lt
+    return out
+
+
+def sharded_compress_device(nrows, rows_dev, cols_dev, vals_dev, col_splits, rank, dist=None, group=None, complex_values=False):
+    """compress (Sparse.hs:184-255) of triplets spread over the ranks and resident in HBM (torch int32 /
+    int32 / float64 tensors; complex values as 2 float64 per entry): returns this rank's column block
+    A[:, c0:c1] as a Matrix.  Bucket by owner on the device (input order kept), one all-to-all-v of the
+    three arrays, local device assembly (duplicates summed in (source rank, input position) order)."""
+    import torch
+    from .matrix import compress_dev
+    world = len(col_splits) - 1
+    p = "z" if complex_values else "d"
+    w = 2 if complex_values else 1
+    n = int(rows_dev.numel())
+    cs = np.ascontiguousarray(col_splits, dtype=np.int32)
+    orow, ocol, oval = torch.empty_like(rows_dev), torch.empty_like(cols_dev), torch.empty_like(vals_dev)
+    counts = (C.c_int64 * world)()
+    _check(getattr(_capi.lib(), "slc_%s_coo_bucket_dev" % p)(
+        n, C.c_void_p(rows_dev.data_ptr()), C.c_void_p(cols_dev.data_ptr()), C.c_void_p(vals_dev.data_ptr()), world,
+        cs.ctypes.data_as(C.c_void_p), C.c_void_p(orow.data_ptr()), C.c_void_p(ocol.data_ptr()), C.c_void_p(oval.data_ptr()), counts))
+    send_counts = [int(c) for c in counts]
+    rrow, recv_counts = _all_to_all_v(orow, send_counts, dist, group)
+    rcol, _ = _all_to_all_v(ocol, send_counts, dist, group)
+    rval, _ = _all_to_all_v(oval, send_counts, dist, group, width=w)
+    width = int(cs[rank + 1] - cs[rank])
+    total = sum(recv_counts)
+    return compress_dev(nrows, width, total, rrow.data_ptr() if total else 0, rcol.data_ptr() if total else 0,
+                        rval.data_ptr() if total else 0, np.complex128 if complex_values else np.float64)
+
+
 # ---- device side --------------------------------------------------------------------------------------
 
 class ShardedSpMV:
-    """y_local = A[r0:r1, :] x with x sliced by `splits` over the ranks.
+    """y_local = A[r0:r1, :] x with x sliced by `splits` over the ranks (one process per GPU).
 
     local: Matrix of shape (r1-r0) x ncols held by this rank.  Each rank owns x[splits[r]:splits[r+1]]
-    in a cudaMalloc'ed buffer that every other rank maps through CUDA IPC.
+    in TWO cudaMalloc'ed buffers that every other rank maps through CUDA IPC; products alternate
+    between them (set_x writes the buffer the NEXT product reads), which is what makes rewriting x
+    every step safe without a second handshake (include/slc.h, "Ordering contract").
+    The ranks' dependency sets (who reads whose slice) are exchanged once, so a product waits for its
+    neighbours only, not for every rank.
     """
 
     def __init__(self, local, splits, rank, world, dist=None, cpu_group=None, k=None, mode="halo"):
@@ -232,42 +358,64 @@ class ShardedSpMV:
         self.el = 16 if self.p == "z" else 8
         lib = _capi.lib()
         self.nloc_x = int(self.splits[rank + 1] - self.splits[rank])
-        self.x_ptr = C.c_void_p()
-        _check(lib.slc_dev_alloc(C.byref(self.x_ptr), max(self.nloc_x * ncol, 1) * self.el))
+        # two operand buffers carved from ONE allocation (one IPC handle per rank; see slc_ipc_export)
+        self.x_bytes = -(-max(self.nloc_x * ncol, 1) * self.el // 256) * 256
+        self.x_base = C.c_void_p()
+        _check(lib.slc_dev_alloc(C.byref(self.x_base), 2 * self.x_bytes))
+        self.x_bufs = [self.x_base.value, self.x_base.value + self.x_bytes]
+        self.cur = 0                    # buffer the next product reads is x_bufs[cur ^ 1] until set_x / product flips
         self.y_ptr = C.c_void_p()
         _check(lib.slc_dev_alloc(C.byref(self.y_ptr), max(local.nrows * ncol, 1) * self.el))
         self.xfull_ptr = C.c_void_p()
         if mode == "allgather":
             _check(lib.slc_dev_alloc(C.byref(self.xfull_ptr), max(local.ncols, 1) * self.el))
         handle = C.create_string_buffer(IPC_BYTES)
-        _check(lib.slc_ipc_export(self.x_ptr, handle))
+        _check(lib.slc_ipc_export(self.x_base, handle))
         self.group = C.c_void_p()
         ghandle = C.create_string_buffer(IPC_BYTES)
         _check(lib.slc_peer_group_create(world, rank, C.byref(self.group), ghandle))
-        both = exchange_objects((bytes(handle.raw), bytes(ghandle.raw)), dist, cpu_group)
+        self.local.device().prepare()
+        need = C.c_uint32(0)
+        _check(getattr(lib, "slc_%s_dist_needs" % self.p)(self.local.device().handle, world, rank,
+                                                          self.splits.ctypes.data_as(C.c_void_p), C.byref(need)))
+        if mode == "allgather":
+            need = C.c_uint32((1 << world) - 1)
+        both = exchange_objects((bytes(handle.raw), bytes(ghandle.raw), int(need.value)), dist, cpu_group)
         handles = [b[0] for b in both]
         _check(lib.slc_peer_group_connect(self.group, C.create_string_buffer(b"".join(b[1] for b in both),
                                                                             IPC_BYTES * world)))
+        self.deps = dependency_mask([b[2] for b in both], rank)
+        _check(lib.slc_peer_group_set_deps(self.group, self.deps))
         self.use_nccl_barrier = os.environ.get("SLC_BARRIER", "peer") == "nccl"
-        self.parts = (C.c_void_p * world)()
+        self.tables = [(C.c_void_p * world)(), (C.c_void_p * world)()]    # part pointers of buffer 0 / 1
         self._imported = []
         for r in range(world):
             if r == rank:
-                self.parts[r] = self.x_ptr.value
+                base = self.x_base.value
+                xb = self.x_bytes
             else:
                 ptr = C.c_void_p()
                 _check(lib.slc_ipc_import(C.create_string_buffer(handles[r], IPC_BYTES), C.byref(ptr)))
-                self.parts[r] = ptr.value
                 self._imported.append(ptr)
-        self.local.device().prepare()
+                base = ptr.value
+                nloc = int(self.splits[r + 1] - self.splits[r])
+                xb = -(-max(nloc * ncol, 1) * self.el // 256) * 256
+            self.tables[0][r] = base
+            self.tables[1][r] = base + xb
         self._fn = getattr(lib, "slc_%s_%s_dist_dev" % (self.p, "mulv" if k is None else "mulm"))
         self._fn_ag = getattr(lib, "slc_%s_mulv_allgather_dev" % self.p)
         # every part's block is packed: leading dimension = its own row count
         self.lds = np.ascontiguousarray(np.diff(self.splits).astype(np.int64))
         self._flag = None
 
+    @property
+    def x_ptr(self):
+        """Device address of the buffer the next product reads (fill it, then call product / mulv)."""
+        return C.c_void_p(self.x_bufs[self.cur ^ 1])
+
     def set_x(self, x_local):
-        """This rank's slice of x (vector) or its row block of X (nloc x k, stored column-major)."""
+        """This rank's slice of x (vector) or its row block of X (nloc x k, stored column-major) for the
+        NEXT product: written into the buffer the previous product did not read."""
         if self.k is None:
             x_local = np.ascontiguousarray(x_local, dtype=self.local.dtype)
             assert len(x_local) == self.nloc_x
@@ -295,20 +443,36 @@ class ShardedSpMV:
         _check(_capi.lib().slc_peer_group_timed_out(self.group, C.byref(f)))
         return bool(f.value)
 
+    def stats(self, reset=False):
+        """(epochs completed, timed waits, ns waited in total, longest wait in ns); synchronises."""
+        out = (C.c_int64 * 4)()
+        _check(_capi.lib().slc_peer_group_stats(self.group, out, 1 if reset else 0))
+        return tuple(int(v) for v in out)
+
     def product(self, sync=None):
+        """One product over the buffer set_x / x_ptr last designated; flips the buffers."""
+        self.cur ^= 1
+        table = self.tables[self.cur]
         if self.mode == "allgather":
             _check(self._fn_ag(self.local.device().handle, self.world, self.rank,
-                               self.splits.ctypes.data_as(C.c_void_p), C.cast(self.parts, C.c_void_p),
+                               self.splits.ctypes.data_as(C.c_void_p), C.cast(table, C.c_void_p),
                                self.xfull_ptr, self.y_ptr, sync))
         elif self.k is None:
             _check(self._fn(self.local.device().handle, self.world, self.rank,
-                            self.splits.ctypes.data_as(C.c_void_p), C.cast(self.parts, C.c_void_p), self.y_ptr,
+                            self.splits.ctypes.data_as(C.c_void_p), C.cast(table, C.c_void_p), self.y_ptr,
                             sync))
         else:
             _check(self._fn(self.local.device().handle, self.world, self.rank,
-                            self.splits.ctypes.data_as(C.c_void_p), C.cast(self.parts, C.c_void_p),
+                            self.splits.ctypes.data_as(C.c_void_p), C.cast(table, C.c_void_p),
                             self.lds.ctypes.data_as(C.c_void_p), self.y_ptr, max(self.local.nrows, 1), self.k,
                             sync))
+
+    def repeat_x(self):
+        """Keep the operand for another product without re-sending it: copy the current buffer into the
+        other one on the device (benchmarks that time products of a fixed x)."""
+        lib = _capi.lib()
+        src, dst = self.x_bufs[self.cur], self.x_bufs[self.cur ^ 1]
+        _check(lib.slc_memcpy_d2d(C.c_void_p(dst), C.c_void_p(src), self.x_bytes))
 
     def mulv(self):
         """One distributed product, ordered against the peers.  Default: the library signals, runs
@@ -336,9 +500,9 @@ class ShardedSpMV:
         if self.group:
             lib.slc_peer_group_free(self.group)
             self.group = None
-        if self.x_ptr:
-            lib.slc_dev_free(self.x_ptr)
-            self.x_ptr = None
+        if self.x_base:
+            lib.slc_dev_free(self.x_base)
+            self.x_base = None
         if self.y_ptr:
             lib.slc_dev_free(self.y_ptr)
             self.y_ptr = None
@@ -347,379 +511,65 @@ class ShardedSpMV:
             self.xfull_ptr = None
 
 
-# ---- bench.py --gpus N ------------------------------------------------------------------------------------
+def dependency_mask(needs, rank):
+    """needs[q] = bit mask of the parts rank q reads from.  Rank `rank` depends on the parts it reads
+    and on the ranks that read it (they must be done with a buffer before it is rewritten)."""
+    deps = int(needs[rank])
+    for q, nq in enumerate(needs):
+        if (int(nq) >> rank) & 1:
+            deps |= 1 << q
+    return deps & ~(1 << rank)
 
-def bench_main(args, rank, world, local_rank, dist):
-    """cfg 5 row-partitioned over `world` GPUs.  strong: the 200^3 grid is cut into z-slabs;
-    weak: every rank holds its own 200-plane slab of a (200*world) x 200 x 200 grid."""
-    import torch
-    import sparse_linear_b200 as sl
-    from . import generators as g
-    import bench as B
 
-    if args.workload == "cfg3":
-        return bench_spgemm_sharded(args, rank, world, local_rank, dist)
-    if args.workload == "cfg4":
-        return bench_powerlaw_sharded(args, rank, world, local_rank, dist)
-    if args.workload in ("cfg3t", "cfg3a"):
-        return bench_structural_sharded(args, rank, world, local_rank, dist)
-    n = args.grid or 200
-    if args.scaling == "weak":
-        shape = (n * world, n, n)
-    else:
-        shape = (n, n, n)
-    plane = shape[1] * shape[2]
-    ntot = shape[0] * plane
-    splits = uniform_splits(shape[0], world) * plane        # z-slabs
-    r0, r1 = int(splits[rank]), int(splits[rank + 1])
-    stream = torch.cuda.current_stream()
-    sl.set_stream(stream.cuda_stream)
-    cpu_group = dist.new_group(backend="gloo") if world > 1 else None
+class ShardedMatrix:
+    """One process, several GPUs: slc_{d,z}_upload_sharded / mulv_sharded / mulm_sharded (include/slc.h).
+    The host-side mirror of what the Haskell shim binds for the multi-GPU products."""
 
-    # A is symmetric, so the row block A[r0:r1, :] is the transpose of the column block A[:, r0:r1]
-    colblock = g.stencil3d_27pt(shape, col_range=(r0, r1))
-    cb = Matrix(colblock.ncols, colblock.nrows, colblock.colptr, colblock.rowidx, colblock.values)
-    local = sl.transpose(cb)                                 # (r1-r0) x ntot, on the device
-    del cb
-    k = 64 if args.workload == "cfg5mm" else None
-    sh = ShardedSpMV(local, splits, rank, world, dist, cpu_group, k=k)
-    xfull = g.uniform_vector(ntot, seed=0)
-    nnz_local = int(colblock.colptr[-1])
-    if k is None:
-        sh.set_x(xfull[r0:r1])
-        abytes_local = g.spmv_bytes(r1 - r0, r1 - r0, nnz_local)   # every x entry is read from HBM once, by its owner
-    else:
-        # column j of the block is x scaled by 1 + j/64, so one host SpMV checks all 64 columns
-        colscale = 1.0 + np.arange(k) / 64.0
-        sh.set_x(np.asfortranarray(xfull[r0:r1, None] * colscale[None, :]))
-        abytes_local = g.spmm_bytes(r1 - r0, r1 - r0, nnz_local, k)
-    tot = torch.tensor([float(abytes_local), float(nnz_local)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(tot)
-    abytes, nnz = float(tot[0].item()), int(tot[1].item())
-
-    for _ in range(max(args.warmup, 3)):
-        sh.mulv()
-    torch.cuda.synchronize()
-    # parity on this rank's rows: y_local = (column block)^T x, summed on the host
-    want = np.add.reduceat(colblock.values * xfull[colblock.rowidx], colblock.colptr[:-1].astype(np.int64))
-    got = sh.y()
-    if k is not None:
-        want = want[:, None] * colscale[None, :]
-    err = float(np.linalg.norm(got - want) / max(np.linalg.norm(want), 1e-300))
-
-    sampler = B.ClockSampler(local_rank)
-    l0 = sl.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    sampler.start()
-    e0.record(stream)
-    for _ in range(args.steps):
-        sh.mulv()
-    e1.record(stream)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    clocks = sampler.stop()
-    launches = sl.launch_count() - l0
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
-    errt = torch.tensor([err], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(errt, op=dist.ReduceOp.MAX)
-    ms = float(t.item()) / args.steps
-    value = abytes / (ms * 1e-3) / 1e9
-
-    # end to end: every step moves this rank's x slice from pinned host memory, multiplies, and
-    # brings its y slice back
-    e2e = None
-    if not args.no_e2e:
+    def __init__(self, m, ndev, devices=None):
         lib = _capi.lib()
-        ncol = 1 if k is None else k
-        if k is None:
-            xp = torch.from_numpy(np.ascontiguousarray(xfull[r0:r1])).pin_memory()
-        else:
-            xp = torch.from_numpy(np.ascontiguousarray((xfull[r0:r1, None] * colscale[None, :]).T)).pin_memory()
-        yp = torch.empty((r1 - r0) * ncol, dtype=torch.float64).pin_memory()
-        steps_e2e = max(3, min(args.steps, 20 if k is None else 5))
+        self.p = m._p
+        self.dtype = m.dtype
+        self.nrows, self.ncols = m.nrows, m.ncols
+        self.h = C.c_void_p()
+        dv = None if devices is None else np.ascontiguousarray(devices, dtype=np.int32)
+        _check(getattr(lib, "slc_%s_upload_sharded" % self.p)(
+            int(ndev), None if dv is None else dv.ctypes.data_as(C.c_void_p), m.nrows, m.ncols,
+            C.c_void_p(m.pointers.ctypes.data), C.c_void_p(m.indices.ctypes.data), C.c_void_p(m.values.ctypes.data),
+            C.byref(self.h)))
+        self.ndev = int(ndev)
 
-        def hstep():
-            _check(lib.slc_memcpy_h2d(sh.x_ptr, C.c_void_p(xp.data_ptr()), xp.numel() * 8))
-            sh.mulv()
-            _check(lib.slc_memcpy_d2h(C.c_void_p(yp.data_ptr()), sh.y_ptr, yp.numel() * 8))
-        for _ in range(2):
-            hstep()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(steps_e2e):
-            hstep()
-        torch.cuda.synchronize()
-        dt = torch.tensor([(time.perf_counter() - t0) / steps_e2e], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        dt = float(dt.item())
-        e2e = {"value": abytes / dt / 1e9, "unit": "GB/s", "ms_per_step": dt * 1e3, "steps": steps_e2e,
-               "h2d_bytes_per_step": int(ntot * 8 * ncol), "d2h_bytes_per_step": int(ntot * 8 * ncol),
-               "api": "ShardedSpMV (slc_memcpy_h2d + slc_d_%s_dist_dev + slc_memcpy_d2h per rank)"
-                      % ("mulv" if k is None else "mulm")}
+    def splits(self):
+        rs = np.zeros(self.ndev + 1, dtype=np.int32)
+        cs = np.zeros(self.ndev + 1, dtype=np.int32)
+        _check(_capi.lib().slc_sharded_splits(self.h, rs.ctypes.data_as(C.c_void_p), cs.ctypes.data_as(C.c_void_p)))
+        return rs, cs
 
-    if rank == 0:
-        peak, peak_src = B.peaks()
-        per_gpu = value / world
-        line = {
-            "metric": B.METRIC if k is None else "spmm_effective_hbm_gbps", "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True,
-            "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic (seeded numpy PCG64)",
-            "config": {"workload": ("cfg5: 3D 27-point stencil %dx%dx%d, Double SpMV, row-partitioned in z-slabs over %d GPU(s); "
-                                    "halo entries gathered from peer HBM over NVLink inside the product kernel; "
-                                    "the inter-GPU barrier (peer-memory flags) is fused into the same launch" % (shape + (world,)))
-                       if k is None else
-                       ("cfg5: 3D 27-point stencil %dx%dx%d, Double SpMM k=64, row-partitioned in z-slabs over %d GPU(s); "
-                        "signal, interior rows (k_spmm_panel), wait, boundary rows gathering the peers' rows of X "
-                        "over NVLink (k_spmm_boundary)" % (shape + (world,))),
-                       "rows": ntot, "nnz": nnz, "algorithmic_bytes_per_step": abytes,
-                       "plan": local.device().plan_info(),
-                       "l2": "inputs larger than L2 (%.0f MB per GPU per step)" % (abytes / world / 1e6),
-                       "pct_of_nominal_8TBs_per_gpu": 100.0 * per_gpu / B.NOMINAL_HBM_GBS,
-                       "max_rel_err_vs_host_sum": float(errt.item())},
-            "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e,
-            "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
-                         "traffic": None, "peak_source": peak_src,
-                         "kernel": "k_spmv_sell_dist" if k is None else "k_spmm_panel + k_spmm_boundary",
-                         "note": "per-GPU figure; step time includes the inter-GPU barrier",
-                         "barrier": "nccl all-reduce" if sh.use_nccl_barrier else
-                         ("peer-memory flags, fused in k_spmv_sell_dist" if k is None else "peer-memory flags (signal / wait kernels)"),
-                         "barrier_timed_out": sh.timed_out()},
-            "cpu_baseline": None,
-        }
-        print(json.dumps(line), flush=True)
-    sh.close()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    def mulV(self, x):
+        x = np.ascontiguousarray(x, dtype=self.dtype)
+        if x.ndim != 1 or len(x) != self.ncols:
+            raise SparseLinearError("axpy_: column dimension %d does not match operand dimension %d" % (self.ncols, x.size))
+        y = np.empty(self.nrows, dtype=self.dtype)
+        _check(getattr(_capi.lib(), "slc_%s_mulv_sharded" % self.p)(self.h, C.c_void_p(x.ctypes.data), C.c_void_p(y.ctypes.data)))
+        return y
 
+    def mulM(self, X):
+        X = np.asarray(X)
+        if X.ndim != 2 or X.shape[0] != self.ncols:
+            raise SparseLinearError("mulM: inner dimension mismatch")
+        Xf = np.asfortranarray(X, dtype=self.dtype)
+        k = Xf.shape[1]
+        Y = np.empty((self.nrows, k), dtype=self.dtype, order="F")
+        _check(getattr(_capi.lib(), "slc_%s_mulm_sharded" % self.p)(
+            self.h, C.c_void_p(Xf.ctypes.data), max(self.ncols, 1), C.c_void_p(Y.ctypes.data), max(self.nrows, 1), k))
+        return Y
 
-def _max_over_ranks(ms, dist, world):
-    import torch
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+    def close(self):
+        if self.h:
+            _capi.lib().slc_sharded_free(self.h)
+            self.h = None
 
-
-def _sum_over_ranks(vals, dist, world):
-    import torch
-    t = torch.tensor([float(v) for v in vals], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t)
-    return [float(v) for v in t.tolist()]
-
-
-def bench_spgemm_sharded(args, rank, world, local_rank, dist):
-    """cfg 3, C = A A, strong-scaled: A cut into row blocks, B = A replicated, no exchange while
-    computing; value = output nnz of all blocks / slowest rank's time (symbolic + numeric)."""
-    import torch
-    import sparse_linear_b200 as sl
-    from . import generators as g
-    import bench as B
-    n = args.grid or 128
-    a = g.laplace3d_7pt(n)
-    stream = torch.cuda.current_stream()
-    sl.set_stream(stream.cuda_stream)
-    bm = Matrix(a.ncols, a.nrows, a.colptr, a.rowidx, a.values)
-    splits = uniform_splits(n, world) * (n * n)           # z-slabs: equal work per rank
-    r0, r1 = int(splits[rank]), int(splits[rank + 1])
-    blk = row_block(a, r0, r1)
-    local = Matrix(blk.ncols, blk.nrows, blk.colptr, blk.rowidx, blk.values)
-    c = sl.mm(local, bm)
-    sl.synchronize()
-    nnzc_local = sl.nonZero(c)
-    # parity of this rank's block against the closed form of the whole product and, on a small
-    # grid, the structure of a host product (scipy is a second opinion only; tests use the oracle)
-    del c
-    steps = max(1, min(args.steps, 10))
-    for _ in range(2):
-        c = sl.mm(local, bm)
-        del c
-    sampler = B.ClockSampler(local_rank)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    l0 = sl.launch_count()
-    sampler.start()
-    e0.record(stream)
-    for _ in range(steps):
-        c = sl.mm(local, bm)
-        del c
-    e1.record(stream)
-    torch.cuda.synchronize()
-    clocks = sampler.stop()
-    launches = sl.launch_count() - l0
-    ms = _max_over_ranks(e0.elapsed_time(e1) / steps, dist, world)
-    nnzc, nnza = _sum_over_ranks([nnzc_local, blk.colptr[-1]], dist, world)
-    if rank == 0:
-        peak, peak_src = B.peaks()
-        nnzb = int(a.colptr[-1])
-        floor_bytes = (nnza + nnzb * world + nnzc) * 12 + 3 * (a.ncols + 1) * 4 * world
-        gbs = floor_bytes / (ms * 1e-3) / 1e9 / world
-        expect = None
-        if n >= 5:   # nnz(A A) of the 7-point Laplacian on an n^3 grid: the 25-point radius-2 diamond, clipped
-            import itertools
-            offs = {(dx + ex, dy + ey, dz + ez) for (dx, dy, dz) in [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0), (0, 0, 1), (0, 0, -1)]
-                    for (ex, ey, ez) in [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0), (0, 0, 1), (0, 0, -1)]}
-            expect = sum((n - abs(dx)) * (n - abs(dy)) * (n - abs(dz)) for dx, dy, dz in offs)
-        line = {"metric": "spgemm_output_nnz_per_s", "value": nnzc / (ms * 1e-3), "unit": "nnz/s", "n_gpus": world,
-                "steps": steps, "warmup": 2, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
-                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": "cfg3: SpGEMM A*A, 3D 7-point Laplacian %d^3, A in %d row blocks (z-slabs), "
-                                       "B replicated, no exchange during the product" % (n, world),
-                           "nnz_in": int(nnzb), "nnz_out": int(nnzc), "nnz_out_closed_form": expect,
-                           "structure_count_matches_closed_form": (int(nnzc) == expect) if expect else None},
-                "clocks": clocks, "gpu_launches": int(launches),
-                "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
-                             "traffic": None, "peak_source": peak_src, "kernel": "k_mm_merge (numeric)",
-                             "note": "per-GPU share of the one-pass byte floor (B counted once per rank)"}}
-        print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-
-
-def bench_powerlaw_sharded(args, rank, world, local_rank, dist):
-    """cfg 4 over `world` GPUs: R-MAT rows cut into blocks of equal nonzeros, x sliced by the same
-    bounds; every product all-gathers x over NVLink (k_allgather_pull) and runs the balanced kernel."""
-    import torch
-    import sparse_linear_b200 as sl
-    from . import generators as g
-    import bench as B
-    scale = args.grid or 24
-    stream = torch.cuda.current_stream()
-    sl.set_stream(stream.cuda_stream)
-    cpu_group = dist.new_group(backend="gloo") if world > 1 else None
-    n, r, c, v = g.rmat_triplets(scale, 16, seed=0)          # every rank generates the same edge list
-    splits = balanced_splits(np.bincount(r, minlength=n), world)
-    r0, r1 = int(splits[rank]), int(splits[rank + 1])
-    keep = (r >= r0) & (r < r1)
-    rl, cl, vl = (r[keep] - r0).astype(np.int32), c[keep], v[keep]
-    del r, c, v, keep
-    local = sl.compress(r1 - r0, n, rl, cl, vl)               # device assembly, duplicates summed
-    nnz_local = sl.nonZero(local)
-    sh = ShardedSpMV(local, splits, rank, world, dist, cpu_group, mode="allgather")
-    xfull = g.uniform_vector(n, seed=0)
-    sh.set_x(xfull[r0:r1])
-    for _ in range(max(args.warmup, 3)):
-        sh.mulv()
-    torch.cuda.synchronize()
-    want = np.bincount(rl, weights=vl * xfull[cl], minlength=r1 - r0)
-    got = sh.y()
-    err = float(np.linalg.norm(got - want) / max(np.linalg.norm(want), 1e-300))
-    del rl, cl, vl
-    sampler = B.ClockSampler(local_rank)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    l0 = sl.launch_count()
-    sampler.start()
-    e0.record(stream)
-    for _ in range(args.steps):
-        sh.mulv()
-    e1.record(stream)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    clocks = sampler.stop()
-    launches = sl.launch_count() - l0
-    ms = _max_over_ranks(e0.elapsed_time(e1) / args.steps, dist, world)
-    nnz, errsq = _sum_over_ranks([nnz_local, err * err], dist, world)
-    abytes = g.spmv_bytes(n, n, int(nnz))
-    value = abytes / (ms * 1e-3) / 1e9
-    if rank == 0:
-        peak, peak_src = B.peaks()
-        per_gpu = value / world
-        line = {"metric": B.METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
-                "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
-                "vs_baseline": None, "dtype": "f64", "data": "synthetic (seeded numpy PCG64)",
-                "config": {"workload": "cfg4: R-MAT scale %d edge factor 16, Double SpMV, rows in %d blocks of equal "
-                                       "nonzeros; x all-gathered over NVLink peer memory every product (%.0f MB inbound "
-                                       "per GPU), then the balanced kernel" % (scale, world, n * 8 * (world - 1) / world / 1e6),
-                           "rows": n, "nnz": int(nnz), "algorithmic_bytes_per_step": abytes,
-                           "plan": local.device().plan_info(), "splits": [int(x) for x in splits],
-                           "rel_err_vs_host_sum_rms_over_ranks": float(np.sqrt(errsq / world))},
-                "clocks": clocks, "gpu_launches": int(launches), "e2e": None,
-                "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
-                             "traffic": None, "peak_source": peak_src,
-                             "kernel": "k_allgather_pull + k_spmv_bal",
-                             "note": "per-GPU figure; the step includes the barrier and the all-gather of x",
-                             "barrier_timed_out": sh.timed_out()},
-                "cpu_baseline": None}
-        print(json.dumps(line), flush=True)
-    sh.close()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-
-
-def bench_structural_sharded(args, rank, world, local_rank, dist):
-    """cfg 3 transpose / assembly over `world` GPUs: column blocks in, column blocks out, one
-    all-to-all-v (NCCL), local kernels on each GPU.  The pieces are cut, shipped and stacked through
-    host memory this round, so the figure is the whole step (device kernels + PCIe + host stacking),
-    wall clock, max over ranks."""
-    import torch
-    import sparse_linear_b200 as sl
-    from . import generators as g
-    import bench as B
-    n = args.grid or 128
-    a = g.laplace3d_7pt(n)
-    sl.set_stream(torch.cuda.current_stream().cuda_stream)
-    cs = uniform_splits(n, world) * (n * n)
-    c0, c1 = int(cs[rank]), int(cs[rank + 1])
-    blk = col_block(a, c0, c1)
-    steps = max(1, min(args.steps, 5))
-    if args.workload == "cfg3t":
-        def step():
-            return sharded_transpose(blk, cs, dist)
-        ref = blk          # the Laplacian is symmetric: block c of the transpose is block c of A
-        units, unit, metric = int(a.colptr[-1]), "nnz/s", "transpose_nnz_per_s"
-    else:
-        r, c, v = g.split_duplicates(a, seed=0)       # every rank generates the same shuffled triplets
-        lo, hi = (len(r) * rank) // world, (len(r) * (rank + 1)) // world
-        r, c, v = r[lo:hi], c[lo:hi], v[lo:hi]
-
-        def step():
-            m = sharded_compress(a.nrows, r, c, v, cs, rank, dist)
-            return CSC(m.nrows, m.ncols, m.pointers, m.indices, m.values)
-        ref = blk          # 0.25 v + 0.75 v == v exactly
-        units, unit, metric = 2 * int(a.colptr[-1]), "triplets/s", "assembly_triplets_per_s"
-    got = step()
-    ok = bool(np.array_equal(got.colptr, ref.colptr) and np.array_equal(got.rowidx, ref.rowidx)
-              and np.array_equal(got.values, ref.values))
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    l0 = sl.launch_count()
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        step()
-    torch.cuda.synchronize()
-    ms = _max_over_ranks((time.perf_counter() - t0) / steps * 1e3, dist, world)
-    oks = _sum_over_ranks([1.0 if ok else 0.0], dist, world)[0]
-    if rank == 0:
-        line = {"metric": metric, "value": units / (ms * 1e-3), "unit": unit, "n_gpus": world, "steps": steps, "warmup": 1,
-                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-                "dtype": "u32 keys + f64 values", "data": "synthetic (seeded numpy PCG64)",
-                "config": {"workload": "cfg3: %s of the 3D 7-point Laplacian %d^3 held as %d column blocks; local %s on each GPU, "
-                                       "one all-to-all-v over NCCL, pieces cut and stacked on the host"
-                                       % ("transpose" if args.workload == "cfg3t" else "triplet assembly (2x duplicates)", n, world,
-                                          "slc_d_transpose" if args.workload == "cfg3t" else "slc_d_compress"),
-                           "blocks_equal_expected_bit_exact_on_ranks": int(oks), "timing": "wall clock, max over ranks"},
-                "gpu_launches": int(sl.launch_count() - l0), "roofline": None}
-        print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
