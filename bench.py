@@ -233,7 +233,7 @@ def stored_bytes_note(plan, abytes, nnz, ms):
 
 
 def spmv_kernel_name(plan):
-    if "sell" in plan:
+    if plan.startswith("sell32"):
         return "k_spmv_sell"
     return ("k_spmv_merge" if plan.startswith("csr-merge") else "k_spmv_bal") + " + k_spmv_bal_fixup"
 
@@ -346,7 +346,7 @@ def entry_spmv(args, sl, tm, name, desc, host_m=None, dev_m=None, dtype=np.float
         entry["cpu_baseline"] = {"value": abytes / best / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
                                  "sample": "whole matrix, %d passes, best pass" % passes,
                                  "host_cores_available": os.cpu_count(), "ms_per_pass": best * 1e3}
-        exact = "sell" in plan
+        exact = plan.startswith("sell32")     # one thread per row: the reference's summation order
         want_last = want if last == 0 else oracle.mulv(om, xh[last])
         entry["parity"] = {"oracle": "oracle.mulv (Sparse.hs:433-471)", "call": "slc_%s_mulv_dev, last timed step" % p,
                            "bit_exact": bool(np.array_equal(y_dev, want_last)),
@@ -363,7 +363,7 @@ def entry_spmv(args, sl, tm, name, desc, host_m=None, dev_m=None, dtype=np.float
 # ---- SpMM -----------------------------------------------------------------------------------------
 
 def spmm_kernel_name(plan):
-    if "sell" not in plan:
+    if not plan.startswith("sell32"):
         return "k_spmm_rows"
     maxlen = int(plan.split("max_rowlen=")[1].split()[0])
     if maxlen > 8:

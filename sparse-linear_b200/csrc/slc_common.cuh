@@ -177,6 +177,16 @@ struct BalancedPlan {
   double hot_share = 0.0;         // fraction of the nonzeros that sit in hot columns
 };
 
+// Offset-slot plan for matrices whose rows all follow one 3 x 3 x 3 offset pattern (slc_spmm_brick.cu)
+struct BrickPlan {
+  int state = -1;            // -1 not looked at, 0 the matrix does not qualify, 1 built
+  int32_t L = 0, P = 0;      // line and plane strides
+  int64_t shift = 0;         // column of a row's centre entry minus the row (row blocks keep global columns)
+  int64_t nrows_pad = 0;
+  double *dia = nullptr;     // [27][nrows_pad] values by offset slot
+  uint32_t *mask = nullptr;  // [nrows_pad] which slots a row has
+};
+
 }  // namespace slc
 
 struct slc_matrix {
@@ -207,6 +217,7 @@ struct slc_matrix {
   int spmv_active = slc::SPMV_AUTO;    // chosen
   slc::SellPlan sell;
   slc::BalancedPlan bal;
+  slc::BrickPlan brick;
   // streams and events of the pipelined host-operand product (upload / compute / download overlap)
   cudaStream_t pipe_in = nullptr, pipe_out = nullptr;
   std::vector<cudaEvent_t> pipe_events;
@@ -395,6 +406,15 @@ int ensure_csr(slc_matrix *m);
 // built in slc_spmm_window.cu: the TMA-staged SpMM for banded short-row matrices (*done = it ran)
 template <class T>
 int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, YInit<T> yi, bool *done);
+
+// built in slc_spmm_brick.cu: the register-blocked SpMM for 27-offset matrices (*done = it ran)
+int spmm_brick_try(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
+                   const YInit<double> &yi, int32_t row_begin, int32_t row_end, bool *done);
+inline int spmm_brick_try(slc_matrix *, const double2 *, int64_t, double2 *, int64_t, int32_t, const YInit<double2> &,
+                          int32_t, int32_t, bool *done) {
+  *done = false;  // Complex Double rows of 27 entries keep the panel kernel (54 values per row do not fit registers)
+  return SLC_OK;
+}
 
 inline int bits_for(uint32_t n) {  // bits needed to represent values in [0, n)
   int b = 1;

@@ -98,6 +98,8 @@ void matrix_release(slc_matrix *m) {
   dev_free(m->bal.hot_cols);
   dev_free(m->bal.colidx_hot);
   dev_free(m->dist_table);
+  dev_free(m->brick.dia);
+  dev_free(m->brick.mask);
   if (m->pipe_in) {
     cudaStreamSynchronize(m->pipe_in);
     cudaStreamSynchronize(m->pipe_out);

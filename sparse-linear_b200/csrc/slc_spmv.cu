@@ -1910,6 +1910,11 @@ template <class T>
 static int launch_panel(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, const YInit<T> &yi,
                         int32_t row_begin = 0, int32_t row_end = -1) {
   if (row_end < 0) row_end = m->nrows;
+  {  // 27-offset matrices: the register-blocked brick kernel (slc_spmm_brick.cu)
+    bool done = false;
+    SLC_TRY(spmm_brick_try(m, X, ldx, Y, ldy, k, yi, row_begin, row_end, &done));
+    if (done) return SLC_OK;
+  }
   static const int threads_env = env_int("SLC_PANEL_THREADS", 0);
   static const int smem_env = env_int("SLC_PANEL_SMEM_KB", 0);
   static const int jt_env = env_int("SLC_PANEL_JT", 0);
@@ -2227,9 +2232,9 @@ int slc_plan_info(const slc_matrix *m, char *buf, int32_t buflen) {
   const double pad = m->nnz ? 100.0 * (double)(m->sell.padded - m->nnz) / (double)m->nnz : 0.0;
   const double unit = (m->sell.kbase && m->nnz) ? 100.0 * (double)m->sell.unit_entries / (double)m->nnz : 0.0;
   snprintf(buf, (size_t)buflen,
-           "%s rows=%d cols=%d nnz=%lld max_rowlen=%d sell_padding=%.2f%% chunks=%d unit_stride=%.2f%% hot_cols=%d",
+           "%s rows=%d cols=%d nnz=%lld max_rowlen=%d sell_padding=%.2f%% chunks=%d unit_stride=%.2f%% hot_cols=%d brick=%d",
            names[m->spmv_active], m->nrows, m->ncols, (long long)m->nnz, m->max_rowlen, pad, m->bal.nchunks, unit,
-           m->bal.hot_k > 0 ? m->bal.hot_k : 0);
+           m->bal.hot_k > 0 ? m->bal.hot_k : 0, m->brick.state == 1 ? 1 : 0);
   return SLC_OK;
 }
 

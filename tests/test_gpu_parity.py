@@ -461,3 +461,55 @@ def test_upload_download_round_trip_and_validation(sl):
     bad2 = sl.Matrix(2, 3, [0, 1, 2], [0, 7], np.ones(2))        # row out of range
     with pytest.raises(sl.SparseLinearError, match="upload"):
         bad2.device()
+
+
+# ---- the register-blocked brick SpMM for 27-offset matrices (csrc/slc_spmm_brick.cu) ---------------------
+
+def _band27(n, L, P, rng, keep=1.0):
+    """Every row r holds the 27 offsets a P + b L + c that stay inside [0, n): unlike a grid stencil, rows at
+    'line ends' keep their wrapped neighbours, so the kernel's linear addressing (not a grid assumption) is
+    what makes it right.  keep < 1 drops random entries (rows with holes: the masked path)."""
+    offs = np.array([a * P + b * L + c for a in (-1, 0, 1) for b in (-1, 0, 1) for c in (-1, 0, 1)])
+    cols = np.arange(n)[:, None] + offs[None, :]           # row r, slot s -> column
+    ok = (cols >= 0) & (cols < n)
+    if keep < 1.0:
+        ok &= rng.random(ok.shape) < keep
+        ok[n // 2] = (cols[n // 2] >= 0) & (cols[n // 2] < n)      # the row the detector reads stays complete
+    r, s = np.nonzero(ok)
+    return oracle.compress(n, n, r, cols[r, s], rng.uniform(-1, 1, len(r)))
+
+
+@pytest.mark.parametrize("rvariant", ["2", "3"])
+def test_spmm_brick_matches_oracle(sl, monkeypatch, rvariant):
+    monkeypatch.setenv("SLC_BRICK_R", rvariant)
+    rng = np.random.default_rng(41)
+    cases = [g.stencil3d_27pt((9, 10, 37)),            # line length not a multiple of 32, odd line count
+             g.stencil3d_27pt((5, 16, 64)),
+             _band27(6000, 50, 400, rng),              # wrapped neighbours present
+             _band27(5000, 24, 240, rng, keep=0.8)]    # holes: masked path everywhere
+    for gm in cases:
+        m, om = to_matrix(sl, gm), oracle.csc(*gm)
+        for k in (1, 4, 7, 64):
+            X = g.uniform_block(gm.ncols, k, seed=k)
+            got = sl.mulM(m, X)
+            assert "brick=1" in m.device().plan_info()
+            np.testing.assert_array_equal(got, oracle.mulm(om, X))
+        Y0 = g.uniform_block(gm.nrows, 5, seed=3)
+        X = g.uniform_block(gm.ncols, 5, seed=4)
+        want = np.stack([oracle.axpy(om, np.ascontiguousarray(X[:, j]), np.ascontiguousarray(Y0[:, j])) for j in range(5)], axis=1)
+        np.testing.assert_array_equal(sl.mulM(m, X, Y0), want)
+
+
+def test_spmm_brick_vetoed_by_an_off_pattern_entry(sl):
+    """One entry outside the 27 offsets (far away, in a row the detector does not sample): the plan builder
+    must notice and the general kernel must serve the product."""
+    gm = g.stencil3d_27pt((8, 12, 40))
+    rows = np.repeat(np.arange(gm.ncols), np.diff(gm.colptr))      # symmetric pattern: (col, row) listing is fine
+    r = np.concatenate([gm.rowidx, [7]])
+    c = np.concatenate([rows, [3000]])
+    v = np.concatenate([gm.values, [0.5]])
+    bad = oracle.compress(gm.nrows, gm.ncols, r, c, v)
+    m, om = to_matrix(sl, bad), oracle.csc(*bad)
+    X = g.uniform_block(bad.ncols, 6, seed=1)
+    np.testing.assert_array_equal(sl.mulM(m, X), oracle.mulm(om, X))
+    assert "brick=0" in m.device().plan_info()

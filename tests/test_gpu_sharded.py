@@ -66,7 +66,8 @@ def test_partitioned_block_product_matches_oracle(sl, dtype):
     pfx = "z" if np.dtype(dtype).kind == "c" else "d"
     fn = getattr(lib, "slc_%s_mulm_dist_dev" % pfx)
     for gm, nparts, k in ((g.stencil3d_27pt((8, 6, 7), dtype), 4, 11), (g.laplace2d_5pt(30, dtype), 3, 5),
-                          (g.stencil3d_27pt((12, 12, 10), dtype), 2, 64)):
+                          (g.stencil3d_27pt((12, 12, 10), dtype), 2, 64),
+                          (g.stencil3d_27pt((8, 16, 40), dtype), 2, 9)):     # row blocks of 2560 rows: brick plan with a row shift
         om = oracle.csc(*gm)
         X = rng.uniform(-1, 1, (gm.ncols, k)).astype(dtype)
         if np.dtype(dtype).kind == "c":
