@@ -5,7 +5,9 @@ include/slc.h).  This package is the thin host layer tests and benchmarks drive:
 binding and a mirror of the reference's Data.Matrix.Sparse interface for the path.
 Import as `sparse_linear_b200` (see sparse_linear_b200.py at the repo root).
 """
-from . import _capi, generators, sharded  # noqa: F401
+from . import _capi, feast, generators, sharded  # noqa: F401
+from .feast import FeastWorkspace  # noqa: F401
+from .sharded import ShardedMatrix, ShardedSpMV  # noqa: F401
 from .matrix import (  # noqa: F401
     DeviceMatrix, Matrix, SparseLinearError,
     axpy, axpy_, cmap, compress, compress_dev, ctrans, decompress, device_count, diag, fromTriples, hermitian, ident,

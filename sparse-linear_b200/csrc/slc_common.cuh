@@ -221,6 +221,8 @@ struct slc_matrix {
   // streams and events of the pipelined host-operand product (upload / compute / download overlap)
   cudaStream_t pipe_in = nullptr, pipe_out = nullptr;
   std::vector<cudaEvent_t> pipe_events;
+  void *pipe_x = nullptr, *pipe_y = nullptr;  // device copies of the host operands (kept between calls)
+  size_t pipe_x_bytes = 0, pipe_y_bytes = 0;
   // partition tables of the recent distributed products (device copies + host shadows).  A caller that
   // double-buffers its operand alternates between two tables; with a few cached slots neither costs a
   // host-to-device copy per product, and the device addresses stay fixed (CUDA-graph friendly).

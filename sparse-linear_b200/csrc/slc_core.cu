@@ -100,6 +100,8 @@ void matrix_release(slc_matrix *m) {
   dev_free(m->dist_table);
   dev_free(m->brick.dia);
   dev_free(m->brick.mask);
+  if (m->pipe_x) cudaFree(m->pipe_x);
+  if (m->pipe_y) cudaFree(m->pipe_y);
   if (m->pipe_in) {
     cudaStreamSynchronize(m->pipe_in);
     cudaStreamSynchronize(m->pipe_out);

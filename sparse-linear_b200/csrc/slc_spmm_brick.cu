@@ -23,6 +23,7 @@
 // order (plane, then line, then point), product and sum rounded separately: bit-identical to the
 // reference (Sparse.hs:433-453), checked against the oracle at full size.
 #include <algorithm>
+#include <vector>
 
 #include "slc_common.cuh"
 
@@ -67,11 +68,21 @@ static int brick_plan(slc_matrix *m) {
   static const int env = env_int("SLC_SPMM_BRICK", 1);
   if (!env || m->elem != ELEM_D || !m->has_csr || m->max_rowlen != 27 || m->nrows < 1024) return SLC_OK;
   cudaStream_t s = cur_stream();
-  const int32_t r = m->nrows / 2;
-  int32_t rp[2];
-  SLC_CUDA(cudaMemcpyAsync(rp, m->rowptr + r, sizeof rp, cudaMemcpyDeviceToHost, s));
+  // a row with all 27 entries near the middle of the matrix (the very middle row of an even grid sits on a
+  // grid face): scan the pointers of a window of rows
+  const int32_t w0 = m->nrows / 2, wn = std::min<int32_t>(8192, m->nrows - w0);
+  std::vector<int32_t> win((size_t)wn + 1);
+  SLC_CUDA(cudaMemcpyAsync(win.data(), m->rowptr + w0, win.size() * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
   SLC_CUDA(cudaStreamSynchronize(s));
-  if (rp[1] - rp[0] != 27) return SLC_OK;
+  int32_t r = -1;
+  int32_t rp[2] = {0, 0};
+  for (int32_t i = 0; i < wn && r < 0; ++i)
+    if (win[(size_t)i + 1] - win[(size_t)i] == 27) {
+      r = w0 + i;
+      rp[0] = win[(size_t)i];
+      rp[1] = win[(size_t)i + 1];
+    }
+  if (r < 0) return SLC_OK;
   int32_t cols[27];
   SLC_CUDA(cudaMemcpyAsync(cols, m->colidx + rp[0], sizeof cols, cudaMemcpyDeviceToHost, s));
   SLC_CUDA(cudaStreamSynchronize(s));

@@ -1471,6 +1471,30 @@ static int spmv_dev_entry(slc_matrix *m, const double *x, double *y, const char 
 // stream: H2D, compute and D2H overlap (PCIe is full duplex) instead of running back to back.
 constexpr int PIPE_MAX_CHUNKS = 32;
 
+// chunk i of `n` of the pipelined product covers rows [cut(i), cut(i+1)): equal pieces, except that with
+// `taper` the last quarter is cut finer and finer, so that what is left after the last upload piece
+// lands (one small kernel, one small download) is a few per cent of the call instead of 1/n of it
+static void pipeline_cuts(int32_t nrows, int want, int taper, std::vector<int32_t> &cuts) {
+  cuts.clear();
+  cuts.push_back(0);
+  auto round256 = [&](double r) { return (int32_t)std::min<int64_t>(nrows, (int64_t)(r / 256.0 + 0.5) * 256); };
+  if (!taper || want < 4) {
+    const int32_t per = (int32_t)(ceil_div(ceil_div(nrows, want), 256) * 256);
+    for (int64_t r = per; r < nrows; r += per) cuts.push_back((int32_t)r);
+  } else {
+    const int big = want - 3;                       // equal pieces over the first 7/8 of the rows ...
+    const double body = 0.875 * nrows;
+    for (int i = 1; i <= big; ++i) cuts.push_back(round256(body * i / big));
+    cuts.push_back(round256(0.9375 * nrows));       // ... then 1/16, 1/32, 1/32
+    cuts.push_back(round256(0.96875 * nrows));
+  }
+  std::vector<int32_t> uniq;
+  for (int32_t c : cuts)
+    if (uniq.empty() || c > uniq.back()) uniq.push_back(c);
+  if (uniq.back() < nrows) uniq.push_back(nrows);
+  cuts.swap(uniq);
+}
+
 template <class T, bool ACC>
 static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
   *done = false;
@@ -1478,14 +1502,18 @@ static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
   const int diag = env_int("SLC_E2E_DIAG", 0);          // timing diagnosis: 1 = no download, 2 = no upload, 4 = no kernels
   const int align_env = env_int("SLC_E2E_ALIGN", 512);
   const int mode = env_int("SLC_E2E_MODE", 0);          // 0 = three streams chained by events, 1 = downloads follow their kernels
+  const int taper = env_int("SLC_E2E_TAPER", 1);        // finer chunks at the end (see pipeline_cuts)
+  const int trace = env_int("SLC_E2E_TRACE", 0);        // print a timeline of the call (timed events) to stderr
   const int want = chunks_env < 1 ? 1 : (chunks_env > PIPE_MAX_CHUNKS ? PIPE_MAX_CHUNKS : chunks_env);
   if (want == 1 || m->nnz == 0 || m->nrows < (1 << 18)) return SLC_OK;
   SLC_TRY(ensure_plan<T>(m));
   if (m->spmv_active != SPMV_SELL) return SLC_OK;
   SLC_TRY(fetch_slice_ranges(m));
   SellPlan &sp = m->sell;
-  const int32_t rows_per = (int32_t)(ceil_div(ceil_div(m->nrows, want), 256) * 256);
-  const int nch = (int)ceil_div(m->nrows, rows_per);
+  std::vector<int32_t> cuts;
+  pipeline_cuts(m->nrows, want, taper, cuts);
+  const int nch = (int)cuts.size() - 1;
+  if (nch > PIPE_MAX_CHUNKS) return SLC_OK;
   if (!m->pipe_in) {
     SLC_CUDA(cudaStreamCreateWithFlags(&m->pipe_in, cudaStreamNonBlocking));
     SLC_CUDA(cudaStreamCreateWithFlags(&m->pipe_out, cudaStreamNonBlocking));
@@ -1493,60 +1521,99 @@ static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
     for (auto &e : m->pipe_events) SLC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
   cudaStream_t main_s = cur_stream();
-  DevBuf<T> dx, dy, dcold;
-  SLC_TRY(dx.alloc((size_t)m->ncols));
-  SLC_TRY(dy.alloc((size_t)m->nrows));
+  // the device copies of x and y live with the handle: no allocation per call
+  const size_t need_x = (size_t)m->ncols * sizeof(T), need_y = (size_t)m->nrows * sizeof(T);
+  if (m->pipe_x_bytes < need_x) {
+    if (m->pipe_x) SLC_CUDA(cudaFree(m->pipe_x));
+    m->pipe_x = nullptr;
+    SLC_CUDA(cudaMalloc(&m->pipe_x, need_x));
+    m->pipe_x_bytes = need_x;
+  }
+  if (m->pipe_y_bytes < need_y) {
+    if (m->pipe_y) SLC_CUDA(cudaFree(m->pipe_y));
+    m->pipe_y = nullptr;
+    SLC_CUDA(cudaMalloc(&m->pipe_y, need_y));
+    m->pipe_y_bytes = need_y;
+  }
+  T *dx = (T *)m->pipe_x, *dy = (T *)m->pipe_y;
+  DevBuf<T> dcold;
   if (diag & 8) SLC_TRY(dcold.alloc((size_t)m->nrows));  // diagnosis: downloads read memory no kernel has written
-  const T *dsrc = (diag & 8) ? dcold.p : dy.p;
+  const T *dsrc = (diag & 8) ? dcold.p : dy;
+  std::vector<cudaEvent_t> tev;  // trace: start, then (upload, kernel, download) per chunk
+  auto mark = [&](cudaStream_t st) {
+    if (!trace) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, st);
+    tev.push_back(e);
+  };
   cudaEvent_t ev_start = m->pipe_events[2 * PIPE_MAX_CHUNKS];
+  mark(main_s);
   SLC_CUDA(cudaEventRecord(ev_start, main_s));
   SLC_CUDA(cudaStreamWaitEvent(m->pipe_in, ev_start, 0));
   SLC_CUDA(cudaStreamWaitEvent(m->pipe_out, ev_start, 0));
   int32_t sent = 0;  // x[0, sent) is on its way
   for (int i = 0; i < nch; ++i) {
-    const int32_t r0 = i * rows_per, r1 = (int32_t)std::min<int64_t>(m->nrows, (int64_t)(i + 1) * rows_per);
+    const int32_t r0 = cuts[i], r1 = cuts[i + 1];
     int32_t need = sent;
     for (int32_t sl = r0 / SELL_C; sl < (int32_t)ceil_div(r1, SELL_C); ++sl) need = std::max(need, sp.h_cmax[sl] + 1);
     // piece boundaries on 512-element (4 KB) multiples: both ends of every copy stay page-aligned
     if (align_env > 0) need = (int32_t)std::min<int64_t>(m->ncols, ceil_div(need, align_env) * (int64_t)align_env);
+    if (i == nch - 1) need = m->ncols;
     if (need > sent) {
       if (!(diag & 2))
-        SLC_CUDA(cudaMemcpyAsync(dx.p + sent, x + sent, (size_t)(need - sent) * sizeof(T), cudaMemcpyHostToDevice,
+        SLC_CUDA(cudaMemcpyAsync(dx + sent, x + sent, (size_t)(need - sent) * sizeof(T), cudaMemcpyHostToDevice,
                                  m->pipe_in));
       sent = need;
     }
     if (ACC)
-      SLC_CUDA(cudaMemcpyAsync(dy.p + r0, y + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyHostToDevice, m->pipe_in));
+      SLC_CUDA(cudaMemcpyAsync(dy + r0, y + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyHostToDevice, m->pipe_in));
+    mark(m->pipe_in);
     cudaEvent_t ev_in = m->pipe_events[i], ev_k = m->pipe_events[PIPE_MAX_CHUNKS + i];
     SLC_CUDA(cudaEventRecord(ev_in, m->pipe_in));
     if (mode == 1) {
       // chunk kernels alternate between the caller's stream and the side stream, and each chunk's
       // download follows its kernel on the same stream: one cross-stream dependency per chunk (upload
-      // -> kernel) instead of two.  A dependency between copy-engine work on different streams costs
-      // tens of microseconds (scripts/e2e_probe.py: upload + download alone ran 1.78 ms through the
-      // event chain, 1.32 ms as two plain copies).
+      // -> kernel) instead of two.
       cudaStream_t cs = (i & 1) ? m->pipe_out : main_s;
       SLC_CUDA(cudaStreamWaitEvent(cs, ev_in, 0));
       if (!(diag & 4)) {
         tls().stream = cs;
-        const int rc = launch_sell<T, ACC, LocalX<T>>(m, LocalX<T>{dx.p}, dy.p, r0, r1);
+        const int rc = launch_sell<T, ACC, LocalX<T>>(m, LocalX<T>{dx}, dy, r0, r1);
         tls().stream = main_s;
         SLC_TRY(rc);
       }
+      mark(cs);
       if (!(diag & 1))
         SLC_CUDA(cudaMemcpyAsync(y + r0, dsrc + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyDeviceToHost, cs));
+      mark(cs);
       continue;
     }
     SLC_CUDA(cudaStreamWaitEvent(main_s, ev_in, 0));
-    if (!(diag & 4)) SLC_TRY((launch_sell<T, ACC, LocalX<T>>(m, LocalX<T>{dx.p}, dy.p, r0, r1)));
+    if (!(diag & 4)) SLC_TRY((launch_sell<T, ACC, LocalX<T>>(m, LocalX<T>{dx}, dy, r0, r1)));
+    mark(main_s);
     SLC_CUDA(cudaEventRecord(ev_k, main_s));
     SLC_CUDA(cudaStreamWaitEvent(m->pipe_out, ev_k, 0));
     if (!(diag & 1))
       SLC_CUDA(cudaMemcpyAsync(y + r0, dsrc + r0, (size_t)(r1 - r0) * sizeof(T), cudaMemcpyDeviceToHost, m->pipe_out));
+    mark(m->pipe_out);
   }
+  // one wait: everything the call enqueued ends in the last download (or, in mode 1, on the two kernel streams)
+  if (mode == 1) SLC_CUDA(cudaStreamSynchronize(main_s));
   SLC_CUDA(cudaStreamSynchronize(m->pipe_out));
-  SLC_CUDA(cudaStreamSynchronize(m->pipe_in));
-  SLC_CUDA(cudaStreamSynchronize(main_s));
+  if (trace) {
+    cudaStreamSynchronize(m->pipe_in);
+    cudaStreamSynchronize(main_s);
+    fprintf(stderr, "slc e2e trace (ms after the call started): chunk rows | upload done | kernel done | download done\n");
+    for (int i = 0; i < nch && 3 * i + 3 < (int)tev.size(); ++i) {
+      float a = 0, b = 0, c = 0;
+      cudaEventElapsedTime(&a, tev[0], tev[3 * i + 1]);
+      cudaEventElapsedTime(&b, tev[0], tev[3 * i + 2]);
+      cudaEventElapsedTime(&c, tev[0], tev[3 * i + 3]);
+      fprintf(stderr, "  %2d [%8d, %8d) | %7.3f | %7.3f | %7.3f\n", i, cuts[i], cuts[i + 1], a, b, c);
+    }
+    for (auto e : tev) cudaEventDestroy(e);
+  }
   *done = true;
   return SLC_OK;
 }

@@ -1,3 +1,4 @@
+{-# LANGUAGE ExistentialQuantification #-}
 {-# LANGUAGE FlexibleContexts #-}
 {-# LANGUAGE ForeignFunctionInterface #-}
 {-# LANGUAGE RecordWildCards #-}
@@ -19,6 +20,18 @@
 --   * a negative status becomes 'errorWithStackTrace' with the library's message, which already
 --     carries the reference's prefix ("axpy_: ...", "mm: ...", "compress: ...").
 --
+-- UNCHANGED CALLERS.  `mulV a x` on an ordinary host 'Matrix' must not re-upload A on every call
+-- (SURVEY.md section 8(b): "a memo keyed on the host matrix").  'resident' below keeps one device copy
+-- per host matrix: the key is the 'StableName' of the record's @values@ vector (the heap object every
+-- copy of the record shares), the entry holds the device handle through a 'Weak' pointer keyed on that
+-- same vector, so the device copy is finalised (slc_free) when the host matrix is collected.  Every
+-- product, transpose and mm below goes through it.
+--
+-- THREADS.  A handle may be shared by several Haskell threads: the library serialises the calls that
+-- build plans or use the handle's transfer pipeline behind a per-handle mutex (csrc/slc_common.cuh,
+-- HandleLock), so two sparks forcing @mulV a x@ and @mulV a y@ are safe; they run one after the other.
+-- The foreign imports are 'safe' calls for that reason (a blocked call must not stop the capability).
+--
 -- The functions exported here have the types of their namesakes in Data.Matrix.Sparse
 -- (Data/Matrix/Sparse.hs:13-30), so replacing the import is the whole integration:
 --
@@ -26,13 +39,17 @@
 -- > import Data.Matrix.Sparse.Device
 module Data.Matrix.Sparse.Device
        ( DeviceMatrix, SlcElem
-       , toDevice, fromDevice
-       , mulV, axpy, axpy_, mulM_, mulVD
+       , toDevice, fromDevice, resident
+       , mulV, axpy, axpy_, mulM_, mulMAcc_, mulVD
        , mm, transpose, ctrans, hermitian
        , compress, fromTriples, lin
+         -- * one process, several GPUs (slc_*_upload_sharded ...)
+       , ShardedMatrix, toDevices, mulVS, mulMS_
        ) where
 
+import Control.Concurrent.MVar (MVar, modifyMVar, newMVar)
 import Control.Monad (when)
+import qualified Data.IntMap.Strict as IM
 import Data.Complex (Complex)
 import qualified Data.Vector.Storable as VS
 import qualified Data.Vector.Storable.Mutable as VSM
@@ -47,6 +64,9 @@ import Foreign.Ptr (FunPtr, Ptr, castPtr, nullPtr)
 import Foreign.Storable (Storable, peek)
 import GHC.Stack (errorWithStackTrace)
 import System.IO.Unsafe (unsafePerformIO)
+import System.Mem.StableName (StableName, eqStableName, hashStableName, makeStableName)
+import System.Mem.Weak (Weak, deRefWeak, mkWeak)
+import Unsafe.Coerce (unsafeCoerce)
 
 import Data.Matrix.Sparse (Matrix(..))
 import Data.Matrix.Sparse.Foreign (fromForeign, withConstMatrix)
@@ -65,7 +85,7 @@ foreign import ccall unsafe "slc_dims"
 type Upload a = CInt -> CInt -> Ptr CInt -> Ptr CInt -> Ptr a -> Ptr (Ptr SlcMatrix) -> IO CInt
 type Download a = Ptr SlcMatrix -> Ptr CInt -> Ptr CInt -> Ptr a -> IO CInt
 type MulV a = Ptr SlcMatrix -> Ptr a -> Ptr a -> IO CInt
-type MulM a = Ptr SlcMatrix -> Ptr a -> CLLong -> Ptr a -> CLLong -> CInt -> IO CInt
+type MulM a = Ptr SlcMatrix -> Ptr a -> CLLong -> Ptr a -> CLLong -> CInt -> Ptr a -> IO CInt
 type Binary = Ptr SlcMatrix -> Ptr SlcMatrix -> Ptr (Ptr SlcMatrix) -> IO CInt
 type Transpose = Ptr SlcMatrix -> CInt -> Ptr (Ptr SlcMatrix) -> IO CInt
 type Hermitian = Ptr SlcMatrix -> Ptr CInt -> IO CInt
@@ -167,9 +187,33 @@ fromDevice (DeviceMatrix fp) =
       c_download p pp pr pv >>= check
       fromForeign True nr nc pp pr pv
 
+-- | The memo for unchanged callers: host matrix -> its device copy (see the module header).
+-- Keys are compared with 'eqStableName' inside a bucket of the hash; a dead 'Weak' is dropped when met.
+data Entry = forall a. Entry (StableName (Vector a)) (Weak (DeviceMatrix a))
+
+{-# NOINLINE memo #-}
+memo :: MVar (IM.IntMap [Entry])
+memo = unsafePerformIO (newMVar IM.empty)
+
+-- | The device copy of a host matrix: uploaded on first use, reused afterwards, freed with the matrix.
+resident :: forall a. SlcElem a => Matrix Vector a -> IO (DeviceMatrix a)
+resident mat = do
+  key <- makeStableName (values mat)
+  let h = hashStableName key
+  modifyMVar memo $ \tbl -> do
+    let bucket = IM.findWithDefault [] h tbl
+    alive <- mapM (\e@(Entry k w) -> fmap (\m -> (e, k `eqStableName` key, unsafeCoerce m)) (deRefWeak w)) bucket
+    case [d | (_, True, Just d) <- alive] of
+      (d : _) -> return (tbl, d :: DeviceMatrix a)
+      [] -> do
+        d <- toDevice mat
+        w <- mkWeak (values mat) d Nothing      -- the ForeignPtr's own finalizer (slc_free) releases the HBM
+        let kept = [e | (e, _, Just (_ :: DeviceMatrix a)) <- alive]
+        return (IM.insert h (Entry key w : kept) tbl, d)
+
 onDevice :: SlcElem a => Matrix Vector a -> (Ptr SlcMatrix -> IO b) -> IO b
 onDevice mat act = do
-  DeviceMatrix fp <- toDevice mat
+  DeviceMatrix fp <- resident mat
   withForeignPtr fp act
 
 -- | y <- A x + y in place (axpy_, Data/Matrix/Sparse.hs:433-453), operands in host memory.
@@ -195,7 +239,7 @@ axpy a x y = unsafePerformIO $ do
 -- | A x (mulV, Data/Matrix/Sparse.hs:464-471).
 mulV :: SlcElem a => Matrix Vector a -> Vector a -> Vector a
 mulV a x = unsafePerformIO $ do
-  d <- toDevice a
+  d <- resident a            -- uploaded once per host matrix, not once per product
   mulVD d (nrows a) (ncols a) x
 
 -- | A x for a matrix that is already resident: repeated products never re-copy A.
@@ -214,7 +258,16 @@ mulM_ :: SlcElem a => DeviceMatrix a -> Int -> Int -> VSM.IOVector a -> VSM.IOVe
 mulM_ (DeviceMatrix fp) n k xs ys =
   withForeignPtr fp $ \p ->
   VSM.unsafeWith xs $ \px -> VSM.unsafeWith ys $ \py ->
-    c_mulm p px (fromIntegral n) py (fromIntegral n) (fromIntegral k) >>= check
+    c_mulm p px (fromIntegral n) py (fromIntegral n) (fromIntegral k) nullPtr >>= check
+
+-- | Y[:, j] <- A X[:, j] + Y[:, j]: the reference's 'axpy_' into blocks the caller filled
+-- (Data/Matrix/Sparse.hs:485-488), beta = 1 of slc_*_mulm.
+mulMAcc_ :: SlcElem a => DeviceMatrix a -> Int -> Int -> VSM.IOVector a -> VSM.IOVector a -> IO ()
+mulMAcc_ (DeviceMatrix fp) n k xs ys =
+  withForeignPtr fp $ \p ->
+  VSM.unsafeWith xs $ \px -> VSM.unsafeWith ys $ \py ->
+  with 1 $ \pone ->
+    c_mulm p px (fromIntegral n) py (fromIntegral n) (fromIntegral k) pone >>= check
 
 binary :: SlcElem a => Binary -> Matrix Vector a -> Matrix Vector a -> Matrix Vector a
 binary f a b = unsafePerformIO $
@@ -277,3 +330,59 @@ lin alpha a beta b
       alloca $ \out -> do
         c_lin pal pa pbe pb out >>= check
         adopt out >>= fromDevice
+
+-- ---------------------------------------------------------------------------------------------------
+-- One process, several GPUs: the sharded handle of include/slc.h.  The matrix is cut into row blocks,
+-- one per device, by the library; products take and return whole host vectors.
+
+data SlcSharded
+newtype ShardedMatrix a = ShardedMatrix (ForeignPtr SlcSharded)
+
+type UploadS a = CInt -> Ptr CInt -> CInt -> CInt -> Ptr CInt -> Ptr CInt -> Ptr a -> Ptr (Ptr SlcSharded) -> IO CInt
+type MulVS a = Ptr SlcSharded -> Ptr a -> Ptr a -> IO CInt
+type MulMS a = Ptr SlcSharded -> Ptr a -> CLLong -> Ptr a -> CLLong -> CInt -> IO CInt
+
+foreign import ccall unsafe "&slc_sharded_free" slc_sharded_free :: FunPtr (Ptr SlcSharded -> IO ())
+foreign import ccall "slc_d_upload_sharded" slc_d_upload_sharded :: UploadS Double
+foreign import ccall "slc_z_upload_sharded" slc_z_upload_sharded :: UploadS (Complex Double)
+foreign import ccall "slc_d_mulv_sharded" slc_d_mulv_sharded :: MulVS Double
+foreign import ccall "slc_z_mulv_sharded" slc_z_mulv_sharded :: MulVS (Complex Double)
+foreign import ccall "slc_d_mulm_sharded" slc_d_mulm_sharded :: MulMS Double
+foreign import ccall "slc_z_mulm_sharded" slc_z_mulm_sharded :: MulMS (Complex Double)
+
+class SlcElem a => SlcSharded a where
+  c_upload_sharded :: UploadS a
+  c_mulv_sharded :: MulVS a
+  c_mulm_sharded :: MulMS a
+
+instance SlcSharded Double where
+  c_upload_sharded = slc_d_upload_sharded
+  c_mulv_sharded = slc_d_mulv_sharded
+  c_mulm_sharded = slc_d_mulm_sharded
+
+instance SlcSharded (Complex Double) where
+  c_upload_sharded = slc_z_upload_sharded
+  c_mulv_sharded = slc_z_mulv_sharded
+  c_mulm_sharded = slc_z_mulm_sharded
+
+-- | Cut a host matrix into @ndev@ row blocks on devices 0 .. ndev-1.
+toDevices :: SlcSharded a => Int -> Matrix Vector a -> IO (ShardedMatrix a)
+toDevices ndev mat =
+  withConstMatrix mat $ \nr nc ptrs rows vals ->
+  alloca $ \out -> do
+    c_upload_sharded (fromIntegral ndev) nullPtr nr nc ptrs rows vals out >>= check
+    peek out >>= fmap ShardedMatrix . newForeignPtr slc_sharded_free
+
+-- | A x over all devices (mulV, Data/Matrix/Sparse.hs:464-471).
+mulVS :: SlcSharded a => ShardedMatrix a -> Int -> Vector a -> IO (Vector a)
+mulVS (ShardedMatrix fp) nr x = withForeignPtr fp $ \p -> do
+  ys <- VSM.new nr
+  VS.unsafeWith (VS.convert x) $ \px -> VSM.unsafeWith ys $ \py -> c_mulv_sharded p px py >>= check
+  VS.convert <$> VS.freeze ys
+
+-- | FEAST's multiplyWork over all devices: k columns of column-major blocks with leading dimension n.
+mulMS_ :: SlcSharded a => ShardedMatrix a -> Int -> Int -> VSM.IOVector a -> VSM.IOVector a -> IO ()
+mulMS_ (ShardedMatrix fp) n k xs ys =
+  withForeignPtr fp $ \p ->
+  VSM.unsafeWith xs $ \px -> VSM.unsafeWith ys $ \py ->
+    c_mulm_sharded p px (fromIntegral n) py (fromIntegral n) (fromIntegral k) >>= check
