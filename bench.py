@@ -367,7 +367,7 @@ def spmm_kernel_name(plan):
         return "k_spmm_rows"
     maxlen = int(plan.split("max_rowlen=")[1].split()[0])
     if maxlen > 8:
-        return "k_spmm_brick / k_spmm_panel" if "brick=1" in plan else "k_spmm_panel"
+        return "k_spmm_planes" if "brick=1" in plan else "k_spmm_panel"
     return "k_spmm_short" if os.environ.get("SLC_SPMM_WINDOW", "1") == "0" else "k_spmm_window (TMA)"
 
 

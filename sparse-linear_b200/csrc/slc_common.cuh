@@ -397,6 +397,10 @@ int sort_pairs_u32(const uint32_t *src, uint32_t *ka, uint32_t *kb, uint32_t *va
                    int end_bit, bool iota_vals, uint32_t **res_k, uint32_t **res_v);
 int sort_pairs_u64(const uint64_t *src, uint64_t *ka, uint64_t *kb, uint32_t *va, uint32_t *vb, int64_t n,
                    int end_bit, bool iota_vals, uint64_t **res_k, uint32_t **res_v);
+// bucket sort: keys in [0, nkeys) read in place from src, values = the input positions; besides the
+// sorted pairs it fills ptr_out[0 .. nkeys] = first sorted position of every key value (n > 0).
+int sort_buckets_u32(const uint32_t *src, uint32_t *ka, uint32_t *kb, uint32_t *va, uint32_t *vb, int64_t n,
+                     int32_t nkeys, uint32_t **res_k, uint32_t **res_v, int32_t *ptr_out);
 
 // built in slc_transpose.cu
 template <class T>
@@ -409,12 +413,13 @@ int ensure_csr(slc_matrix *m);
 template <class T>
 int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, YInit<T> yi, bool *done);
 
-// built in slc_spmm_brick.cu: the register-blocked SpMM for 27-offset matrices (*done = it ran)
+// built in slc_spmm_brick.cu: the TMA-staged SpMM for 27-offset matrices (*done = it ran).  X is indexed
+// by column number; only its entries [xlo, xhi) exist (xhi < 0: all of [0, ncols)).
 int spmm_brick_try(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
-                   const YInit<double> &yi, int32_t row_begin, int32_t row_end, bool *done);
+                   const YInit<double> &yi, int32_t row_begin, int32_t row_end, int64_t xlo, int64_t xhi, bool *done);
 inline int spmm_brick_try(slc_matrix *, const double2 *, int64_t, double2 *, int64_t, int32_t, const YInit<double2> &,
-                          int32_t, int32_t, bool *done) {
-  *done = false;  // Complex Double rows of 27 entries keep the panel kernel (54 values per row do not fit registers)
+                          int32_t, int32_t, int64_t, int64_t, bool *done) {
+  *done = false;  // Complex Double rows of 27 entries keep the panel kernel
   return SLC_OK;
 }
 

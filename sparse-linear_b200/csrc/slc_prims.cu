@@ -190,11 +190,16 @@ __device__ __forceinline__ unsigned digit_peers(int d) {
 // threads hold neighbouring keys of the same digit, whose global positions are consecutive, so the
 // writes are coalesced runs instead of one sector per key.  IOTA: the values are the input positions
 // themselves (first pass of a sort that carries positions) and are not read.
-template <class K, bool IOTA>
+// PTRS (last pass of a 32-bit sort whose keys are bucket numbers): the pass also emits the bucket
+// pointers, ptr[r] = first sorted position whose key is >= r.  Inside a digit run of the tile two
+// neighbours of the parked tile are neighbours in the output, so a change of key between them is a
+// bucket boundary at a known position; the first key of each run has its predecessor in another
+// tile and is left to k_ptrs_run_starts.  This replaces a separate pass over the sorted keys.
+template <class K, bool IOTA, bool PTRS>
 __global__ void __launch_bounds__(RS_THREADS, 3)
 k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals_in, K *__restrict__ keys_out,
                 uint32_t *__restrict__ vals_out, int64_t n, int shift, int64_t ntiles,
-                const int32_t *__restrict__ hist_scanned, uint32_t zmask) {
+                const int32_t *__restrict__ hist_scanned, uint32_t zmask, int32_t *__restrict__ ptr_out) {
   extern __shared__ __align__(16) unsigned char rs_smem[];
   K *skeys = reinterpret_cast<K *>(rs_smem);                         // [RS_TILE]
   uint32_t *svals = reinterpret_cast<uint32_t *>(skeys + RS_TILE);   // [RS_TILE]
@@ -310,6 +315,32 @@ k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals
     const int64_t pos = (int64_t)gshift[d] + i;
     keys_out[pos] = kk;
     vals_out[pos] = svals[i];
+    if constexpr (PTRS) {
+      if (i > local_base[d]) {
+        const K pk = skeys[i - 1];
+        for (int64_t r = (int64_t)pk + 1; r <= (int64_t)kk; ++r) ptr_out[r] = (int32_t)pos;
+      }
+    }
+  }
+}
+
+// The bucket boundaries k_radix_scatter<.., PTRS> could not see: the first key of every (digit, tile)
+// run, whose predecessor was written by another tile, and the tail after the last key.  One thread
+// per entry of the scanned histogram (digit-major, so the entries are in output order).
+__global__ void __launch_bounds__(256)
+k_ptrs_run_starts(int64_t n, int32_t nkeys, int64_t nentries, const int32_t *__restrict__ hist_scanned,
+                  const uint32_t *__restrict__ sorted, int32_t *__restrict__ ptr) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nentries) return;
+  const int64_t start = hist_scanned[j];
+  const int64_t end = j + 1 < nentries ? (int64_t)hist_scanned[j + 1] : n;
+  if (end <= start) return;
+  const int64_t cur = sorted[start];
+  const int64_t prev = start > 0 ? (int64_t)sorted[start - 1] : -1;
+  for (int64_t r = prev + 1; r <= cur; ++r) ptr[r] = (int32_t)start;
+  if (end == n) {
+    const int64_t last = sorted[n - 1];
+    for (int64_t r = last + 1; r <= nkeys; ++r) ptr[r] = (int32_t)n;
   }
 }
 
@@ -317,9 +348,19 @@ k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals
 // scratch.  The first pass reads its keys from `src` when given (which is left untouched) and from ka
 // otherwise; its values are va, or the positions 0..n-1 when iota_vals.  *res_k / *res_v say which
 // scratch buffers hold the sorted pairs.
+template <class K, bool IOTA, bool PTRS>
+static void launch_scatter(const K *kin, const uint32_t *vin, K *kout, uint32_t *vout, int64_t n, int shift,
+                           int64_t ntiles, const int32_t *hist, int32_t *ptr_out, cudaStream_t s) {
+  k_radix_scatter<K, IOTA, PTRS><<<(unsigned)ntiles, RS_THREADS, radix_scatter_smem<K>(), s>>>(
+      kin, vin, kout, vout, n, shift, ntiles, hist, 0u, ptr_out);
+}
+
+// ptr_out (32-bit keys only): also produce ptr_out[0 .. nkeys], the first sorted position of every key
+// value, fused into the last pass.
 template <class K>
 static int sort_pairs_impl(const K *src, K *ka, K *kb, uint32_t *va, uint32_t *vb, int64_t n, int end_bit,
-                           bool iota_vals, K **res_k, uint32_t **res_v) {
+                           bool iota_vals, K **res_k, uint32_t **res_v, int32_t *ptr_out = nullptr,
+                           int32_t nkeys = 0) {
   *res_k = ka;
   *res_v = va;
   if (n <= 0) return SLC_OK;
@@ -332,9 +373,16 @@ static int sort_pairs_impl(const K *src, K *ka, K *kb, uint32_t *va, uint32_t *v
   const int64_t ntiles = ceil_div(n, RS_TILE);
   DevBuf<int32_t> hist;
   SLC_TRY(hist.alloc((size_t)ntiles * RS_BINS));
-  static PerDevice<size_t> smem_a, smem_b;  // per instantiation (K), per device
-  SLC_CUDA(ensure_dyn_smem(k_radix_scatter<K, false>, smem_a, radix_scatter_smem<K>()));
-  SLC_CUDA(ensure_dyn_smem(k_radix_scatter<K, true>, smem_b, radix_scatter_smem<K>()));
+  static PerDevice<size_t> smem_a, smem_b, smem_c, smem_d;  // per instantiation (K), per device
+  SLC_CUDA(ensure_dyn_smem(k_radix_scatter<K, false, false>, smem_a, radix_scatter_smem<K>()));
+  SLC_CUDA(ensure_dyn_smem(k_radix_scatter<K, true, false>, smem_b, radix_scatter_smem<K>()));
+  constexpr bool CAN_PTRS = sizeof(K) == 4;
+  if constexpr (CAN_PTRS) {
+    SLC_CUDA(ensure_dyn_smem(k_radix_scatter<K, false, true>, smem_c, radix_scatter_smem<K>()));
+    SLC_CUDA(ensure_dyn_smem(k_radix_scatter<K, true, true>, smem_d, radix_scatter_smem<K>()));
+  } else if (ptr_out) {
+    return fail(SLC_ERR_INVALID, "radix sort: bucket pointers need 32-bit keys");
+  }
   const K *kin = src ? src : ka;
   const uint32_t *vin = va;
   K *kout = src ? ka : kb;
@@ -345,13 +393,25 @@ static int sort_pairs_impl(const K *src, K *ka, K *kb, uint32_t *va, uint32_t *v
     k_radix_hist<K><<<(unsigned)ntiles, RS_THREADS, 0, s>>>(kin, n, shift, ntiles, hist.p);
     SLC_LAUNCHED();
     SLC_TRY(exclusive_scan_i32(hist.p, hist.p, ntiles * RS_BINS));
-    if (p == 0 && iota_vals)
-      k_radix_scatter<K, true><<<(unsigned)ntiles, RS_THREADS, radix_scatter_smem<K>(), s>>>(kin, nullptr, kout, vout, n,
-                                                                                           shift, ntiles, hist.p, 0u);
-    else
-      k_radix_scatter<K, false><<<(unsigned)ntiles, RS_THREADS, radix_scatter_smem<K>(), s>>>(kin, vin, kout, vout, n,
-                                                                                            shift, ntiles, hist.p, 0u);
+    const bool iota = p == 0 && iota_vals;
+    const bool ptrs = ptr_out != nullptr && p == passes - 1;
+    if constexpr (CAN_PTRS) {
+      if (ptrs && iota) launch_scatter<K, true, true>(kin, nullptr, kout, vout, n, shift, ntiles, hist.p, ptr_out, s);
+      else if (ptrs) launch_scatter<K, false, true>(kin, vin, kout, vout, n, shift, ntiles, hist.p, ptr_out, s);
+    }
+    if (!ptrs) {
+      if (iota) launch_scatter<K, true, false>(kin, nullptr, kout, vout, n, shift, ntiles, hist.p, nullptr, s);
+      else launch_scatter<K, false, false>(kin, vin, kout, vout, n, shift, ntiles, hist.p, nullptr, s);
+    }
     SLC_LAUNCHED();
+    if constexpr (CAN_PTRS) {
+      if (ptrs) {
+        const int64_t nentries = ntiles * RS_BINS;
+        k_ptrs_run_starts<<<(unsigned)ceil_div(nentries, 256), 256, 0, s>>>(n, nkeys, nentries, hist.p,
+                                                                          reinterpret_cast<const uint32_t *>(kout), ptr_out);
+        SLC_LAUNCHED();
+      }
+    }
     *res_k = kout;
     *res_v = vout;
     kin = kout;
@@ -365,6 +425,11 @@ static int sort_pairs_impl(const K *src, K *ka, K *kb, uint32_t *va, uint32_t *v
 int sort_pairs_u32(const uint32_t *src, uint32_t *ka, uint32_t *kb, uint32_t *va, uint32_t *vb, int64_t n,
                    int end_bit, bool iota_vals, uint32_t **res_k, uint32_t **res_v) {
   return sort_pairs_impl<uint32_t>(src, ka, kb, va, vb, n, end_bit, iota_vals, res_k, res_v);
+}
+int sort_buckets_u32(const uint32_t *src, uint32_t *ka, uint32_t *kb, uint32_t *va, uint32_t *vb, int64_t n,
+                     int32_t nkeys, uint32_t **res_k, uint32_t **res_v, int32_t *ptr_out) {
+  return sort_pairs_impl<uint32_t>(src, ka, kb, va, vb, n, bits_for((uint32_t)nkeys), true, res_k, res_v, ptr_out,
+                                   nkeys);
 }
 int sort_pairs_u64(const uint64_t *src, uint64_t *ka, uint64_t *kb, uint32_t *va, uint32_t *vb, int64_t n,
                    int end_bit, bool iota_vals, uint64_t **res_k, uint32_t **res_v) {

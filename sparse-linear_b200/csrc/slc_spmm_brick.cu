@@ -3,25 +3,32 @@
 // FEAST-shaped op of Feast.hs:203-208 on the headline matrix.
 //
 // What round 1's k_spmm_panel ran into (ncu, profiles/r1g_ncu_full_spmm_panel_cfg5mm.txt): one gather of X
-// per product -- 443 M warp requests of ~2.9 L1 lines each, 38 GB from L2 to L1, 3.5 x the algorithmic
-// bytes -- and A re-read from shared memory for every product.  The ceiling was the L1 tag stage, not HBM.
-// This kernel removes loads instead of scheduling them better:
+// per product through L1 -- 443 M warp requests of ~2.9 cache lines each (the +-1 and +-L neighbours are
+// misaligned), 38 GB from L2 to L1 -- plus the column index and value of every product re-read from
+// shared memory.  The ceiling was the L1 tag stage (74 % busy), not HBM.
 //
+// Round 2, first attempt (kept in git history, profiles/r2_ncu_brick_registers.txt): rows that are
+// neighbours in y owned by one thread with all their values in registers, X through L1.  255 registers,
+// 8 warps per SM, every L1 miss exposed: 8.6-9.5 ms against the panel kernel's 6.3 ms.  Dropped.
+//
+// This kernel (k_spmm_planes) takes the gathers off the L1 path instead:
 //   * the matrix is detected to have every row's columns in  row + shift + {a P + b L + c : a, b, c in
 //     {-1, 0, 1}}  (P, L = plane and line strides, read off one row and then VERIFIED for all rows by the
 //     plan builder; anything else keeps the panel kernel).  The values are stored by offset slot,
 //     dia[slot][row] -- no column indices at all -- plus one 27-bit presence mask per row (grid
 //     boundaries drop entries; an absent entry must not be added, not even as 0 * x);
-//   * a thread owns R rows that are neighbours in y (row, row + L, ...) and keeps their R x 27 values in
-//     REGISTERS for all k columns (A is read from HBM exactly once and never again, from any memory);
-//   * the rows of a thread share X: lines y-1 .. y+R of the three planes, 9 (R + 2) loads for 27 R
-//     products (0.67 loads per product at R = 2, 0.56 at R = 3, against 1);
-//   * a block is a brick of 4 planes x (2 R lines) x 32 grid points, so the (6 x (2R+2) x 34)-point box of X
-//     it touches is fetched from L2 once (L1 serves the reuse between the block's warps): ~2.4 x the
-//     algorithmic bytes of X instead of 9 x.
-// Every (row, column) is still owned by one thread which adds the row's terms in increasing column
-// order (plane, then line, then point), product and sum rounded separately: bit-identical to the
-// reference (Sparse.hs:433-453), checked against the oracle at full size.
+//   * a block owns PL_ROWS consecutive rows.  The entries of X they touch are three contiguous windows
+//     (one per plane offset a) of PL_ROWS + 2 L + 2 entries: a producer lane has the TMA engine copy
+//     them from L2 into shared memory (cp.async.bulk, completion on an mbarrier), JT columns per
+//     pipeline stage, nstage stages in flight -- no register, LSU instruction or L1 line is spent on
+//     fetching X, and the 27 reads per row hit shared memory at fixed offsets (t + b L + c): always
+//     two wavefronts per warp, whatever the alignment;
+//   * a thread keeps its row's 27 values in registers for all k columns (A is read from HBM once).
+// Every (row, column) is owned by one thread which adds the row's terms in increasing column order
+// (plane, then line, then point), product and sum rounded separately: bit-identical to the reference
+// (Sparse.hs:433-453), checked against the oracle at full size.
+// Every mbarrier wait is bounded (as in slc_spmm_window.cu): a protocol bug raises the window error
+// flag and gives a wrong answer that the parity tests catch; it cannot hang the GPU.
 #include <algorithm>
 #include <vector>
 
@@ -30,9 +37,9 @@
 namespace slc {
 
 constexpr uint32_t BRICK_FULL = (1u << 27) - 1u;
-constexpr int BRICK_BZ = 4;        // planes per block (warp & 3)
-constexpr int BRICK_YG = 2;        // y-groups per block (warp >> 2)
-constexpr int BRICK_THREADS = 32 * BRICK_BZ * BRICK_YG;
+constexpr int PL_ROWS = 512;                 // rows per block = consumer threads
+constexpr int PL_THREADS = PL_ROWS + 32;     // + one producer warp
+constexpr uint32_t PL_SPIN_LIMIT = 1u << 22;
 
 // one thread per row: file the row's entries by offset slot; any entry off the pattern vetoes the plan
 template <class T>
@@ -65,8 +72,7 @@ static int brick_plan(slc_matrix *m) {
   BrickPlan &bp = m->brick;
   if (bp.state >= 0) return SLC_OK;
   bp.state = 0;
-  static const int env = env_int("SLC_SPMM_BRICK", 1);
-  if (!env || m->elem != ELEM_D || !m->has_csr || m->max_rowlen != 27 || m->nrows < 1024) return SLC_OK;
+  if (m->elem != ELEM_D || !m->has_csr || m->max_rowlen != 27 || m->nrows < 1024) return SLC_OK;
   cudaStream_t s = cur_stream();
   // a row with all 27 entries near the middle of the matrix (the very middle row of an even grid sits on a
   // grid face): scan the pointers of a window of rows
@@ -122,133 +128,214 @@ static int brick_plan(slc_matrix *m) {
   return SLC_OK;
 }
 
+// ---- mbarrier / bulk-copy primitives (see slc_spmm_window.cu) ------------------------------------------
+
+__device__ __forceinline__ uint32_t pl_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void pl_mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(pl_smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void pl_mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(pl_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void pl_mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pl_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool pl_mbar_wait(uint64_t *bar, uint32_t parity, int *err) {
+  for (uint32_t spin = 0; spin < PL_SPIN_LIMIT; ++spin) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(pl_smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (ok) return true;
+  }
+  *(volatile int *)err = 3;  // mapped host word: a plain store
+  return false;
+}
+__device__ __forceinline__ void pl_bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(pl_smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(pl_smem_u32(bar))
+               : "memory");
+}
+
 // ---- the product ---------------------------------------------------------------------------------------
-// Thread (warp w, lane): plane z = z0 + (w & 3), lines y0 + (w >> 2) R + i for i < R, point x = x0 + lane.
-// Global row index g = z P + y L + x; the stored row is g - shift (row blocks of a partitioned matrix keep
-// their global column numbering).  Rows outside [row_begin, row_end) are left alone: a distributed product
-// runs its boundary planes elsewhere.
-template <int R, int JT, bool FULL>
-__device__ __forceinline__ void brick_columns(const double (&a)[R][27], const uint32_t (&msk)[R], const bool (&live)[R],
-                                              const int64_t g0, const int32_t L, const int32_t P, const int64_t ncols,
-                                              const double *__restrict__ X, const int64_t ldx, double *__restrict__ Y,
-                                              const int64_t ldy, const int64_t (&row)[R], const int32_t k,
-                                              const YInit<double> &yi, const uint64_t pol_x) {
-  for (int32_t j0 = 0; j0 < k; j0 += JT) {
-    const int32_t jn = min(JT, k - j0);  // columns of this tile (JT except in the last one)
-    double acc[R][JT];
+// Block b owns rows [row_begin + b PL_ROWS, ...) of the launch's range.  Window a (a = 0, 1, 2) holds the
+// entries of X[:, j] with index in [lo_a, lo_a + W): lo_a = first row + shift + (a - 1) P - L - 1 rounded
+// down to an even index (16-byte alignment of the copy), clipped to the entries of X that exist: [0, ncols),
+// or the owned slice when the interior rows of a partitioned matrix run here.  Thread t reads slot
+// (a, b, c) of its row at window index t + d_a + b L + c, d_a = the rounding.
+
+// the 27 terms of one column tile, X read from the staged windows
+template <int JT, bool FULL>
+__device__ __forceinline__ void planes_tile(const double (&a)[27], const uint32_t msk, const double *__restrict__ xs,
+                                            const int32_t W, const int32_t L, const int32_t (&off)[3], const int jn,
+                                            double (&acc)[JT]) {
 #pragma unroll
-    for (int i = 0; i < R; ++i)
+  for (int pa = 0; pa < 3; ++pa) {
 #pragma unroll
-      for (int j = 0; j < JT; ++j) acc[i][j] = (live[i] && j < jn) ? yi(Y + (int64_t)(j0 + j) * ldy + row[i]) : 0.0;
-    const double *xt = X + (int64_t)j0 * ldx;
+    for (int b = 0; b < 3; ++b) {
+      const double *xl = xs + (int64_t)pa * W + off[pa] + b * L;
 #pragma unroll
-    for (int pa = 0; pa < 3; ++pa) {
+      for (int c = 0; c < 3; ++c) {
+        const int slot = pa * 9 + b * 3 + c;
+        if (FULL || ((msk >> slot) & 1u)) {
 #pragma unroll
-      for (int bq = 0; bq < R + 2; ++bq) {  // line y0 + bq - 1 of plane z + pa - 1
-        const int64_t col0 = g0 + (int64_t)(pa - 1) * P + (int64_t)(bq - 1) * L;  // the point straight below/above
-        double xv[3][JT];
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          int64_t col = col0 + (c - 1);
-          if (!FULL) col = min(max(col, (int64_t)0), ncols - 1);  // an absent entry may point outside X: never dereferenced out of range
-#pragma unroll
-          for (int j = 0; j < JT; ++j) xv[c][j] = (FULL || j < jn) ? ld_gather(xt + (int64_t)j * ldx + col, pol_x) : 0.0;
-        }
-#pragma unroll
-        for (int i = 0; i < R; ++i) {
-          const int b = bq - i;  // this line is offset b - 1 of row i
-          if (b < 0 || b > 2) continue;
-#pragma unroll
-          for (int c = 0; c < 3; ++c) {
-            const int slot = pa * 9 + b * 3 + c;
-            if (FULL || ((msk[i] >> slot) & 1u)) {
-#pragma unroll
-              for (int j = 0; j < JT; ++j) acc[i][j] = __dadd_rn(__dmul_rn(a[i][slot], xv[c][j]), acc[i][j]);
-            }
-          }
+          for (int j = 0; j < JT; ++j)
+            if (FULL || j < jn) acc[j] = __dadd_rn(__dmul_rn(a[slot], xl[(int64_t)j * 3 * W + c]), acc[j]);
         }
       }
     }
-#pragma unroll
-    for (int i = 0; i < R; ++i)
-#pragma unroll
-      for (int j = 0; j < JT; ++j)
-        if (live[i] && j < jn) st_stream(Y + (int64_t)(j0 + j) * ldy + row[i], acc[i][j]);
   }
 }
 
-template <int R, int JT>
-__global__ void __launch_bounds__(BRICK_THREADS, 1)
-k_spmm_brick(int32_t row_begin, int32_t row_end, int64_t shift, int32_t L, int32_t P, int32_t Ny, int64_t z_first,
-             int32_t nbx, int32_t nby, int64_t nrows_pad, int64_t ncols, const double *__restrict__ dia,
-             const uint32_t *__restrict__ mask, const double *__restrict__ X, int64_t ldx, double *__restrict__ Y,
-             int64_t ldy, int32_t k, const YInit<double> yi) {
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int32_t bx = blockIdx.x % nbx, by = (blockIdx.x / nbx) % nby;
-  const int64_t bz = blockIdx.x / ((int64_t)nbx * nby);
-  const int64_t z = z_first + bz * BRICK_BZ + (w & (BRICK_BZ - 1));
-  const int32_t y0 = (by * BRICK_YG + (w >> 2)) * R;
-  const int32_t x = bx * 32 + lane;
-  const int64_t g0 = z * P + (int64_t)y0 * L + x;
-  const uint64_t pol_x = policy_evict_last();
+template <int JT>
+__global__ void __launch_bounds__(PL_THREADS, 1)
+k_spmm_planes(int32_t row_begin, int32_t row_end, int64_t shift, int32_t L, int32_t P, int64_t nrows_pad, int64_t xlo,
+              int64_t xhi, int32_t nstage, int32_t W, const double *__restrict__ dia, const uint32_t *__restrict__ mask,
+              const double *__restrict__ X, int64_t ldx, double *__restrict__ Y, int64_t ldy, int32_t k,
+              const YInit<double> yi, int *__restrict__ err) {
+  extern __shared__ __align__(128) unsigned char pl_smem[];
+  double *stage0 = reinterpret_cast<double *>(pl_smem);                                  // [nstage][JT][3][W]
+  const size_t stage_elems = (size_t)JT * 3 * W;
+  uint64_t *full = reinterpret_cast<uint64_t *>(pl_smem + (size_t)nstage * stage_elems * sizeof(double));  // [nstage]
+  uint64_t *empty = full + nstage;                                                       // [nstage]
+  const int tid = threadIdx.x;
+  const int64_t row0 = (int64_t)row_begin + (int64_t)blockIdx.x * PL_ROWS;
+  if (tid == 0) {
+    for (int st = 0; st < nstage; ++st) {
+      pl_mbar_init(full + st, 1);
+      pl_mbar_init(empty + st, PL_ROWS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  // window a: [lo[a], lo[a] + W) in X's row numbering, before clipping
+  int64_t lo[3];
+#pragma unroll
+  for (int pa = 0; pa < 3; ++pa) {
+    const int64_t l = row0 + shift + (int64_t)(pa - 1) * P - L - 1;
+    lo[pa] = l - (l & 1);
+  }
+  const int32_t ntiles = (k + JT - 1) / JT;
+
+  if (tid >= PL_ROWS) {
+    // ---- producer: one lane feeds the ring -------------------------------------------------------
+    if ((tid & 31) != 0) return;
+    int64_t c0[3], c1[3];  // clipped copy range of every window
+    uint32_t bytes_col = 0;
+#pragma unroll
+    for (int pa = 0; pa < 3; ++pa) {
+      c0[pa] = max(lo[pa], xlo);  // [xlo, xhi): the entries of X that exist (even bounds)
+      c1[pa] = min(lo[pa] + W, xhi);
+      if (c1[pa] > c0[pa]) bytes_col += (uint32_t)(c1[pa] - c0[pa]) * (uint32_t)sizeof(double);
+    }
+    int32_t st = 0, use = 0;
+    for (int32_t t = 0; t < ntiles; ++t) {
+      const int32_t jn = min(JT, k - t * JT);
+      if (use > 0 && !pl_mbar_wait(empty + st, (uint32_t)((use - 1) & 1), err)) return;
+      pl_mbar_arrive_expect_tx(full + st, bytes_col * (uint32_t)jn);
+      double *dst = stage0 + (size_t)st * stage_elems;
+      for (int32_t j = 0; j < jn; ++j) {
+        const double *xc = X + (int64_t)(t * JT + j) * ldx;
+#pragma unroll
+        for (int pa = 0; pa < 3; ++pa)
+          if (c1[pa] > c0[pa])
+            pl_bulk_g2s(dst + ((size_t)j * 3 + pa) * W + (c0[pa] - lo[pa]), xc + c0[pa],
+                        (uint32_t)(c1[pa] - c0[pa]) * (uint32_t)sizeof(double), full + st);
+      }
+      if (bytes_col == 0) pl_mbar_arrive(full + st);  // nothing to copy: cannot happen for a row that has entries
+      if (++st == nstage) {
+        st = 0;
+        ++use;
+      }
+    }
+    return;
+  }
+
+  // ---- consumers ---------------------------------------------------------------------------------------
   const uint64_t pol_s = policy_evict_first();
-  double a[R][27];
-  uint32_t msk[R];
-  bool live[R];
-  int64_t row[R];
-  bool all_full = true;
+  const int64_t row = row0 + tid;
+  const bool live = row < row_end;
+  const uint32_t msk = live ? __ldg(mask + row) : 0u;
+  double a[27];
 #pragma unroll
-  for (int i = 0; i < R; ++i) {
-    row[i] = g0 + (int64_t)i * L - shift;
-    live[i] = x < L && y0 + i < Ny && row[i] >= row_begin && row[i] < row_end;
-    msk[i] = live[i] ? __ldg(mask + row[i]) : 0u;
-    all_full = all_full && msk[i] == BRICK_FULL;
+  for (int s = 0; s < 27; ++s) a[s] = live ? ld_stream(dia + (int64_t)s * nrows_pad + row, pol_s) : 0.0;
+  int32_t off[3];
 #pragma unroll
-    for (int s = 0; s < 27; ++s) a[i][s] = live[i] ? ld_stream(dia + (int64_t)s * nrows_pad + row[i], pol_s) : 0.0;
+  for (int pa = 0; pa < 3; ++pa) off[pa] = (int32_t)(row + shift + (int64_t)(pa - 1) * P - L - 1 - lo[pa]);
+  const bool full_warp = __all_sync(0xffffffffu, msk == BRICK_FULL);
+  int32_t st = 0;
+  uint32_t parity = 0;
+  for (int32_t t = 0; t < ntiles; ++t) {
+    const int32_t j0 = t * JT, jn = min(JT, k - j0);
+    double acc[JT];
+#pragma unroll
+    for (int j = 0; j < JT; ++j) acc[j] = (live && j < jn) ? yi(Y + (int64_t)(j0 + j) * ldy + row) : 0.0;
+    if (!pl_mbar_wait(full + st, parity, err)) return;
+    const double *xs = stage0 + (size_t)st * stage_elems;
+    if (full_warp && jn == JT) planes_tile<JT, true>(a, msk, xs, W, L, off, jn, acc);
+    else planes_tile<JT, false>(a, msk, xs, W, L, off, jn, acc);
+    pl_mbar_arrive(empty + st);  // this thread is done reading the stage
+#pragma unroll
+    for (int j = 0; j < JT; ++j)
+      if (live && j < jn) st_stream(Y + (int64_t)(j0 + j) * ldy + row, acc[j]);
+    if (++st == nstage) {
+      st = 0;
+      parity ^= 1u;
+    }
   }
-  bool any = false;
-#pragma unroll
-  for (int i = 0; i < R; ++i) any = any || live[i];
-  if (!__any_sync(0xffffffffu, any)) return;
-  // interior warps (every lane has all 27 entries in all its rows, and whole column tiles): no predicates
-  if (__all_sync(0xffffffffu, all_full) && k % JT == 0)
-    brick_columns<R, JT, true>(a, msk, live, g0, L, P, ncols, X, ldx, Y, ldy, row, k, yi, pol_x);
-  else
-    brick_columns<R, JT, false>(a, msk, live, g0, L, P, ncols, X, ldx, Y, ldy, row, k, yi, pol_x);
 }
 
-template <int R, int JT>
-static int launch_brick(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
-                        const YInit<double> &yi, int32_t row_begin, int32_t row_end) {
+int spmm_window_err_word(int **out);  // slc_spmm_window.cu: the mapped host word both staged kernels raise
+
+template <int JT>
+static int launch_planes(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
+                         const YInit<double> &yi, int32_t row_begin, int32_t row_end, int64_t xlo, int64_t xhi,
+                         int32_t nstage, int32_t W) {
   const BrickPlan &bp = m->brick;
-  const int32_t Ny = bp.P / bp.L;
-  const int64_t z_first = (row_begin + bp.shift) / bp.P, z_last = (row_end - 1 + bp.shift) / bp.P;
-  const int32_t nbx = (int32_t)ceil_div(bp.L, 32), nby = (int32_t)ceil_div(Ny, BRICK_YG * R);
-  const int64_t nbz = ceil_div(z_last - z_first + 1, BRICK_BZ);
-  const int64_t nb = (int64_t)nbx * nby * nbz;
-  if (nb > 0x7fffffffLL) return fail(SLC_ERR_RANGE, "mulM: grid too large");
-  k_spmm_brick<R, JT><<<(unsigned)nb, BRICK_THREADS, 0, cur_stream()>>>(
-      row_begin, row_end, bp.shift, bp.L, bp.P, Ny, z_first, nbx, nby, bp.nrows_pad, m->ncols, bp.dia, bp.mask, X, ldx, Y,
-      ldy, k, yi);
+  const size_t smem = (size_t)nstage * JT * 3 * W * sizeof(double) + (size_t)nstage * 2 * sizeof(uint64_t);
+  auto kern = k_spmm_planes<JT>;
+  static PerDevice<size_t> smem_set;  // per instantiation, per device
+  SLC_CUDA(ensure_dyn_smem(kern, smem_set, smem));
+  int *err_flag = nullptr;
+  SLC_TRY(spmm_window_err_word(&err_flag));
+  const int64_t nb = ceil_div((int64_t)row_end - row_begin, PL_ROWS);
+  kern<<<(unsigned)nb, PL_THREADS, smem, cur_stream()>>>(row_begin, row_end, bp.shift, bp.L, bp.P, bp.nrows_pad, xlo, xhi,
+                                                        nstage, W, bp.dia, bp.mask, X, ldx, Y, ldy, k, yi, err_flag);
   SLC_LAUNCHED();
   return SLC_OK;
 }
 
-// Runs rows [row_begin, row_end) of the block product on the brick kernel when the matrix has the plan.
+// Runs rows [row_begin, row_end) of the block product on the staged kernel when the matrix has the plan
+// and the operands qualify (X 16-byte aligned, even column stride and bounds, windows that fit).  X is
+// indexed by column number and only its entries [xlo, xhi) exist (xhi < 0: all of [0, ncols)).
 int spmm_brick_try(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
-                   const YInit<double> &yi, int32_t row_begin, int32_t row_end, bool *done) {
+                   const YInit<double> &yi, int32_t row_begin, int32_t row_end, int64_t xlo, int64_t xhi, bool *done) {
   *done = false;
+  if (xhi < 0) xhi = m->ncols;
+  const char *env = getenv("SLC_SPMM_BRICK");  // read on every call so a test can switch it
+  if (env && env[0] == '0') return SLC_OK;
+  if (k < 1 || row_end <= row_begin) return SLC_OK;
+  if (((uintptr_t)X & 15) != 0 || (ldx & 1) != 0 || (xlo & 1) != 0 || (xhi & 1) != 0) return SLC_OK;
   SLC_TRY(brick_plan(m));
-  if (m->brick.state != 1 || k < 1 || row_end <= row_begin) return SLC_OK;
-  static const int r_env = env_int("SLC_BRICK_R", 2);
-  static const int jt_env = env_int("SLC_BRICK_JT", 0);
-  const int jt = jt_env ? jt_env : (r_env == 3 ? 2 : 4);
-  if (r_env == 3 && jt <= 2) SLC_TRY((launch_brick<3, 2>(m, X, ldx, Y, ldy, k, yi, row_begin, row_end)));
-  else if (r_env == 3) SLC_TRY((launch_brick<3, 4>(m, X, ldx, Y, ldy, k, yi, row_begin, row_end)));
-  else if (r_env == 1) SLC_TRY((launch_brick<1, 8>(m, X, ldx, Y, ldy, k, yi, row_begin, row_end)));
-  else if (jt <= 2) SLC_TRY((launch_brick<2, 2>(m, X, ldx, Y, ldy, k, yi, row_begin, row_end)));
-  else if (jt >= 8) SLC_TRY((launch_brick<2, 8>(m, X, ldx, Y, ldy, k, yi, row_begin, row_end)));
-  else SLC_TRY((launch_brick<2, 4>(m, X, ldx, Y, ldy, k, yi, row_begin, row_end)));
+  if (m->brick.state != 1) return SLC_OK;
+  const int32_t W = (PL_ROWS + 2 * m->brick.L + 4 + 1) / 2 * 2;  // window entries incl. alignment slack, even
+  const size_t col_bytes = (size_t)3 * W * sizeof(double);
+  const size_t budget = 200 * 1024;
+  const int jt_env = env_int("SLC_PLANES_JT", 2);      // read on every call so a test can switch them
+  const int stage_env = env_int("SLC_PLANES_STAGES", 0);
+  int jt = jt_env >= 4 ? 4 : jt_env >= 2 ? 2 : 1;
+  while (jt > 1 && budget / (col_bytes * jt) < 3) jt >>= 1;
+  int32_t nstage = (int32_t)std::min<size_t>(8, budget / (col_bytes * jt));
+  if (nstage < 2) return SLC_OK;  // lines too long for shared memory: the panel kernel serves the product
+  if (stage_env >= 2) nstage = std::min(nstage, stage_env);
+  nstage = std::min(nstage, std::max(2, (k + jt - 1) / jt));
+  if (jt == 4) SLC_TRY((launch_planes<4>(m, X, ldx, Y, ldy, k, yi, row_begin, row_end, xlo, xhi, nstage, W)));
+  else if (jt == 2) SLC_TRY((launch_planes<2>(m, X, ldx, Y, ldy, k, yi, row_begin, row_end, xlo, xhi, nstage, W)));
+  else SLC_TRY((launch_planes<1>(m, X, ldx, Y, ldy, k, yi, row_begin, row_end, xlo, xhi, nstage, W)));
   *done = true;
   return SLC_OK;
 }

@@ -241,6 +241,8 @@ static int window_err_flag(int **out) {
   return SLC_OK;
 }
 
+int spmm_window_err_word(int **out) { return window_err_flag(out); }
+
 int spmm_window_error(int *flag) {
   *flag = 0;
   int *p = g_window_err.load(std::memory_order_acquire);

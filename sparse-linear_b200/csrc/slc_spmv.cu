@@ -1482,9 +1482,19 @@ static void pipeline_cuts(int32_t nrows, int want, int taper, std::vector<int32_
     const int32_t per = (int32_t)(ceil_div(ceil_div(nrows, want), 256) * 256);
     for (int64_t r = per; r < nrows; r += per) cuts.push_back((int32_t)r);
   } else {
-    const int big = want - 3;                       // equal pieces over the first 7/8 of the rows ...
-    const double body = 0.875 * nrows;
-    for (int i = 1; i <= big; ++i) cuts.push_back(round256(body * i / big));
+    // taper 2: the first pieces are small as well (1/64, 1/32, 1/16 of the rows) -- the downloads cannot
+    // start before the first piece has been uploaded and multiplied, and with both directions of the
+    // link busy for the rest of the call that lag is pure latency (trace, round 2: 0.31 ms with 8 equal
+    // pieces of the 27-point stencil's 64 MB vectors)
+    const double head = taper >= 2 ? 7.0 / 64.0 : 0.0;
+    if (taper >= 2) {
+      cuts.push_back(round256(nrows / 64.0));
+      cuts.push_back(round256(3.0 * nrows / 64.0));
+      cuts.push_back(round256(head * nrows));
+    }
+    const int big = want - 3;                       // equal pieces up to 7/8 of the rows ...
+    const double body = 0.875 * nrows - head * nrows;
+    for (int i = 1; i <= big; ++i) cuts.push_back(round256(head * nrows + body * i / big));
     cuts.push_back(round256(0.9375 * nrows));       // ... then 1/16, 1/32, 1/32
     cuts.push_back(round256(0.96875 * nrows));
   }
@@ -1502,7 +1512,7 @@ static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
   const int diag = env_int("SLC_E2E_DIAG", 0);          // timing diagnosis: 1 = no download, 2 = no upload, 4 = no kernels
   const int align_env = env_int("SLC_E2E_ALIGN", 512);
   const int mode = env_int("SLC_E2E_MODE", 0);          // 0 = three streams chained by events, 1 = downloads follow their kernels
-  const int taper = env_int("SLC_E2E_TAPER", 1);        // finer chunks at the end (see pipeline_cuts)
+  const int taper = env_int("SLC_E2E_TAPER", 2);        // 1: finer chunks at the end, 2: at both ends (see pipeline_cuts)
   const int trace = env_int("SLC_E2E_TRACE", 0);        // print a timeline of the call (timed events) to stderr
   const int want = chunks_env < 1 ? 1 : (chunks_env > PIPE_MAX_CHUNKS ? PIPE_MAX_CHUNKS : chunks_env);
   if (want == 1 || m->nnz == 0 || m->nrows < (1 << 18)) return SLC_OK;
@@ -1975,11 +1985,11 @@ static int launch_panel_inst(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64
 
 template <class T>
 static int launch_panel(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, const YInit<T> &yi,
-                        int32_t row_begin = 0, int32_t row_end = -1) {
+                        int32_t row_begin = 0, int32_t row_end = -1, int64_t xlo = 0, int64_t xhi = -1) {
   if (row_end < 0) row_end = m->nrows;
-  {  // 27-offset matrices: the register-blocked brick kernel (slc_spmm_brick.cu)
+  {  // 27-offset matrices: X staged in shared memory by the TMA engine (slc_spmm_brick.cu)
     bool done = false;
-    SLC_TRY(spmm_brick_try(m, X, ldx, Y, ldy, k, yi, row_begin, row_end, &done));
+    SLC_TRY(spmm_brick_try(m, X, ldx, Y, ldy, k, yi, row_begin, row_end, xlo, xhi, &done));
     if (done) return SLC_OK;
   }
   static const int threads_env = env_int("SLC_PANEL_THREADS", 0);
@@ -2146,7 +2156,8 @@ static int spmm_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   SLC_TRY(dist_interior(m, xa.self_lo, xa.self_hi, &r0, &r1));
   if (sync) SLC_TRY(slc_peer_signal(sync));  // "my rows of X are written" (stream order)
   // interior rows: columns are global, so shift the local block's base by the first owned row
-  SLC_TRY(launch_panel<T>(m, xa.self_X - xa.self_lo, xa.self_ld, (T *)Y, ldy, k, yinit_zero<T>(), r0, r1));
+  SLC_TRY(launch_panel<T>(m, xa.self_X - xa.self_lo, xa.self_ld, (T *)Y, ldy, k, yinit_zero<T>(), r0, r1, xa.self_lo,
+                          xa.self_hi));
   if (sync) SLC_TRY(slc_peer_wait(sync));
   const int64_t nb = ceil_div(r0, 128) + ceil_div(m->nrows - r1, 128);
   if (nb > 0) {

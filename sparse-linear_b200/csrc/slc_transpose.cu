@@ -5,41 +5,13 @@
 //
 // Device formulation: a stable LSD radix sort of (row index -> source position) over only the
 // bits a row index needs, reading the row indices in place; the output pointers fall out of the
-// sorted keys (first position of each key) with no histogram or atomics; the column of every
-// stored position is expanded once (k_expand_cols) and one gather kernel then moves column ids
-// and values.  (Round 1 searched colptr per entry inside the gather: 23 dependent loads each.)
+// last pass of the sort (a change of key between two neighbours is a row boundary: sort_buckets_u32)
+// with no histogram, atomics or extra pass over the sorted keys; the column of every stored
+// position is expanded once (k_expand_cols) and one gather kernel then moves column ids and values.
+// (Round 1 searched colptr per entry inside the gather: 23 dependent loads each.)
 #include "slc_common.cuh"
 
 namespace slc {
-
-// ptr[r] = first sorted position whose key is >= r, for r in [0, nkeys]; each entry is written by
-// exactly one thread (the one sitting on the boundary that passes r).  A thread takes 8 consecutive
-// keys (two 128-bit loads): with one key per thread the kernel was bound by thread turnover, not bytes.
-constexpr int PTR_ITEMS = 8;
-__global__ void __launch_bounds__(256)
-k_ptrs_from_sorted(int64_t n, int32_t nkeys, const uint32_t *__restrict__ sorted, int32_t *__restrict__ ptr) {
-  const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * PTR_ITEMS;
-  if (i0 > n) return;
-  uint32_t key[PTR_ITEMS];
-  if (i0 + PTR_ITEMS <= n) {
-    const uint4 a = *reinterpret_cast<const uint4 *>(sorted + i0);
-    const uint4 b = *reinterpret_cast<const uint4 *>(sorted + i0 + 4);
-    key[0] = a.x; key[1] = a.y; key[2] = a.z; key[3] = a.w;
-    key[4] = b.x; key[5] = b.y; key[6] = b.z; key[7] = b.w;
-  } else {
-#pragma unroll
-    for (int e = 0; e < PTR_ITEMS; ++e) key[e] = i0 + e < n ? sorted[i0 + e] : (uint32_t)nkeys;
-  }
-  int64_t prev = (i0 == 0) ? -1 : (int64_t)sorted[i0 - 1];
-#pragma unroll
-  for (int e = 0; e < PTR_ITEMS; ++e) {
-    const int64_t i = i0 + e;
-    if (i > n) break;
-    const int64_t cur = (i == n) ? (int64_t)nkeys : (int64_t)key[e];
-    for (int64_t r = prev + 1; r <= cur; ++r) ptr[r] = (int32_t)i;
-    prev = cur;
-  }
-}
 
 // column that owns stored position p: the c with colptr[c] <= p < colptr[c+1]
 __device__ __forceinline__ int32_t owner_of(const int32_t *__restrict__ ptr, int32_t n, int32_t p) {
@@ -52,24 +24,70 @@ __device__ __forceinline__ int32_t owner_of(const int32_t *__restrict__ ptr, int
   return lo - 1;
 }
 
-// colid[p] = the column that owns stored position p.  A thread takes 16 consecutive positions: one
-// binary search for the first, then a walk along colptr (empty columns are stepped over).
+// colid[p] = the column that owns stored position p, one block per tile of EXPAND_TILE positions.
+// k_tile_first_col records for every tile the column that owns its first position (a thread per
+// column writes the tiles whose first position falls inside that column), so a block knows its
+// column window without searching.  The window of colptr goes to shared memory; a thread then takes
+// 16 consecutive positions: one search of the window for the first, a walk along it for the rest
+// (empty columns are stepped over).  Round 1 searched all of colptr from global memory per thread,
+// 23 dependent L2 loads each -- latency, not bytes, was the limit (ncu: 0.58 ms for 0.86 GB).
 constexpr int EXPAND_ITEMS = 16;
-__global__ void k_expand_cols(int64_t nnz, int32_t ncols, const int32_t *__restrict__ colptr,
-                              uint32_t *__restrict__ colid) {
-  const int64_t p0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * EXPAND_ITEMS;
+constexpr int EXPAND_THREADS = 256;
+constexpr int EXPAND_TILE = EXPAND_ITEMS * EXPAND_THREADS;
+constexpr int EXPAND_WINDOW = EXPAND_TILE + 2;  // pointers of a window with no empty column, + 1
+
+__global__ void __launch_bounds__(256)
+k_tile_first_col(int32_t ncols, const int32_t *__restrict__ colptr, int32_t *__restrict__ tile_col) {
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncols) return;
+  const int64_t lo = colptr[c], hi = colptr[c + 1];
+  for (int64_t b = (lo + EXPAND_TILE - 1) / EXPAND_TILE; b * EXPAND_TILE < hi; ++b) tile_col[b] = (int32_t)c;
+}
+
+__global__ void __launch_bounds__(EXPAND_THREADS)
+k_expand_cols(int64_t nnz, int32_t ncols, int64_t ntiles, const int32_t *__restrict__ colptr,
+              const int32_t *__restrict__ tile_col, uint32_t *__restrict__ colid) {
+  __shared__ int32_t win[EXPAND_WINDOW];
+  const int32_t c_lo = tile_col[blockIdx.x];
+  const int32_t c_hi = (int64_t)blockIdx.x + 1 < ntiles ? tile_col[blockIdx.x + 1] : ncols - 1;
+  const int32_t span = c_hi - c_lo + 2;  // pointers colptr[c_lo .. c_hi + 1]
+  const bool staged = span <= EXPAND_WINDOW;
+  if (staged)
+    for (int32_t i = threadIdx.x; i < span; i += EXPAND_THREADS) win[i] = colptr[c_lo + i];
+  __syncthreads();
+  const int64_t p0 = (int64_t)blockIdx.x * EXPAND_TILE + (int64_t)threadIdx.x * EXPAND_ITEMS;
   if (p0 >= nnz) return;
-  int32_t c = owner_of(colptr, ncols, (int32_t)p0);
-  int32_t next = __ldg(colptr + c + 1);
   uint32_t out[EXPAND_ITEMS];
-#pragma unroll
-  for (int e = 0; e < EXPAND_ITEMS; ++e) {
-    const int64_t p = p0 + e;
-    while (p < nnz && next <= p) {  // p < nnz: some column owns p, so c + 1 stays below ncols
-      ++c;
-      next = __ldg(colptr + c + 1);
+  if (staged) {
+    int32_t lo = 0, hi = span - 1;  // first index in [0, span - 1] with win[idx] > p0; win[0] <= p0
+    while (lo < hi) {
+      const int32_t mid = lo + ((hi - lo) >> 1);
+      if (win[mid] <= (int32_t)p0) lo = mid + 1;
+      else hi = mid;
     }
-    out[e] = (uint32_t)c;
+    int32_t c = lo - 1;  // local column
+    int32_t next = win[c + 1];
+#pragma unroll
+    for (int e = 0; e < EXPAND_ITEMS; ++e) {
+      const int64_t p = p0 + e;
+      while (p < nnz && next <= p) {  // p < nnz: some column of the window owns p
+        ++c;
+        next = win[c + 1];
+      }
+      out[e] = (uint32_t)(c_lo + c);
+    }
+  } else {  // a window with many empty columns: search colptr itself, between the tile's bounds
+    int32_t c = c_lo + owner_of(colptr + c_lo, span - 1, (int32_t)p0);
+    int32_t next = __ldg(colptr + c + 1);
+#pragma unroll
+    for (int e = 0; e < EXPAND_ITEMS; ++e) {
+      const int64_t p = p0 + e;
+      while (p < nnz && next <= p) {
+        ++c;
+        next = __ldg(colptr + c + 1);
+      }
+      out[e] = (uint32_t)c;
+    }
   }
   if (p0 + EXPAND_ITEMS <= nnz) {
     uint4 *dst = reinterpret_cast<uint4 *>(colid + p0);  // p0 is a multiple of 16: 64-byte aligned
@@ -129,12 +147,15 @@ int transpose_csc(int32_t nrows, int32_t ncols, int64_t nnz, const int32_t *colp
   SLC_TRY(p1.alloc(nnz));
   // keys = the row indices, read in place by the first pass; values = source positions
   uint32_t *skey = nullptr, *sperm = nullptr;
-  SLC_TRY(sort_pairs_u32(reinterpret_cast<const uint32_t *>(rowidx), k0.p, k1.p, p0.p, p1.p, nnz,
-                         bits_for((uint32_t)nrows), true, &skey, &sperm));
-  k_ptrs_from_sorted<<<(unsigned)ceil_div(ceil_div(nnz + 1, PTR_ITEMS), 256), 256, 0, s>>>(nnz, nrows, skey, out_ptr);
-  SLC_LAUNCHED();
+  SLC_TRY(sort_buckets_u32(reinterpret_cast<const uint32_t *>(rowidx), k0.p, k1.p, p0.p, p1.p, nnz, nrows, &skey,
+                           &sperm, out_ptr));
   uint32_t *colid = (skey == k0.p) ? k1.p : k0.p;  // the key buffer the sort left free
-  k_expand_cols<<<(unsigned)ceil_div(ceil_div(nnz, EXPAND_ITEMS), 256), 256, 0, s>>>(nnz, ncols, colptr, colid);
+  const int64_t ntiles = ceil_div(nnz, EXPAND_TILE);
+  DevBuf<int32_t> tile_col;
+  SLC_TRY(tile_col.alloc((size_t)ntiles));
+  k_tile_first_col<<<(unsigned)ceil_div(ncols, 256), 256, 0, s>>>(ncols, colptr, tile_col.p);
+  SLC_LAUNCHED();
+  k_expand_cols<<<(unsigned)ntiles, EXPAND_THREADS, 0, s>>>(nnz, ncols, ntiles, colptr, tile_col.p, colid);
   SLC_LAUNCHED();
   k_transpose_gather<T><<<(unsigned)ceil_div(nnz, 256 * GATHER_ITEMS), 256, 0, s>>>(nnz, colid, vals, sperm, conj,
                                                                                   out_idx, out_vals);
