@@ -1512,7 +1512,7 @@ static int spmv_host_pipelined(slc_matrix *m, const T *x, T *y, bool *done) {
   const int diag = env_int("SLC_E2E_DIAG", 0);          // timing diagnosis: 1 = no download, 2 = no upload, 4 = no kernels
   const int align_env = env_int("SLC_E2E_ALIGN", 512);
   const int mode = env_int("SLC_E2E_MODE", 0);          // 0 = three streams chained by events, 1 = downloads follow their kernels
-  const int taper = env_int("SLC_E2E_TAPER", 2);        // 1: finer chunks at the end, 2: at both ends (see pipeline_cuts)
+  const int taper = env_int("SLC_E2E_TAPER", 1);        // 1: finer chunks at the end, 2: at both ends (measured no better: pipeline_cuts)
   const int trace = env_int("SLC_E2E_TRACE", 0);        // print a timeline of the call (timed events) to stderr
   const int want = chunks_env < 1 ? 1 : (chunks_env > PIPE_MAX_CHUNKS ? PIPE_MAX_CHUNKS : chunks_env);
   if (want == 1 || m->nnz == 0 || m->nrows < (1 << 18)) return SLC_OK;

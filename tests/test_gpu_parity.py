@@ -479,17 +479,22 @@ def _band27(n, L, P, rng, keep=1.0):
     return oracle.compress(n, n, r, cols[r, s], rng.uniform(-1, 1, len(r)))
 
 
-@pytest.mark.parametrize("jt", ["1", "2", "4"])
-def test_spmm_brick_matches_oracle(sl, monkeypatch, jt):
+@pytest.mark.parametrize("jt,rows,pair", [("1", "512", "0"), ("2", "512", "0"), ("4", "512", "0"), ("1", "256", "0"),
+                                          ("2", "256", "0"), ("1", "512", "384"), ("1", "512", "256")])
+def test_spmm_brick_matches_oracle(sl, monkeypatch, jt, rows, pair):
     """The TMA-staged kernel for 27-offset matrices (k_spmm_planes): bit-exact against the oracle for every
     column-tile width, with wrapped neighbours, holes (masked path), column counts that leave a partial
     tile, and the accumulate form."""
     monkeypatch.setenv("SLC_PLANES_JT", jt)
+    monkeypatch.setenv("SLC_PLANES_ROWS", rows)
+    monkeypatch.setenv("SLC_PLANES_PAIR", "0" if pair == "0" else "1")     # two rows per thread (even strides only)
+    monkeypatch.setenv("SLC_PLANES_CONS", pair)
     rng = np.random.default_rng(41)
     cases = [g.stencil3d_27pt((9, 10, 37)),            # line length not a multiple of 32, odd line count
              g.stencil3d_27pt((5, 16, 64)),
              _band27(6000, 50, 400, rng),              # wrapped neighbours present
-             _band27(5000, 24, 240, rng, keep=0.8)]    # holes: masked path everywhere
+             _band27(7000, 40, 400, rng, keep=0.97),   # a few holes, still a sliced plan: masked path of the kernel
+             _band27(5000, 24, 240, rng, keep=0.8)]    # many holes: balanced-CSR plan, the general kernel serves it
     for gm in cases:
         m, om = to_matrix(sl, gm), oracle.csc(*gm)
         for k in (1, 4, 7, 64):
