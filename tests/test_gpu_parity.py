@@ -490,18 +490,20 @@ def test_spmm_brick_matches_oracle(sl, monkeypatch, jt, rows, pair):
     monkeypatch.setenv("SLC_PLANES_PAIR", "0" if pair == "0" else "1")     # two rows per thread (even strides only)
     monkeypatch.setenv("SLC_PLANES_CONS", pair)
     rng = np.random.default_rng(41)
-    cases = [g.stencil3d_27pt((9, 10, 37)),            # line length not a multiple of 32, odd line count
-             g.stencil3d_27pt((5, 16, 64)),
-             _band27(6000, 50, 400, rng),              # wrapped neighbours present
-             _band27(7000, 40, 400, rng, keep=0.97),   # a few holes, still a sliced plan: masked path of the kernel
-             _band27(5000, 24, 240, rng, keep=0.8)]    # many holes: balanced-CSR plan, the general kernel serves it
-    for gm in cases:
+    # (matrix, must the staged kernel serve it).  Grids are big enough for a sliced plan (padding <= 12.5 %).
+    cases = [(g.stencil3d_27pt((14, 30, 67)), True),        # odd line length: the one-row-per-thread kernel
+             (g.stencil3d_27pt((16, 32, 64)), True),        # even strides: two rows per thread when enabled
+             (_band27(6000, 50, 400, rng), True),           # wrapped neighbours present
+             (_band27(7000, 40, 400, rng, keep=0.97), True),   # a few holes, still a sliced plan: predicated sums
+             (g.stencil3d_27pt((9, 10, 37)), False),        # small grid: balanced-CSR plan, the general kernel
+             (_band27(5000, 24, 240, rng, keep=0.8), False)]   # many holes: the same
+    for gm, staged in cases:
         m, om = to_matrix(sl, gm), oracle.csc(*gm)
         for k in (1, 4, 7, 64):
             X = g.uniform_block(gm.ncols, k, seed=k)
             got = sl.mulM(m, X)
             plan = m.device().plan_info()
-            assert "brick=1" in plan or not plan.startswith("sell32"), plan   # only sliced plans reach the kernel
+            assert ("brick=1" in plan and plan.startswith("sell32")) == staged, plan
             np.testing.assert_array_equal(got, oracle.mulm(om, X))
         Y0 = g.uniform_block(gm.nrows, 5, seed=3)
         X = g.uniform_block(gm.ncols, 5, seed=4)
@@ -516,6 +518,7 @@ def test_spmm_brick_switch_gives_the_same_bits(sl, monkeypatch):
     m = to_matrix(sl, gm)
     X = g.uniform_block(gm.ncols, 9, seed=2)
     a = sl.mulM(m, X)
+    assert "brick=1" in m.device().plan_info()
     monkeypatch.setenv("SLC_SPMM_BRICK", "0")
     b = sl.mulM(m, X)
     np.testing.assert_array_equal(a, b)
