@@ -4,13 +4,14 @@ over z-slabs (or weak with --scaling weak); `suite` adds cfg 5 SpMM, cfg 3 SpGEM
 sharded transpose / assembly at the same N.  Every entry carries an oracle verdict computed AFTER its
 timed loop on what the loop left in HBM, AND-reduced over the ranks.
 
-Timing protocol: barrier + synchronize, ONE untimed product that lines the GPUs up (each rank's
-boundary rows wait for its neighbours, so the kernels of all ranks end within microseconds of each
-other), event, K products, event, synchronize, barrier; device time, max over ranks.  Without the
-aligning product the first timed step absorbs the skew with which the host processes leave the NCCL
-barrier (hundreds of microseconds against a 45 us step at 8 GPUs).  By default the K products are
-captured once in a CUDA graph and the graph is launched inside the timed region (--no-graph: K host
-launches)."""
+Timing protocol: barrier + synchronize, then -- untimed, on the device -- a rendezvous of all GPUs
+(slc_peer_barrier_all: every rank waits for every rank in a one-warp kernel over peer memory) and ONE
+aligning product, event, K products, event, synchronize, barrier; device time, max over ranks.  Without
+the device-side rendezvous the first timed steps absorb the skew with which the host processes leave the
+NCCL barrier (hundreds of microseconds against a 45 us step at 8 GPUs; the products themselves only wait
+for their neighbours, so a late rank holds its neighbours' first event back but not the far ranks').
+By default the K products are captured once in a CUDA graph, the graph is replayed once untimed (which
+uploads it) and launched inside the timed region (--no-graph: K host launches)."""
 import ctypes as C
 import json
 import os
@@ -35,7 +36,7 @@ def _reduce(vals, dist, world, op="sum"):
     return [float(v) for v in t.tolist()]
 
 
-def timed_region(steps, step, align, stream, dist, world, local_rank, sl, use_graph):
+def timed_region(steps, step, align, stream, dist, world, local_rank, sl, use_graph, rendezvous=None):
     """The protocol of the module docstring.  Returns (ms per step max over ranks, clocks, launches, how)."""
     import torch
     how = "host launches"
@@ -56,14 +57,21 @@ def timed_region(steps, step, align, stream, dist, world, local_rank, sl, use_gr
             how = "host launches (graph capture failed: %r)" % (ex,)
         finally:
             sl.set_stream(stream.cuda_stream)
+    if graph is not None:
+        graph.replay()            # untimed: the first launch uploads the graph to the device
+        torch.cuda.synchronize()
     sampler = B.ClockSampler(local_rank)
-    l0 = sl.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     sampler.start()
-    align()                       # untimed: lines the GPUs up
+    if rendezvous is not None and world > 1:
+        rendezvous()              # untimed, on the device: every GPU waits for every GPU
+    la = sl.launch_count()
+    align()                       # untimed: one product, so the boundary waits of the first timed one are warm
+    l0 = sl.launch_count()
+    per_step = l0 - la
     e0.record(stream)
     if graph is not None:
         graph.replay()
@@ -75,8 +83,12 @@ def timed_region(steps, step, align, stream, dist, world, local_rank, sl, use_gr
     if world > 1:
         dist.barrier()
     clocks = sampler.stop()
-    launches = (sl.launch_count() - l0 - 1) if graph is None else steps * max(1, (sl.launch_count() - l0 - 1))
-    ms = _reduce([e0.elapsed_time(e1) / steps], dist, world, "max")[0]
+    launches = (sl.launch_count() - l0) if graph is None else steps * max(1, per_step)
+    mine = e0.elapsed_time(e1) / steps
+    ms = _reduce([mine], dist, world, "max")[0]
+    rank = dist.get_rank() if world > 1 else 0
+    per_rank = _reduce([mine if r == rank else 0.0 for r in range(world)], dist, world, "sum")
+    how += "; ms per step by rank: " + " ".join("%.4f" % v for v in per_rank)
     return ms, clocks, int(launches), how
 
 
@@ -125,7 +137,8 @@ def stencil_entry(args, rank, world, local_rank, dist, sl, stream, cpu_group, k)
     torch.cuda.synchronize()
     sh.stats(reset=True)
     ms, clocks, launches, how = timed_region(steps, sh.mulv, sh.mulv, stream, dist, world, local_rank, sl,
-                                             use_graph=not args.no_graph and not sh.use_nccl_barrier)
+                                             use_graph=not args.no_graph and not sh.use_nccl_barrier,
+                                             rendezvous=None if sh.use_nccl_barrier else sh.barrier_all)
     st = sh.stats()
     value = abytes / (ms * 1e-3) / 1e9
     # parity AFTER the timed loop, on what it left in HBM: this rank's rows against the oracle
@@ -187,7 +200,7 @@ def stencil_entry(args, rank, world, local_rank, dist, sl, stream, cpu_group, k)
                    "rows": ntot, "nnz": int(nnz), "algorithmic_bytes_per_step": abytes, "plan": local.device().plan_info(),
                    "l2": "inputs larger than L2 (%.0f MB per GPU per step)" % (abytes / world / 1e6),
                    "pct_of_nominal_8TBs_per_gpu": 100.0 * per_gpu / B.NOMINAL_HBM_GBS,
-                   "timed_region": how + "; one untimed aligning product before the first event",
+                   "timed_region": how + "; untimed before the first event: a device-side rendezvous of all ranks and one aligning product",
                    "operand": "two exported buffers per rank, alternated per product (double buffering)",
                    "dependency_mask_rank0": sh.deps},
         "clocks": clocks, "gpu_launches": launches, "e2e": e2e,
@@ -273,7 +286,8 @@ def powerlaw_entry(args, rank, world, local_rank, dist, sl, stream, cpu_group):
         sh.mulv()
     torch.cuda.synchronize()
     steps = max(3, min(args.steps, 50))
-    ms, clocks, launches, how = timed_region(steps, sh.mulv, sh.mulv, stream, dist, world, local_rank, sl, use_graph=False)
+    ms, clocks, launches, how = timed_region(steps, sh.mulv, sh.mulv, stream, dist, world, local_rank, sl, use_graph=False,
+                                             rendezvous=None if sh.use_nccl_barrier else sh.barrier_all)
     got = sh.y()
     oblk = oracle.csc(local.nrows, local.ncols, local.pointers, local.indices, local.values)
     want = oracle.mulv(oblk, xfull)

@@ -235,6 +235,10 @@ int slc_ipc_close(void *dev_ptr);
 int slc_peer_group_create(int32_t nparts, int32_t self, slc_peer_group **out, void *handle72);
 int slc_peer_group_connect(slc_peer_group *g, const void *handles72);
 int slc_peer_barrier(slc_peer_group *g);
+/* The same with every rank signalling and waiting for every other rank, whatever dependencies
+   slc_peer_group_set_deps installed: a full rendezvous of the GPUs on their streams (e.g. to line the
+   devices up before a timed region; the products themselves only ever wait for the ranks they read). */
+int slc_peer_barrier_all(slc_peer_group *g);
 /* The two halves of the barrier: signal = "my slice of x is written",
    wait = "every rank of my dependency set has signalled this epoch" (and closes the epoch).  The epoch
    counter lives in device memory and is advanced by the kernels, so barriers and products can be

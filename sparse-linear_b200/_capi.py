@@ -47,6 +47,7 @@ SIGNATURES = {
     "slc_peer_group_create": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(_vp), _vp]),
     "slc_peer_group_connect": (C.c_int, [_vp, _vp]),
     "slc_peer_barrier": (C.c_int, [_vp]),
+    "slc_peer_barrier_all": (C.c_int, [_vp]),
     "slc_peer_signal": (C.c_int, [_vp]),
     "slc_peer_wait": (C.c_int, [_vp]),
     "slc_peer_group_timed_out": (C.c_int, [_vp, C.POINTER(C.c_int)]),

@@ -26,8 +26,8 @@ __global__ void k_peer_barrier(PeerSync ps, uint32_t wait_mask, int mode) {
   const int p = threadIdx.x;
   const unsigned long long epoch = peer_epoch(ps);
   if (p < ps.nparts && p != ps.self) {
-    if ((mode & 1) && ((ps.signal_mask >> p) & 1u)) peer_signal_one(ps, p, epoch);
-    if ((mode & 2) && ((wait_mask >> p) & 1u)) peer_wait_one(ps, p, epoch);
+    if ((mode & 1) && ((mode & 4) || ((ps.signal_mask >> p) & 1u))) peer_signal_one(ps, p, epoch);
+    if ((mode & 2) && ((mode & 4) || ((wait_mask >> p) & 1u))) peer_wait_one(ps, p, epoch);
   }
   if (mode & 2) {
     __syncthreads();
@@ -185,6 +185,7 @@ int slc_peer_group_set_deps(slc_peer_group *g, uint32_t mask) {
 }
 
 int slc_peer_barrier(slc_peer_group *g) { return peer_launch(g, 3, "slc_peer_barrier"); }
+int slc_peer_barrier_all(slc_peer_group *g) { return peer_launch(g, 7, "slc_peer_barrier_all"); }
 int slc_peer_signal(slc_peer_group *g) { return peer_launch(g, 1, "slc_peer_signal"); }
 int slc_peer_wait(slc_peer_group *g) { return peer_launch(g, 2, "slc_peer_wait"); }
 

@@ -27,6 +27,10 @@
 // Every (row, column) is owned by one thread which adds the row's terms in increasing column order
 // (plane, then line, then point), product and sum rounded separately: bit-identical to the reference
 // (Sparse.hs:433-453), checked against the oracle at full size.
+// Measured and dropped (profiles/r2h_ncu_full_spmm_planes2_cfg5mm.txt): two rows per thread with 16-byte
+// shared loads (72 instead of 108 wavefronts per 64 rows, but 128-151 registers and 8-12 consumer warps per
+// SM: 4.30-5.26 ms against 4.29-4.35 ms); two or four columns per stage (6.7 ms: coarser hand-over between
+// producer and consumers); 256-row blocks, two per SM (4.34 ms: no difference).
 // Every mbarrier wait is bounded (as in slc_spmm_window.cu): a protocol bug raises the window error
 // flag and gives a wrong answer that the parity tests catch; it cannot hang the GPU.
 #include <algorithm>
@@ -181,14 +185,12 @@ __device__ __forceinline__ void planes_tile(const double (&a)[27], const uint32_
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
         const int slot = pa * 9 + b * 3 + c;
-        // rows with holes: the load and the product are unconditional (the index is inside the window for
-        // every slot; what it holds for an absent slot is never added), only the sum is predicated -- no
-        // branch per slot (ncu, round 2: the branchy form spent 12 BRA + 15 ISETP per warp and column)
-        const bool on = FULL || ((msk >> slot) & 1u);
+        // rows with holes: a branch per slot.  The branch-free form (unconditional load and product,
+        // predicated sum) compiled to FSEL pairs and measured 5.33 ms against 4.35 ms (round 2, pass 8)
+        if (FULL || ((msk >> slot) & 1u)) {
 #pragma unroll
-        for (int j = 0; j < JT; ++j) {
-          const double t = __dmul_rn(a[slot], xl[(int64_t)j * 3 * W + c]);
-          if (on && (FULL || j < jn)) acc[j] = __dadd_rn(t, acc[j]);
+          for (int j = 0; j < JT; ++j)
+            if (FULL || j < jn) acc[j] = __dadd_rn(__dmul_rn(a[slot], xl[(int64_t)j * 3 * W + c]), acc[j]);
         }
       }
     }
@@ -313,153 +315,6 @@ static int launch_planes(slc_matrix *m, const double *X, int64_t ldx, double *Y,
   return SLC_OK;
 }
 
-// ---- two rows per thread -----------------------------------------------------------------------------------
-// k_spmm_planes reads 27 entries of X from shared memory per row and column: 54 wavefronts of the
-// shared-memory pipe per warp and column, 3.07 ms for the 200^3 stencil with k = 64 at one wavefront per
-// clock per SM -- the kernel ran at 4.3 ms with that pipe 77 % busy (profiles/r2g_ncu_full_spmm_planes_cfg5mm.txt).
-// Here a thread owns rows r and r + 1.  Their slots (a, b, .) read window entries i .. i+2 and i+1 .. i+3:
-// four consecutive entries, fetched as TWO 16-byte loads when i is even.  The block's first row is chosen so
-// that it is (plane and line strides even; otherwise the one-row kernel runs): 18 LDS.128 = 72 wavefronts
-// for 64 rows instead of 108.  The price is 54 values of A per thread in registers (about 150 registers, 12
-// consumer warps per SM).  Summation order per row is unchanged (slots ascending): bit-identical.
-template <bool FULL>
-__device__ __forceinline__ void planes2_column(const double (&a0)[27], const double (&a1)[27], const uint32_t m0,
-                                               const uint32_t m1, const double *__restrict__ xs, const int32_t W,
-                                               const int32_t L, const int32_t t2, double &acc0, double &acc1) {
-#pragma unroll
-  for (int pa = 0; pa < 3; ++pa) {
-#pragma unroll
-    for (int b = 0; b < 3; ++b) {
-      const double2 *xl = reinterpret_cast<const double2 *>(xs + (int64_t)pa * W + t2 + b * L);  // 16-byte aligned
-      const double2 u = xl[0], v = xl[1];
-      const double x[4] = {u.x, u.y, v.x, v.y};
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const int slot = pa * 9 + b * 3 + c;
-        const double p0 = __dmul_rn(a0[slot], x[c]);
-        const double p1 = __dmul_rn(a1[slot], x[c + 1]);
-        if (FULL || ((m0 >> slot) & 1u)) acc0 = __dadd_rn(p0, acc0);
-        if (FULL || ((m1 >> slot) & 1u)) acc1 = __dadd_rn(p1, acc1);
-      }
-    }
-  }
-}
-
-template <int CONS>
-__global__ void __launch_bounds__(CONS + 32, 1)
-k_spmm_planes2(int64_t row_first, int32_t row_begin, int32_t row_end, int64_t shift, int32_t L, int32_t P, int64_t nrows_pad,
-               int64_t xlo, int64_t xhi, int32_t nstage, int32_t W, const double *__restrict__ dia,
-               const uint32_t *__restrict__ mask, const double *__restrict__ X, int64_t ldx, double *__restrict__ Y,
-               int64_t ldy, int32_t k, const YInit<double> yi, int *__restrict__ err) {
-  extern __shared__ __align__(128) unsigned char pl_smem[];
-  double *stage0 = reinterpret_cast<double *>(pl_smem);                                  // [nstage][3][W]
-  const size_t stage_elems = (size_t)3 * W;
-  uint64_t *full = reinterpret_cast<uint64_t *>(pl_smem + (size_t)nstage * stage_elems * sizeof(double));
-  uint64_t *empty = full + nstage;
-  const int tid = threadIdx.x;
-  // row_first may be row_begin - 1: the rows of a block start where the window index of slot (., ., 0) is even
-  const int64_t row0 = row_first + (int64_t)blockIdx.x * (2 * CONS);
-  if (tid == 0) {
-    for (int st = 0; st < nstage; ++st) {
-      pl_mbar_init(full + st, 1);
-      pl_mbar_init(empty + st, CONS);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
-  int64_t lo[3];  // window a: [lo[a], lo[a] + W); even by the choice of row_first
-#pragma unroll
-  for (int pa = 0; pa < 3; ++pa) lo[pa] = row0 + shift + (int64_t)(pa - 1) * P - L - 1;
-
-  if (tid >= CONS) {
-    if ((tid & 31) != 0) return;
-    int64_t c0[3], c1[3];
-    uint32_t bytes_col = 0;
-#pragma unroll
-    for (int pa = 0; pa < 3; ++pa) {
-      c0[pa] = max(lo[pa], xlo);
-      c1[pa] = min(lo[pa] + W, xhi);
-      if (c1[pa] > c0[pa]) bytes_col += (uint32_t)(c1[pa] - c0[pa]) * (uint32_t)sizeof(double);
-    }
-    int32_t st = 0, use = 0;
-    for (int32_t j = 0; j < k; ++j) {
-      if (use > 0 && !pl_mbar_wait(empty + st, (uint32_t)((use - 1) & 1), err)) return;
-      pl_mbar_arrive_expect_tx(full + st, bytes_col);
-      double *dst = stage0 + (size_t)st * stage_elems;
-      const double *xc = X + (int64_t)j * ldx;
-#pragma unroll
-      for (int pa = 0; pa < 3; ++pa)
-        if (c1[pa] > c0[pa])
-          pl_bulk_g2s(dst + (size_t)pa * W + (c0[pa] - lo[pa]), xc + c0[pa],
-                      (uint32_t)(c1[pa] - c0[pa]) * (uint32_t)sizeof(double), full + st);
-      if (bytes_col == 0) pl_mbar_arrive(full + st);
-      if (++st == nstage) {
-        st = 0;
-        ++use;
-      }
-    }
-    return;
-  }
-
-  const uint64_t pol_s = policy_evict_first();
-  const int64_t ra = row0 + 2 * tid, rb = ra + 1;
-  const bool live0 = ra >= row_begin && ra < row_end, live1 = rb >= row_begin && rb < row_end;
-  const uint32_t m0 = live0 ? __ldg(mask + ra) : 0u, m1 = live1 ? __ldg(mask + rb) : 0u;
-  double a0[27], a1[27];
-#pragma unroll
-  for (int s = 0; s < 27; ++s) {
-    a0[s] = live0 ? ld_stream(dia + (int64_t)s * nrows_pad + ra, pol_s) : 0.0;
-    a1[s] = live1 ? ld_stream(dia + (int64_t)s * nrows_pad + rb, pol_s) : 0.0;
-  }
-  const int32_t t2 = 2 * tid;
-  const bool full_warp = __all_sync(0xffffffffu, m0 == BRICK_FULL && m1 == BRICK_FULL);
-  int32_t st = 0;
-  uint32_t parity = 0;
-  for (int32_t j = 0; j < k; ++j) {
-    double *ycol = Y + (int64_t)j * ldy;
-    double acc0 = live0 ? yi(ycol + ra) : 0.0, acc1 = live1 ? yi(ycol + rb) : 0.0;
-    if (!pl_mbar_wait(full + st, parity, err)) return;
-    const double *xs = stage0 + (size_t)st * stage_elems;
-    if (full_warp) planes2_column<true>(a0, a1, m0, m1, xs, W, L, t2, acc0, acc1);
-    else planes2_column<false>(a0, a1, m0, m1, xs, W, L, t2, acc0, acc1);
-    pl_mbar_arrive(empty + st);
-    if (live0) st_stream(ycol + ra, acc0);
-    if (live1) st_stream(ycol + rb, acc1);
-    if (++st == nstage) {
-      st = 0;
-      parity ^= 1u;
-    }
-  }
-}
-
-template <int CONS>
-static int launch_planes2(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
-                          const YInit<double> &yi, int32_t row_begin, int32_t row_end, int64_t xlo, int64_t xhi,
-                          int stage_env, bool *done) {
-  const BrickPlan &bp = m->brick;
-  const int32_t W = 2 * CONS + 2 * bp.L + 4;  // rows + 2 L + 2 entries and one spare pair, even
-  const size_t col_bytes = (size_t)3 * W * sizeof(double);
-  int32_t nstage = (int32_t)std::min<size_t>(8, (size_t)(200 * 1024) / col_bytes);
-  if (nstage < 3) return SLC_OK;
-  if (stage_env >= 2) nstage = std::min(nstage, stage_env);
-  nstage = std::min(nstage, std::max(2, k));
-  // first row of block 0: row_begin or row_begin - 1, whichever makes row + shift - L - 1 even
-  const int64_t row_first = (int64_t)row_begin - (((int64_t)row_begin + bp.shift - bp.L - 1) & 1);
-  const size_t smem = (size_t)nstage * col_bytes + (size_t)nstage * 2 * sizeof(uint64_t);
-  auto kern = k_spmm_planes2<CONS>;
-  static PerDevice<size_t> smem_set;
-  SLC_CUDA(ensure_dyn_smem(kern, smem_set, smem));
-  int *err_flag = nullptr;
-  SLC_TRY(spmm_window_err_word(&err_flag));
-  const int64_t nb = ceil_div((int64_t)row_end - row_first, 2 * CONS);
-  kern<<<(unsigned)nb, CONS + 32, smem, cur_stream()>>>(row_first, row_begin, row_end, bp.shift, bp.L, bp.P, bp.nrows_pad,
-                                                       xlo, xhi, nstage, W, bp.dia, bp.mask, X, ldx, Y, ldy, k, yi,
-                                                       err_flag);
-  SLC_LAUNCHED();
-  *done = true;
-  return SLC_OK;
-}
-
 // Runs rows [row_begin, row_end) of the block product on the staged kernel when the matrix has the plan
 // and the operands qualify (X 16-byte aligned, even column stride and bounds, windows that fit).  X is
 // indexed by column number and only its entries [xlo, xhi) exist (xhi < 0: all of [0, ncols)).
@@ -475,15 +330,6 @@ int spmm_brick_try(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64
   if (m->brick.state != 1) return SLC_OK;
   // SLC_PLANES_ROWS / _JT / _STAGES: rows per block (512 or 256), columns per stage, stages; read on every
   // call so a test can switch them.  Measured on the 200^3 stencil, k = 64: see DESIGN.md 4.3.
-  const int pair_env = env_int("SLC_PLANES_PAIR", 1);  // two rows per thread (k_spmm_planes2); 0: one row per thread
-  const int cons_env = env_int("SLC_PLANES_CONS", 384);
-  if (pair_env && (m->brick.L & 1) == 0 && (m->brick.P & 1) == 0) {
-    if (cons_env <= 256) SLC_TRY((launch_planes2<256>(m, X, ldx, Y, ldy, k, yi, row_begin, row_end, xlo, xhi,
-                                                      env_int("SLC_PLANES_STAGES", 0), done)));
-    else SLC_TRY((launch_planes2<384>(m, X, ldx, Y, ldy, k, yi, row_begin, row_end, xlo, xhi,
-                                      env_int("SLC_PLANES_STAGES", 0), done)));
-    if (*done) return SLC_OK;
-  }
   const int rows_env = env_int("SLC_PLANES_ROWS", 512);
   const int jt_env = env_int("SLC_PLANES_JT", 1);
   const int stage_env = env_int("SLC_PLANES_STAGES", 0);

@@ -438,6 +438,11 @@ class ShardedSpMV:
         else:
             _check(_capi.lib().slc_peer_barrier(self.group))
 
+    def barrier_all(self):
+        """Full rendezvous of all ranks' streams (every rank waits for every rank), on the device."""
+        if self.world > 1:
+            _check(_capi.lib().slc_peer_barrier_all(self.group))
+
     def timed_out(self):
         f = C.c_int(0)
         _check(_capi.lib().slc_peer_group_timed_out(self.group, C.byref(f)))

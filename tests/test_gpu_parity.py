@@ -479,22 +479,19 @@ def _band27(n, L, P, rng, keep=1.0):
     return oracle.compress(n, n, r, cols[r, s], rng.uniform(-1, 1, len(r)))
 
 
-@pytest.mark.parametrize("jt,rows,pair", [("1", "512", "0"), ("2", "512", "0"), ("4", "512", "0"), ("1", "256", "0"),
-                                          ("2", "256", "0"), ("1", "512", "384"), ("1", "512", "256")])
-def test_spmm_brick_matches_oracle(sl, monkeypatch, jt, rows, pair):
+@pytest.mark.parametrize("jt,rows", [("1", "512"), ("2", "512"), ("4", "512"), ("1", "256"), ("2", "256")])
+def test_spmm_brick_matches_oracle(sl, monkeypatch, jt, rows):
     """The TMA-staged kernel for 27-offset matrices (k_spmm_planes): bit-exact against the oracle for every
-    column-tile width, with wrapped neighbours, holes (masked path), column counts that leave a partial
-    tile, and the accumulate form."""
+    block shape, with odd and even strides, wrapped neighbours, holes (masked path), column counts that leave
+    a partial tile, and the accumulate form."""
     monkeypatch.setenv("SLC_PLANES_JT", jt)
     monkeypatch.setenv("SLC_PLANES_ROWS", rows)
-    monkeypatch.setenv("SLC_PLANES_PAIR", "0" if pair == "0" else "1")     # two rows per thread (even strides only)
-    monkeypatch.setenv("SLC_PLANES_CONS", pair)
     rng = np.random.default_rng(41)
     # (matrix, must the staged kernel serve it).  Grids are big enough for a sliced plan (padding <= 12.5 %).
-    cases = [(g.stencil3d_27pt((14, 30, 67)), True),        # odd line length: the one-row-per-thread kernel
-             (g.stencil3d_27pt((16, 32, 64)), True),        # even strides: two rows per thread when enabled
+    cases = [(g.stencil3d_27pt((14, 30, 67)), True),        # odd line length: window starts that need rounding
+             (g.stencil3d_27pt((16, 32, 64)), True),        # even strides
              (_band27(6000, 50, 400, rng), True),           # wrapped neighbours present
-             (_band27(7000, 40, 400, rng, keep=0.97), True),   # a few holes, still a sliced plan: predicated sums
+             (_band27(7000, 40, 400, rng, keep=0.97), True),   # a few holes, still a sliced plan: masked path
              (g.stencil3d_27pt((9, 10, 37)), False),        # small grid: balanced-CSR plan, the general kernel
              (_band27(5000, 24, 240, rng, keep=0.8), False)]   # many holes: the same
     for gm, staged in cases:
