@@ -10,6 +10,7 @@
 #include <cstring>
 #include <atomic>
 #include <mutex>
+#include <utility>
 #include <new>
 #include <string>
 #include <vector>
@@ -87,6 +88,34 @@ struct DevBuf {
   }
   U *take() { U *q = p; p = nullptr; n = 0; return q; }
 };
+
+// ---- programmatic dependent launch (PDL) ----------------------------------------------------------
+// A kernel launched with launch_pdl(..., pdl = true) may have its blocks scheduled while the previous
+// kernel of the stream is still draining (after every block of that kernel has executed
+// pdl_launch_dependents).  Such a block may only touch memory that no earlier kernel writes -- the
+// matrix -- until it has passed pdl_wait(), which returns when the previous kernel has completed and
+// its writes are visible.  Without the launch attribute both instructions do nothing.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t s,
+                              bool pdl, Args &&...args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(block, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(std::forward<Args>(args))...);
+}
+#endif
 
 inline int env_int(const char *name, int dflt) {
   const char *v = getenv(name);

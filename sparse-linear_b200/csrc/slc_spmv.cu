@@ -451,13 +451,33 @@ __device__ __forceinline__ void sell_row(int32_t row, const int64_t *__restrict_
   st_stream(y + row, acc);
 }
 
+// PDL prologue of the SELL kernels: let the next kernel of the stream start launching, pull this row
+// block's values towards L2 (the matrix is immutable, so this may overlap the previous kernel's tail),
+// then wait for the previous kernel.  One 128-byte line per lane that starts one; only the blocks of the
+// first wave prefetch (later blocks start in the steady state, where the one-batch-ahead prefetch of
+// sell_row is enough).
+template <class T>
+__device__ __forceinline__ void sell_pdl_prologue(int32_t row, int32_t row_end, int32_t first_wave,
+                                                  const int64_t *__restrict__ slice_ptr,
+                                                  const int32_t *__restrict__ rowlen, const T *__restrict__ vals) {
+  pdl_launch_dependents();
+  const int lane = threadIdx.x & 31;
+  if ((int32_t)blockIdx.x < first_wave && row < row_end && (lane * sizeof(T)) % 128 == 0) {
+    const T *va = vals + __ldg(slice_ptr + (row >> 5)) + lane;
+    const int32_t len = __ldg(rowlen + row);
+    for (int32_t k = 0; k < len; ++k) prefetch_l2(va + (int64_t)k * SELL_C);
+  }
+  pdl_wait();
+}
+
 template <class T, int U, bool ACC, class XA, bool KB = false, int MINB = 0>
 __global__ void __launch_bounds__(256, MINB)
 k_spmv_sell(int32_t row_begin, int32_t row_end, const int64_t *__restrict__ slice_ptr,
             const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
             const T *__restrict__ vals, const XA xa, T *__restrict__ y, const int32_t *__restrict__ kbase = nullptr,
-            int pf = 0) {
+            int pf = 0, int first_wave = 0) {
   const int32_t row = row_begin + blockIdx.x * blockDim.x + threadIdx.x;  // row_begin % 32 == 0
+  sell_pdl_prologue<T>(row, row_end, first_wave, slice_ptr, rowlen, vals);
   if (row >= row_end) return;
   sell_row<T, U, ACC, XA, KB>(row, slice_ptr, rowlen, colidx, vals, xa, y, kbase, pf);
 }
@@ -489,7 +509,11 @@ k_spmv_sell_dist(int32_t nrows, int32_t r0, int32_t r1, const int64_t *__restric
                  const int32_t *__restrict__ rowlen, const int32_t *__restrict__ colidx,
                  const T *__restrict__ vals, const DistX<T> xa, T *__restrict__ y, const PeerSync ps,
                  const uint32_t wait_lo, const uint32_t wait_hi, const int32_t *__restrict__ kbase,
-                 const int32_t lead) {
+                 const int32_t lead, const int32_t first_wave) {
+  {  // PDL prologue on the rows this block would own if the grid were all interior (a prefetch hint only)
+    const int32_t prow = min((int32_t)(blockIdx.x * 256 + threadIdx.x), nrows - 1);
+    sell_pdl_prologue<T>(prow, nrows, first_wave, slice_ptr, rowlen, vals);
+  }
   const int32_t nbl = (r0 + 255) >> 8;            // boundary blocks below the interior
   const int32_t nbh = (nrows - r1 + 255) >> 8;    // and above it
   // Block order: [`lead` interior blocks | low boundary | high boundary | the other interior blocks].
@@ -1338,22 +1362,30 @@ static int launch_sell(slc_matrix *m, const XA &xa, T *y, int32_t row_begin = 0,
   // with compressed indices: U=4 0.379 ms (40 registers, 6 blocks per SM), held to 32 registers (8 blocks)
   // 0.338 ms, plus an L2 prefetch one batch ahead 0.326 ms (two: 0.330, three: 0.334, five: 0.340); U=8 0.471 ms (64 registers); off 0.430 ms
   if (u == 0) u = (m->max_rowlen <= 4 || sp.kbase) ? 4 : 8;
+  // SLC_PDL (1): programmatic dependent launch -- back-to-back products overlap the next kernel's first
+  // wave (launch, values towards L2) with the previous kernel's tail; 0 = plain stream order
+  static const int pdl_env = env_int("SLC_PDL", 1);
+  const bool pdl = pdl_env != 0;
+  const int first_wave = pdl ? sm_count() * 8 : 0;
+  const int32_t *no_kbase = nullptr;
+  cudaError_t le = cudaSuccess;
 #define SLC_SELL_CASE(UU)                                                                          \
   do {                                                                                             \
     if (sp.kbase && cap_env && UU == 4 && sizeof(T) == 8)                                          \
-      k_spmv_sell<T, 4, ACC, XA, true, 8><<<nb, 256, 0, s>>>(row_begin, row_end, sp.slice_ptr, sp.rowlen, \
-                                                             sp.colidx, (const T *)sp.vals, xa, y, sp.kbase, pf_env); \
+      le = launch_pdl(k_spmv_sell<T, 4, ACC, XA, true, 8>, nb, 256, 0, s, pdl, row_begin, row_end, sp.slice_ptr, \
+                      sp.rowlen, sp.colidx, (const T *)sp.vals, xa, y, sp.kbase, pf_env, first_wave); \
     else if (sp.kbase)                                                                             \
-      k_spmv_sell<T, UU, ACC, XA, true><<<nb, 256, 0, s>>>(row_begin, row_end, sp.slice_ptr, sp.rowlen, \
-                                                           sp.colidx, (const T *)sp.vals, xa, y, sp.kbase, pf_env); \
+      le = launch_pdl(k_spmv_sell<T, UU, ACC, XA, true>, nb, 256, 0, s, pdl, row_begin, row_end, sp.slice_ptr, \
+                      sp.rowlen, sp.colidx, (const T *)sp.vals, xa, y, sp.kbase, pf_env, first_wave); \
     else                                                                                           \
-      k_spmv_sell<T, UU, ACC, XA><<<nb, 256, 0, s>>>(row_begin, row_end, sp.slice_ptr, sp.rowlen,  \
-                                                     sp.colidx, (const T *)sp.vals, xa, y);        \
+      le = launch_pdl(k_spmv_sell<T, UU, ACC, XA>, nb, 256, 0, s, pdl, row_begin, row_end, sp.slice_ptr, \
+                      sp.rowlen, sp.colidx, (const T *)sp.vals, xa, y, no_kbase, 0, first_wave);   \
   } while (0)
   if (u <= 4) SLC_SELL_CASE(4);
   else if (u <= 8) SLC_SELL_CASE(8);
   else SLC_SELL_CASE(16);
 #undef SLC_SELL_CASE
+  SLC_CUDA(le);
   SLC_LAUNCHED();
   return SLC_OK;
 }
@@ -1806,9 +1838,13 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   cudaStream_t s = cur_stream();
   static const int u_env = env_int("SLC_SELL_U", 0);
   const int u = u_env ? u_env : ((m->max_rowlen <= 4 || sp.kbase) ? 4 : 8);
+  static const int pdl_env = env_int("SLC_PDL", 1);  // see launch_sell
+  const bool pdl = pdl_env != 0;
+  const int32_t first_wave = pdl ? sm_count() * 8 : 0;
+  cudaError_t le = cudaSuccess;
 #define SLC_DIST_CASE(UU, KB_)                                                                                  \
-  k_spmv_sell_dist<T, UU, KB_><<<(unsigned)nblocks, 256, 0, s>>>(m->nrows, r0, r1, sp.slice_ptr, sp.rowlen, sp.colidx, \
-                                                                 (const T *)sp.vals, xa, (T *)y, ps, wait_lo, wait_hi, sp.kbase, lead)
+  le = launch_pdl(k_spmv_sell_dist<T, UU, KB_>, (unsigned)nblocks, 256, 0, s, pdl, m->nrows, r0, r1, sp.slice_ptr, \
+                  sp.rowlen, sp.colidx, (const T *)sp.vals, xa, (T *)y, ps, wait_lo, wait_hi, sp.kbase, lead, first_wave)
   if (sp.kbase) {
     if (u <= 4) SLC_DIST_CASE(4, true);
     else SLC_DIST_CASE(8, true);
@@ -1817,6 +1853,7 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
     else SLC_DIST_CASE(8, false);
   }
 #undef SLC_DIST_CASE
+  SLC_CUDA(le);
   SLC_LAUNCHED();
   return SLC_OK;
 }
