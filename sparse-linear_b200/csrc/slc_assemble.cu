@@ -63,6 +63,192 @@ __global__ void k_ptrs_from_sorted_u32(int64_t n, int32_t nkeys, const uint32_t 
   for (int64_t r = prev + 1; r <= cur; ++r) ptr[r] = (int32_t)i;
 }
 
+// ---- compress, bucket path (round 2) ---------------------------------------------------------------
+// When no column receives more than ASM_BUCKET_LIMIT triplets (finite-element and stencil assembly: a
+// few dozen per column) the full sort is replaced by the reference's own shape -- count per column,
+// prefix sum, place (computePtrs + the scatter of Sparse.hs:282-329) -- followed by a sort of each
+// column's few triplets:
+//   k_coo_check_count   bounds check + triplets per column; the value the atomic returns is the
+//                       triplet's rank inside its bucket and is kept (2 B), so this is the only
+//                       pass with atomics
+//   exclusive scan      bucket starts
+//   k_bucket_scatter    triplet i -> slot start[col] + rank[i] as ONE 16/32-byte record
+//                       { row << 32 | i, value }: a single sector written per triplet, values carried
+//                       along so nothing is gathered later.  The order inside a bucket is whatever
+//                       the atomics gave; the next step removes that freedom.
+//   k_bucket_reduce     128 columns per block: keys of the block's contiguous span staged in shared
+//                       memory, each thread insertion-sorts its column by (row, i), sums runs of equal
+//                       row in increasing i (= input order, the same convention as the sort path and
+//                       the oracle) and the block writes its reduced entries contiguously
+//   exclusive scan      distinct rows per column -> colptr
+//   k_bucket_compact    block-contiguous copy into the result
+// Traffic on n triplets -> m entries (Double): 10n + 18n + 32n (sector per record) + 16n + 12m + 24m against
+// 6 passes x 20n B of the sort path.  Deterministic: (row, i) is a total order.
+constexpr int ASM_BUCKET_LIMIT = 512;   // longest bucket the per-thread insertion sort is allowed to see
+constexpr int ASM_COLS = 128;           // columns (= threads) per block
+constexpr int ASM_CAP = 3072;           // staged keys per pass (24 KB + 6 KB of local indices)
+
+__global__ void k_coo_check_count(int64_t n, int32_t nrows, int32_t ncols, const int32_t *__restrict__ rows,
+                                  const int32_t *__restrict__ cols, int32_t *__restrict__ cnt,
+                                  uint16_t *__restrict__ rank, unsigned long long *__restrict__ first_bad) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int32_t r = rows[i], c = cols[i];
+  const bool bad_r = r < 0 || r >= nrows;
+  const bool bad_c = c < 0 || c >= ncols;
+  if (bad_r) atomicMin(first_bad + 0, (unsigned long long)i);
+  if (bad_c) atomicMin(first_bad + 1, (unsigned long long)i);
+  // a rank that does not fit 16 bits belongs to a bucket far over the limit: the path is not taken then
+  if (!bad_c) rank[i] = (uint16_t)min(atomicAdd(cnt + c, 1), 65535);
+}
+
+template <class T>
+__global__ void k_bucket_scatter(int64_t n, const int32_t *__restrict__ rows, const int32_t *__restrict__ cols,
+                                 const T *__restrict__ vals, const int32_t *__restrict__ start,
+                                 const uint16_t *__restrict__ rank, AsmEnt<T> *__restrict__ ent) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int32_t slot = __ldg(start + cols[i]) + rank[i];
+  AsmEnt<T> e;
+  e.key = ((uint64_t)(uint32_t)rows[i] << 32) | (uint32_t)i;
+  e.val = vals[i];
+  ent[slot] = e;
+}
+
+
+template <class T>
+__global__ void __launch_bounds__(ASM_COLS)
+k_bucket_reduce(int32_t ncols, const int32_t *__restrict__ start, const AsmEnt<T> *__restrict__ ent,
+                int32_t *__restrict__ red_row, T *__restrict__ red_val, int32_t *__restrict__ ndist) {
+  __shared__ uint64_t sk[ASM_CAP];
+  __shared__ uint16_t si[ASM_CAP];
+  __shared__ int32_t wsum[ASM_COLS / 32];
+  const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
+  const int32_t cbeg = blockIdx.x * ASM_COLS;
+  const int32_t cend = min(cbeg + ASM_COLS, ncols);
+  int32_t c0 = cbeg;
+  int32_t wr = start[cbeg];  // next free slot of the block's reduced output (block-uniform)
+  while (c0 < cend) {
+    const int32_t s0 = start[c0];
+    const int32_t c = c0 + t;
+    const int32_t e_t = c < cend ? start[c + 1] : 0;
+    const int ncover = __syncthreads_count(c < cend && e_t - s0 <= ASM_CAP);  // a prefix: ends are monotone
+    // (the launch guarantees every bucket <= ASM_BUCKET_LIMIT <= ASM_CAP, so ncover >= 1)
+    const int32_t s1 = start[c0 + ncover];
+    const int32_t len = s1 - s0;
+    for (int32_t i = t; i < len; i += ASM_COLS) {
+      sk[i] = ent[s0 + i].key;
+      si[i] = (uint16_t)i;
+    }
+    __syncthreads();
+    int32_t a = 0, b = 0, k = 0;
+    if (t < ncover) {
+      a = start[c] - s0;
+      b = e_t - s0;
+      for (int32_t i = a + 1; i < b; ++i) {
+        const uint64_t key = sk[i];
+        const uint16_t idx = si[i];
+        int32_t j = i;
+        while (j > a && sk[j - 1] > key) {
+          sk[j] = sk[j - 1];
+          si[j] = si[j - 1];
+          --j;
+        }
+        sk[j] = key;
+        si[j] = idx;
+      }
+      for (int32_t i = a; i < b; ++i) k += (i == a) || ((sk[i] >> 32) != (sk[i - 1] >> 32));
+      ndist[c] = k;
+    }
+    // exclusive prefix of k over the block
+    int32_t incl = k;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) wsum[wid] = incl;
+    __syncthreads();
+    int32_t before = 0, total = 0;
+    for (int w = 0; w < ASM_COLS / 32; ++w) {
+      const int32_t v = wsum[w];
+      if (w < wid) before += v;
+      total += v;
+    }
+    int32_t w_out = wr + before + incl - k;
+    for (int32_t i = a; i < b;) {
+      const uint32_t row = (uint32_t)(sk[i] >> 32);
+      T acc = ent[s0 + si[i]].val;
+      for (++i; i < b && (uint32_t)(sk[i] >> 32) == row; ++i) acc = Num<T>::add(acc, ent[s0 + si[i]].val);
+      red_row[w_out] = (int32_t)row;
+      red_val[w_out] = acc;
+      ++w_out;
+    }
+    wr += total;
+    c0 += ncover;
+    __syncthreads();  // sk / si / wsum are reused by the next pass
+  }
+}
+
+template <class T>
+__global__ void __launch_bounds__(ASM_COLS)
+k_bucket_compact(int32_t ncols, const int32_t *__restrict__ start, const int32_t *__restrict__ colptr,
+                 const int32_t *__restrict__ red_row, const T *__restrict__ red_val,
+                 int32_t *__restrict__ out_row, T *__restrict__ out_val) {
+  const int32_t cbeg = blockIdx.x * ASM_COLS;
+  const int32_t cend = min(cbeg + ASM_COLS, ncols);
+  const int32_t src = start[cbeg];
+  const int32_t dst = colptr[cbeg];
+  const int32_t cnt = colptr[cend] - dst;
+  for (int32_t i = threadIdx.x; i < cnt; i += ASM_COLS) {
+    out_row[dst + i] = red_row[src + i];
+    out_val[dst + i] = red_val[src + i];
+  }
+}
+
+template <class T>
+static int compress_buckets(int32_t nrows, int32_t ncols, int64_t n, const int32_t *rows_d, const int32_t *cols_d,
+                            const T *vals_d, DevBuf<int32_t> &cnt, DevBuf<uint16_t> &rank, slc_matrix **out) {
+  cudaStream_t s = cur_stream();
+  DevBuf<int32_t> start, ndist, red_row;
+  DevBuf<T> red_val;
+  DevBuf<AsmEnt<T>> ent;
+  SLC_TRY(start.alloc((size_t)ncols + 1));
+  SLC_TRY(exclusive_scan_i32(cnt.p, start.p, (int64_t)ncols + 1));
+  cnt.release();
+  SLC_TRY(ent.alloc((size_t)n));
+  k_bucket_scatter<T><<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(n, rows_d, cols_d, vals_d, start.p, rank.p,
+                                                                 ent.p);
+  SLC_LAUNCHED();
+  rank.release();
+  SLC_TRY(ndist.alloc((size_t)ncols + 1));
+  SLC_TRY(red_row.alloc((size_t)n));
+  SLC_TRY(red_val.alloc((size_t)n));
+  SLC_CUDA(cudaMemsetAsync(ndist.p + ncols, 0, sizeof(int32_t), s));
+  const unsigned nblk = (unsigned)ceil_div((int64_t)ncols, ASM_COLS);
+  k_bucket_reduce<T><<<nblk, ASM_COLS, 0, s>>>(ncols, start.p, ent.p, red_row.p, red_val.p, ndist.p);
+  SLC_LAUNCHED();
+  ent.release();
+  SLC_TRY(exclusive_scan_i32(ndist.p, ndist.p, (int64_t)ncols + 1));
+  int32_t nnz_out = 0;
+  SLC_CUDA(cudaMemcpyAsync(&nnz_out, ndist.p + ncols, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  slc_matrix *m = nullptr;
+  SLC_TRY(matrix_alloc(Num<T>::elem, nrows, ncols, nnz_out, &m));
+  cudaError_t e = cudaMemcpyAsync(m->colptr, ndist.p, ((size_t)ncols + 1) * sizeof(int32_t), cudaMemcpyDeviceToDevice, s);
+  if (e == cudaSuccess) {
+    k_bucket_compact<T><<<nblk, ASM_COLS, 0, s>>>(ncols, start.p, ndist.p, red_row.p, red_val.p, m->rowidx,
+                                                  (T *)m->vals);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    e = cudaGetLastError();
+  }
+  if (e != cudaSuccess) {
+    matrix_release(m);
+    return fail(SLC_ERR_CUDA, "compress: %s", cudaGetErrorString(e));
+  }
+  *out = m;
+  return SLC_OK;
+}
+
 template <class T>
 static int compress_entry(int32_t nrows, int32_t ncols, int64_t n, const int32_t *rows, const int32_t *cols,
                           const double *vals, slc_matrix **out, int64_t *bad_pos, bool on_device) {
@@ -103,16 +289,27 @@ static int compress_entry(int32_t nrows, int32_t ncols, int64_t n, const int32_t
     cols_d = dcols.p;
     vals_d = dvals.p;
   }
-  SLC_TRY(k0.alloc(n));
-  SLC_TRY(k1.alloc(n));
-  SLC_TRY(p0.alloc(n));
-  SLC_TRY(p1.alloc(n));
-  SLC_TRY(bad.alloc(2));
+  SLC_TRY(bad.alloc(3));
   SLC_CUDA(cudaMemsetAsync(bad.p, 0xff, 2 * sizeof(unsigned long long), s));
+  SLC_CUDA(cudaMemsetAsync(bad.p + 2, 0, sizeof(unsigned long long), s));
   const unsigned nb = (unsigned)ceil_div(n, 256);
-  k_coo_check_pack<<<nb, 256, 0, s>>>(n, nrows, ncols, rowbits, rows_d, cols_d, k0.p, bad.p);
-  SLC_LAUNCHED();
-  unsigned long long hbad[2];
+  // SLC_ASM_BUCKET (1): count / place / sort-per-column path when every column is short; 0 = always sort
+  const bool try_buckets = env_int("SLC_ASM_BUCKET", 1) != 0 && ncols > 0;
+  DevBuf<int32_t> cnt;
+  DevBuf<uint16_t> rank;
+  if (try_buckets) {
+    SLC_TRY(cnt.alloc((size_t)ncols + 1));
+    SLC_CUDA(cudaMemsetAsync(cnt.p, 0, ((size_t)ncols + 1) * sizeof(int32_t), s));
+    SLC_TRY(rank.alloc((size_t)n));
+    k_coo_check_count<<<nb, 256, 0, s>>>(n, nrows, ncols, rows_d, cols_d, cnt.p, rank.p, bad.p);
+    SLC_LAUNCHED();
+    SLC_TRY(max_i32_into(cnt.p, ncols, bad.p + 2));  // bad[2] <- longest bucket
+  } else {
+    SLC_TRY(k0.alloc(n));
+    k_coo_check_pack<<<nb, 256, 0, s>>>(n, nrows, ncols, rowbits, rows_d, cols_d, k0.p, bad.p);
+    SLC_LAUNCHED();
+  }
+  unsigned long long hbad[3];
   SLC_CUDA(cudaMemcpyAsync(hbad, bad.p, sizeof hbad, cudaMemcpyDeviceToHost, s));
   SLC_CUDA(cudaStreamSynchronize(s));
   if (hbad[0] != ~0ull) {  // rows are checked first (Sparse.hs:200-205)
@@ -125,6 +322,18 @@ static int compress_entry(int32_t nrows, int32_t ncols, int64_t n, const int32_t
     return fail(SLC_ERR_COL_BOUNDS, "compress: column index out of bounds (0,%d) at %lld", ncols,
                 (long long)hbad[1]);
   }
+  if (try_buckets && hbad[2] <= (unsigned long long)ASM_BUCKET_LIMIT)
+    return compress_buckets<T>(nrows, ncols, n, rows_d, cols_d, vals_d, cnt, rank, out);
+  if (try_buckets) {  // a long column: the sort path, whose keys have not been packed yet
+    cnt.release();
+    rank.release();
+    SLC_TRY(k0.alloc(n));
+    k_coo_check_pack<<<nb, 256, 0, s>>>(n, nrows, ncols, rowbits, rows_d, cols_d, k0.p, bad.p);
+    SLC_LAUNCHED();
+  }
+  SLC_TRY(k1.alloc(n));
+  SLC_TRY(p0.alloc(n));
+  SLC_TRY(p1.alloc(n));
   drows.release();
   dcols.release();
 

@@ -117,6 +117,14 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), unsigned grid, unsigned bl
 }
 #endif
 
+// One record of the count / place / sort-per-bucket paths (compress: key = row << 32 | input position;
+// transpose: key = column).  16 bytes for Double, 32 for Complex Double: one sector per record.
+template <class T>
+struct __align__(16) AsmEnt {
+  uint64_t key;
+  T val;
+};
+
 inline int env_int(const char *name, int dflt) {
   const char *v = getenv(name);
   return v && *v ? atoi(v) : dflt;
@@ -417,6 +425,8 @@ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 int sm_count();
 
 // device primitives implemented in slc_prims.cu (radix sort, scans)
+// *out <- max(*out, max(v[0 .. n)))  (values >= 0; *out is a device word the caller has initialised)
+int max_i32_into(const int32_t *v, int64_t n, unsigned long long *out);
 int exclusive_scan_i32(const int32_t *in, int32_t *out, int64_t n);  // out may alias in
 int exclusive_scan_i64(const int64_t *in, int64_t *out, int64_t n);
 // stable sort of (key, value) pairs on key bits [0, end_bit).  (ka, va) / (kb, vb) are ping-pong

@@ -109,6 +109,20 @@ static int exclusive_scan_impl(const U *in, U *out, int64_t n) {
   return SLC_OK;
 }
 
+__global__ void k_max_i32(int64_t n, const int32_t *__restrict__ v, unsigned long long *__restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int32_t m = i < n ? v[i] : 0;
+  for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, (unsigned long long)m);
+}
+
+int max_i32_into(const int32_t *v, int64_t n, unsigned long long *out) {
+  if (n <= 0) return SLC_OK;
+  k_max_i32<<<(unsigned)ceil_div(n, 256), 256, 0, cur_stream()>>>(n, v, out);
+  SLC_LAUNCHED();
+  return SLC_OK;
+}
+
 int exclusive_scan_i32(const int32_t *in, int32_t *out, int64_t n) {
   return exclusive_scan_impl<int32_t>(in, out, n);
 }

@@ -44,10 +44,12 @@ k_tile_first_col(int32_t ncols, const int32_t *__restrict__ colptr, int32_t *__r
   for (int64_t b = (lo + EXPAND_TILE - 1) / EXPAND_TILE; b * EXPAND_TILE < hi; ++b) tile_col[b] = (int32_t)c;
 }
 
-__global__ void __launch_bounds__(EXPAND_THREADS)
-k_expand_cols(int64_t nnz, int32_t ncols, int64_t ntiles, const int32_t *__restrict__ colptr,
-              const int32_t *__restrict__ tile_col, uint32_t *__restrict__ colid) {
-  __shared__ int32_t win[EXPAND_WINDOW];
+// The columns of positions p0 .. p0 + 15 (p0 = the calling thread's first position in the block's tile),
+// as described above.  Every thread of the block must call it (it contains a barrier).
+__device__ __forceinline__ void tile_columns(int64_t nnz, int32_t ncols, int64_t ntiles,
+                                             const int32_t *__restrict__ colptr,
+                                             const int32_t *__restrict__ tile_col, int32_t *win, int64_t p0,
+                                             uint32_t (&out)[EXPAND_ITEMS]) {
   const int32_t c_lo = tile_col[blockIdx.x];
   const int32_t c_hi = (int64_t)blockIdx.x + 1 < ntiles ? tile_col[blockIdx.x + 1] : ncols - 1;
   const int32_t span = c_hi - c_lo + 2;  // pointers colptr[c_lo .. c_hi + 1]
@@ -55,9 +57,7 @@ k_expand_cols(int64_t nnz, int32_t ncols, int64_t ntiles, const int32_t *__restr
   if (staged)
     for (int32_t i = threadIdx.x; i < span; i += EXPAND_THREADS) win[i] = colptr[c_lo + i];
   __syncthreads();
-  const int64_t p0 = (int64_t)blockIdx.x * EXPAND_TILE + (int64_t)threadIdx.x * EXPAND_ITEMS;
   if (p0 >= nnz) return;
-  uint32_t out[EXPAND_ITEMS];
   if (staged) {
     int32_t lo = 0, hi = span - 1;  // first index in [0, span - 1] with win[idx] > p0; win[0] <= p0
     while (lo < hi) {
@@ -89,6 +89,16 @@ k_expand_cols(int64_t nnz, int32_t ncols, int64_t ntiles, const int32_t *__restr
       out[e] = (uint32_t)c;
     }
   }
+}
+
+__global__ void __launch_bounds__(EXPAND_THREADS)
+k_expand_cols(int64_t nnz, int32_t ncols, int64_t ntiles, const int32_t *__restrict__ colptr,
+              const int32_t *__restrict__ tile_col, uint32_t *__restrict__ colid) {
+  __shared__ int32_t win[EXPAND_WINDOW];
+  const int64_t p0 = (int64_t)blockIdx.x * EXPAND_TILE + (int64_t)threadIdx.x * EXPAND_ITEMS;
+  uint32_t out[EXPAND_ITEMS];
+  tile_columns(nnz, ncols, ntiles, colptr, tile_col, win, p0, out);
+  if (p0 >= nnz) return;
   if (p0 + EXPAND_ITEMS <= nnz) {
     uint4 *dst = reinterpret_cast<uint4 *>(colid + p0);  // p0 is a multiple of 16: 64-byte aligned
 #pragma unroll
@@ -131,6 +141,166 @@ k_transpose_gather(int64_t nnz, const uint32_t *__restrict__ colid, const T *__r
   }
 }
 
+// ---- bucket path (round 2): the reference's own shape ----------------------------------------------
+// Sparse.hs:301-329 counts the entries of every row, prefix-sums the counts and places each entry at
+// its row's cursor, walking the columns in order.  On the device the walk is parallel, so the cursor
+// order inside a row is whatever the atomics gave; a row's entries are then sorted by column (unique
+// inside a row), which restores exactly the stable order.  Taken when no row has more than
+// TB_LIMIT entries (stencils, finite elements, banded matrices); the radix sort above stays for rows
+// that are longer (power-law matrices).
+//   k_row_rank    rank[p] = atomicAdd(cnt[row[p]], 1)            the only pass with atomics; 6 B per entry
+//   scan          cnt -> out_ptr (final: a transpose has no duplicates to merge)
+//   k_row_place   record {column, value} -> slot out_ptr[row] + rank; columns from the tile's window of
+//                 colptr (tile_columns), one 16/32-byte record = one sector per entry
+//   k_row_sort    128 rows per block, keys of the block's contiguous span in shared memory, insertion
+//                 sort per thread (nearly sorted already: blocks run roughly in column order), coalesced
+//                 write of column ids and values
+constexpr int TB_LIMIT = 512;
+constexpr int TB_ROWS = 128;
+constexpr int TB_CAP = 4096;
+constexpr int RANK_ITEMS = 4;
+
+__global__ void __launch_bounds__(256)
+k_row_rank(int64_t nnz, const int32_t *__restrict__ rowidx, int32_t *__restrict__ cnt, uint16_t *__restrict__ rank) {
+  const int64_t base = (int64_t)blockIdx.x * (256 * RANK_ITEMS) + threadIdx.x;
+  int32_t r[RANK_ITEMS];
+#pragma unroll
+  for (int u = 0; u < RANK_ITEMS; ++u) {
+    const int64_t p = base + u * 256;
+    r[u] = p < nnz ? rowidx[p] : -1;
+  }
+  int32_t k[RANK_ITEMS];
+#pragma unroll
+  for (int u = 0; u < RANK_ITEMS; ++u) k[u] = r[u] >= 0 ? atomicAdd(cnt + r[u], 1) : 0;
+#pragma unroll
+  for (int u = 0; u < RANK_ITEMS; ++u) {
+    const int64_t p = base + u * 256;
+    if (p < nnz) rank[p] = (uint16_t)min(k[u], 65535);  // 65535: a row far over TB_LIMIT, path not taken
+  }
+}
+
+template <class T>
+__global__ void __launch_bounds__(EXPAND_THREADS)
+k_row_place(int64_t nnz, int32_t ncols, int64_t ntiles, const int32_t *__restrict__ colptr,
+            const int32_t *__restrict__ tile_col, const int32_t *__restrict__ rowidx, const T *__restrict__ vals,
+            bool conj, const int32_t *__restrict__ rowstart, const uint16_t *__restrict__ rank,
+            AsmEnt<T> *__restrict__ ent) {
+  __shared__ int32_t win[EXPAND_WINDOW];
+  __shared__ uint32_t scol[EXPAND_TILE];
+  const int64_t tile0 = (int64_t)blockIdx.x * EXPAND_TILE;
+  {
+    uint32_t out[EXPAND_ITEMS];
+    tile_columns(nnz, ncols, ntiles, colptr, tile_col, win, tile0 + (int64_t)threadIdx.x * EXPAND_ITEMS, out);
+    if (tile0 + (int64_t)threadIdx.x * EXPAND_ITEMS < nnz) {
+#pragma unroll
+      for (int e = 0; e < EXPAND_ITEMS; ++e) scol[threadIdx.x * EXPAND_ITEMS + e] = out[e];
+    }
+  }
+  __syncthreads();
+  // lanes now take consecutive positions: coalesced reads of rowidx, rank and vals
+#pragma unroll 4
+  for (int e = 0; e < EXPAND_ITEMS; ++e) {
+    const int32_t l = e * EXPAND_THREADS + threadIdx.x;
+    const int64_t p = tile0 + l;
+    if (p < nnz) {
+      const int32_t slot = __ldg(rowstart + rowidx[p]) + rank[p];
+      AsmEnt<T> rec;
+      rec.key = scol[l];
+      const T v = vals[p];
+      rec.val = conj ? Num<T>::conj(v) : v;
+      ent[slot] = rec;
+    }
+  }
+}
+
+template <class T>
+__global__ void __launch_bounds__(TB_ROWS)
+k_row_sort(int32_t nrows, const int32_t *__restrict__ start, const AsmEnt<T> *__restrict__ ent,
+           int32_t *__restrict__ out_idx, T *__restrict__ out_vals) {
+  __shared__ uint32_t sk[TB_CAP];
+  __shared__ uint16_t si[TB_CAP];
+  const int t = threadIdx.x;
+  const int32_t rend = min((int32_t)(blockIdx.x + 1) * TB_ROWS, nrows);
+  int32_t r0 = blockIdx.x * TB_ROWS;
+  while (r0 < rend) {
+    const int32_t s0 = start[r0];
+    const int32_t r = r0 + t;
+    const int32_t e_t = r < rend ? start[r + 1] : 0;
+    const int ncover = __syncthreads_count(r < rend && e_t - s0 <= TB_CAP);  // a prefix; >= 1 (TB_LIMIT <= TB_CAP)
+    const int32_t len = start[r0 + ncover] - s0;
+    for (int32_t i = t; i < len; i += TB_ROWS) {
+      sk[i] = (uint32_t)ent[s0 + i].key;
+      si[i] = (uint16_t)i;
+    }
+    __syncthreads();
+    if (t < ncover) {
+      const int32_t a = start[r] - s0, b = e_t - s0;
+      for (int32_t i = a + 1; i < b; ++i) {
+        const uint32_t key = sk[i];
+        if (sk[i - 1] <= key) continue;
+        const uint16_t idx = si[i];
+        int32_t j = i;
+        while (j > a && sk[j - 1] > key) {
+          sk[j] = sk[j - 1];
+          si[j] = si[j - 1];
+          --j;
+        }
+        sk[j] = key;
+        si[j] = idx;
+      }
+    }
+    __syncthreads();
+    for (int32_t i = t; i < len; i += TB_ROWS) {
+      out_idx[s0 + i] = (int32_t)sk[i];
+      out_vals[s0 + i] = ent[s0 + si[i]].val;
+    }
+    r0 += ncover;
+    __syncthreads();  // sk / si are reused by the next pass
+  }
+}
+
+// returns SLC_OK with *done = true when the bucket path produced the transpose, *done = false when a row is
+// too long for it (nothing written)
+template <class T>
+static int transpose_buckets(int32_t nrows, int32_t ncols, int64_t nnz, const int32_t *colptr,
+                             const int32_t *rowidx, const T *vals, bool conj, int32_t *out_ptr, int32_t *out_idx,
+                             T *out_vals, bool *done) {
+  cudaStream_t s = cur_stream();
+  *done = false;
+  DevBuf<int32_t> cnt;
+  DevBuf<uint16_t> rank;
+  DevBuf<unsigned long long> longest;
+  SLC_TRY(cnt.alloc((size_t)nrows + 1));
+  SLC_TRY(rank.alloc((size_t)nnz));
+  SLC_TRY(longest.alloc(1));
+  SLC_CUDA(cudaMemsetAsync(cnt.p, 0, ((size_t)nrows + 1) * sizeof(int32_t), s));
+  SLC_CUDA(cudaMemsetAsync(longest.p, 0, sizeof(unsigned long long), s));
+  k_row_rank<<<(unsigned)ceil_div(nnz, 256 * RANK_ITEMS), 256, 0, s>>>(nnz, rowidx, cnt.p, rank.p);
+  SLC_LAUNCHED();
+  SLC_TRY(max_i32_into(cnt.p, nrows, longest.p));
+  unsigned long long hmax = 0;
+  SLC_CUDA(cudaMemcpyAsync(&hmax, longest.p, sizeof hmax, cudaMemcpyDeviceToHost, s));
+  SLC_CUDA(cudaStreamSynchronize(s));
+  if (hmax > (unsigned long long)TB_LIMIT) return SLC_OK;
+  SLC_TRY(exclusive_scan_i32(cnt.p, out_ptr, (int64_t)nrows + 1));
+  cnt.release();
+  DevBuf<AsmEnt<T>> ent;
+  SLC_TRY(ent.alloc((size_t)nnz));
+  const int64_t ntiles = ceil_div(nnz, EXPAND_TILE);
+  DevBuf<int32_t> tile_col;
+  SLC_TRY(tile_col.alloc((size_t)ntiles));
+  k_tile_first_col<<<(unsigned)ceil_div(ncols, 256), 256, 0, s>>>(ncols, colptr, tile_col.p);
+  SLC_LAUNCHED();
+  k_row_place<T><<<(unsigned)ntiles, EXPAND_THREADS, 0, s>>>(nnz, ncols, ntiles, colptr, tile_col.p, rowidx, vals,
+                                                            conj, out_ptr, rank.p, ent.p);
+  SLC_LAUNCHED();
+  k_row_sort<T><<<(unsigned)ceil_div((int64_t)nrows, TB_ROWS), TB_ROWS, 0, s>>>(nrows, out_ptr, ent.p, out_idx,
+                                                                                out_vals);
+  SLC_LAUNCHED();
+  *done = true;
+  return SLC_OK;
+}
+
 template <class T>
 int transpose_csc(int32_t nrows, int32_t ncols, int64_t nnz, const int32_t *colptr,
                   const int32_t *rowidx, const T *vals, bool conj, int32_t *out_ptr, int32_t *out_idx,
@@ -139,6 +309,12 @@ int transpose_csc(int32_t nrows, int32_t ncols, int64_t nnz, const int32_t *colp
   if (nnz == 0) {
     SLC_CUDA(cudaMemsetAsync(out_ptr, 0, ((size_t)nrows + 1) * sizeof(int32_t), s));
     return SLC_OK;
+  }
+  // SLC_TR_BUCKET (1): count / place / sort-per-row when every row is short; 0 = always the radix sort
+  if (env_int("SLC_TR_BUCKET", 1) != 0 && nrows > 0) {
+    bool done = false;
+    SLC_TRY(transpose_buckets<T>(nrows, ncols, nnz, colptr, rowidx, vals, conj, out_ptr, out_idx, out_vals, &done));
+    if (done) return SLC_OK;
   }
   DevBuf<uint32_t> k0, k1, p0, p1;
   SLC_TRY(k0.alloc(nnz));

@@ -294,10 +294,15 @@ def test_mulm_stencil_block_and_column_range(sl):
 
 # ---- transpose ---------------------------------------------------------------------------------------
 
+@pytest.mark.parametrize("bucket", ["1", "0"])
 @pytest.mark.parametrize("dtype", DTYPES)
-def test_transpose_and_ctrans(sl, dtype):
+def test_transpose_and_ctrans(sl, dtype, bucket, monkeypatch):
+    """Both transpose paths: count / place / sort-per-row (rows of at most 512 entries; (40, 2000) makes a
+    block take several passes over its rows, (5000, 300) spreads over many blocks, (7, 3000) has rows too
+    long for it and falls through) and the radix sort."""
+    monkeypatch.setenv("SLC_TR_BUCKET", bucket)
     rng = np.random.default_rng(31)
-    for nr, nc, dens in shapes():
+    for nr, nc, dens in shapes() + [(40, 2000, 0.2), (5000, 300, 0.03)]:
         om = random_csc(rng, nr, nc, dens, dtype)
         m = to_matrix(sl, om)
         for fn, ofn in ((sl.transpose, oracle.transpose), (sl.ctrans, oracle.ctrans)):
@@ -328,10 +333,15 @@ def test_ctrans_known_answers_and_hermitian(sl):
 
 # ---- triplet assembly ----------------------------------------------------------------------------------
 
+@pytest.mark.parametrize("bucket", ["1", "0"])
 @pytest.mark.parametrize("dtype", DTYPES)
-def test_compress_matches_oracle(sl, dtype):
+def test_compress_matches_oracle(sl, dtype, bucket, monkeypatch):
+    """Both assembly paths: count / place / sort-per-column (short columns; (513, 129) makes a block
+    take several passes over its span, (64, 3000) spreads over many blocks, (2000, 3) has columns
+    longer than the bucket limit and falls through to the sort) and the full radix sort."""
+    monkeypatch.setenv("SLC_ASM_BUCKET", bucket)
     rng = np.random.default_rng(41)
-    for nr, nc in [(1, 1), (3, 5), (40, 40), (200, 10), (10, 2000), (513, 129)]:
+    for nr, nc in [(1, 1), (3, 5), (40, 40), (200, 10), (10, 2000), (513, 129), (64, 3000), (2000, 3)]:
         for integer in (True, False):
             r, c, v = arbitrary_triples(rng, nr, nc, dtype, integer)
             want = oracle.compress(nr, nc, r, c, v)
