@@ -55,6 +55,11 @@ extern std::atomic<int64_t> g_launches;
 
 // ---- stream-ordered device buffer ------------------------------------------------------------
 
+// The device's default memory pool keeps what is freed into it (release threshold = max), so the work
+// buffers of one call are reused by the next instead of going back to the driver at the first
+// synchronisation.  Cheap after the first call per thread and device.
+int configure_pool_once();
+
 // Owns one cudaMallocAsync allocation.  Freed on the current stream, so a buffer may be
 // released right after the last kernel that reads it has been enqueued.
 template <class U>
@@ -72,6 +77,7 @@ struct DevBuf {
   ~DevBuf() { release(); }
   int alloc(size_t count) {
     release();
+    if (int rc = configure_pool_once(); rc != SLC_OK) return rc;
     n = count;
     size_t bytes = (count ? count : 1) * sizeof(U);
     cudaError_t e = cudaMallocAsync((void **)&p, bytes, cur_stream());
@@ -425,6 +431,13 @@ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 int sm_count();
 
 // device primitives implemented in slc_prims.cu (radix sort, scans)
+// tile shape of the radix kernels (a block takes RS_TILE consecutive keys, 256 digit values per pass)
+constexpr int RS_THREADS = 256;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 keys per block
+constexpr int RS_BINS = 256;
+// offsets[d * ntiles + t], ntiles = ceil(n / RS_TILE): see slc_prims.cu
+int tile_digit_offsets_u32(const uint32_t *keys, int64_t n, int shift, int32_t *offsets);
 // *out <- max(*out, max(v[0 .. n)))  (values >= 0; *out is a device word the caller has initialised)
 int max_i32_into(const int32_t *v, int64_t n, unsigned long long *out);
 int exclusive_scan_i32(const int32_t *in, int32_t *out, int64_t n);  // out may alias in

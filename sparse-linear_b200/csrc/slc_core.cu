@@ -35,7 +35,7 @@ int sm_count() {
   return cached;
 }
 
-static int configure_pool_once() {
+int configure_pool_once() {
   // Keep freed blocks in the stream-ordered pool: repeated products and SpGEMM calls reuse
   // them instead of going back to the driver.
   static thread_local int done_dev = -1;

@@ -132,11 +132,7 @@ int exclusive_scan_i64(const int64_t *in, int64_t *out, int64_t n) {
 
 // ---- radix sort -------------------------------------------------------------------------------------
 
-constexpr int RS_THREADS = 256;
-constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 keys per block
-constexpr int RS_BINS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;   // RS_THREADS, RS_ITEMS, RS_TILE, RS_BINS: slc_common.cuh
 
 __device__ __forceinline__ uint32_t ld_once(const uint32_t *p) {
   uint32_t v;
@@ -434,6 +430,17 @@ static int sort_pairs_impl(const K *src, K *ka, K *kb, uint32_t *va, uint32_t *v
     vout = (vout == va) ? vb : va;
   }
   return SLC_OK;
+}
+
+// One histogram pass on its own: offsets[d * ntiles + t] = where the keys of tile t (RS_TILE consecutive
+// keys) whose digit (key >> shift) & 255 is d start in an array partitioned by digit (tiles in order
+// inside a digit).  Used by the coarse column partition of compress.
+int tile_digit_offsets_u32(const uint32_t *keys, int64_t n, int shift, int32_t *offsets) {
+  if (n <= 0) return SLC_OK;
+  const int64_t ntiles = ceil_div(n, RS_TILE);
+  k_radix_hist<uint32_t><<<(unsigned)ntiles, RS_THREADS, 0, cur_stream()>>>(keys, n, shift, ntiles, offsets);
+  SLC_LAUNCHED();
+  return exclusive_scan_i32(offsets, offsets, ntiles * RS_BINS);
 }
 
 int sort_pairs_u32(const uint32_t *src, uint32_t *ka, uint32_t *kb, uint32_t *va, uint32_t *vb, int64_t n,

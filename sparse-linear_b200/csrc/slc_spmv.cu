@@ -1309,7 +1309,11 @@ k_spmm_boundary(int32_t nrows, int32_t r0, int32_t r1, uint32_t zmask, const int
   const int32_t len = __ldg(rowlen + row);
   const int32_t *ci = colidx + base;
   const T *va = vals + base;
-  for (int32_t j0 = 0; j0 < k; j0 += JT) {
+  // blockIdx.y = column tile: the two boundary planes are a few per cent of the rows, and a thread that
+  // walked all k columns left 17 warps per SM waiting out one NVLink round trip after the other (a third
+  // of the 8-GPU step); with a thread per (row, tile) k / JT times as many loads are in flight
+  {
+    const int32_t j0 = blockIdx.y * JT;
     T acc[JT];
 #pragma unroll
     for (int j = 0; j < JT; ++j) acc[j] = (j0 + j < k) ? yi(Y + (int64_t)(j0 + j) * ldy + row) : Num<T>::zero();
@@ -2215,7 +2219,7 @@ static int spmm_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   if (nb > 0) {
     const SellPlan &sp = m->sell;
     constexpr int JT = sizeof(T) == 16 ? 4 : 8;
-    k_spmm_boundary<T, JT><<<(unsigned)nb, 128, 0, s>>>(m->nrows, r0, r1, 0u, sp.slice_ptr, sp.rowlen, sp.colidx,
+    k_spmm_boundary<T, JT><<<dim3((unsigned)nb, (unsigned)ceil_div(k, JT)), 128, 0, s>>>(m->nrows, r0, r1, 0u, sp.slice_ptr, sp.rowlen, sp.colidx,
                                                         (const T *)sp.vals, xa, (T *)Y, ldy, k, yinit_zero<T>());
     SLC_LAUNCHED();
   }

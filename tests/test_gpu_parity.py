@@ -333,13 +333,15 @@ def test_ctrans_known_answers_and_hermitian(sl):
 
 # ---- triplet assembly ----------------------------------------------------------------------------------
 
-@pytest.mark.parametrize("bucket", ["1", "0"])
+@pytest.mark.parametrize("bucket", ["1", "coarse", "0"])
 @pytest.mark.parametrize("dtype", DTYPES)
 def test_compress_matches_oracle(sl, dtype, bucket, monkeypatch):
-    """Both assembly paths: count / place / sort-per-column (short columns; (513, 129) makes a block
+    """The assembly paths: count / place / sort-per-column (short columns; (513, 129) makes a block
     take several passes over its span, (64, 3000) spreads over many blocks, (2000, 3) has columns
-    longer than the bucket limit and falls through to the sort) and the full radix sort."""
-    monkeypatch.setenv("SLC_ASM_BUCKET", bucket)
+    longer than the bucket limit and falls through to the sort), the same behind the coarse column
+    partition (forced on: by default only inputs that outgrow L2 take it), and the full radix sort."""
+    monkeypatch.setenv("SLC_ASM_BUCKET", "0" if bucket == "0" else "1")
+    monkeypatch.setenv("SLC_ASM_COARSE", "1" if bucket == "coarse" else "0")
     rng = np.random.default_rng(41)
     for nr, nc in [(1, 1), (3, 5), (40, 40), (200, 10), (10, 2000), (513, 129), (64, 3000), (2000, 3)]:
         for integer in (True, False):
@@ -366,8 +368,10 @@ def test_compress_many_duplicates_zeros_and_empty(sl):
     assert z.pointers.tolist() == [0, 1, 2] and z.values.tolist() == [0.0, 0.0]   # zeros are kept
 
 
-def test_compress_bounds_errors(sl):
+@pytest.mark.parametrize("coarse", ["0", "1"])
+def test_compress_bounds_errors(sl, coarse, monkeypatch):
     """Sparse.hs:196-212: rows are checked before columns; the first offending position is reported."""
+    monkeypatch.setenv("SLC_ASM_COARSE", coarse)
     with pytest.raises(sl.SparseLinearError, match=r"compress: row index out of bounds \(0,3\) at 1") as e:
         sl.compress(3, 3, [0, 3, 5], [0, 9, 0], [1.0, 1.0, 1.0])
     assert e.value.pos == 1 and e.value.code == sl._capi.ERR_ROW_BOUNDS
@@ -502,7 +506,7 @@ def test_spmm_brick_matches_oracle(sl, monkeypatch, jt, rows):
              (g.stencil3d_27pt((16, 32, 64)), True),        # even strides
              (_band27(6000, 50, 400, rng), True),           # wrapped neighbours present
              (_band27(7000, 40, 400, rng, keep=0.97), True),   # a few holes, still a sliced plan: masked path
-             (g.stencil3d_27pt((9, 10, 37)), False),        # small grid: balanced-CSR plan, the general kernel
+             (g.stencil3d_27pt((9, 10, 37)), True),         # small grid (5 % padding: still a sliced plan), blocks mostly boundary
              (_band27(5000, 24, 240, rng, keep=0.8), False)]   # many holes: the same
     for gm, staged in cases:
         m, om = to_matrix(sl, gm), oracle.csc(*gm)
