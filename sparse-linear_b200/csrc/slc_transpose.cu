@@ -310,8 +310,12 @@ int transpose_csc(int32_t nrows, int32_t ncols, int64_t nnz, const int32_t *colp
     SLC_CUDA(cudaMemsetAsync(out_ptr, 0, ((size_t)nrows + 1) * sizeof(int32_t), s));
     return SLC_OK;
   }
-  // SLC_TR_BUCKET (1): count / place / sort-per-row when every row is short; 0 = always the radix sort
-  if (env_int("SLC_TR_BUCKET", 1) != 0 && nrows > 0) {
+  // SLC_TR_BUCKET (0): 1 = count / place / sort-per-row when every row is short.  Measured on B200 (round 2,
+  // profiles/bench/r2j_cfg*t_*.json): cfg 3 0.445 ms against 0.497 ms for the radix sort, but cfg 5 6.30
+  // against 5.87 ms (a record of 16 bytes moved three times is no less traffic than 8-byte (key, position)
+  // pairs moved three times plus one gather) and cfg 4 pays 3.6 ms of contended atomics before it finds out
+  // that its rows are too long -- so the radix sort stays the default and this path is opt-in.
+  if (env_int("SLC_TR_BUCKET", 0) != 0 && nrows > 0) {
     bool done = false;
     SLC_TRY(transpose_buckets<T>(nrows, ncols, nnz, colptr, rowidx, vals, conj, out_ptr, out_idx, out_vals, &done));
     if (done) return SLC_OK;
