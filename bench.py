@@ -297,7 +297,7 @@ def entry_spmv(args, sl, tm, name, desc, host_m=None, dev_m=None, dtype=np.float
     plan = dm.plan_info()
     value = abytes / (ms * 1e-3) / 1e9
     entry = {"name": name, "metric": METRIC, "value": value, "unit": "GB/s", "ms_per_step": ms, "steps": steps,
-             "dtype": "c128" if p == "z" else "f64", "clocks": r["clocks"], "gpu_launches": r["launches"],
+             "dtype": "c128" if p == "z" else "f64", "clocks": r["clocks"], "gpu_launches": r["launches"], "ms_per_repeat": r.get("ms_per_repeat"),
              "config": {"workload": desc, "rows": nrows, "cols": ncols, "nnz": nnz, "plan": plan,
                         "algorithmic_bytes_per_step": abytes, "operand": "x rotates through 3 device buffers",
                         "l2": "inputs larger than L2 (%.0f MB streamed per step)" % (abytes / 1e6)
@@ -416,7 +416,7 @@ def entry_spmm(args, sl, tm, name, desc, host_m, dtype, k, check_cols, traffic_k
     value = abytes / (ms * 1e-3) / 1e9
     plan = dm.plan_info()
     entry = {"name": name, "metric": "spmm_effective_hbm_gbps", "value": value, "unit": "GB/s", "ms_per_step": ms,
-             "steps": steps, "dtype": "c128" if p == "z" else "f64", "clocks": r["clocks"], "gpu_launches": r["launches"],
+             "steps": steps, "dtype": "c128" if p == "z" else "f64", "clocks": r["clocks"], "gpu_launches": r["launches"], "ms_per_repeat": r.get("ms_per_repeat"),
              "config": {"workload": desc, "rows": nrows, "cols": ncols, "nnz": nnz, "k": k, "plan": plan,
                         "algorithmic_bytes_per_step": abytes, "l2": "inputs larger than L2 (%.0f MB per step)" % (abytes / 1e6),
                         "pct_of_nominal_8TBs": 100.0 * value / NOMINAL_HBM_GBS},
@@ -516,7 +516,7 @@ def entry_spgemm(args, sl, tm, host_m, n):
     floor_bytes = (2 * nnz + nnzc) * 12 + 3 * (nc + 1) * 4
     gbs = floor_bytes / (ms * 1e-3) / 1e9
     entry = {"name": "cfg3_spgemm", "metric": "spgemm_output_nnz_per_s", "value": nnzc / (ms * 1e-3), "unit": "nnz/s",
-             "ms_per_step": ms, "steps": steps, "dtype": "f64", "clocks": r["clocks"], "gpu_launches": r["launches"],
+             "ms_per_step": ms, "steps": steps, "dtype": "f64", "clocks": r["clocks"], "gpu_launches": r["launches"], "ms_per_repeat": r.get("ms_per_repeat"),
              "config": {"workload": "cfg3: SpGEMM A*A, 3D 7-point Laplacian %d^3 (symbolic + numeric, handles resident)" % n,
                         "nnz_in": nnz, "nnz_out": nnzc, "byte_floor": floor_bytes},
              "roofline": roofline(gbs, "k_mm_merge (numeric)", "cfg3",
@@ -574,7 +574,7 @@ def entry_transpose(args, sl, tm, name, desc, m, host_m, traffic_key=None, oracl
     abytes = 2 * nnz * 12 + (nr + nc + 2) * 4
     gbs = abytes / (ms * 1e-3) / 1e9
     entry = {"name": name, "metric": "transpose_nnz_per_s", "value": nnz / (ms * 1e-3), "unit": "nnz/s", "ms_per_step": ms,
-             "steps": steps, "dtype": "u32 keys + f64 values", "clocks": r["clocks"], "gpu_launches": r["launches"],
+             "steps": steps, "dtype": "u32 keys + f64 values", "clocks": r["clocks"], "gpu_launches": r["launches"], "ms_per_repeat": r.get("ms_per_repeat"),
              "config": {"workload": desc, "rows": nr, "cols": nc, "nnz": nnz, "algorithmic_bytes_per_step": abytes},
              "roofline": roofline(gbs, "k_radix_scatter", traffic_key,
                                   note="algorithmic bytes are the two-pass floor 2*nnz*(val+idx); an LSD radix sort moves more")}
@@ -636,7 +636,7 @@ def entry_assembly(args, sl, tm, host_m, n):
     gbs = abytes / (ms * 1e-3) / 1e9
     built = keep["a"]
     entry = {"name": "cfg3_assembly", "metric": "assembly_triplets_per_s", "value": n_in / (ms * 1e-3), "unit": "triplets/s",
-             "ms_per_step": ms, "steps": steps, "dtype": "u64 keys + f64 values", "clocks": r["clocks"], "gpu_launches": r["launches"],
+             "ms_per_step": ms, "steps": steps, "dtype": "u64 keys + f64 values", "clocks": r["clocks"], "gpu_launches": r["launches"], "ms_per_repeat": r.get("ms_per_repeat"),
              "config": {"workload": "cfg3: triplet assembly, 3D 7-point Laplacian %d^3, every entry split in 0.25 v + 0.75 v and "
                                     "shuffled (2x duplicates); triplets resident in HBM (slc_d_compress_dev)" % n,
                         "triplets_in": n_in, "nnz_out": nnz, "algorithmic_bytes_per_step": abytes},

@@ -218,43 +218,49 @@ def stencil_entry(args, rank, world, local_rank, dist, sl, stream, cpu_group, k)
     return entry
 
 
-# ---- cfg 3: SpGEMM, A in row blocks, B replicated ------------------------------------------------------------
+# ---- cfg 3: SpGEMM over ranks: column blocks of B (default) or row blocks of A ------------------------------
 
 def spgemm_entry(args, rank, world, local_rank, dist, sl, stream):
-    import torch
+    """C = A A on the cfg 3 Laplacian.  SLC_MM_PARTITION=cols (default): rank p computes C[:, J_p] = A B[:, J_p]
+    with A resident everywhere -- every per-column pass of the product shrinks with the block and the blocks
+    concatenate as they are.  =rows: C[I_p, :] = A[I_p, :] B with B replicated (round 1: the per-column passes
+    over all of B's columns stay on every rank: 2.8 x at 8 GPUs)."""
     import oracle
     n = args.grid or 128
     a = g.laplace3d_7pt(n)
-    bm = Matrix(a.ncols, a.nrows, a.colptr, a.rowidx, a.values)
+    by_cols = os.environ.get("SLC_MM_PARTITION", "cols") != "rows"
     splits = S.uniform_splits(n, world) * (n * n)           # z-slabs: equal work per rank
-    r0, r1 = int(splits[rank]), int(splits[rank + 1])
-    blk = S.row_block(a, r0, r1)
+    lo, hi = int(splits[rank]), int(splits[rank + 1])
+    whole = Matrix(a.ncols, a.nrows, a.colptr, a.rowidx, a.values)
+    blk = S.col_block(a, lo, hi) if by_cols else S.row_block(a, lo, hi)
     local = Matrix(blk.ncols, blk.nrows, blk.colptr, blk.rowidx, blk.values)
     keep = {}
 
     def step():
-        keep["c"] = sl.mm(local, bm)
+        keep["c"] = sl.mm(whole, local) if by_cols else sl.mm(local, whole)
     steps = max(3, min(args.steps, 20))
     for _ in range(3):
         step()
     ms, clocks, launches, how = timed_region(steps, step, step, stream, dist, world, local_rank, sl, use_graph=False)
     c = keep["c"]
     nnzc_local = sl.nonZero(c)
-    want = oracle.mm(oracle.csc(*blk), oracle.csc(*a))
+    want = oracle.mm(oracle.csc(*a), oracle.csc(*blk)) if by_cols else oracle.mm(oracle.csc(*blk), oracle.csc(*a))
     ok = B.same_matrix(c, want)
     all_ok = _reduce([1.0 if ok else 0.0], dist, world, "min")[0] == 1.0
-    nnzc, nnza = _reduce([nnzc_local, blk.colptr[-1]], dist, world)
-    nnzb = int(a.colptr[-1])
-    floor_bytes = (nnza + nnzb * world + nnzc) * 12 + 3 * (a.ncols + 1) * 4 * world
+    nnzc, nnzblk = _reduce([nnzc_local, blk.colptr[-1]], dist, world)
+    nnzfull = int(a.colptr[-1])
+    floor_bytes = (nnzblk + nnzfull * world + nnzc) * 12 + 3 * (a.ncols + 1) * 4 * world
     gbs = floor_bytes / (ms * 1e-3) / 1e9 / world
+    how_cut = ("B in %d column blocks (z-slabs), A resident on every rank" if by_cols else
+               "A in %d row blocks (z-slabs), B replicated") % world
     return {"name": "cfg3_spgemm", "metric": "spgemm_output_nnz_per_s", "value": nnzc / (ms * 1e-3), "unit": "nnz/s",
             "ms_per_step": ms, "steps": steps, "dtype": "f64", "clocks": clocks, "gpu_launches": launches,
-            "config": {"workload": "cfg3: SpGEMM A*A, 3D 7-point Laplacian %d^3, A in %d row blocks (z-slabs), "
-                                   "B replicated, no exchange during the product" % (n, world),
-                       "nnz_in": nnzb, "nnz_out": int(nnzc)},
-            "parity": {"oracle": "oracle.mm(row block, B) on every rank, after the timed loop",
+            "config": {"workload": "cfg3: SpGEMM A*A, 3D 7-point Laplacian %d^3, %s, no exchange during the product" % (n, how_cut),
+                       "partition": "cols" if by_cols else "rows", "nnz_in": nnzfull, "nnz_out": int(nnzc)},
+            "parity": {"oracle": "oracle.mm on every rank's block (%s), after the timed loop" %
+                                 ("A, B[:, J]" if by_cols else "A[I, :], B"),
                        "bit_exact_all_ranks": all_ok, "ok": all_ok, "required": "structure and values bit-exact"},
-            "roofline": B.roofline(gbs, "k_mm_merge (numeric)", note="per-GPU share of the one-pass byte floor (B counted once per rank)")}
+            "roofline": B.roofline(gbs, "k_mm_merge (numeric)", note="per-GPU share of the one-pass byte floor (the resident operand counted once per rank)")}
 
 
 # ---- cfg 4: power-law SpMV, x all-gathered over peer memory ----------------------------------------------
@@ -275,9 +281,16 @@ def powerlaw_entry(args, rank, world, local_rank, dist, sl, stream, cpu_group):
     del rl, cl, vl
     torch.cuda.empty_cache()
     nnz_local = sl.nonZero(local)
-    sh = S.ShardedSpMV(local, splits, rank, world, dist, cpu_group, mode="allgather")
+    # Who owns which part of x is independent of who owns which rows.  With x cut at the row bounds the rank that
+    # owns the sparsest rows owns most of x (58 of 134 MB at 8 ranks) and the other seven all pull that slice from
+    # it at once: 408 MB through one GPU's NVLink egress, 0.45 ms at line rate -- more than the product itself.
+    # Equal slices of x (SLC_AG_XSPLIT=uniform, default) make every rank serve 7 x 16.8 MB instead.  =rows keeps
+    # the x partition equal to the row partition (what an iteration y -> x without redistribution wants).
+    x_uniform = os.environ.get("SLC_AG_XSPLIT", "uniform") != "rows"
+    xs = S.uniform_splits(n, world) if x_uniform else splits
+    sh = S.ShardedSpMV(local, xs, rank, world, dist, cpu_group, mode="allgather")
     xfull = g.uniform_vector(n, seed=0)
-    xloc = np.ascontiguousarray(xfull[r0:r1])
+    xloc = np.ascontiguousarray(xfull[int(xs[rank]):int(xs[rank + 1])])
     sh.set_x(xloc)
     sh.cur ^= 1
     sh.set_x(xloc)
@@ -299,11 +312,12 @@ def powerlaw_entry(args, rank, world, local_rank, dist, sl, stream, cpu_group):
     per_gpu = value / world
     entry = {"name": "cfg4_spmv", "metric": B.METRIC, "value": value, "unit": "GB/s", "ms_per_step": ms, "steps": steps,
              "dtype": "f64", "clocks": clocks, "gpu_launches": launches,
-             "config": {"workload": "cfg4: R-MAT scale %d edge factor 16, Double SpMV, rows in %d blocks of equal nonzeros; x "
+             "config": {"workload": "cfg4: R-MAT scale %d edge factor 16, Double SpMV, rows in %d blocks of equal nonzeros, x owned in %s; x "
                                     "all-gathered over NVLink peer memory every product (%.0f MB inbound per GPU), then the "
-                                    "balanced kernel" % (scale, world, n * 8 * (world - 1) / world / 1e6),
+                                    "balanced kernel" % (scale, world, "equal slices" if x_uniform else "the same blocks",
+                                                         n * 8 * (world - 1) / world / 1e6),
                         "rows": n, "nnz": int(nnz), "algorithmic_bytes_per_step": abytes, "plan": local.device().plan_info(),
-                        "splits": [int(x) for x in splits]},
+                        "splits": [int(x) for x in splits], "x_splits": [int(x) for x in xs]},
              "parity": {"oracle": "oracle.mulv on every rank's device-assembled row block, after the timed loop",
                         "max_rel_err_over_ranks": worst, "ok": worst <= 1e-12, "required": "1e-12"},
              "roofline": B.roofline(per_gpu, "k_allgather_pull + k_spmv_bal",

@@ -1892,9 +1892,13 @@ static int dist_needs_entry(slc_matrix *m, int32_t nparts, int32_t self, const i
 // of a rank touch columns all over the matrix (power-law graphs: SURVEY.md section 8e, config 4), where
 // per-entry loads across NVLink would be one 32-byte sector per nonzero.
 template <class T>
-__global__ void __launch_bounds__(256) k_allgather_pull(const DistTable *tbl, T *xfull) {
-  const int p = blockIdx.y;
-  if (p >= tbl->nparts) return;
+__global__ void __launch_bounds__(256) k_allgather_pull(const DistTable *tbl, T *xfull, int self) {
+  // The parts are taken in the order self + 1, self + 2, ..., self (blocks are dispatched y-slowest, so
+  // blockIdx.y is also an order in time): every rank starts on a different owner.  With the order 0, 1, 2, ...
+  // all ranks pulled from the same one or two GPUs at any moment and those GPUs' NVLink egress, not the
+  // pullers' ingress, set the pace (8 ranks, R-MAT scale 24: 0.5 of the 0.94 ms step).
+  if ((int)blockIdx.y >= tbl->nparts) return;
+  const int p = (int)((blockIdx.y + (unsigned)self + 1u) % (unsigned)tbl->nparts);
   const int64_t lo = tbl->splits[p], n = (int64_t)tbl->splits[p + 1] - lo;
   const T *src = static_cast<const T *>(tbl->parts[p]);
   T *dst = xfull + lo;
@@ -1933,7 +1937,7 @@ static int spmv_allgather_entry(slc_matrix *m, int32_t nparts, int32_t self, con
     int64_t longest = 0;
     for (int p = 0; p < nparts; ++p) longest = std::max<int64_t>(longest, splits[p + 1] - splits[p]);
     const unsigned bx = (unsigned)std::max<int64_t>(1, std::min<int64_t>(ceil_div(longest, 256 * 8), 148 * 4));
-    k_allgather_pull<T><<<dim3(bx, (unsigned)nparts), 256, 0, cur_stream()>>>(tbl, (T *)x_full);
+    k_allgather_pull<T><<<dim3(bx, (unsigned)nparts), 256, 0, cur_stream()>>>(tbl, (T *)x_full, (int)self);
     SLC_LAUNCHED();
   }
   if (diag_env == 2) return SLC_OK;

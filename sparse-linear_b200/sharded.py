@@ -97,6 +97,39 @@ def mm_row_block(a, b, rank, world, splits=None):
     return mm(local, b), r0, r1
 
 
+def hstack_blocks(blocks):
+    """Column blocks of one matrix (CSC, same nrows, listed left to right) side by side: the arrays are
+    concatenated and the pointers shifted -- in CSC a column block is a contiguous slice, so this is the
+    cheap direction (compare vstack_blocks)."""
+    nrows = blocks[0].nrows
+    ptrs, base = [np.zeros(1, dtype=np.int64)], 0
+    for b in blocks:
+        cp = np.asarray(b.colptr, dtype=np.int64)
+        ptrs.append(cp[1:] + base)
+        base += int(cp[-1])
+    colptr = np.concatenate(ptrs)
+    rowidx = np.concatenate([np.asarray(b.rowidx, dtype=np.int32) for b in blocks]) if blocks else np.zeros(0, np.int32)
+    values = np.concatenate([np.asarray(b.values) for b in blocks])
+    return CSC(nrows, int(len(colptr) - 1), colptr.astype(np.int32), rowidx, values)
+
+
+def mm_col_block(a, b, rank, world, splits=None):
+    """This rank's share of C = A B by COLUMNS of B: C[:, c0:c1] = A B[:, c0:c1] (mm is column by column,
+    Data/Matrix/Sparse.hs:691-702, so a column block of C needs all of A and only that block of B).
+    a: Matrix, the whole A resident on this rank; b: host CSC of the whole B -- only the block is
+    uploaded.  Nothing is exchanged while computing and the blocks concatenate (hstack_blocks).
+    Unlike mm_row_block every per-column pass of the product (bounds, classes, scans, pointers) shrinks
+    with the block, which is what lets it scale: cfg 3 at 8 GPUs, see DESIGN.md section 5.
+    Returns (C block as Matrix, c0, c1)."""
+    from .matrix import mm
+    if splits is None:
+        splits = uniform_splits(b.ncols, world)
+    c0, c1 = int(splits[rank]), int(splits[rank + 1])
+    blk = col_block(b, c0, c1)
+    local = Matrix(blk.ncols, blk.nrows, blk.colptr, blk.rowidx, blk.values)
+    return mm(a, local), c0, c1
+
+
 def gather_blocks(c_local, dist, group=None):
     """One gather of the C blocks when a single result is wanted (host side, rank order)."""
     blk = CSC(c_local.nrows, c_local.ncols, c_local.pointers, c_local.indices, c_local.values)

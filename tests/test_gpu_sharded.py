@@ -194,6 +194,27 @@ def test_row_partitioned_spgemm_concatenates_to_the_oracle(sl):
         assert np.array_equal(got.values, want.values)
 
 
+def test_column_partitioned_spgemm_concatenates_to_the_oracle(sl):
+    """C = A B with B cut into column blocks and A replicated: the blocks side by side are the
+    undistributed product, structure and values bit for bit (uneven splits and an empty block included)."""
+    rng = np.random.default_rng(6)
+    for a, b, splits in ((g.laplace3d_7pt(9), g.laplace3d_7pt(9), None),
+                         (random_csc(rng, 120, 90, 0.08), random_csc(rng, 90, 150, 0.06), [0, 1, 1, 97, 150]),
+                         (rmat_csc(9, 6, seed=1), rmat_csc(9, 6, seed=2), None)):
+        world = 4 if splits is None else len(splits) - 1
+        want = oracle.mm(oracle.csc(*a), oracle.csc(*b))
+        am = to_matrix(sl, a)
+        blocks = []
+        for rank in range(world):
+            c, c0, c1 = sharded.mm_col_block(am, b, rank, world, splits)
+            assert c.ncols == c1 - c0 and c.nrows == a.nrows
+            blocks.append(g.CSC(c.nrows, c.ncols, c.pointers, c.indices, c.values))
+        got = sharded.hstack_blocks(blocks)
+        assert got.ncols == b.ncols
+        assert np.array_equal(got.colptr, want.colptr) and np.array_equal(got.rowidx, want.rowidx)
+        assert np.array_equal(got.values, want.values)
+
+
 @pytest.mark.parametrize("dtype", [np.float64, np.complex128])
 def test_sharded_transpose_and_assembly_device_ops(sl, dtype):
     """The ranks of sharded_transpose / sharded_compress run one after the other in this process, the

@@ -70,6 +70,25 @@ def test_vstack_blocks_inverts_row_block():
         assert oracle.check_format(oracle.csc(*back)) == 0
 
 
+def test_hstack_blocks_inverts_col_block_and_column_partitioned_product():
+    """Column blocks concatenate back (hstack_blocks), and C[:, J] = A B[:, J] block by block is the
+    oracle's product: the column-partitioned SpGEMM's host logic (the device test repeats it with slc_*_mm)."""
+    rng = np.random.default_rng(13)
+    for a, b, nparts in ((random_csc(rng, 40, 30, 0.2), random_csc(rng, 30, 50, 0.15), 4),
+                         (g.laplace3d_7pt(5), g.laplace3d_7pt(5), 3),
+                         (random_csc(rng, 6, 5, 0.5, np.complex128), random_csc(rng, 5, 3, 0.6, np.complex128), 5)):
+        splits = sharded.uniform_splits(b.ncols, nparts)
+        blocks = [sharded.col_block(b, splits[p], splits[p + 1]) for p in range(nparts)]
+        back = sharded.hstack_blocks(blocks)
+        assert np.array_equal(back.colptr, b.colptr) and np.array_equal(back.rowidx, b.rowidx)
+        assert np.array_equal(back.values, b.values)
+        want = oracle.mm(oracle.csc(*a), oracle.csc(*b))
+        parts = [oracle.mm(oracle.csc(*a), oracle.csc(*blk)) for blk in blocks]
+        got = sharded.hstack_blocks([g.CSC(c.nrows, c.ncols, c.colptr, c.rowidx, c.values) for c in parts])
+        assert np.array_equal(got.colptr, want.colptr) and np.array_equal(got.rowidx, want.rowidx)
+        assert np.array_equal(got.values, want.values)
+
+
 def test_row_partitioned_product_of_matrices_is_the_product():
     """mm on row blocks of A against all of B, stacked, equals mm(A, B) (oracle on both sides)."""
     rng = np.random.default_rng(8)
