@@ -2177,6 +2177,30 @@ static int spmm_dev(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
 // Y_local <- A_local X, X partitioned by row blocks over the GPUs of one box (column-major, every
 // part with its own leading dimension).  Sliced-ELL plans only (the stencils this is for): signal,
 // interior rows on the undistributed panel kernel, wait, boundary rows through the peers' memory.
+// Halo staging for the boundary rows of a row-partitioned block product: the columns [cmin, cmin + width)
+// that one side's boundary rows reach -- a few grid planes, partly this rank's own rows of X, partly a
+// neighbour's -- are copied for all k operand columns into one contiguous block W (leading dimension ldw).
+// The remote part crosses NVLink as coalesced streams instead of one 8-byte load per stored entry, and the
+// boundary rows then run on the same kernels as the interior (TMA-staged for 27-offset matrices) with W as
+// their operand.  blockIdx.y = operand column.
+template <class T>
+__global__ void __launch_bounds__(256)
+k_halo_stage(const DistTable *tbl, T *__restrict__ W, int64_t ldw, int32_t cmin, int32_t width) {
+  const int np = tbl->nparts;
+  const int32_t ncols = tbl->splits[np];
+  const int64_t j = blockIdx.y;
+  int q = 0;
+  for (int32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < width; i += gridDim.x * blockDim.x) {
+    const int32_t c = cmin + i;
+    T v = Num<T>::zero();  // columns outside the matrix (alignment slack) are never multiplied
+    if (c >= 0 && c < ncols) {
+      while (q + 1 < np && c >= tbl->splits[q + 1]) ++q;  // i only grows: the owner index only grows
+      v = ld_peer(static_cast<const T *>(tbl->parts[q]) + j * tbl->ld[q] + (c - tbl->splits[q]));
+    }
+    W[j * ldw + i] = v;
+  }
+}
+
 template <class T>
 static int spmm_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const int32_t *splits,
                            const double *const *X_parts, const int64_t *ldx_parts, double *Y, int64_t ldy,
@@ -2219,9 +2243,33 @@ static int spmm_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   SLC_TRY(launch_panel<T>(m, xa.self_X - xa.self_lo, xa.self_ld, (T *)Y, ldy, k, yinit_zero<T>(), r0, r1, xa.self_lo,
                           xa.self_hi));
   if (sync) SLC_TRY(slc_peer_wait(sync));
-  const int64_t nb = ceil_div(r0, 128) + ceil_div(m->nrows - r1, 128);
+  // SLC_SPMM_HALO (1): boundary rows through a staged copy of the columns they reach (k_halo_stage) and the
+  // interior kernels; 0 = k_spmm_boundary (per-entry loads from the owner's HBM) for every boundary row.
+  // A side whose rows reach too far for a staged copy to pay keeps the per-entry kernel.
+  bool staged_side[2] = {false, false};
+  if (env_int("SLC_SPMM_HALO", 1) != 0) {
+    for (int side = 0; side < 2; ++side) {
+      const int32_t ra = side == 0 ? 0 : r1, rb = side == 0 ? r0 : m->nrows;
+      const SellPlan &sp = m->sell;
+      if (rb <= ra || sp.side_cmax[side] < sp.side_cmin[side]) { staged_side[side] = rb <= ra; continue; }
+      const int32_t cmin = sp.side_cmin[side] & ~1;                 // even bounds and leading dimension: the
+      const int32_t cend = (sp.side_cmax[side] + 2) & ~1;           // TMA-staged kernel wants 16-byte alignment
+      const int64_t width = (int64_t)cend - cmin;
+      if (width > 8 * (int64_t)(rb - ra) + 65536 || (size_t)width * k * sizeof(T) > ((size_t)1 << 30)) continue;
+      DevBuf<T> w;
+      SLC_TRY(w.alloc((size_t)width * k));
+      k_halo_stage<T><<<dim3((unsigned)std::min<int64_t>(ceil_div(width, 256 * 4), 1024), (unsigned)k), 256, 0, s>>>(
+          tbl, w.p, width, cmin, (int32_t)width);
+      SLC_LAUNCHED();
+      SLC_TRY(launch_panel<T>(m, w.p - cmin, width, (T *)Y, ldy, k, yinit_zero<T>(), ra, rb, cmin, cend));
+      staged_side[side] = true;  // w is released in stream order behind the kernels that read it
+    }
+  }
+  const int32_t b0 = staged_side[0] ? 0 : r0, b1 = staged_side[1] ? m->nrows : r1;  // rows left for the per-entry kernel
+  const int64_t nb = ceil_div(b0, 128) + ceil_div(m->nrows - b1, 128);
   if (nb > 0) {
     const SellPlan &sp = m->sell;
+    const int32_t r0 = b0, r1 = b1;
     constexpr int JT = sizeof(T) == 16 ? 4 : 8;
     k_spmm_boundary<T, JT><<<dim3((unsigned)nb, (unsigned)ceil_div(k, JT)), 128, 0, s>>>(m->nrows, r0, r1, 0u, sp.slice_ptr, sp.rowlen, sp.colidx,
                                                         (const T *)sp.vals, xa, (T *)Y, ldy, k, yinit_zero<T>());
