@@ -1366,9 +1366,12 @@ static int launch_sell(slc_matrix *m, const XA &xa, T *y, int32_t row_begin = 0,
   // with compressed indices: U=4 0.379 ms (40 registers, 6 blocks per SM), held to 32 registers (8 blocks)
   // 0.338 ms, plus an L2 prefetch one batch ahead 0.326 ms (two: 0.330, three: 0.334, five: 0.340); U=8 0.471 ms (64 registers); off 0.430 ms
   if (u == 0) u = (m->max_rowlen <= 4 || sp.kbase) ? 4 : 8;
-  // SLC_PDL (1): programmatic dependent launch -- back-to-back products overlap the next kernel's first
-  // wave (launch, values towards L2) with the previous kernel's tail; 0 = plain stream order
-  static const int pdl_env = env_int("SLC_PDL", 1);
+  // SLC_PDL (0): 1 = programmatic dependent launch -- back-to-back products overlap the next kernel's first
+  // wave (launch, values towards L2) with the previous kernel's tail.  Measured (round 2): no difference on
+  // one GPU (0.3286 against 0.3280 ms on cfg 5) and 4 % slower at 8 GPUs (0.0555 against 0.0529 ms: the early
+  // blocks of the next product sit on the slots the spinning boundary blocks of this one would take), so
+  // plain stream order is the default.
+  static const int pdl_env = env_int("SLC_PDL", 0);
   const bool pdl = pdl_env != 0;
   const int first_wave = pdl ? sm_count() * 8 : 0;
   const int32_t *no_kbase = nullptr;
@@ -1842,7 +1845,7 @@ static int spmv_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   cudaStream_t s = cur_stream();
   static const int u_env = env_int("SLC_SELL_U", 0);
   const int u = u_env ? u_env : ((m->max_rowlen <= 4 || sp.kbase) ? 4 : 8);
-  static const int pdl_env = env_int("SLC_PDL", 1);  // see launch_sell
+  static const int pdl_env = env_int("SLC_PDL", 0);  // see launch_sell
   const bool pdl = pdl_env != 0;
   const int32_t first_wave = pdl ? sm_count() * 8 : 0;
   cudaError_t le = cudaSuccess;
