@@ -200,6 +200,7 @@ struct SellPlan {
   int32_t side_cmin[2] = {0x7fffffff, 0x7fffffff}, side_cmax[2] = {-1, -1};  // columns the rows below / above the interior reach
   // widest column window of a 1024-row block (k_spmm_window), -1 = not measured yet
   int32_t window_max = -1;
+  int32_t window_max2 = -1;  // widest union window over pairs of neighbouring 1024-row blocks (cluster kernel)
   // k_spmm_panel: distance in rows between grid lines (the near off-diagonal band of a stencil),
   // -1 = not measured yet, 0 = none; and the cached slice order that tiles blocks over lines
   int32_t line_stride = -1;

@@ -2,6 +2,7 @@
 // Reference shapes: Matrix record Data/Matrix/Sparse.hs:67-76; withConstMatrix / fromForeign
 // Data/Matrix/Sparse/Foreign.hs:24-88 (paths relative to /root/reference/sparse-linear/src).
 #include "slc_common.cuh"
+#include <vector>
 
 namespace slc {
 
@@ -327,14 +328,38 @@ int slc_ipc_export(const void *dev_ptr, void *handle72) {
   memcpy((char *)handle72 + sizeof h, &off, sizeof off);
   return SLC_OK;
 }
+// Two exported pointers of one peer can sit in the same driver allocation (small cudaMalloc blocks are
+// sub-allocated), and a process may open an IPC handle only once: imports are therefore reference-counted per
+// (device, handle), the second import reuses the first mapping, and the mapping is closed with its last user.
+namespace {
+struct IpcMapping {
+  int device;
+  cudaIpcMemHandle_t handle;
+  void *base;
+  int refs;
+};
+std::mutex g_ipc_mu;
+std::vector<IpcMapping> g_ipc_open;
+}  // namespace
+
 int slc_ipc_import(const void *handle72, void **dev_ptr) {
   if (!dev_ptr || !handle72) return fail(SLC_ERR_INVALID, "slc_ipc_import: null argument");
   cudaIpcMemHandle_t h;
   int64_t off = 0;
   memcpy(&h, handle72, sizeof h);
   memcpy(&off, (const char *)handle72 + sizeof h, sizeof off);
+  int dev = 0;
+  SLC_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(g_ipc_mu);
+  for (auto &mp : g_ipc_open)
+    if (mp.device == dev && memcmp(&mp.handle, &h, sizeof h) == 0) {
+      ++mp.refs;
+      *dev_ptr = (char *)mp.base + off;
+      return SLC_OK;
+    }
   void *base = nullptr;
   SLC_CUDA(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+  g_ipc_open.push_back(IpcMapping{dev, h, base, 1});
   *dev_ptr = (char *)base + off;
   return SLC_OK;
 }
@@ -342,6 +367,13 @@ int slc_ipc_close(void *dev_ptr) {
   if (!dev_ptr) return SLC_OK;
   void *base = nullptr;
   SLC_TRY(containing_allocation(dev_ptr, &base));
+  std::lock_guard<std::mutex> lock(g_ipc_mu);
+  for (size_t i = 0; i < g_ipc_open.size(); ++i)
+    if (g_ipc_open[i].base == base) {
+      if (--g_ipc_open[i].refs > 0) return SLC_OK;
+      g_ipc_open.erase(g_ipc_open.begin() + (long)i);
+      break;
+    }
   SLC_CUDA(cudaIpcCloseMemHandle(base));
   return SLC_OK;
 }

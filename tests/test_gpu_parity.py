@@ -242,14 +242,19 @@ def test_mulm_stencils_bit_exact(sl, dtype):
         np.testing.assert_array_equal(sl.mulM(m, X), oracle.mulm(om, X))
 
 
+@pytest.mark.parametrize("cluster", ["1", "0"])
 @pytest.mark.parametrize("dtype", DTYPES)
-def test_mulm_banded_window_kernel(sl, dtype):
-    """Banded matrices with short rows take the TMA-staged kernel (k_spmm_window): 1024-row blocks, so
-    use sizes around one and several blocks, a ragged last block, fewer columns than pipeline stages,
+def test_mulm_banded_window_kernel(sl, dtype, cluster, monkeypatch):
+    """Banded matrices with short rows take the TMA-staged kernels: k_spmm_window (one CTA per 1024-row
+    block) and k_spmm_window2 (two CTAs per cluster sharing the union of their windows through TMA
+    multicast).  Sizes around one and several blocks, an odd number of blocks (the last cluster has a CTA
+    with no rows), a ragged last block, fewer columns than pipeline stages, many more columns than stages,
     and a band wide enough that the stage count drops to the minimum."""
+    monkeypatch.setenv("SLC_SPMM_CLUSTER", cluster)
     rng = np.random.default_rng(31)
     cases = [(g.laplace2d_5pt(32, dtype), 3), (g.laplace2d_5pt(46, dtype), 9), (g.laplace2d_5pt(90, dtype), 20),
-             (g.tridiag(5000, dtype=dtype), 1), (g.laplace2d_5pt(300, dtype), 2)]
+             (g.tridiag(5000, dtype=dtype), 1), (g.tridiag(5000, dtype=dtype), 33), (g.laplace2d_5pt(64, dtype), 17),
+             (g.laplace2d_5pt(300, dtype), 2)]
     for gm, k in cases:
         om, m = oracle.csc(*gm), to_matrix(sl, gm)
         X = np.asfortranarray(np.stack([vec(rng, gm.ncols, dtype) for _ in range(k)], axis=1))
