@@ -205,11 +205,38 @@ __device__ __forceinline__ unsigned digit_peers(int d) {
 // neighbours of the parked tile are neighbours in the output, so a change of key between them is a
 // bucket boundary at a known position; the first key of each run has its predecessor in another
 // tile and is left to k_ptrs_run_starts.  This replaces a separate pass over the sorted keys.
+// Bucket pointers of a run of EMPTY buckets: ptr[lo .. hi] = value.  Short runs are written by the thread that
+// found them; a long run (a column block of a banded matrix has a million empty rows in a row: one thread
+// took 3.6 ms over them in the sharded transpose) is queued for k_ptr_fill_gaps, which fills it with a block.
+constexpr int PTR_GAP_INLINE = 64;
+constexpr int PTR_GAP_QUEUE = 4096;
+__device__ __forceinline__ void ptr_fill(int32_t *__restrict__ ptr, int64_t lo, int64_t hi, int32_t value,
+                                         int4 *__restrict__ gaps, int *__restrict__ gap_count) {
+  if (hi - lo >= PTR_GAP_INLINE && gaps) {
+    const int g = atomicAdd(gap_count, 1);
+    if (g < PTR_GAP_QUEUE) {
+      gaps[g] = make_int4((int)lo, (int)hi, value, 0);
+      return;
+    }
+  }
+  for (int64_t r = lo; r <= hi; ++r) ptr[r] = value;
+}
+
+__global__ void __launch_bounds__(256)
+k_ptr_fill_gaps(const int4 *__restrict__ gaps, const int *__restrict__ gap_count, int32_t *__restrict__ ptr) {
+  const int n = min(*gap_count, PTR_GAP_QUEUE);
+  for (int g = blockIdx.x; g < n; g += gridDim.x) {
+    const int4 q = gaps[g];
+    for (int64_t r = (int64_t)q.x + threadIdx.x; r <= q.y; r += blockDim.x) ptr[r] = q.z;
+  }
+}
+
 template <class K, bool IOTA, bool PTRS>
 __global__ void __launch_bounds__(RS_THREADS, 3)
 k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals_in, K *__restrict__ keys_out,
                 uint32_t *__restrict__ vals_out, int64_t n, int shift, int64_t ntiles,
-                const int32_t *__restrict__ hist_scanned, uint32_t zmask, int32_t *__restrict__ ptr_out) {
+                const int32_t *__restrict__ hist_scanned, uint32_t zmask, int32_t *__restrict__ ptr_out,
+                int4 *__restrict__ gaps, int *__restrict__ gap_count) {
   extern __shared__ __align__(16) unsigned char rs_smem[];
   K *skeys = reinterpret_cast<K *>(rs_smem);                         // [RS_TILE]
   uint32_t *svals = reinterpret_cast<uint32_t *>(skeys + RS_TILE);   // [RS_TILE]
@@ -328,7 +355,7 @@ k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals
     if constexpr (PTRS) {
       if (i > local_base[d]) {
         const K pk = skeys[i - 1];
-        for (int64_t r = (int64_t)pk + 1; r <= (int64_t)kk; ++r) ptr_out[r] = (int32_t)pos;
+        if (pk != kk) ptr_fill(ptr_out, (int64_t)pk + 1, (int64_t)kk, (int32_t)pos, gaps, gap_count);
       }
     }
   }
@@ -339,7 +366,8 @@ k_radix_scatter(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals
 // per entry of the scanned histogram (digit-major, so the entries are in output order).
 __global__ void __launch_bounds__(256)
 k_ptrs_run_starts(int64_t n, int32_t nkeys, int64_t nentries, const int32_t *__restrict__ hist_scanned,
-                  const uint32_t *__restrict__ sorted, int32_t *__restrict__ ptr) {
+                  const uint32_t *__restrict__ sorted, int32_t *__restrict__ ptr, int4 *__restrict__ gaps,
+                  int *__restrict__ gap_count) {
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= nentries) return;
   const int64_t start = hist_scanned[j];
@@ -347,10 +375,10 @@ k_ptrs_run_starts(int64_t n, int32_t nkeys, int64_t nentries, const int32_t *__r
   if (end <= start) return;
   const int64_t cur = sorted[start];
   const int64_t prev = start > 0 ? (int64_t)sorted[start - 1] : -1;
-  for (int64_t r = prev + 1; r <= cur; ++r) ptr[r] = (int32_t)start;
+  if (prev != cur) ptr_fill(ptr, prev + 1, cur, (int32_t)start, gaps, gap_count);
   if (end == n) {
     const int64_t last = sorted[n - 1];
-    for (int64_t r = last + 1; r <= nkeys; ++r) ptr[r] = (int32_t)n;
+    ptr_fill(ptr, last + 1, nkeys, (int32_t)n, gaps, gap_count);
   }
 }
 
@@ -360,9 +388,10 @@ k_ptrs_run_starts(int64_t n, int32_t nkeys, int64_t nentries, const int32_t *__r
 // scratch buffers hold the sorted pairs.
 template <class K, bool IOTA, bool PTRS>
 static void launch_scatter(const K *kin, const uint32_t *vin, K *kout, uint32_t *vout, int64_t n, int shift,
-                           int64_t ntiles, const int32_t *hist, int32_t *ptr_out, cudaStream_t s) {
+                           int64_t ntiles, const int32_t *hist, int32_t *ptr_out, cudaStream_t s,
+                           int4 *gaps = nullptr, int *gap_count = nullptr) {
   k_radix_scatter<K, IOTA, PTRS><<<(unsigned)ntiles, RS_THREADS, radix_scatter_smem<K>(), s>>>(
-      kin, vin, kout, vout, n, shift, ntiles, hist, 0u, ptr_out);
+      kin, vin, kout, vout, n, shift, ntiles, hist, 0u, ptr_out, gaps, gap_count);
 }
 
 // ptr_out (32-bit keys only): also produce ptr_out[0 .. nkeys], the first sorted position of every key
@@ -382,6 +411,8 @@ static int sort_pairs_impl(const K *src, K *ka, K *kb, uint32_t *va, uint32_t *v
   const int passes = (end_bit + 7) / 8;
   const int64_t ntiles = ceil_div(n, RS_TILE);
   DevBuf<int32_t> hist;
+  DevBuf<int4> gaps;
+  DevBuf<int> gap_count;
   SLC_TRY(hist.alloc((size_t)ntiles * RS_BINS));
   static PerDevice<size_t> smem_a, smem_b, smem_c, smem_d;  // per instantiation (K), per device
   SLC_CUDA(ensure_dyn_smem(k_radix_scatter<K, false, false>, smem_a, radix_scatter_smem<K>()));
@@ -406,8 +437,15 @@ static int sort_pairs_impl(const K *src, K *ka, K *kb, uint32_t *va, uint32_t *v
     const bool iota = p == 0 && iota_vals;
     const bool ptrs = ptr_out != nullptr && p == passes - 1;
     if constexpr (CAN_PTRS) {
-      if (ptrs && iota) launch_scatter<K, true, true>(kin, nullptr, kout, vout, n, shift, ntiles, hist.p, ptr_out, s);
-      else if (ptrs) launch_scatter<K, false, true>(kin, vin, kout, vout, n, shift, ntiles, hist.p, ptr_out, s);
+      if (ptrs) {  // queue for the long runs of empty buckets (filled by k_ptr_fill_gaps below)
+        SLC_TRY(gaps.alloc(PTR_GAP_QUEUE));
+        SLC_TRY(gap_count.alloc(1));
+        SLC_CUDA(cudaMemsetAsync(gap_count.p, 0, sizeof(int), s));
+      }
+      if (ptrs && iota)
+        launch_scatter<K, true, true>(kin, nullptr, kout, vout, n, shift, ntiles, hist.p, ptr_out, s, gaps.p, gap_count.p);
+      else if (ptrs)
+        launch_scatter<K, false, true>(kin, vin, kout, vout, n, shift, ntiles, hist.p, ptr_out, s, gaps.p, gap_count.p);
     }
     if (!ptrs) {
       if (iota) launch_scatter<K, true, false>(kin, nullptr, kout, vout, n, shift, ntiles, hist.p, nullptr, s);
@@ -417,8 +455,10 @@ static int sort_pairs_impl(const K *src, K *ka, K *kb, uint32_t *va, uint32_t *v
     if constexpr (CAN_PTRS) {
       if (ptrs) {
         const int64_t nentries = ntiles * RS_BINS;
-        k_ptrs_run_starts<<<(unsigned)ceil_div(nentries, 256), 256, 0, s>>>(n, nkeys, nentries, hist.p,
-                                                                          reinterpret_cast<const uint32_t *>(kout), ptr_out);
+        k_ptrs_run_starts<<<(unsigned)ceil_div(nentries, 256), 256, 0, s>>>(
+            n, nkeys, nentries, hist.p, reinterpret_cast<const uint32_t *>(kout), ptr_out, gaps.p, gap_count.p);
+        SLC_LAUNCHED();
+        k_ptr_fill_gaps<<<256, 256, 0, s>>>(gaps.p, gap_count.p, ptr_out);
         SLC_LAUNCHED();
       }
     }

@@ -318,6 +318,24 @@ def test_transpose_and_ctrans(sl, dtype, bucket, monkeypatch):
         assert tt == m
 
 
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_transpose_long_runs_of_empty_rows(sl, dtype):
+    """Row pointers over long runs of empty rows (a column block of a banded matrix: entries near the top and the
+    bottom only, nothing in between, nothing after the last used row) are filled by k_ptr_fill_gaps."""
+    rng = np.random.default_rng(77)
+    nr, nc = 9000, 400
+    rows = np.concatenate([rng.integers(0, 20, 600), rng.integers(4000, 4003, 50), rng.integers(8100, 8130, 600)])
+    cols = rng.integers(0, nc, len(rows))
+    om = oracle.compress(nr, nc, rows, cols, vec(rng, len(rows), dtype))
+    m = to_matrix(sl, om)
+    got, want = sl.transpose(m), oracle.transpose(om)
+    assert_same_structure(got, want)
+    np.testing.assert_array_equal(got.values, want.values)
+    assert sl.transpose(got) == m
+    x = vec(rng, nc, dtype)
+    np.testing.assert_array_equal(sl.mulV(m, x), oracle.mulv(om, x))     # the row-major mirror takes the same path
+
+
 def test_ctrans_known_answers_and_hermitian(sl):
     """sparse-linear/tests/Sparse.hs:61-73"""
     import json, os
