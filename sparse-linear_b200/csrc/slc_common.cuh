@@ -441,6 +441,8 @@ constexpr int RS_BINS = 256;
 int tile_digit_offsets_u32(const uint32_t *keys, int64_t n, int shift, int32_t *offsets);
 // *out <- max(*out, max(v[0 .. n)))  (values >= 0; *out is a device word the caller has initialised)
 int max_i32_into(const int32_t *v, int64_t n, unsigned long long *out);
+// *out += sum of v[0 .. n) (values >= 0), in 64 bits
+int sum_i32_into(const int32_t *v, int64_t n, unsigned long long *out);
 int exclusive_scan_i32(const int32_t *in, int32_t *out, int64_t n);  // out may alias in
 int exclusive_scan_i64(const int64_t *in, int64_t *out, int64_t n);
 // stable sort of (key, value) pairs on key bits [0, end_bit).  (ka, va) / (kb, vb) are ping-pong

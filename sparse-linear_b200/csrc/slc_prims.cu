@@ -116,6 +116,21 @@ __global__ void k_max_i32(int64_t n, const int32_t *__restrict__ v, unsigned lon
   if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, (unsigned long long)m);
 }
 
+__global__ void __launch_bounds__(256) k_sum_i32(int64_t n, const int32_t *__restrict__ v, unsigned long long *__restrict__ out) {
+  unsigned long long acc = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    acc += (unsigned long long)(uint32_t)v[i];
+  for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}
+
+int sum_i32_into(const int32_t *v, int64_t n, unsigned long long *out) {
+  if (n <= 0) return SLC_OK;
+  k_sum_i32<<<(unsigned)std::min<int64_t>(ceil_div(n, 256 * 8), 1184), 256, 0, cur_stream()>>>(n, v, out);
+  SLC_LAUNCHED();
+  return SLC_OK;
+}
+
 int max_i32_into(const int32_t *v, int64_t n, unsigned long long *out) {
   if (n <= 0) return SLC_OK;
   k_max_i32<<<(unsigned)ceil_div(n, 256), 256, 0, cur_stream()>>>(n, v, out);

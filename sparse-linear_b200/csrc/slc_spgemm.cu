@@ -521,15 +521,6 @@ k_mm_dense(int32_t ncols_in_class, const int32_t *__restrict__ cols, int32_t ar,
   }
 }
 
-__global__ void k_widen(int64_t n, const int32_t *__restrict__ in, int64_t *__restrict__ out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = in[i];
-}
-__global__ void k_narrow(int64_t n, const int64_t *__restrict__ in, int32_t *__restrict__ out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = (int32_t)in[i];
-}
-
 template <class T, int G, int H, int THREADS>
 static int run_symbolic(int32_t n, const int32_t *cols, const slc_matrix *a, const slc_matrix *b,
                         int32_t *cnt) {
@@ -630,25 +621,28 @@ static int mm_entry(const slc_matrix *a, const slc_matrix *b, slc_matrix **out) 
     SLC_CUDA(cudaMemsetAsync(stamp.p, 0, (size_t)dense_blocks * ar * sizeof(int32_t), s));
   }
 
-  // counts -> pointers (64-bit scan so an oversized product is reported, not wrapped)
-  DevBuf<int64_t> wide, ptr64;
-  SLC_TRY(wide.alloc((size_t)bc + 1));
-  SLC_TRY(ptr64.alloc((size_t)bc + 1));
-  k_widen<<<(unsigned)ceil_div((int64_t)bc + 1, 256), 256, 0, s>>>((int64_t)bc + 1, cnt.p, wide.p);
-  SLC_LAUNCHED();
-  SLC_TRY(exclusive_scan_i64(wide.p, ptr64.p, (int64_t)bc + 1));
-  int64_t nnzc = 0;
-  SLC_CUDA(cudaMemcpyAsync(&nnzc, ptr64.p + bc, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+  // counts -> pointers.  The total is summed in 64 bits beside a 32-bit scan, so an oversized product is
+  // reported, not wrapped (round 1 widened the counts, scanned them in 64 bits and narrowed the result: three
+  // more passes over the columns than this).
+  DevBuf<int32_t> ptr32;
+  DevBuf<unsigned long long> total;
+  SLC_TRY(ptr32.alloc((size_t)bc + 1));
+  SLC_TRY(total.alloc(1));
+  SLC_CUDA(cudaMemsetAsync(total.p, 0, sizeof(unsigned long long), s));
+  SLC_TRY(sum_i32_into(cnt.p, (int64_t)bc + 1, total.p));
+  SLC_TRY(exclusive_scan_i32(cnt.p, ptr32.p, (int64_t)bc + 1));
+  unsigned long long htotal = 0;
+  SLC_CUDA(cudaMemcpyAsync(&htotal, total.p, sizeof htotal, cudaMemcpyDeviceToHost, s));
   SLC_CUDA(cudaStreamSynchronize(s));
-  if (nnzc > 0x7fffffffLL) return fail(SLC_ERR_RANGE, "mm: product has %lld entries, more than 32-bit pointers hold", (long long)nnzc);
+  if (htotal > 0x7fffffffULL) return fail(SLC_ERR_RANGE, "mm: product has %lld entries, more than 32-bit pointers hold", (long long)htotal);
+  const int64_t nnzc = (int64_t)htotal;
 
   slc_matrix *c = nullptr;
   SLC_TRY(matrix_alloc(a->elem, ar, bc, nnzc, &c));
-  k_narrow<<<(unsigned)ceil_div((int64_t)bc + 1, 256), 256, 0, s>>>((int64_t)bc + 1, ptr64.p, c->colptr);
-  g_launches.fetch_add(1, std::memory_order_relaxed);
-  if (cudaError_t e = cudaGetLastError(); e != cudaSuccess) {
+  if (cudaError_t e = cudaMemcpyAsync(c->colptr, ptr32.p, ((size_t)bc + 1) * sizeof(int32_t), cudaMemcpyDeviceToDevice, s);
+      e != cudaSuccess) {
     matrix_release(c);
-    return fail(SLC_ERR_CUDA, "mm: pointer pass launch failed: %s", cudaGetErrorString(e));
+    return fail(SLC_ERR_CUDA, "mm: pointer copy failed: %s", cudaGetErrorString(e));
   }
 
   // pass 2: numeric
