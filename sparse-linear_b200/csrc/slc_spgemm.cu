@@ -244,12 +244,16 @@ k_mm_merge(int32_t ncols_in_class, const int32_t *__restrict__ cols, const int32
 
 template <class T, int NB, bool NUMERIC>
 static int run_merge(int32_t n, const int32_t *cols, const slc_matrix *a, const slc_matrix *b, int32_t *cnt,
-                     slc_matrix *c) {
+                     slc_matrix *c, int fit_cap = 0) {
   if (n == 0) return SLC_OK;
   static const char *stage_env = getenv("SLC_MM_STAGE");  // SLC_MM_STAGE=0: direct (uncoalesced) stores
-  static const int cap_env = env_int("SLC_MM_STAGE_CAP", MERGE_STAGE);
+  // SLC_MM_STAGE_CAP: entries of a warp's output window.  Default: what the product needs (fit_cap = 32 x the
+  // longest result column, known after the symbolic pass), at most MERGE_STAGE -- a window no larger than the
+  // product leaves more of the SM's memory to L1 (cfg 3: 800 entries instead of 1024, 0.726 -> 0.708 ms)
+  static const int cap_env = env_int("SLC_MM_STAGE_CAP", 0);
   static const int carve_env = env_int("SLC_MM_CARVEOUT", -1);  // preferred shared-memory carve-out, per cent
-  const int cap = std::max(32, std::min(cap_env, 2048)) / 4 * 4;
+  const int cap_want = cap_env > 0 ? cap_env : (fit_cap > 0 ? std::min(fit_cap, (int)MERGE_STAGE) : (int)MERGE_STAGE);
+  const int cap = std::max(32, std::min(cap_want, 2048)) / 4 * 4;
   const int stage = (NUMERIC && !(stage_env && stage_env[0] == '0')) ? cap : 0;
   const size_t smem = stage ? (size_t)(128 / 32) * stage * (sizeof(int32_t) + sizeof(T)) : 0;
   // SLC_MM_MINB=5/6: numeric 8-list merge for Double held to 96 / 80 registers (5 / 6 blocks per SM)
@@ -627,13 +631,16 @@ static int mm_entry(const slc_matrix *a, const slc_matrix *b, slc_matrix **out) 
   DevBuf<int32_t> ptr32;
   DevBuf<unsigned long long> total;
   SLC_TRY(ptr32.alloc((size_t)bc + 1));
-  SLC_TRY(total.alloc(1));
-  SLC_CUDA(cudaMemsetAsync(total.p, 0, sizeof(unsigned long long), s));
+  SLC_TRY(total.alloc(2));
+  SLC_CUDA(cudaMemsetAsync(total.p, 0, 2 * sizeof(unsigned long long), s));
   SLC_TRY(sum_i32_into(cnt.p, (int64_t)bc + 1, total.p));
+  SLC_TRY(max_i32_into(cnt.p, (int64_t)bc, total.p + 1));  // longest result column: sizes the output windows
   SLC_TRY(exclusive_scan_i32(cnt.p, ptr32.p, (int64_t)bc + 1));
-  unsigned long long htotal = 0;
-  SLC_CUDA(cudaMemcpyAsync(&htotal, total.p, sizeof htotal, cudaMemcpyDeviceToHost, s));
+  unsigned long long hboth[2] = {0, 0};
+  SLC_CUDA(cudaMemcpyAsync(hboth, total.p, sizeof hboth, cudaMemcpyDeviceToHost, s));
   SLC_CUDA(cudaStreamSynchronize(s));
+  const unsigned long long htotal = hboth[0];
+  const int fit_cap = (int)std::min<unsigned long long>(((hboth[1] * 32 + 31) / 32) * 32, 1u << 20);
   if (htotal > 0x7fffffffULL) return fail(SLC_ERR_RANGE, "mm: product has %lld entries, more than 32-bit pointers hold", (long long)htotal);
   const int64_t nnzc = (int64_t)htotal;
 
@@ -646,8 +653,8 @@ static int mm_entry(const slc_matrix *a, const slc_matrix *b, slc_matrix **out) 
   }
 
   // pass 2: numeric
-  int rc = run_merge<T, 4, true>(hcount[CLS_MERGE4], cols.p + hbase[CLS_MERGE4], a, b, nullptr, c);
-  if (rc == SLC_OK) rc = run_merge<T, 8, true>(hcount[CLS_MERGE8], cols.p + hbase[CLS_MERGE8], a, b, nullptr, c);
+  int rc = run_merge<T, 4, true>(hcount[CLS_MERGE4], cols.p + hbase[CLS_MERGE4], a, b, nullptr, c, fit_cap);
+  if (rc == SLC_OK) rc = run_merge<T, 8, true>(hcount[CLS_MERGE8], cols.p + hbase[CLS_MERGE8], a, b, nullptr, c, fit_cap);
   if (rc == SLC_OK) rc = run_numeric<T, 8, 128, 128>(hcount[CLS_HASH0], cols.p + hbase[CLS_HASH0], a, b, c);
   if (rc == SLC_OK) rc = run_numeric<T, 32, 1024, 128>(hcount[CLS_HASH1], cols.p + hbase[CLS_HASH1], a, b, c);
   if (rc == SLC_OK) rc = run_numeric<T, 256, 4096, 256>(hcount[CLS_HASH2], cols.p + hbase[CLS_HASH2], a, b, c);
