@@ -207,7 +207,10 @@ class Timer:
         # at least three times and the MEDIAN repeat is reported, with the spread beside it
         ms = statistics.median(per_repeat) if len(per_repeat) >= 3 else total_ms / done
         return {"ms": ms, "clocks": clocks, "launches": int(round(launches * steps / done)), "steps": steps,
-                "repeats_for_clock_sampling": done // steps, "ms_per_repeat": [round(x, 5) for x in per_repeat]}
+                "repeats_for_clock_sampling": done // steps,
+                "ms_per_repeat": ([round(x, 5) for x in per_repeat] if len(per_repeat) <= 12 else
+                                  {"n": len(per_repeat), "min": round(min(per_repeat), 5), "median": round(ms, 5),
+                                   "max": round(max(per_repeat), 5)})}
 
 
 def roofline(achieved_gbs, kernel, traffic_key=None, **extra):
