@@ -361,6 +361,30 @@ int slc_z_coo_bucket_dev(int64_t n, const int32_t *rows_dev, const int32_t *cols
                          int32_t nparts, const int32_t *col_splits, int32_t *out_rows_dev, int32_t *out_cols_dev,
                          double *out_vals_dev, int64_t *counts);
 
+/* ---- the same bucketing for callers that cannot allocate device memory ---------------------------------
+   No counterpart in the reference (it has no device code at all): this exists for hosts that must not
+   trigger a device allocation inside the call -- a process that has already committed all of HBM to its
+   own arena, a Haskell `unsafe` foreign call or a latency-bound loop that cannot afford a driver
+   allocation that may block, a GPU shared with a runtime whose allocator holds every free byte.
+   slc_*_coo_bucket_dev takes nnz-sized sort buffers from the device memory pool; this variant calls no
+   cudaMalloc / cudaMallocAsync / cudaFree and instead works in an area built into the library image
+   (about 0.5 MiB, resident on every GPU that loads the library until the process exits).
+
+   Arguments and result are those of slc_d_coo_bucket_dev / slc_z_coo_bucket_dev (bit for bit the same
+   arrays and counts); elem is 'd' or 'z' and says how wide a value is (8 or 16 bytes).
+   Limits: n <= SLC_NOALLOC_MAX_TRIPLETS and nparts <= 16, otherwise SLC_ERR_RANGE with a message that
+   names the limit, and nothing is written.
+   The work area is shared: one per GPU for all threads and streams, holding the last call's contents (the
+   call clears the cells it needs at zero).  Calls that may overlap on one GPU race on it; issue them on
+   one stream or order them yourself.  The first call on each device also looks up the area's device
+   address (cudaGetSymbolAddress), so make that first call before any stream capture begins.
+   Synchronises the stream (counts is a host array), like the allocating form. */
+#define SLC_NOALLOC_MAX_TRIPLETS 16777216 /* 2^24 */
+int slc_coo_bucket_noalloc_dev(int elem, int64_t n, const int32_t *rows_dev, const int32_t *cols_dev,
+                               const void *vals_dev, int32_t nparts, const int32_t *col_splits,
+                               int32_t *out_rows_dev, int32_t *out_cols_dev, void *out_vals_dev,
+                               int64_t *counts);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

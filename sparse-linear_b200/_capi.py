@@ -63,6 +63,7 @@ SIGNATURES = {
     "slc_sharded_result": (C.c_int, [_vp, C.c_int32, C.POINTER(_vp), C.POINTER(C.c_int64)]),
     "slc_sharded_synchronize": (C.c_int, [_vp]),
     "slc_device_arrays": (C.c_int, [_hp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)]),
+    "slc_coo_bucket_noalloc_dev": (C.c_int, [C.c_int, C.c_int64, _vp, _vp, _vp, C.c_int32, _vp, _vp, _vp, _vp, _vp]),
 }
 for _p in ("d", "z"):
     SIGNATURES.update({
