@@ -202,7 +202,9 @@ int slc_peer_group_stats(slc_peer_group *g, int64_t *out4, int reset) {
   if (prev != g->device) cudaSetDevice(g->device);
   unsigned long long h[PEER_STATE_WORDS];
   cudaError_t e = cudaMemcpy(h, g->state, sizeof h, cudaMemcpyDeviceToHost);
-  if (e == cudaSuccess && reset) e = cudaMemset(g->state + PEER_STAT_WAIT_SUM, 0, 3 * sizeof(unsigned long long));
+  static_assert(PEER_STAT_WAIT_SUM == PEER_STAT_WAITS + 1 && PEER_STAT_WAIT_MAX == PEER_STAT_WAITS + 2,
+                "the three wait statistics are cleared as one run of words");
+  if (e == cudaSuccess && reset) e = cudaMemset(g->state + PEER_STAT_WAITS, 0, 3 * sizeof(unsigned long long));
   if (prev != g->device) cudaSetDevice(prev);
   SLC_CUDA(e);
   out4[0] = (int64_t)h[PEER_EPOCH];

@@ -221,3 +221,34 @@ def test_device_piece_stacking_and_bucketing(sl, dtype):
     a = sharded.sharded_compress_device(230, dev(r, None), dev(c, None), dev(v, np.float64), np.array([0, 170]), 0, complex_values=cx)
     oa = oracle.compress(230, 170, r, c, v)
     assert np.array_equal(a.pointers, oa.colptr) and np.array_equal(a.indices, oa.rowidx) and np.array_equal(a.values, oa.values)
+
+
+def test_peer_statistics_reset_clears_waits_sum_and_longest(sl):
+    """slc_peer_group_stats(reset=1) must zero all three wait statistics (count, summed ns, longest):
+    round 2 cleared the sum, the longest and an unused word, so the count kept the warm-up's waits and
+    the mean wait published from it was too small."""
+    import ctypes as C
+    if sl.device_count() < 2:
+        pytest.skip("waits are only recorded against a peer: needs 2 GPUs")
+    lib = sl._capi.lib()
+    groups = (C.c_void_p * 2)()
+    assert lib.slc_peer_group_create_local(2, None, groups) == 0, sl._capi.last_error()
+    try:
+        for rep in range(5):
+            for d in (0, 1):
+                sl.set_device(d)
+                assert lib.slc_peer_barrier(groups[d]) == 0, sl._capi.last_error()
+        for d in (0, 1):
+            sl.set_device(d)
+            sl.synchronize()
+        out = (C.c_int64 * 4)()
+        for d in (0, 1):
+            assert lib.slc_peer_group_stats(groups[d], out, 1) == 0
+            assert out[0] >= 5 and out[1] >= 5 and out[2] > 0 and out[3] > 0, list(out)
+            epochs = out[0]
+            assert lib.slc_peer_group_stats(groups[d], out, 0) == 0
+            assert out[0] == epochs and list(out)[1:] == [0, 0, 0], list(out)   # the epoch count is not a statistic
+    finally:
+        for d in (0, 1):
+            lib.slc_peer_group_free(groups[d])
+        sl.set_device(0)
