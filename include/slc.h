@@ -148,9 +148,13 @@ int slc_d_mulm_dev(slc_matrix *a, const double *X_dev, int64_t ldx, double *Y_de
 int slc_z_mulm_dev(slc_matrix *a, const double *X_dev, int64_t ldx, double *Y_dev, int64_t ldy,
                    int32_t k, const double *beta);
 
-/* *flag <- nonzero if a launch of the TMA-staged block product (banded matrices with short rows) gave
-   up waiting on one of its shared-memory barriers or met a window wider than planned: its result
-   is then invalid.  A diagnostic for tests and benchmarks; 0 in normal operation. */
+/* *flag <- nonzero if a launch of the TMA-staged block product (banded matrices with short rows) on any
+   device gave up waiting on one of its shared-memory barriers or met a window wider than planned: its
+   result is then invalid.  0 in normal operation.  The host-operand products (slc_*_mulm,
+   slc_*_mulm_sharded, slc_sharded_synchronize) look at their device's word themselves after their final
+   synchronisation: they return SLC_ERR_CUDA for such a product and clear the word, so the next product
+   starts clean.  This call is for users of the asynchronous *_dev forms; it synchronises the current
+   stream, reads, and clears nothing. */
 int slc_spmm_window_error(int *flag);
 
 /* ---- SpGEMM: mm = (*) (Data/Matrix/Sparse.hs:691-702, ScatterGather.hs:37-147) -------- */

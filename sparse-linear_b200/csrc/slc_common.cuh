@@ -468,6 +468,10 @@ int ensure_csr(slc_matrix *m);
 template <class T>
 int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, YInit<T> yi, bool *done);
 
+// slc_spmm_window.cu: after the current device's streams have been synchronised, SLC_ERR_CUDA (and the word
+// cleared) if a TMA-staged block product gave up on a barrier there since the last check; `who` prefixes the message
+int spmm_window_check(const char *who);
+
 // built in slc_spmm_brick.cu: the TMA-staged SpMM for 27-offset matrices (*done = it ran).  X is indexed
 // by column number; only its entries [xlo, xhi) exist (xhi < 0: all of [0, ncols)).
 int spmm_brick_try(slc_matrix *m, const double *X, int64_t ldx, double *Y, int64_t ldy, int32_t k,
@@ -477,6 +481,12 @@ inline int spmm_brick_try(slc_matrix *, const double2 *, int64_t, double2 *, int
   *done = false;  // Complex Double rows of 27 entries keep the panel kernel
   return SLC_OK;
 }
+
+// Builds the handle's offset-slot plan now if it has not been looked at yet (it reads a few words back from
+// the device, i.e. synchronises the stream).  The row-partitioned products call it before they signal their
+// peers: between the signal and the last boundary launch the host must never wait on the stream, or it
+// would wait on a kernel whose peers this thread has not launched yet.
+int spmm_brick_prepare(slc_matrix *m);
 
 inline int bits_for(uint32_t n) {  // bits needed to represent values in [0, n)
   int b = 1;

@@ -232,6 +232,10 @@ static int upload_sharded_impl(int32_t ndev, const int32_t *devices, int32_t nro
 static int sharded_reserve(slc_sharded *h, int64_t k) {
   if (k <= h->cap_cols) return SLC_OK;
   const size_t el = elem_size(h->elem);
+  // The buffers are freed and reallocated one by one: until the last allocation has succeeded the handle
+  // holds none (a failure part-way leaves null pointers, and a later product must come back here to
+  // allocate again instead of trusting the old capacity).
+  h->cap_cols = 0;
   for (int p = 0; p < h->ndev; ++p) {
     DeviceScope scope(h->devices[p], h->streams[p]);
     SLC_CUDA(cudaStreamSynchronize(h->streams[p]));
@@ -294,6 +298,9 @@ static int sharded_sync(slc_sharded *h) {
     DeviceScope scope(h->devices[p], h->streams[p]);
     cudaError_t e = cudaStreamSynchronize(h->streams[p]);
     if (e != cudaSuccess && rc == SLC_OK) rc = fail(SLC_ERR_CUDA, "sharded product: device %d: %s", h->devices[p], cudaGetErrorString(e));
+    // every device's word is read (and cleared) even after a failure, so nothing stale is left behind
+    const int wrc = spmm_window_check("sharded product");
+    if (rc == SLC_OK) rc = wrc;
   }
   if (rc == SLC_OK)
     for (int p = 0; p < h->ndev; ++p) SLC_TRY(peer_check(h->groups[p], "sharded product"));

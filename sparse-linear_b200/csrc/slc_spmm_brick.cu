@@ -315,6 +315,12 @@ static int launch_planes(slc_matrix *m, const double *X, int64_t ldx, double *Y,
   return SLC_OK;
 }
 
+int spmm_brick_prepare(slc_matrix *m) {
+  const char *env = getenv("SLC_SPMM_BRICK");
+  if ((env && env[0] == '0') || m->elem != ELEM_D) return SLC_OK;
+  return brick_plan(m);
+}
+
 // Runs rows [row_begin, row_end) of the block product on the staged kernel when the matrix has the plan
 // and the operands qualify (X 16-byte aligned, even column stride and bounds, windows that fit).  X is
 // indexed by column number and only its entries [xlo, xhi) exist (xhi < 0: all of [0, ncols)).

@@ -412,22 +412,35 @@ __global__ void k_window_max(int32_t nslices, const int32_t *__restrict__ slice_
   if (hi >= lo) atomicMax(out, hi - lo + 1);
 }
 
-// Error flag of the window kernel: one word of mapped pinned host memory shared by every launch of this
-// process on any device (a kernel writes it over PCIe only when a barrier wait gives up), so reading it
-// needs neither a device of its own nor a synchronising copy.
+// Error words of the staged kernels: one word per device ordinal in one block of mapped pinned host memory
+// (a kernel writes its device's word over PCIe only when a barrier wait gives up), so reading a word needs
+// neither a device of its own nor a synchronising copy.  A launch is handed the word of the device it runs on.
+// Who reads them: the host-operand products (slc_*_mulm, slc_*_mulm_sharded, slc_sharded_synchronize) after
+// their final stream synchronisation, through spmm_window_check -- a product whose kernel gave up returns
+// SLC_ERR_CUDA instead of a silently stale block, and the word is cleared so the next product starts clean;
+// and slc_spmm_window_error, for callers of the asynchronous *_dev forms, which only reads.
 static std::atomic<int *> g_window_err{nullptr};
 
-static int window_err_flag(int **out) {
+static int window_err_base(int **out) {
   int *p = g_window_err.load(std::memory_order_acquire);
   if (!p) {
     int *fresh = nullptr;
-    SLC_CUDA(cudaHostAlloc((void **)&fresh, sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable));
-    *fresh = 0;
+    SLC_CUDA(cudaHostAlloc((void **)&fresh, MAX_DEVICES * sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable));
+    for (int d = 0; d < MAX_DEVICES; ++d) fresh[d] = 0;
     int *expected = nullptr;
     if (g_window_err.compare_exchange_strong(expected, fresh, std::memory_order_acq_rel)) p = fresh;
     else { cudaFreeHost(fresh); p = expected; }
   }
   *out = p;
+  return SLC_OK;
+}
+
+static int window_err_flag(int **out) {
+  int *base = nullptr;
+  SLC_TRY(window_err_base(&base));
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) dev = 0;
+  *out = base + dev;
   return SLC_OK;
 }
 
@@ -438,8 +451,30 @@ int spmm_window_error(int *flag) {
   int *p = g_window_err.load(std::memory_order_acquire);
   if (!p) return SLC_OK;
   SLC_CUDA(cudaStreamSynchronize(cur_stream()));
-  *flag = *(volatile int *)p;
+  int any = 0;
+  for (int d = 0; d < MAX_DEVICES; ++d) any |= ((volatile int *)p)[d];
+  *flag = any;
   return SLC_OK;
+}
+
+// After the caller has synchronised the stream(s) of the current device: fail if a staged block product
+// gave up there since the last check, and clear the word.  SLC_DEBUG_WINDOW_FAULT=<code> raises the word
+// from the host first (tests of this reporting path; a real give-up needs a protocol bug).
+int spmm_window_check(const char *who) {
+  int *p = g_window_err.load(std::memory_order_acquire);
+  const int fault = env_int("SLC_DEBUG_WINDOW_FAULT", 0);
+  if (!p && !fault) return SLC_OK;
+  int *word = nullptr;
+  SLC_TRY(window_err_flag(&word));
+  if (fault) *(volatile int *)word = fault;
+  const int code = *(volatile int *)word;
+  if (!code) return SLC_OK;
+  *(volatile int *)word = 0;
+  int dev = 0;
+  (void)cudaGetDevice(&dev);
+  return fail(SLC_ERR_CUDA,
+              "%s: the TMA-staged block product on device %d %s; the result block is invalid", who, dev,
+              code == 2 ? "met a column window wider than its plan" : "gave up waiting on a shared-memory barrier");
 }
 
 template <class T, int LMAX>

@@ -2241,6 +2241,11 @@ static int spmm_dist_entry(slc_matrix *m, int32_t nparts, int32_t self, const in
   xa.tbl = tbl;
   int32_t r0 = 0, r1 = 0;
   SLC_TRY(dist_interior(m, xa.self_lo, xa.self_hi, &r0, &r1));
+  // Plans that are built lazily read words back from the device (a stream synchronisation).  Build them
+  // here: a block without interior rows would otherwise meet the first of them in its boundary launch,
+  // behind slc_peer_wait, and the host would sit on a wait kernel whose peers it has not launched yet.
+  SLC_TRY(spmm_brick_prepare(m));
+  if (env_int("SLC_PANEL_STRIDE", 0) < 0) SLC_TRY(detect_line_stride(m));
   if (sync) SLC_TRY(slc_peer_signal(sync));  // "my rows of X are written" (stream order)
   // interior rows: columns are global, so shift the local block's base by the first owned row
   SLC_TRY(launch_panel<T>(m, xa.self_X - xa.self_lo, xa.self_ld, (T *)Y, ldy, k, yinit_zero<T>(), r0, r1, xa.self_lo,
@@ -2378,6 +2383,7 @@ static int spmm_host_entry(slc_matrix *m, const double *X, int64_t ldx, double *
     SLC_CUDA(cudaStreamSynchronize(m->pipe_out));
     SLC_CUDA(cudaStreamSynchronize(m->pipe_in));
     SLC_CUDA(cudaStreamSynchronize(s));
+    if (rc == SLC_OK) rc = spmm_window_check(fn);
     return rc;
   }
   if (m->ncols)
@@ -2391,7 +2397,7 @@ static int spmm_host_entry(slc_matrix *m, const double *X, int64_t ldx, double *
     SLC_CUDA(cudaMemcpy2DAsync(Y, (size_t)ldy * sizeof(T), dY.p, (size_t)m->nrows * sizeof(T),
                                (size_t)m->nrows * sizeof(T), (size_t)k, cudaMemcpyDeviceToHost, s));
   SLC_CUDA(cudaStreamSynchronize(s));
-  return SLC_OK;
+  return spmm_window_check(fn);
 }
 
 }  // namespace slc

@@ -262,6 +262,31 @@ def test_mulm_banded_window_kernel(sl, dtype, cluster, monkeypatch):
     assert sl.spmm_window_error() == 0
 
 
+def test_mulm_reports_a_staged_kernel_that_gave_up(sl, monkeypatch):
+    """A TMA-staged block product whose bounded barrier wait gives up leaves a stale block; the host-operand
+    product must say so (SLC_ERR_CUDA) instead of returning SLC_OK, and the next product must start clean.
+    A real give-up needs a protocol bug, so the word is raised from the host (SLC_DEBUG_WINDOW_FAULT)."""
+    gm = g.laplace2d_5pt(46)
+    om, m = oracle.csc(*gm), to_matrix(sl, gm)
+    X = g.uniform_block(gm.ncols, 5, seed=3)
+    np.testing.assert_array_equal(sl.mulM(m, X), oracle.mulm(om, X))
+    monkeypatch.setenv("SLC_DEBUG_WINDOW_FAULT", "1")
+    with pytest.raises(sl.SparseLinearError, match="gave up waiting on a shared-memory barrier"):
+        sl.mulM(m, X)
+    monkeypatch.delenv("SLC_DEBUG_WINDOW_FAULT")
+    assert sl.spmm_window_error() == 0                     # reported once, then cleared
+    np.testing.assert_array_equal(sl.mulM(m, X), oracle.mulm(om, X))
+    from sparse_linear_b200 import sharded
+    sm = sharded.ShardedMatrix(to_matrix(sl, g.stencil3d_27pt((6, 8, 64))), 1)
+    Xs = g.uniform_block(6 * 8 * 64, 3, seed=4)
+    monkeypatch.setenv("SLC_DEBUG_WINDOW_FAULT", "2")
+    with pytest.raises(sl.SparseLinearError, match="wider than its plan"):
+        sm.mulM(Xs)
+    monkeypatch.delenv("SLC_DEBUG_WINDOW_FAULT")
+    np.testing.assert_array_equal(sm.mulM(Xs), oracle.mulm(oracle.csc(*g.stencil3d_27pt((6, 8, 64))), Xs))
+    sm.close()
+
+
 @pytest.mark.parametrize("dtype", DTYPES)
 def test_mulm_panel_line_tiling(sl, dtype):
     """Stencils large enough that k_spmm_panel tiles its blocks over grid lines (the slice-order
