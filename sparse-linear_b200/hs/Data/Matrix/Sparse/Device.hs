@@ -22,7 +22,7 @@
 --
 -- UNCHANGED CALLERS.  `mulV a x` on an ordinary host 'Matrix' must not re-upload A on every call
 -- (SURVEY.md section 8(b): "a memo keyed on the host matrix").  'resident' below keeps one device copy
--- per host matrix: the key is the 'StableName' of the record's @values@ vector (the heap object every
+-- per host matrix: the key is the 'StableName' of the record's evaluated @values@ vector (the heap object every
 -- copy of the record shares), the entry holds the device handle through a 'Weak' pointer keyed on that
 -- same vector, so the device copy is finalised (slc_free) when the host matrix is collected.  Every
 -- product, transpose and mm below goes through it.
@@ -35,19 +35,20 @@
 -- The functions exported here have the types of their namesakes in Data.Matrix.Sparse
 -- (Data/Matrix/Sparse.hs:13-30), so replacing the import is the whole integration:
 --
--- > import Data.Matrix.Sparse hiding (mulV, axpy_, axpy, transpose, ctrans, hermitian, compress, fromTriples, lin)
+-- > import Data.Matrix.Sparse hiding (mulV, axpy_, axpy, mm, kronecker, transpose, ctrans, hermitian, compress, fromTriples, lin)
 -- > import Data.Matrix.Sparse.Device
 module Data.Matrix.Sparse.Device
        ( DeviceMatrix, SlcElem
        , toDevice, fromDevice, resident
        , mulV, axpy, axpy_, mulM_, mulMAcc_, mulVD
-       , mm, transpose, ctrans, hermitian
+       , mm, kronecker, transpose, ctrans, hermitian
        , compress, fromTriples, lin
          -- * one process, several GPUs (slc_*_upload_sharded ...)
        , ShardedMatrix, toDevices, mulVS, mulMS_
        ) where
 
 import Control.Concurrent.MVar (MVar, modifyMVar, newMVar)
+import Control.Exception (evaluate)
 import Control.Monad (when)
 import qualified Data.IntMap.Strict as IM
 import Data.Complex (Complex)
@@ -105,6 +106,8 @@ foreign import ccall "slc_d_mulm" slc_d_mulm :: MulM Double
 foreign import ccall "slc_z_mulm" slc_z_mulm :: MulM (Complex Double)
 foreign import ccall "slc_d_mm" slc_d_mm :: Binary
 foreign import ccall "slc_z_mm" slc_z_mm :: Binary
+foreign import ccall "slc_d_kronecker" slc_d_kronecker :: Binary
+foreign import ccall "slc_z_kronecker" slc_z_kronecker :: Binary
 foreign import ccall "slc_d_transpose" slc_d_transpose :: Transpose
 foreign import ccall "slc_z_transpose" slc_z_transpose :: Transpose
 foreign import ccall "slc_d_hermitian" slc_d_hermitian :: Hermitian
@@ -124,6 +127,7 @@ class (Num a, Storable a, Unbox a) => SlcElem a where
   c_axpy :: MulV a
   c_mulm :: MulM a
   c_mm :: proxy a -> Binary
+  c_kronecker :: proxy a -> Binary
   c_transpose :: proxy a -> Transpose
   c_hermitian :: proxy a -> Hermitian
   c_compress :: Compress a
@@ -136,6 +140,7 @@ instance SlcElem Double where
   c_axpy = slc_d_axpy
   c_mulm = slc_d_mulm
   c_mm _ = slc_d_mm
+  c_kronecker _ = slc_d_kronecker
   c_transpose _ = slc_d_transpose
   c_hermitian _ = slc_d_hermitian
   c_compress = slc_d_compress
@@ -148,6 +153,7 @@ instance SlcElem (Complex Double) where
   c_axpy = slc_z_axpy
   c_mulm = slc_z_mulm
   c_mm _ = slc_z_mm
+  c_kronecker _ = slc_z_kronecker
   c_transpose _ = slc_z_transpose
   c_hermitian _ = slc_z_hermitian
   c_compress = slc_z_compress
@@ -198,7 +204,14 @@ memo = unsafePerformIO (newMVar IM.empty)
 -- | The device copy of a host matrix: uploaded on first use, reused afterwards, freed with the matrix.
 resident :: forall a. SlcElem a => Matrix Vector a -> IO (DeviceMatrix a)
 resident mat = do
-  key <- makeStableName (values mat)
+  -- The @values@ field is lazy (Data/Matrix/Sparse.hs:68-76), so @values mat@ may still be a selector
+  -- thunk: a 'StableName' taken of a thunk differs from the one taken after it has been evaluated, and a
+  -- 'Weak' keyed on a thunk dies at the next collection.  Force the field first; key and weak pointer are
+  -- then taken of the evaluated vector, the one heap object every later @values mat@ of this record (and of
+  -- every copy of it) returns.  Without this the memo may never hit: A is uploaded again per product and
+  -- dead entries pile up in their buckets.
+  v <- evaluate (values mat)
+  key <- makeStableName v
   let h = hashStableName key
   modifyMVar memo $ \tbl -> do
     let bucket = IM.findWithDefault [] h tbl
@@ -207,7 +220,7 @@ resident mat = do
       (d : _) -> return (tbl, d :: DeviceMatrix a)
       [] -> do
         d <- toDevice mat
-        w <- mkWeak (values mat) d Nothing      -- the ForeignPtr's own finalizer (slc_free) releases the HBM
+        w <- mkWeak v d Nothing                 -- the ForeignPtr's own finalizer (slc_free) releases the HBM
         let kept = [e | (e, _, Just (_ :: DeviceMatrix a)) <- alive]
         return (IM.insert h (Entry key w : kept) tbl, d)
 
@@ -281,6 +294,10 @@ mm :: forall a. SlcElem a => Matrix Vector a -> Matrix Vector a -> Matrix Vector
 mm a b
   | ncols a /= nrows b = errorWithStackTrace "mm: inner dimension mismatch"
   | otherwise = binary (c_mm ([] :: [a])) a b
+
+-- | Kronecker product (kronecker, Data/Matrix/Sparse.hs:597-638): no dimension condition.
+kronecker :: forall a. SlcElem a => Matrix Vector a -> Matrix Vector a -> Matrix Vector a
+kronecker = binary (c_kronecker ([] :: [a]))
 
 transposeWith :: forall a. SlcElem a => CInt -> Matrix Vector a -> Matrix Vector a
 transposeWith conj a = unsafePerformIO $
