@@ -501,6 +501,18 @@ def same_matrix(mat, o):
                 and np.array_equal(mat.indices, o.rowidx) and np.array_equal(mat.values, o.values))
 
 
+def timed_host(hstep, repeats=5):
+    """End-to-end timing of a handle-producing call on host arrays: one untimed call, then `repeats` timed
+    ones; the median is the figure (round 2 published a single un-repeated step)."""
+    hstep()
+    ts = []
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        hstep()
+        ts.append(time.perf_counter() - t0)
+    return float(np.median(ts)), [round(t * 1e3, 3) for t in ts]
+
+
 def entry_spgemm(args, sl, tm, host_m, n):
     import oracle
     from sparse_linear_b200 import generators as g
@@ -529,13 +541,11 @@ def entry_spgemm(args, sl, tm, host_m, n):
             a = sl.Matrix(host_m.ncols, host_m.nrows, host_m.colptr, host_m.rowidx, host_m.values)
             cc = sl.mm(a, a)
             return cc.pointers, cc.indices, cc.values            # download
-        hstep()
-        t0 = time.perf_counter()
-        hstep()
-        dt = time.perf_counter() - t0
-        entry["e2e"] = {"value": nnzc / dt, "unit": "nnz/s", "ms_per_step": dt * 1e3, "steps": 1,
+        dt, reps = timed_host(hstep)
+        entry["e2e"] = {"value": nnzc / dt, "unit": "nnz/s", "ms_per_step": dt * 1e3, "steps": len(reps), "ms_per_repeat": reps,
                         "h2d_bytes_per_step": int(nnz * 12 + (nc + 1) * 4), "d2h_bytes_per_step": int(nnzc * 12 + (nc + 1) * 4),
-                        "api": "slc_d_upload + slc_d_mm + slc_d_download (pageable host arrays, as the shim passes them)"}
+                        "api": "slc_d_upload + slc_d_mm + slc_d_download (pageable host arrays, as the shim passes them; "
+                               "results into fresh numpy buffers); median of the repeats"}
     if not args.no_cpu:
         om = oracle.csc(*host_m)
         t0 = time.perf_counter()
@@ -582,18 +592,19 @@ def entry_transpose(args, sl, tm, name, desc, m, host_m, traffic_key=None, oracl
              "roofline": roofline(gbs, "k_radix_scatter", traffic_key,
                                   note="algorithmic bytes are the two-pass floor 2*nnz*(val+idx); an LSD radix sort moves more")}
     t = keep["t"]
+    if host_m is None and not (args.no_e2e and args.no_cpu):
+        from sparse_linear_b200 import generators as g
+        host_m = g.CSC(nr, nc, m.pointers, m.indices, m.values)       # the handle's arrays, downloaded once
     if not args.no_e2e and host_m is not None:
         def hstep():
             a = sl.Matrix(host_m.ncols, host_m.nrows, host_m.colptr, host_m.rowidx, host_m.values)
             tt = sl.transpose(a)
             return tt.pointers, tt.indices, tt.values
-        hstep()
-        t0 = time.perf_counter()
-        hstep()
-        dt = time.perf_counter() - t0
-        entry["e2e"] = {"value": nnz / dt, "unit": "nnz/s", "ms_per_step": dt * 1e3, "steps": 1,
+        dt, reps = timed_host(hstep, 5 if nnz < 100_000_000 else 3)
+        entry["e2e"] = {"value": nnz / dt, "unit": "nnz/s", "ms_per_step": dt * 1e3, "steps": len(reps), "ms_per_repeat": reps,
                         "h2d_bytes_per_step": int(nnz * 12 + (nc + 1) * 4), "d2h_bytes_per_step": int(nnz * 12 + (nr + 1) * 4),
-                        "api": "slc_d_upload + slc_d_transpose + slc_d_download"}
+                        "api": "slc_d_upload + slc_d_transpose + slc_d_download (pageable host arrays; results into fresh "
+                               "numpy buffers); median of the repeats"}
     if not args.no_cpu:
         par = {"required": "structure and values bit-exact"}
         if oracle_check and host_m is not None:
@@ -603,6 +614,9 @@ def entry_transpose(args, sl, tm, name, desc, m, host_m, traffic_key=None, oracl
             dt = time.perf_counter() - t0
             par.update(oracle="oracle.transpose (Sparse.hs:301-329)", bit_exact=same_matrix(t, want))
             par["ok"] = par["bit_exact"]
+            if symmetric:
+                par["fixed_point_bit_exact"] = bool(t == m)
+                par["ok"] = par["ok"] and par["fixed_point_bit_exact"]
             entry["cpu_baseline"] = {"value": nnz / dt, "unit": "nnz/s", "cores": 1, "kind": "port",
                                      "sample": "whole matrix, one pass: %.2f s" % dt, "host_cores_available": os.cpu_count()}
         else:
@@ -646,15 +660,12 @@ def entry_assembly(args, sl, tm, host_m, n):
              "roofline": roofline(gbs, "k_coarse_scatter", "cfg3a", note="algorithmic bytes are the one-pass floor of SURVEY.md 8(d)")}
     if not args.no_e2e:
         def hstep():
-            a = sl.compress(nr, nc, r_, c_, v_)
+            a = sl.compress(nr, nc, r32, c32, v_)           # 32-bit index arrays, as the C ABI takes them
             return a.pointers, a.indices, a.values
-        hstep()
-        t0 = time.perf_counter()
-        hstep()
-        dt = time.perf_counter() - t0
-        entry["e2e"] = {"value": n_in / dt, "unit": "triplets/s", "ms_per_step": dt * 1e3, "steps": 1,
+        dt, reps = timed_host(hstep)
+        entry["e2e"] = {"value": n_in / dt, "unit": "triplets/s", "ms_per_step": dt * 1e3, "steps": len(reps), "ms_per_repeat": reps,
                         "h2d_bytes_per_step": int(n_in * 16), "d2h_bytes_per_step": int(nnz * 12 + (nc + 1) * 4),
-                        "api": "slc_d_compress (host triplets) + slc_d_download"}
+                        "api": "slc_d_compress (pageable host triplets) + slc_d_download (fresh numpy buffers); median of the repeats"}
     if not args.no_cpu:
         t0 = time.perf_counter()
         want = oracle.compress(nr, nc, r_, c_, v_)
@@ -919,7 +930,7 @@ def main():
             out.append(e)
         if which in ("both", "t"):
             e = entry_transpose(args, sl, tm, "cfg4_transpose", "cfg4: R-MAT scale %d, transpose (handle -> handle)" % scale, m, None,
-                                traffic_key="cfg4t", oracle_check=False)
+                                traffic_key="cfg4t", oracle_check=True)
             out.append(e)
         return out
 
@@ -933,8 +944,8 @@ def main():
         q = n or 200
         hm = hm if hm is not None else g.stencil3d_27pt(q)
         m = m if m is not None else sl.Matrix(hm.ncols, hm.nrows, hm.colptr, hm.rowidx, hm.values)
-        return entry_transpose(args, sl, tm, "cfg5_transpose", "cfg5: transpose, 3D 27-point stencil %d^3" % q, m, None,
-                               traffic_key="cfg5t", oracle_check=False, symmetric=True)
+        return entry_transpose(args, sl, tm, "cfg5_transpose", "cfg5: transpose, 3D 27-point stencil %d^3" % q, m, hm,
+                               traffic_key="cfg5t", oracle_check=True, symmetric=True)
 
     if w != "cfg5":            # a single workload as its own headline (development runs)
         single = {"cfg1": cfg1, "cfg2": cfg2, "cfg3": cfg3, "cfg3t": cfg3t, "cfg3a": cfg3a, "cfg5mm": cfg5mm, "cfg5t": cfg5t,

@@ -554,9 +554,9 @@ static int compress_entry(int32_t nrows, int32_t ncols, int64_t n, const int32_t
     SLC_TRY(drows.alloc(n));
     SLC_TRY(dcols.alloc(n));
     SLC_TRY(dvals.alloc(n));
-    SLC_CUDA(cudaMemcpyAsync(drows.p, rows, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
-    SLC_CUDA(cudaMemcpyAsync(dcols.p, cols, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
-    SLC_CUDA(cudaMemcpyAsync(dvals.p, vals, (size_t)n * sizeof(T), cudaMemcpyHostToDevice, s));
+    SLC_TRY(host_to_dev(drows.p, rows, (size_t)n * sizeof(int32_t), s));
+    SLC_TRY(host_to_dev(dcols.p, cols, (size_t)n * sizeof(int32_t), s));
+    SLC_TRY(host_to_dev(dvals.p, vals, (size_t)n * sizeof(T), s));
     rows_d = drows.p;
     cols_d = dcols.p;
     vals_d = dvals.p;

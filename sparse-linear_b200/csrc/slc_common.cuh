@@ -468,6 +468,13 @@ int ensure_csr(slc_matrix *m);
 template <class T>
 int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, int32_t k, YInit<T> yi, bool *done);
 
+// slc_hostxfer.cu: copies between lent host arrays and HBM.  Pinned (or small) host memory goes straight to
+// cudaMemcpyAsync; large pageable memory is moved through a ring of pinned buffers by a few host threads.
+// host_to_dev: the source has been read when it returns.  dev_to_host: complete after the next
+// synchronisation of the stream.
+int host_to_dev(void *dst_dev, const void *src_host, size_t bytes, cudaStream_t s);
+int dev_to_host(void *dst_host, const void *src_dev, size_t bytes, cudaStream_t s);
+
 // slc_spmm_window.cu: after the current device's streams have been synchronised, SLC_ERR_CUDA (and the word
 // cleared) if a TMA-staged block product gave up on a barrier there since the last check; `who` prefixes the message
 int spmm_window_check(const char *who);

@@ -119,20 +119,39 @@ void matrix_release(slc_matrix *m) {
 // starts at p, so: one thread per entry counts the descents, one thread per non-empty column counts
 // the descents that sit on its start, and the matrix is well formed iff the two counts agree.
 // acc[0] = out-of-bounds flag, acc[1] = descents, acc[2] = descents at column starts.
-__global__ void k_validate_entries(int32_t nrows, int64_t nnz, const int32_t *__restrict__ rowidx,
-                                   unsigned long long *__restrict__ acc) {
-  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  bool oob = false, descent = false;
-  if (p < nnz) {
+// Grid-stride over the entries, counts kept in registers, reduced per warp and per block: one atomic per
+// block (round 2 issued one per warp on a single address -- 4.5 ms for the 214 M entries of the 200^3
+// stencil, where reading the indices takes 0.15 ms).
+constexpr int VALIDATE_THREADS = 256;
+__global__ void __launch_bounds__(VALIDATE_THREADS)
+k_validate_entries(int32_t nrows, int64_t nnz, const int32_t *__restrict__ rowidx,
+                   unsigned long long *__restrict__ acc) {
+  __shared__ unsigned s_desc[VALIDATE_THREADS / 32];
+  __shared__ unsigned s_oob[VALIDATE_THREADS / 32];
+  unsigned descents = 0, oob = 0;
+  const int64_t stride = (int64_t)gridDim.x * VALIDATE_THREADS;
+  for (int64_t p = (int64_t)blockIdx.x * VALIDATE_THREADS + threadIdx.x; p < nnz; p += stride) {
     const int32_t r = rowidx[p];
-    oob = r < 0 || r >= nrows;
-    descent = p > 0 && rowidx[p - 1] >= r;
+    oob |= (unsigned)(r < 0 || r >= nrows);
+    descents += (unsigned)(p > 0 && rowidx[p - 1] >= r);
   }
-  const unsigned d = __ballot_sync(0xffffffffu, descent);
-  const unsigned o = __ballot_sync(0xffffffffu, oob);
-  if ((threadIdx.x & 31) == 0) {
+  descents = __reduce_add_sync(0xffffffffu, descents);
+  oob = __reduce_or_sync(0xffffffffu, oob);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    s_desc[warp] = descents;
+    s_oob[warp] = oob;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned d = 0, o = 0;
+#pragma unroll
+    for (int w = 0; w < VALIDATE_THREADS / 32; ++w) {
+      d += s_desc[w];
+      o |= s_oob[w];
+    }
     if (o) atomicOr(acc, 1ull);
-    if (d) atomicAdd(acc + 1, (unsigned long long)__popc(d));
+    if (d) atomicAdd(acc + 1, (unsigned long long)d);
   }
 }
 
@@ -164,19 +183,18 @@ static int upload_impl(int32_t nrows, int32_t ncols, const int32_t *colptr, cons
   slc_matrix *m = nullptr;
   SLC_TRY(matrix_alloc(Num<T>::elem, nrows, ncols, nnz, &m));
   cudaStream_t s = cur_stream();
-  cudaError_t e = cudaMemcpyAsync(m->colptr, colptr, ((size_t)ncols + 1) * sizeof(int32_t),
-                                  cudaMemcpyHostToDevice, s);
-  if (e == cudaSuccess && nnz)
-    e = cudaMemcpyAsync(m->rowidx, rowidx, (size_t)nnz * sizeof(int32_t), cudaMemcpyHostToDevice, s);
-  if (e == cudaSuccess && nnz)
-    e = cudaMemcpyAsync(m->vals, vals, (size_t)nnz * sizeof(T), cudaMemcpyHostToDevice, s);
+  cudaError_t e = cudaSuccess;
+  int rc = host_to_dev(m->colptr, colptr, ((size_t)ncols + 1) * sizeof(int32_t), s);
+  if (rc == SLC_OK && nnz) rc = host_to_dev(m->rowidx, rowidx, (size_t)nnz * sizeof(int32_t), s);
+  if (rc == SLC_OK && nnz) rc = host_to_dev(m->vals, vals, (size_t)nnz * sizeof(T), s);
   DevBuf<unsigned long long> acc;
   unsigned long long hacc[3] = {0, 0, 0};
-  int rc = SLC_OK;
-  if (e == cudaSuccess) rc = acc.alloc(3);
+  if (rc == SLC_OK) rc = acc.alloc(3);
   if (e == cudaSuccess && rc == SLC_OK) e = cudaMemsetAsync(acc.p, 0, sizeof hacc, s);
   if (e == cudaSuccess && rc == SLC_OK && nnz) {
-    k_validate_entries<<<(unsigned)ceil_div(nnz, 256), 256, 0, s>>>(nrows, nnz, m->rowidx, acc.p);
+    // a few blocks per SM, each thread takes several entries
+    const unsigned vblocks = (unsigned)std::min<int64_t>(ceil_div(nnz, VALIDATE_THREADS * 4), (int64_t)sm_count() * 16);
+    k_validate_entries<<<vblocks, VALIDATE_THREADS, 0, s>>>(nrows, nnz, m->rowidx, acc.p);
     k_validate_starts<<<(unsigned)ceil_div(ncols, 256), 256, 0, s>>>(ncols, m->colptr, m->rowidx, acc.p);
     g_launches.fetch_add(2, std::memory_order_relaxed);
     e = cudaGetLastError();
@@ -203,14 +221,9 @@ static int download_impl(const slc_matrix *m, int32_t *colptr, int32_t *rowidx, 
   if (!m) return fail(SLC_ERR_INVALID, "download: null handle");
   if (m->elem != Num<T>::elem) return fail(SLC_ERR_INVALID, "download: element type mismatch");
   cudaStream_t s = cur_stream();
-  if (colptr)
-    SLC_CUDA(cudaMemcpyAsync(colptr, m->colptr, ((size_t)m->ncols + 1) * sizeof(int32_t),
-                             cudaMemcpyDeviceToHost, s));
-  if (rowidx && m->nnz)
-    SLC_CUDA(cudaMemcpyAsync(rowidx, m->rowidx, (size_t)m->nnz * sizeof(int32_t),
-                             cudaMemcpyDeviceToHost, s));
-  if (vals && m->nnz)
-    SLC_CUDA(cudaMemcpyAsync(vals, m->vals, (size_t)m->nnz * sizeof(T), cudaMemcpyDeviceToHost, s));
+  if (colptr) SLC_TRY(dev_to_host(colptr, m->colptr, ((size_t)m->ncols + 1) * sizeof(int32_t), s));
+  if (rowidx && m->nnz) SLC_TRY(dev_to_host(rowidx, m->rowidx, (size_t)m->nnz * sizeof(int32_t), s));
+  if (vals && m->nnz) SLC_TRY(dev_to_host(vals, m->vals, (size_t)m->nnz * sizeof(T), s));
   SLC_CUDA(cudaStreamSynchronize(s));
   return SLC_OK;
 }

@@ -14,7 +14,7 @@ what is reproduced is everything on the Haskell side of `feast_rci` that touches
 Here the per-column loop is ONE `slc_{d,z}_mulm` over the active range: the column range is chosen by
 offsetting the two base pointers, the blocks stay in (pinned) host memory exactly as FEAST owns them,
 and the library pipelines upload / product / download by column groups.  `oracle.mulm` restates the
-reference loop; tests/test_gpu_feast.py compares every call with it.
+reference loop; tests/test_gpu_boundary.py (test_feast_multiply_work_moving_range) compares every call with it.
 """
 import ctypes as C
 

@@ -236,18 +236,22 @@ def zeros(nrows, ncols, dtype=np.float64):
 
 def compress(nrows, ncols, rows, cols, vals):
     """COO -> CSC on the GPU (Sparse.hs:184-255)."""
-    rows = np.ascontiguousarray(rows, dtype=np.int64)
-    cols = np.ascontiguousarray(cols, dtype=np.int64)
     vals = np.ascontiguousarray(vals)
     if len(rows) != len(cols):
         raise SparseLinearError("compress: row and column array lengths differ")
     if len(rows) != len(vals):
         raise SparseLinearError("compress: row and value array lengths differ")
     p = _prefix(vals.dtype)
-    # indices beyond int32 cannot be valid for a 32-bit matrix; clamp so they fail the bounds check
-    big = np.iinfo(np.int32).max
-    r32 = np.clip(rows, -1, big).astype(np.int32)
-    c32 = np.clip(cols, -1, big).astype(np.int32)
+
+    def as_i32(a):
+        # 32-bit index arrays (what the C ABI takes, Foreign.hs:24-41) are lent as they are; anything wider
+        # is narrowed here, and indices beyond int32 -- which cannot be valid for a 32-bit matrix -- are
+        # clamped so that they fail the bounds check
+        if isinstance(a, np.ndarray) and a.dtype == np.int32:
+            return np.ascontiguousarray(a)
+        a = np.ascontiguousarray(a, dtype=np.int64)
+        return np.clip(a, -1, np.iinfo(np.int32).max).astype(np.int32)
+    r32, c32 = as_i32(rows), as_i32(cols)
     v = np.ascontiguousarray(vals, dtype=_elem_dtype(p))
     h = C.c_void_p()
     bad = C.c_int64(-1)

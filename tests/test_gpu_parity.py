@@ -417,6 +417,36 @@ def test_compress_many_duplicates_zeros_and_empty(sl):
 
 
 @pytest.mark.parametrize("coarse", ["0", "1"])
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_compress_any_duplicate_order_stays_inside_the_tolerance(sl, dtype, coarse, monkeypatch):
+    """The reference sorts the triplets with an unstable introsort before it sums duplicates
+    (Sparse.hs:219,257-280), so the order in which the terms of one entry are added is unspecified; the
+    oracle and the device both add them in input order.  Feeding the same triplets in several random
+    orders covers whatever order the reference might have used: the structure must not change at all, and
+    the values must stay within north_star's 1e-12 norm-wise bound of the oracle on the original order."""
+    monkeypatch.setenv("SLC_ASM_COARSE", coarse)
+    rng = np.random.default_rng(17)
+    nr, nc, n = 300, 200, 120_000                      # two duplicates per entry on average, up to ~10
+    r = rng.integers(0, nr, n)
+    c = rng.integers(0, nc, n)
+    v = rng.uniform(-1, 1, n) * 10.0 ** rng.integers(-6, 7, n)     # mixed magnitudes: order matters in the last bits
+    v = v.astype(dtype)
+    if np.dtype(dtype).kind == "c":
+        v = v + 1j * rng.uniform(-1, 1, n) * 10.0 ** rng.integers(-6, 7, n)
+    want = oracle.compress(nr, nc, r, c, v)
+    differing = 0
+    for trial in range(6):
+        perm = rng.permutation(n)
+        got = sl.compress(nr, nc, r[perm], c[perm], v[perm])
+        assert_same_structure(got, want)
+        assert_values_close(got.values, want.values)
+        # and the device agrees bit for bit with the oracle fed the same order
+        np.testing.assert_array_equal(got.values, oracle.compress(nr, nc, r[perm], c[perm], v[perm]).values)
+        differing += int(not np.array_equal(got.values, want.values))
+    assert differing > 0          # the orders did change some last bits: the test is not vacuous
+
+
+@pytest.mark.parametrize("coarse", ["0", "1"])
 def test_compress_bounds_errors(sl, coarse, monkeypatch):
     """Sparse.hs:196-212: rows are checked before columns; the first offending position is reported."""
     monkeypatch.setenv("SLC_ASM_COARSE", coarse)
