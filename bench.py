@@ -351,6 +351,16 @@ def entry_spmv(args, sl, tm, name, desc, host_m=None, dev_m=None, dtype=np.float
         entry["e2e"] = {"value": abytes / dt / 1e9, "unit": "GB/s", "ms_per_step": dt * 1e3, "steps": steps_e2e,
                         "h2d_bytes_per_step": ncols * val, "d2h_bytes_per_step": nrows * val,
                         "api": "slc_%s_mulv (host pointers, pinned)" % p}
+        # the same call on the memory an unchanged caller of the reference owns: plain (pageable) arrays
+        xg = np.array(xh[0], copy=True)
+        yg = np.zeros(nrows, dtype=xg.dtype)
+
+        def gstep():
+            lib_call(sl, hfn(dm.handle, xg.ctypes.data_as(C.c_void_p), yg.ctypes.data_as(C.c_void_p)))
+        dtg, repsg = timed_host(gstep, 5)
+        entry["e2e_pageable"] = {"value": abytes / dtg / 1e9, "unit": "GB/s", "ms_per_step": dtg * 1e3, "steps": len(repsg),
+                                 "ms_per_repeat": repsg, "api": "slc_%s_mulv (host pointers, pageable numpy arrays, reused)" % p,
+                                 "same_result_as_pinned": bool(np.array_equal(yg, yp.numpy()))}
     # CPU leg: the baseline, and the checker of what the timed calls produced
     if not args.no_cpu:
         if host_m is None:
@@ -461,6 +471,17 @@ def entry_spmm(args, sl, tm, name, desc, host_m, dtype, k, check_cols, traffic_k
                         "api": "slc_%s_mulm (host pointers, pinned; pipelined by column groups)" % p}
         if want is not None:
             entry["e2e"]["matches_oracle_bit_exact"] = bool(np.array_equal(yp[cols].numpy().T, want))
+        # the same call on plain (pageable) blocks, reused from call to call as FEAST reuses its work arrays
+        xg = np.array(xp.numpy(), copy=True)
+        yg = np.zeros_like(yp.numpy())
+
+        def gstep():
+            lib_call(sl, hfn(dm.handle, xg.ctypes.data_as(C.c_void_p), ncols, yg.ctypes.data_as(C.c_void_p), nrows, k, None))
+        dtg, repsg = timed_host(gstep, 3)
+        entry["e2e_pageable"] = {"value": abytes / dtg / 1e9, "unit": "GB/s", "ms_per_step": dtg * 1e3, "steps": len(repsg),
+                                 "ms_per_repeat": repsg, "api": "slc_%s_mulm (host pointers, pageable numpy blocks, reused)" % p,
+                                 "same_result_as_pinned": bool(np.array_equal(yg, yp.numpy()))}
+        del xg, yg
         if feast_leg:
             entry["through_feast"] = feast_leg_run(sl, m, host_m, dtype, k, xp, want, cols, abytes)
         del xp, yp
@@ -845,7 +866,7 @@ def line_from_entry(args, entry, suite=None):
             "steps": entry.get("steps"), "warmup": max(args.warmup, 3), "ms_per_step": entry.get("ms_per_step"),
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": entry.get("dtype"),
             "data": "synthetic (seeded numpy PCG64 / torch Philox)"}
-    for k in ("config", "clocks", "gpu_launches", "e2e", "roofline", "cpu_baseline", "parity", "cold_l2", "cuda_graph",
+    for k in ("config", "clocks", "gpu_launches", "e2e", "e2e_pageable", "roofline", "cpu_baseline", "parity", "cold_l2", "cuda_graph",
               "through_feast", "error", "trace"):
         if k in entry:
             line[k] = entry[k]

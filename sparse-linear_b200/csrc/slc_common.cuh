@@ -472,8 +472,14 @@ int spmm_window_try(slc_matrix *m, const T *X, int64_t ldx, T *Y, int64_t ldy, i
 // cudaMemcpyAsync; large pageable memory is moved through a ring of pinned buffers by a few host threads.
 // host_to_dev: the source has been read when it returns.  dev_to_host: complete after the next
 // synchronisation of the stream.
+bool host_needs_staging(const void *host, size_t bytes);  // large and not pinned: the ring will carry it
 int host_to_dev(void *dst_dev, const void *src_host, size_t bytes, cudaStream_t s);
 int dev_to_host(void *dst_host, const void *src_dev, size_t bytes, cudaStream_t s);
+// the same for `height` columns of `width` bytes (pitches in bytes), all columns in one pipeline
+int host_to_dev_2d(void *dst_dev, size_t dpitch, const void *src_host, size_t spitch, size_t width, size_t height,
+                   cudaStream_t s);
+int dev_to_host_2d(void *dst_host, size_t dpitch, const void *src_dev, size_t spitch, size_t width, size_t height,
+                   cudaStream_t s);
 
 // slc_spmm_window.cu: after the current device's streams have been synchronised, SLC_ERR_CUDA (and the word
 // cleared) if a TMA-staged block product gave up on a barrier there since the last check; `who` prefixes the message

@@ -121,69 +121,96 @@ bool staging_wanted(const void *host, size_t bytes) {
 
 }  // namespace
 
-// dst_dev[0, bytes) <- src_host.  On return the source has been read (the caller may reuse it); the device
-// side completes in stream order.
-int host_to_dev(void *dst_dev, const void *src_host, size_t bytes, cudaStream_t s) {
-  if (bytes == 0) return SLC_OK;
-  if (staging_wanted(src_host, bytes)) {
+bool host_needs_staging(const void *host, size_t bytes) { return staging_wanted(host, bytes); }
+
+// A block of `height` columns of `width` bytes each (pitches in bytes), cut into pieces of at most one ring
+// slot: piece q is bytes [off, off + len) of column col.
+struct Pieces {
+  size_t width, height, per_col, total;
+  Pieces(size_t w, size_t h) : width(w), height(h), per_col((w + XFER_CHUNK - 1) / XFER_CHUNK), total(per_col * h) {}
+  void at(size_t q, size_t *col, size_t *off, size_t *len) const {
+    *col = q / per_col;
+    *off = (q % per_col) * XFER_CHUNK;
+    *len = std::min(XFER_CHUNK, width - *off);
+  }
+};
+
+// dst_dev <- src_host, `height` columns of `width` bytes.  On return the source has been read (the caller
+// may reuse it); the device side completes in stream order.  The pieces of all columns form one pipeline:
+// the host threads fill slot q+1 while the DMA engine drains slot q.
+int host_to_dev_2d(void *dst_dev, size_t dpitch, const void *src_host, size_t spitch, size_t width, size_t height,
+                   cudaStream_t s) {
+  if (width == 0 || height == 0) return SLC_OK;
+  if (staging_wanted(src_host, width)) {
     std::lock_guard<std::mutex> lock(g_ring.mu);
     cudaEvent_t *ev = nullptr;
     if (ring_ready(&ev)) {
       const char *src = static_cast<const char *>(src_host);
       char *dst = static_cast<char *>(dst_dev);
-      int i = 0;
-      for (size_t off = 0; off < bytes; off += XFER_CHUNK, ++i) {
-        const size_t len = std::min(XFER_CHUNK, bytes - off);
-        const int k = i % XFER_SLOTS;
-        if (i >= XFER_SLOTS) SLC_CUDA(cudaEventSynchronize(ev[k]));  // the DMA that last read this slot
-        parallel_memcpy(g_ring.slot[k], src + off, len);
-        SLC_CUDA(cudaMemcpyAsync(dst + off, g_ring.slot[k], len, cudaMemcpyHostToDevice, s));
+      const Pieces pc(width, height);
+      for (size_t q = 0; q < pc.total; ++q) {
+        size_t col, off, len;
+        pc.at(q, &col, &off, &len);
+        const int k = (int)(q % XFER_SLOTS);
+        if (q >= (size_t)XFER_SLOTS) SLC_CUDA(cudaEventSynchronize(ev[k]));  // the DMA that last read this slot
+        parallel_memcpy(g_ring.slot[k], src + col * spitch + off, len);
+        SLC_CUDA(cudaMemcpyAsync(dst + col * dpitch + off, g_ring.slot[k], len, cudaMemcpyHostToDevice, s));
         SLC_CUDA(cudaEventRecord(ev[k], s));
       }
-      for (int k = 0; k < std::min(i, XFER_SLOTS); ++k) SLC_CUDA(cudaEventSynchronize(ev[k]));  // ring idle again
+      for (size_t k = 0; k < std::min<size_t>(pc.total, XFER_SLOTS); ++k) SLC_CUDA(cudaEventSynchronize(ev[k]));  // ring idle again
       return SLC_OK;
     }
   }
-  SLC_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, s));
+  if (height == 1) SLC_CUDA(cudaMemcpyAsync(dst_dev, src_host, width, cudaMemcpyHostToDevice, s));
+  else SLC_CUDA(cudaMemcpy2DAsync(dst_dev, dpitch, src_host, spitch, width, height, cudaMemcpyHostToDevice, s));
   return SLC_OK;
 }
 
-// dst_host[0, bytes) <- src_dev, in stream order behind whatever produces src_dev.  The destination is
-// complete after the caller's next synchronisation of `s` (the staged path has already waited for it).
-int dev_to_host(void *dst_host, const void *src_dev, size_t bytes, cudaStream_t s) {
-  if (bytes == 0) return SLC_OK;
-  if (staging_wanted(dst_host, bytes)) {
+// dst_host <- src_dev, in stream order behind whatever produces src_dev.  The destination is complete after
+// the caller's next synchronisation of `s` (the staged path has already waited for it).
+int dev_to_host_2d(void *dst_host, size_t dpitch, const void *src_dev, size_t spitch, size_t width, size_t height,
+                   cudaStream_t s) {
+  if (width == 0 || height == 0) return SLC_OK;
+  if (staging_wanted(dst_host, width)) {
     std::lock_guard<std::mutex> lock(g_ring.mu);
     cudaEvent_t *ev = nullptr;
     if (ring_ready(&ev)) {
       char *dst = static_cast<char *>(dst_host);
       const char *src = static_cast<const char *>(src_dev);
-      {  // a hint only: fresh anonymous memory is then faulted in 2 MiB at a time where the system allows it
-        const uintptr_t lo = ((uintptr_t)dst + 4095) & ~(uintptr_t)4095, hi = ((uintptr_t)dst + bytes) & ~(uintptr_t)4095;
+      for (size_t c = 0; c < height; ++c) {  // a hint only: fresh anonymous memory is then faulted in 2 MiB at a time where the system allows it
+        const uintptr_t b = (uintptr_t)(dst + c * dpitch);
+        const uintptr_t lo = (b + 4095) & ~(uintptr_t)4095, hi = (b + width) & ~(uintptr_t)4095;
         if (hi > lo) (void)madvise((void *)lo, hi - lo, MADV_HUGEPAGE);
       }
-      const size_t nchunks = (bytes + XFER_CHUNK - 1) / XFER_CHUNK;
-      for (size_t i = 0; i < nchunks + XFER_SLOTS; ++i) {
-        if (i >= (size_t)XFER_SLOTS) {  // chunk j has landed in its slot: copy it out, which frees the slot for chunk i
-          const size_t j = i - XFER_SLOTS;
-          if (j < nchunks) {
-            SLC_CUDA(cudaEventSynchronize(ev[j % XFER_SLOTS]));
-            const size_t off = j * XFER_CHUNK;
-            parallel_memcpy(dst + off, g_ring.slot[j % XFER_SLOTS], std::min(XFER_CHUNK, bytes - off));
-          }
+      const Pieces pc(width, height);
+      for (size_t q = 0; q < pc.total + XFER_SLOTS; ++q) {
+        if (q >= (size_t)XFER_SLOTS) {  // piece j has landed in its slot: copy it out, which frees the slot for piece q
+          const size_t j = q - XFER_SLOTS;
+          size_t col, off, len;
+          pc.at(j, &col, &off, &len);
+          SLC_CUDA(cudaEventSynchronize(ev[j % XFER_SLOTS]));
+          parallel_memcpy(dst + col * dpitch + off, g_ring.slot[j % XFER_SLOTS], len);
         }
-        if (i < nchunks) {
-          const size_t off = i * XFER_CHUNK;
-          SLC_CUDA(cudaMemcpyAsync(g_ring.slot[i % XFER_SLOTS], src + off, std::min(XFER_CHUNK, bytes - off),
-                                   cudaMemcpyDeviceToHost, s));
-          SLC_CUDA(cudaEventRecord(ev[i % XFER_SLOTS], s));
+        if (q < pc.total) {
+          size_t col, off, len;
+          pc.at(q, &col, &off, &len);
+          SLC_CUDA(cudaMemcpyAsync(g_ring.slot[q % XFER_SLOTS], src + col * spitch + off, len, cudaMemcpyDeviceToHost, s));
+          SLC_CUDA(cudaEventRecord(ev[q % XFER_SLOTS], s));
         }
       }
       return SLC_OK;
     }
   }
-  SLC_CUDA(cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost, s));
+  if (height == 1) SLC_CUDA(cudaMemcpyAsync(dst_host, src_dev, width, cudaMemcpyDeviceToHost, s));
+  else SLC_CUDA(cudaMemcpy2DAsync(dst_host, dpitch, src_dev, spitch, width, height, cudaMemcpyDeviceToHost, s));
   return SLC_OK;
+}
+
+int host_to_dev(void *dst_dev, const void *src_host, size_t bytes, cudaStream_t s) {
+  return host_to_dev_2d(dst_dev, bytes, src_host, bytes, bytes, 1, s);
+}
+int dev_to_host(void *dst_host, const void *src_dev, size_t bytes, cudaStream_t s) {
+  return dev_to_host_2d(dst_host, bytes, src_dev, bytes, bytes, 1, s);
 }
 
 }  // namespace slc

@@ -1683,20 +1683,25 @@ static int spmv_host_entry(slc_matrix *m, const double *x, double *y, const char
   SLC_TRY(check_handle<T>(m, fn));
   HandleLock lock(m);
   if ((m->ncols && !x) || (m->nrows && !y)) return fail(SLC_ERR_INVALID, "%s: null vector", fn);
-  bool done = false;
-  SLC_TRY((spmv_host_pipelined<T, ACC>(m, (const T *)x, (T *)y, &done)));
-  if (done) return SLC_OK;
+  // The chunked pipeline below overlaps upload, product and download of PINNED operands (the copies are
+  // asynchronous DMA).  On pageable memory every cudaMemcpyAsync of it degenerates into the driver's own
+  // staging (11 GB/s in, 19 out, profiles/r3_probe_host_link.txt), so large pageable vectors -- what a
+  // Storable vector on the GHC heap is -- take the whole-vector path through the pinned ring instead.
+  const bool pageable = host_needs_staging(x, (size_t)m->ncols * sizeof(T)) ||
+                        host_needs_staging(y, (size_t)m->nrows * sizeof(T));
+  if (!pageable) {
+    bool done = false;
+    SLC_TRY((spmv_host_pipelined<T, ACC>(m, (const T *)x, (T *)y, &done)));
+    if (done) return SLC_OK;
+  }
   cudaStream_t s = cur_stream();
   DevBuf<T> dx, dy;
   SLC_TRY(dx.alloc((size_t)m->ncols));
   SLC_TRY(dy.alloc((size_t)m->nrows));
-  if (m->ncols)
-    SLC_CUDA(cudaMemcpyAsync(dx.p, x, (size_t)m->ncols * sizeof(T), cudaMemcpyHostToDevice, s));
-  if (ACC && m->nrows)
-    SLC_CUDA(cudaMemcpyAsync(dy.p, y, (size_t)m->nrows * sizeof(T), cudaMemcpyHostToDevice, s));
+  if (m->ncols) SLC_TRY(host_to_dev(dx.p, x, (size_t)m->ncols * sizeof(T), s));
+  if (ACC && m->nrows) SLC_TRY(host_to_dev(dy.p, y, (size_t)m->nrows * sizeof(T), s));
   SLC_TRY((spmv_dev<T, ACC>(m, dx.p, dy.p)));
-  if (m->nrows)
-    SLC_CUDA(cudaMemcpyAsync(y, dy.p, (size_t)m->nrows * sizeof(T), cudaMemcpyDeviceToHost, s));
+  if (m->nrows) SLC_TRY(dev_to_host(y, dy.p, (size_t)m->nrows * sizeof(T), s));
   SLC_CUDA(cudaStreamSynchronize(s));
   return SLC_OK;
 }
@@ -2360,6 +2365,54 @@ static int spmm_host_entry(slc_matrix *m, const double *X, int64_t ldx, double *
     SLC_CUDA(cudaStreamWaitEvent(m->pipe_out, ev_start, 0));
     const int32_t per = (int32_t)ceil_div(k, ngroups);
     int rc = SLC_OK;
+    // Pageable blocks (what FEAST's MV.replicate'd work arrays are, Feast.hs:149-155): a cudaMemcpy2DAsync on
+    // them is the driver's own staging at 11 GB/s in and 19 (2 into untouched pages) out.  Each column goes
+    // through the pinned ring instead; the host is then the serial resource, so the order is: upload and
+    // launch group g+1, then copy group g out while the device multiplies g+1.
+    const bool pageable = host_needs_staging(X, (size_t)m->ncols * sizeof(T)) ||
+                          host_needs_staging(Y, (size_t)m->nrows * sizeof(T));
+    if (pageable) {
+      const int G = (int)ceil_div(k, per);
+      auto cols_of = [&](int g) { return std::min<int32_t>(per, k - g * per); };
+      auto upload = [&](int g) -> int {
+        const int32_t j0 = g * per;
+        SLC_TRY(host_to_dev_2d(dX.p + (size_t)j0 * m->ncols, (size_t)m->ncols * sizeof(T), (const T *)X + (size_t)j0 * ldx,
+                               (size_t)ldx * sizeof(T), (size_t)m->ncols * sizeof(T), (size_t)cols_of(g), m->pipe_in));
+        if (yi.mode != 0)
+          SLC_TRY(host_to_dev_2d(dY.p + (size_t)j0 * m->nrows, (size_t)m->nrows * sizeof(T), (const T *)Y + (size_t)j0 * ldy,
+                                 (size_t)ldy * sizeof(T), (size_t)m->nrows * sizeof(T), (size_t)cols_of(g), m->pipe_in));
+        SLC_CUDA(cudaEventRecord(m->pipe_events[g], m->pipe_in));
+        return SLC_OK;
+      };
+      auto product = [&](int g) -> int {
+        const int32_t j0 = g * per;
+        SLC_CUDA(cudaStreamWaitEvent(s, m->pipe_events[g], 0));
+        SLC_TRY(spmm_dev<T>(m, dX.p + (size_t)j0 * m->ncols, m->ncols, dY.p + (size_t)j0 * m->nrows, m->nrows, cols_of(g), yi));
+        SLC_CUDA(cudaEventRecord(m->pipe_events[PIPE_MAX_CHUNKS + g], s));
+        return SLC_OK;
+      };
+      auto download = [&](int g) -> int {
+        const int32_t j0 = g * per;
+        SLC_CUDA(cudaStreamWaitEvent(m->pipe_out, m->pipe_events[PIPE_MAX_CHUNKS + g], 0));
+        SLC_TRY(dev_to_host_2d((T *)Y + (size_t)j0 * ldy, (size_t)ldy * sizeof(T), dY.p + (size_t)j0 * m->nrows,
+                               (size_t)m->nrows * sizeof(T), (size_t)m->nrows * sizeof(T), (size_t)cols_of(g), m->pipe_out));
+        return SLC_OK;
+      };
+      rc = upload(0);
+      if (rc == SLC_OK) rc = product(0);
+      for (int g = 0; g < G && rc == SLC_OK; ++g) {
+        if (g + 1 < G) {
+          rc = upload(g + 1);
+          if (rc == SLC_OK) rc = product(g + 1);
+        }
+        if (rc == SLC_OK) rc = download(g);
+      }
+      cudaStreamSynchronize(m->pipe_out);
+      cudaStreamSynchronize(m->pipe_in);
+      SLC_CUDA(cudaStreamSynchronize(s));
+      if (rc == SLC_OK) rc = spmm_window_check(fn);
+      return rc;
+    }
     for (int g = 0; g * per < k && rc == SLC_OK; ++g) {
       const int32_t j0 = g * per, kk = std::min<int32_t>(per, k - j0);
       const T *Xg = (const T *)X + (size_t)j0 * ldx;
